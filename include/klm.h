@@ -1,0 +1,304 @@
+/*
+ * klm.h — C ABI of libklm.so: the B200 (sm_100a) data path behind
+ * k8s-llm-monitor's scheduler and metrics manager.
+ *
+ * The reference (Sabre94/k8s-llm-monitor, pure Go) has no plugin or FFI
+ * interface around this path (internal/scheduler/controller.go:174 is an
+ * unexported method), so this header DEFINES the boundary a cgo shim binds.
+ * Every entry point cites the reference code whose arithmetic it replaces.
+ * INTEGRATION.md shows the Go side.
+ *
+ * Conventions
+ *  - extern "C", plain pointers and sizes; no C++ or torch types.
+ *  - Return 0 on success, a negative KLM_E* code otherwise; the message is
+ *    in klm_last_error() (thread-local).
+ *  - Host-buffer API (klm_*): the caller owns every array. Inputs are copied
+ *    to device memory owned by the handle before the call returns; outputs
+ *    are completely written before the call returns. No pointer is retained
+ *    (cgo pointer rules).
+ *  - Device-pointer API (klm_dev_*): arrays are device pointers on the
+ *    current CUDA device, `stream` is a cudaStream_t passed as void*; calls
+ *    only enqueue work. This is what a caller that keeps its data in HBM
+ *    (bench.py's `value` leg, or a multi-process host) uses.
+ *  - There is no CPU fallback anywhere: without a CUDA device klm_create
+ *    fails with KLM_ENODEV and the klm_dev_* calls return the CUDA error.
+ *  - Inputs must not contain NaN (JSON cannot carry it and Go's
+ *    sort.SliceStable is unspecified for it).
+ */
+#ifndef KLM_H_
+#define KLM_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define KLM_OK 0
+#define KLM_EINVAL (-1)  /* bad argument */
+#define KLM_ECUDA (-2)   /* CUDA runtime error; text in klm_last_error() */
+#define KLM_ENODEV (-3)  /* no usable CUDA device */
+#define KLM_ESTATE (-4)  /* call order (e.g. schedule before nodes_set) */
+#define KLM_ELIMIT (-5)  /* size beyond a documented maximum */
+
+/* node flags (klm_nodes_set / klm_dev_*): which of the reference's per-item
+ * filters the node passes. controller.go:190 and :198. */
+#define KLM_NODE_HAS_NAME 0x1u  /* spec.node_name != "" */
+#define KLM_NODE_STATUS_OK 0x2u /* lower(status.collection_status) in {"", "active"} */
+#define KLM_NODE_ELIGIBLE 0x3u
+
+/* klm_schedule_batch algorithms; both give identical results. */
+#define KLM_ALGO_DECOMPOSED 0 /* node_best_reduce + O(K) probe per request */
+#define KLM_ALGO_BRUTEFORCE 1 /* every request scans every node (verifier) */
+
+/* cluster health (manager.go:558-564) */
+#define KLM_HEALTH_HEALTHY 0
+#define KLM_HEALTH_WARNING 1
+#define KLM_HEALTH_CRITICAL 2
+/* cluster issue bits (manager.go:547-555), in the order Go appends them */
+#define KLM_ISSUE_UNHEALTHY_NODES 0x1u
+#define KLM_ISSUE_HIGH_CPU 0x2u
+#define KLM_ISSUE_HIGH_MEMORY 0x4u
+
+typedef struct klm_handle klm_handle;
+
+/* Columns of the node snapshot that calculateClusterMetrics reads
+ * (pkg/metrics/types.go:8-47; manager.go:499-535). gpu_usage is the
+ * concatenation of every node's GPUUsage slice (n_gpu_usage entries). */
+typedef struct klm_node_cols {
+  const int64_t* cpu_capacity;    /* [N] millicores */
+  const int64_t* cpu_usage;       /* [N] */
+  const int64_t* memory_capacity; /* [N] bytes */
+  const int64_t* memory_usage;    /* [N] */
+  const int32_t* gpu_count;       /* [N] */
+  const uint8_t* healthy;         /* [N] 0/1 */
+  const double* gpu_usage;        /* [n_gpu_usage] percent */
+  int64_t n_gpu_usage;
+} klm_node_cols;
+
+/* pkg/metrics/types.go:114-139 ClusterMetrics, numeric part. */
+typedef struct klm_cluster_out {
+  int64_t total_nodes;
+  int64_t healthy_nodes;
+  int64_t total_pods;
+  int64_t running_pods;
+  int64_t total_cpu;
+  int64_t used_cpu;
+  int64_t total_memory;
+  int64_t used_memory;
+  int64_t total_gpus;
+  int64_t available_gpus;
+  double cpu_usage_rate;
+  double memory_usage_rate;
+  int32_t health_status; /* KLM_HEALTH_* */
+  uint32_t issues;       /* KLM_ISSUE_* bits */
+} klm_cluster_out;
+
+/* ---------------------------------------------------------------- handle */
+
+/* One handle drives one GPU. device_ids/n_dev: round 1 accepts n_dev == 1
+ * (multi-GPU runs are one process/handle per GPU).
+ * Thread-safe: every call takes the handle's mutex and makes its device
+ * current, so cgo may enter on any OS thread. */
+int klm_create(const int* device_ids, int n_dev, klm_handle** out);
+void klm_destroy(klm_handle* h);
+const char* klm_last_error(void);
+/* ABI version of this header: major*1000 + minor. */
+int klm_abi_version(void);
+
+/* ------------------------------------------------------------ scheduling */
+
+/* Install the UAV snapshot of one reconcile (controller.go:96-98): one entry
+ * per UAVMetric item in list order. battery = readFloat(spec, "battery",
+ * "remaining_percent") (controller.go:187, :252-272; missing -> 0). */
+int klm_nodes_set(klm_handle* h, int64_t n_nodes, const double* battery,
+                  const uint8_t* flags);
+
+/* Replaces buildCandidates + sort.SliceStable + candidates[0]
+ * (controller.go:152-161, :174-221) for a batch of R independent requests
+ * against the snapshot installed by klm_nodes_set.
+ *   min_battery[r]             spec.MinBatteryPercent (gate only when > 0, :194)
+ *   pref_ids[pref_off[r]..pref_off[r+1])  indices of the nodes whose
+ *       lower-cased name is in lower(spec.PreferredNodes) (:175-178, :206);
+ *       ids outside [0, n_nodes) are ignored.
+ *   out_idx[r]   index of the chosen node, -1 when no candidate (:153-158)
+ *   out_score[r] chosen.Score (:167); 0 when out_idx[r] == -1
+ * Ties go to the lowest index (stable sort, :160). */
+int klm_schedule_batch(klm_handle* h, int64_t n_requests,
+                       const double* min_battery, const int32_t* pref_off,
+                       const int32_t* pref_ids, int32_t* out_idx,
+                       double* out_score, int algo);
+
+/* ----------------------------------------------------- cluster aggregate */
+
+/* Replaces Manager.calculateClusterMetrics (manager.go:493-565).
+ * pod_running[p] = (Phase == "Running") (:509). */
+int klm_cluster_aggregate(klm_handle* h, const klm_node_cols* nodes,
+                          int64_t n_nodes, const uint8_t* pod_running,
+                          int64_t n_pods, klm_cluster_out* out);
+
+/* Per-node arithmetic of buildNodeMetrics (sources/node_metrics.go:116-140)
+ * and NodeMetrics.IsUnderPressure (pkg/metrics/types.go:159-162).
+ * disk_allocatable may be NULL (then disk_usage = 0, node_metrics.go:117).
+ * Outputs (any may be NULL): rates in percent, disk_usage bytes,
+ * under_pressure 0/1. */
+int klm_node_rates(klm_handle* h, int64_t n_nodes, const int64_t* cpu_capacity,
+                   const int64_t* cpu_usage, const int64_t* memory_capacity,
+                   const int64_t* memory_usage, const int64_t* disk_capacity,
+                   const int64_t* disk_allocatable, double* cpu_rate,
+                   double* memory_rate, int64_t* disk_usage, double* disk_rate,
+                   uint8_t* under_pressure);
+
+/* Per-pod arithmetic of buildPodMetrics (sources/pod_metrics.go:104-171):
+ * containers of pod p are rows ctr_off[p]..ctr_off[p+1] of the six container
+ * columns. Outputs: pod_totals[6][P] in the order cpu_usage, memory_usage,
+ * cpu_request, cpu_limit, memory_request, memory_limit; rates vs limit
+ * (:162-171); utilisation vs request (types.go:165-173); over_limit
+ * (types.go:176-184, with its int64(float64(limit)*0.9) truncation). */
+int klm_pod_rates(klm_handle* h, int64_t n_pods, const int32_t* ctr_off,
+                  const int64_t* ctr_cpu_usage, const int64_t* ctr_memory_usage,
+                  const int64_t* ctr_cpu_request, const int64_t* ctr_cpu_limit,
+                  const int64_t* ctr_memory_request,
+                  const int64_t* ctr_memory_limit, int64_t* pod_totals,
+                  double* cpu_rate, double* memory_rate, double* cpu_util,
+                  double* memory_util, uint8_t* over_limit);
+
+/* Fleet scans of sources/uav_metrics.go:197-233: number of UAVs whose
+ * Health.SystemStatus == "OK" (status_ok[i] != 0), and the indices, in
+ * ascending order, of UAVs with RemainingPercent < threshold. low_idx has
+ * room for n entries; *n_low receives how many were written. */
+int klm_fleet_scan(klm_handle* h, int64_t n, const uint8_t* status_ok,
+                   const double* remaining_percent, double threshold,
+                   int64_t* healthy_count, int32_t* low_idx, int64_t* n_low);
+
+/* --------------------------------------------------- metric window rings */
+
+/* Allocate the metric ring: n_series rows of `window` f32 samples, one row
+ * per (node|pod|UAV, channel) series. The reference keeps only the latest
+ * snapshot (manager.go:29, :289-290) and lists time-series storage as future
+ * work, so the ring and its statistics have no reference implementation:
+ * their definition is in DESIGN.md and their parity is "unpinned". */
+int klm_ring_create(klm_handle* h, int64_t n_series, int32_t window);
+/* Append one sample to each listed series (UpdateUAVReport, manager.go:391-449,
+ * and the end of Collect, :286, are the producers). series_ids must be
+ * distinct within one call. */
+int klm_ring_ingest(klm_handle* h, int64_t n, const int64_t* series_ids,
+                    const float* values);
+/* Append one sample to EVERY series: values[n_series] (one collection tick). */
+int klm_ring_ingest_tick(klm_handle* h, const float* values);
+/* Bulk-load history: rows [s0, s1) each get `count` (<= window) samples from
+ * data[(s - s0) * count + t], replacing what the rows held. */
+int klm_ring_load(klm_handle* h, int64_t s0, int64_t s1, int32_t count,
+                  const float* data);
+/* Window statistics of series [s0, s1) over the last n = min(window, seen)
+ * samples of each: min, max (exact f32), mean (f64 sum / n), p95 =
+ * nearest-rank sorted[ceil(0.95 n) - 1] (an input element). Series with no
+ * sample give min = max = p95 = 0 and mean = 0. Any output may be NULL. */
+int klm_ring_stats(klm_handle* h, int64_t s0, int64_t s1, float* out_min,
+                   float* out_max, double* out_mean, float* out_p95);
+
+/* ================================================= device-pointer layer */
+/* All pointers below are DEVICE pointers; nothing is allocated or freed;
+ * work is enqueued on `stream` and the call returns without synchronising.
+ * `scratch` arguments are caller-provided device memory of at least the
+ * stated size, 256-byte aligned, zero-filled ONCE after allocation (they hold
+ * self-resetting tickets); a kernel leaves its scratch ready for the next
+ * launch. Two launches that share a scratch area must not overlap. */
+
+/* Bytes of scratch the two scheduling kernels need. */
+int64_t klm_dev_node_best_scratch_bytes(void);
+/* K1 node_best_reduce: (battery, index) of the lowest-index node with the
+ * largest battery among nodes with (flags & 3) == 3; best[0] = index as
+ * int64 (-1 if none), best[1] = bits of the f64 battery. controller.go:190,
+ * :198 (filters) + :160-161 (first maximum). node_base is added to the
+ * index (node-range sharding). */
+int klm_dev_node_best(const double* battery, const uint8_t* flags,
+                      int64_t n_nodes, int64_t node_base, int64_t* best,
+                      void* scratch, void* stream);
+/* K2 schedule_batch (decomposed form of controller.go:174-221 + :160-161).
+ * Node arrays hold global indices [node_base, node_base + n_nodes);
+ * pref_ids are global; ids outside the local range are skipped, so with
+ * node-range sharding each rank yields its partial winner and
+ * klm_dev_merge_partials finishes the job. */
+int klm_dev_schedule(const double* battery, const uint8_t* flags,
+                     int64_t n_nodes, int64_t node_base, const int64_t* best,
+                     int64_t n_requests, const double* min_battery,
+                     const int32_t* pref_off, const int32_t* pref_ids,
+                     int32_t* out_idx, double* out_score, void* stream);
+/* K2b schedule_bruteforce: same result, every request scans every node
+ * through shared-memory tiles — the literal loop of controller.go:181-218. */
+int klm_dev_schedule_bruteforce(const double* battery, const uint8_t* flags,
+                                int64_t n_nodes, int64_t node_base,
+                                int64_t n_requests, const double* min_battery,
+                                const int32_t* pref_off,
+                                const int32_t* pref_ids, int32_t* out_idx,
+                                double* out_score, void* stream);
+/* K3 merge_partials: part_idx/part_score are [n_parts][n_requests] partial
+ * winners (global indices, -1 = none) as gathered from the ranks; picks the
+ * highest score, lowest global index on ties (controller.go:160). */
+int klm_dev_merge_partials(int n_parts, int64_t n_requests,
+                           const int32_t* part_idx, const double* part_score,
+                           int32_t* out_idx, double* out_score, void* stream);
+
+int64_t klm_dev_cluster_scratch_bytes(void);
+/* K4 cluster_aggregate (manager.go:493-565). `out` is a device
+ * klm_cluster_out. node_cols members are device pointers. */
+int klm_dev_cluster_aggregate(const klm_node_cols* nodes, int64_t n_nodes,
+                              const uint8_t* pod_running, int64_t n_pods,
+                              klm_cluster_out* out, void* scratch,
+                              void* stream);
+/* Partial sums only (for node/pod sharding across ranks): writes the ten
+ * int64 counters of klm_cluster_out to sums[10]; klm_dev_cluster_finish
+ * turns (all-reduced) sums into rates and health. */
+int klm_dev_cluster_sums(const klm_node_cols* nodes, int64_t n_nodes,
+                         const uint8_t* pod_running, int64_t n_pods,
+                         int64_t* sums, void* scratch, void* stream);
+int klm_dev_cluster_finish(const int64_t* sums, klm_cluster_out* out,
+                           void* stream);
+
+/* K5 element-wise rates; same arithmetic as klm_node_rates/klm_pod_rates. */
+int klm_dev_node_rates(int64_t n_nodes, const int64_t* cpu_capacity,
+                       const int64_t* cpu_usage, const int64_t* memory_capacity,
+                       const int64_t* memory_usage,
+                       const int64_t* disk_capacity,
+                       const int64_t* disk_allocatable, double* cpu_rate,
+                       double* memory_rate, int64_t* disk_usage,
+                       double* disk_rate, uint8_t* under_pressure,
+                       void* stream);
+int klm_dev_pod_rates(int64_t n_pods, const int32_t* ctr_off,
+                      const int64_t* ctr_cpu_usage,
+                      const int64_t* ctr_memory_usage,
+                      const int64_t* ctr_cpu_request,
+                      const int64_t* ctr_cpu_limit,
+                      const int64_t* ctr_memory_request,
+                      const int64_t* ctr_memory_limit, int64_t* pod_totals,
+                      double* cpu_rate, double* memory_rate, double* cpu_util,
+                      double* memory_util, uint8_t* over_limit, void* stream);
+/* counters[0] = healthy count, counters[1] = n_low; both are overwritten by
+ * the call. low_idx is written in ascending order. */
+int64_t klm_dev_fleet_scan_scratch_bytes(int64_t n);
+int klm_dev_fleet_scan(int64_t n, const uint8_t* status_ok,
+                       const double* remaining_percent, double threshold,
+                       int64_t* counters, int32_t* low_idx, void* scratch,
+                       void* stream);
+
+/* Ring layout: ring[s * pitch + slot], pitch a multiple of 4 floats and the
+ * base 16-byte aligned; seen[s] = samples ever appended to series s (u32,
+ * saturating); the valid slots of a row are [0, min(seen, window)). */
+/* K6 window_ingest: scatter (series_ids, values), or one value per series
+ * when series_ids == NULL (then n == n_series). */
+int klm_dev_ring_ingest(float* ring, uint32_t* seen, int64_t n_series,
+                        int32_t window, int32_t pitch, int64_t n,
+                        const int64_t* series_ids, const float* values,
+                        void* stream);
+/* K7 window_stats over series [s0, s1). Outputs are indexed from s0
+ * (out[s - s0]); any may be NULL. */
+int klm_dev_window_stats(const float* ring, const uint32_t* seen,
+                         int32_t window, int32_t pitch, int64_t s0, int64_t s1,
+                         float* out_min, float* out_max, double* out_mean,
+                         float* out_p95, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* KLM_H_ */

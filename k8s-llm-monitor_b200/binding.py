@@ -1,0 +1,380 @@
+"""ctypes binding of libklm.so (include/klm.h).
+
+The library is the product; this module only declares its C signatures and
+gives numpy / torch callers a thin, typed way in. There is no CPU path here:
+if libklm.so is missing the import fails loudly, and every call needs a GPU.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import Optional, Tuple
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libklm.so")
+
+KLM_OK, KLM_EINVAL, KLM_ECUDA, KLM_ENODEV, KLM_ESTATE, KLM_ELIMIT = 0, -1, -2, -3, -4, -5
+NODE_HAS_NAME, NODE_STATUS_OK, NODE_ELIGIBLE = 1, 2, 3
+ALGO_DECOMPOSED, ALGO_BRUTEFORCE = 0, 1
+HEALTH_NAMES = ("healthy", "warning", "critical")  # manager.go:558-564
+
+
+class KlmError(RuntimeError):
+    def __init__(self, code: int, msg: str):
+        super().__init__(f"libklm error {code}: {msg}")
+        self.code = code
+
+
+class NodeCols(C.Structure):  # klm_node_cols
+    _fields_ = [
+        ("cpu_capacity", C.c_void_p), ("cpu_usage", C.c_void_p),
+        ("memory_capacity", C.c_void_p), ("memory_usage", C.c_void_p),
+        ("gpu_count", C.c_void_p), ("healthy", C.c_void_p),
+        ("gpu_usage", C.c_void_p), ("n_gpu_usage", C.c_int64),
+    ]
+
+
+class ClusterOut(C.Structure):  # klm_cluster_out
+    _fields_ = [
+        ("total_nodes", C.c_int64), ("healthy_nodes", C.c_int64),
+        ("total_pods", C.c_int64), ("running_pods", C.c_int64),
+        ("total_cpu", C.c_int64), ("used_cpu", C.c_int64),
+        ("total_memory", C.c_int64), ("used_memory", C.c_int64),
+        ("total_gpus", C.c_int64), ("available_gpus", C.c_int64),
+        ("cpu_usage_rate", C.c_double), ("memory_usage_rate", C.c_double),
+        ("health_status", C.c_int32), ("issues", C.c_uint32),
+    ]
+
+    def as_dict(self) -> dict:
+        return {name: getattr(self, name) for name, _ in self._fields_}
+
+
+CLUSTER_OUT_DTYPE = np.dtype([
+    ("total_nodes", "<i8"), ("healthy_nodes", "<i8"), ("total_pods", "<i8"), ("running_pods", "<i8"),
+    ("total_cpu", "<i8"), ("used_cpu", "<i8"), ("total_memory", "<i8"), ("used_memory", "<i8"),
+    ("total_gpus", "<i8"), ("available_gpus", "<i8"), ("cpu_usage_rate", "<f8"),
+    ("memory_usage_rate", "<f8"), ("health_status", "<i4"), ("issues", "<u4")])
+assert CLUSTER_OUT_DTYPE.itemsize == C.sizeof(ClusterOut) == 104
+
+_P = C.c_void_p
+_I64, _I32, _F64 = C.c_int64, C.c_int32, C.c_double
+
+# name -> (restype, argtypes); every symbol include/klm.h declares
+SIGNATURES = {
+    "klm_create": (C.c_int, [C.POINTER(C.c_int), C.c_int, C.POINTER(_P)]),
+    "klm_destroy": (None, [_P]),
+    "klm_last_error": (C.c_char_p, []),
+    "klm_abi_version": (C.c_int, []),
+    "klm_nodes_set": (C.c_int, [_P, _I64, _P, _P]),
+    "klm_schedule_batch": (C.c_int, [_P, _I64, _P, _P, _P, _P, _P, C.c_int]),
+    "klm_cluster_aggregate": (C.c_int, [_P, C.POINTER(NodeCols), _I64, _P, _I64, C.POINTER(ClusterOut)]),
+    "klm_node_rates": (C.c_int, [_P, _I64] + [_P] * 11),
+    "klm_pod_rates": (C.c_int, [_P, _I64] + [_P] * 13),
+    "klm_fleet_scan": (C.c_int, [_P, _I64, _P, _P, _F64, C.POINTER(_I64), _P, C.POINTER(_I64)]),
+    "klm_ring_create": (C.c_int, [_P, _I64, _I32]),
+    "klm_ring_ingest": (C.c_int, [_P, _I64, _P, _P]),
+    "klm_ring_ingest_tick": (C.c_int, [_P, _P]),
+    "klm_ring_load": (C.c_int, [_P, _I64, _I64, _I32, _P]),
+    "klm_ring_stats": (C.c_int, [_P, _I64, _I64, _P, _P, _P, _P]),
+    "klm_dev_node_best_scratch_bytes": (_I64, []),
+    "klm_dev_node_best": (C.c_int, [_P, _P, _I64, _I64, _P, _P, _P]),
+    "klm_dev_schedule": (C.c_int, [_P, _P, _I64, _I64, _P, _I64, _P, _P, _P, _P, _P, _P]),
+    "klm_dev_schedule_bruteforce": (C.c_int, [_P, _P, _I64, _I64, _I64, _P, _P, _P, _P, _P, _P]),
+    "klm_dev_merge_partials": (C.c_int, [C.c_int, _I64, _P, _P, _P, _P, _P]),
+    "klm_dev_cluster_scratch_bytes": (_I64, []),
+    "klm_dev_cluster_aggregate": (C.c_int, [C.POINTER(NodeCols), _I64, _P, _I64, _P, _P, _P]),
+    "klm_dev_cluster_sums": (C.c_int, [C.POINTER(NodeCols), _I64, _P, _I64, _P, _P, _P]),
+    "klm_dev_cluster_finish": (C.c_int, [_P, _P, _P]),
+    "klm_dev_node_rates": (C.c_int, [_I64] + [_P] * 12),
+    "klm_dev_pod_rates": (C.c_int, [_I64] + [_P] * 14),
+    "klm_dev_fleet_scan_scratch_bytes": (_I64, [_I64]),
+    "klm_dev_fleet_scan": (C.c_int, [_I64, _P, _P, _F64, _P, _P, _P, _P]),
+    "klm_dev_ring_ingest": (C.c_int, [_P, _P, _I64, _I32, _I32, _I64, _P, _P, _P]),
+    "klm_dev_window_stats": (C.c_int, [_P, _P, _I32, _I32, _I64, _I64, _P, _P, _P, _P, _P]),
+}
+
+_lib: Optional[C.CDLL] = None
+
+
+def load() -> C.CDLL:
+    """Load libklm.so and declare every signature. Fails loudly if it is missing."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(
+            f"{LIB_PATH} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+            "(make -C k8s-llm-monitor_b200/csrc). libklm has no CPU fallback.")
+    lib = C.CDLL(LIB_PATH)
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(lib, name)  # AttributeError here = header/library mismatch
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+def last_error() -> str:
+    return load().klm_last_error().decode("utf-8", "replace")
+
+
+def check(rc: int) -> None:
+    if rc != KLM_OK:
+        raise KlmError(rc, last_error())
+
+
+def _np(a, dtype) -> np.ndarray:
+    return np.ascontiguousarray(a, dtype=dtype)
+
+
+def _ptr(a: Optional[np.ndarray]) -> Optional[int]:
+    return None if a is None else a.ctypes.data
+
+
+class Handle:
+    """Host-buffer API: numpy in, numpy out, everything computed on the GPU."""
+
+    def __init__(self, device: int = 0):
+        self._lib = load()
+        self._h = _P()
+        dev = (C.c_int * 1)(device)
+        check(self._lib.klm_create(dev, 1, C.byref(self._h)))
+
+    def close(self) -> None:
+        if getattr(self, "_h", None) is not None and self._h:
+            self._lib.klm_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    # -- scheduling (controller.go:152-161, :174-221)
+    def nodes_set(self, battery, flags) -> None:
+        b, f = _np(battery, np.float64), _np(flags, np.uint8)
+        if b.shape != f.shape or b.ndim != 1:
+            raise ValueError("battery and flags must be 1-D and the same length")
+        check(self._lib.klm_nodes_set(self._h, b.size, _ptr(b), _ptr(f)))
+
+    def schedule_batch(self, min_battery, pref_off, pref_ids, algo: int = ALGO_DECOMPOSED
+                       ) -> Tuple[np.ndarray, np.ndarray]:
+        mb, off, ids = _np(min_battery, np.float64), _np(pref_off, np.int32), _np(pref_ids, np.int32)
+        r = mb.size
+        if off.size != r + 1:
+            raise ValueError("pref_off must have n_requests + 1 entries")
+        out_idx = np.empty(r, np.int32)
+        out_score = np.empty(r, np.float64)
+        if ids.size == 0:
+            ids = np.zeros(1, np.int32)
+        check(self._lib.klm_schedule_batch(self._h, r, _ptr(mb), _ptr(off), _ptr(ids),
+                                           _ptr(out_idx), _ptr(out_score), algo))
+        return out_idx, out_score
+
+    # -- aggregation (manager.go:493-565)
+    def cluster_aggregate(self, cpu_capacity, cpu_usage, memory_capacity, memory_usage, gpu_count,
+                          healthy, gpu_usage, pod_running) -> dict:
+        cols = [_np(cpu_capacity, np.int64), _np(cpu_usage, np.int64), _np(memory_capacity, np.int64),
+                _np(memory_usage, np.int64), _np(gpu_count, np.int32), _np(healthy, np.uint8)]
+        gu = _np(gpu_usage, np.float64)
+        pr = _np(pod_running, np.uint8)
+        n = cols[0].size
+        nc = NodeCols(*[a.ctypes.data if a.size else None for a in cols],
+                      gu.ctypes.data if gu.size else None, gu.size)
+        out = ClusterOut()
+        check(self._lib.klm_cluster_aggregate(self._h, C.byref(nc), n, _ptr(pr) if pr.size else None,
+                                              pr.size, C.byref(out)))
+        return out.as_dict()
+
+    def node_rates(self, cpu_capacity, cpu_usage, memory_capacity, memory_usage, disk_capacity,
+                   disk_allocatable=None) -> dict:
+        a = [_np(x, np.int64) for x in (cpu_capacity, cpu_usage, memory_capacity, memory_usage, disk_capacity)]
+        da = None if disk_allocatable is None else _np(disk_allocatable, np.int64)
+        n = a[0].size
+        out = {"cpu_rate": np.empty(n, np.float64), "memory_rate": np.empty(n, np.float64),
+               "disk_usage": np.empty(n, np.int64), "disk_rate": np.empty(n, np.float64),
+               "under_pressure": np.empty(n, np.uint8)}
+        check(self._lib.klm_node_rates(self._h, n, *[_ptr(x) for x in a], _ptr(da),
+                                       *[_ptr(v) for v in out.values()]))
+        return out
+
+    def pod_rates(self, ctr_off, cpu_usage, memory_usage, cpu_request, cpu_limit, memory_request,
+                  memory_limit) -> dict:
+        off = _np(ctr_off, np.int32)
+        cols = [_np(x, np.int64) for x in (cpu_usage, memory_usage, cpu_request, cpu_limit,
+                                           memory_request, memory_limit)]
+        p = off.size - 1
+        out = {"pod_totals": np.empty((6, p), np.int64), "cpu_rate": np.empty(p, np.float64),
+               "memory_rate": np.empty(p, np.float64), "cpu_util": np.empty(p, np.float64),
+               "memory_util": np.empty(p, np.float64), "over_limit": np.empty(p, np.uint8)}
+        check(self._lib.klm_pod_rates(self._h, p, _ptr(off), *[_ptr(x) if x.size else None for x in cols],
+                                      *[_ptr(v) for v in out.values()]))
+        return out
+
+    def fleet_scan(self, status_ok, remaining_percent, threshold: float) -> Tuple[int, np.ndarray]:
+        ok, pct = _np(status_ok, np.uint8), _np(remaining_percent, np.float64)
+        n = ok.size
+        low = np.empty(max(n, 1), np.int32)
+        healthy, n_low = _I64(0), _I64(0)
+        check(self._lib.klm_fleet_scan(self._h, n, _ptr(ok), _ptr(pct), float(threshold),
+                                       C.byref(healthy), _ptr(low), C.byref(n_low)))
+        return healthy.value, low[: n_low.value].copy()
+
+    # -- metric ring
+    def ring_create(self, n_series: int, window: int) -> None:
+        check(self._lib.klm_ring_create(self._h, n_series, window))
+        self._ring_shape = (n_series, window)
+
+    def ring_ingest(self, series_ids, values) -> None:
+        ids, v = _np(series_ids, np.int64), _np(values, np.float32)
+        check(self._lib.klm_ring_ingest(self._h, ids.size, _ptr(ids), _ptr(v)))
+
+    def ring_ingest_tick(self, values) -> None:
+        v = _np(values, np.float32)
+        if v.size != self._ring_shape[0]:
+            raise ValueError("one value per series expected")
+        check(self._lib.klm_ring_ingest_tick(self._h, _ptr(v)))
+
+    def ring_load(self, s0: int, data) -> None:
+        d = _np(data, np.float32)
+        if d.ndim != 2:
+            raise ValueError("data must be [rows, count]")
+        check(self._lib.klm_ring_load(self._h, s0, s0 + d.shape[0], d.shape[1], _ptr(d)))
+
+    def ring_stats(self, s0: int = 0, s1: Optional[int] = None, p95: bool = True) -> dict:
+        if s1 is None:
+            s1 = self._ring_shape[0]
+        n = s1 - s0
+        out = {"min": np.empty(n, np.float32), "max": np.empty(n, np.float32),
+               "mean": np.empty(n, np.float64), "p95": np.empty(n, np.float32) if p95 else None}
+        check(self._lib.klm_ring_stats(self._h, s0, s1, _ptr(out["min"]), _ptr(out["max"]),
+                                       _ptr(out["mean"]), _ptr(out["p95"])))
+        return out
+
+
+# --------------------------------------------------------------------------
+# Device-pointer layer for callers that keep their data in HBM (torch tensors).
+# torch is plumbing here: it owns the memory and the stream, nothing else.
+# --------------------------------------------------------------------------
+
+def _dp(t) -> Optional[int]:
+    return None if t is None else t.data_ptr()
+
+
+def _stream_ptr(stream=None) -> int:
+    import torch
+    s = stream if stream is not None else torch.cuda.current_stream()
+    return s.cuda_stream
+
+
+def _need(t, dtype, name):
+    if t is None:
+        return
+    if not t.is_cuda or t.dtype != dtype or not t.is_contiguous():
+        raise ValueError(f"{name}: need a contiguous CUDA tensor of {dtype}, got {t.dtype} on {t.device}")
+
+
+class Dev:
+    """klm_dev_* calls on torch CUDA tensors; only enqueues work on the current stream."""
+
+    def __init__(self, device=None):
+        import torch
+        self.torch = torch
+        self.lib = load()
+        self.device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        with torch.cuda.device(self.device):
+            # scratch areas carry tickets that must start at zero
+            self.best_scratch = torch.zeros(self.lib.klm_dev_node_best_scratch_bytes(), dtype=torch.uint8,
+                                            device=self.device)
+            self.cluster_scratch = torch.zeros(self.lib.klm_dev_cluster_scratch_bytes(), dtype=torch.uint8,
+                                               device=self.device)
+
+    def node_best(self, battery, flags, best, node_base: int = 0, stream=None, scratch=None):
+        t = self.torch
+        _need(battery, t.float64, "battery"); _need(flags, t.uint8, "flags"); _need(best, t.int64, "best")
+        sc = self.best_scratch if scratch is None else scratch
+        check(self.lib.klm_dev_node_best(_dp(battery), _dp(flags), battery.numel(), node_base, _dp(best),
+                                         _dp(sc), _stream_ptr(stream)))
+
+    def schedule(self, battery, flags, best, min_battery, pref_off, pref_ids, out_idx, out_score,
+                 node_base: int = 0, stream=None):
+        t = self.torch
+        _need(min_battery, t.float64, "min_battery"); _need(pref_off, t.int32, "pref_off")
+        _need(pref_ids, t.int32, "pref_ids"); _need(out_idx, t.int32, "out_idx")
+        _need(out_score, t.float64, "out_score")
+        check(self.lib.klm_dev_schedule(_dp(battery), _dp(flags), battery.numel(), node_base, _dp(best),
+                                        min_battery.numel(), _dp(min_battery), _dp(pref_off), _dp(pref_ids),
+                                        _dp(out_idx), _dp(out_score), _stream_ptr(stream)))
+
+    def schedule_bruteforce(self, battery, flags, min_battery, pref_off, pref_ids, out_idx, out_score,
+                            node_base: int = 0, stream=None):
+        check(self.lib.klm_dev_schedule_bruteforce(_dp(battery), _dp(flags), battery.numel(), node_base,
+                                                   min_battery.numel(), _dp(min_battery), _dp(pref_off),
+                                                   _dp(pref_ids), _dp(out_idx), _dp(out_score),
+                                                   _stream_ptr(stream)))
+
+    def merge_partials(self, part_idx, part_score, out_idx, out_score, stream=None):
+        t = self.torch
+        _need(part_idx, t.int32, "part_idx"); _need(part_score, t.float64, "part_score")
+        n_parts, r = part_idx.shape
+        check(self.lib.klm_dev_merge_partials(n_parts, r, _dp(part_idx), _dp(part_score), _dp(out_idx),
+                                              _dp(out_score), _stream_ptr(stream)))
+
+    def _cols(self, cols: dict) -> NodeCols:
+        gu = cols.get("gpu_usage")
+        return NodeCols(_dp(cols["cpu_capacity"]), _dp(cols["cpu_usage"]), _dp(cols["memory_capacity"]),
+                        _dp(cols["memory_usage"]), _dp(cols["gpu_count"]), _dp(cols["healthy"]),
+                        _dp(gu) if gu is not None and gu.numel() else None,
+                        0 if gu is None else gu.numel())
+
+    def cluster_aggregate(self, cols: dict, pod_running, out, stream=None):
+        """out: uint8 tensor of 104 bytes (klm_cluster_out)."""
+        nc = self._cols(cols)
+        check(self.lib.klm_dev_cluster_aggregate(C.byref(nc), cols["cpu_capacity"].numel(), _dp(pod_running),
+                                                 pod_running.numel(), _dp(out), _dp(self.cluster_scratch),
+                                                 _stream_ptr(stream)))
+
+    def cluster_sums(self, cols: dict, pod_running, sums, stream=None):
+        nc = self._cols(cols)
+        check(self.lib.klm_dev_cluster_sums(C.byref(nc), cols["cpu_capacity"].numel(), _dp(pod_running),
+                                            pod_running.numel(), _dp(sums), _dp(self.cluster_scratch),
+                                            _stream_ptr(stream)))
+
+    def cluster_finish(self, sums, out, stream=None):
+        check(self.lib.klm_dev_cluster_finish(_dp(sums), _dp(out), _stream_ptr(stream)))
+
+    def node_rates(self, cols: dict, disk_capacity, disk_allocatable, out: dict, stream=None):
+        check(self.lib.klm_dev_node_rates(cols["cpu_capacity"].numel(), _dp(cols["cpu_capacity"]),
+                                          _dp(cols["cpu_usage"]), _dp(cols["memory_capacity"]),
+                                          _dp(cols["memory_usage"]), _dp(disk_capacity), _dp(disk_allocatable),
+                                          _dp(out.get("cpu_rate")), _dp(out.get("memory_rate")),
+                                          _dp(out.get("disk_usage")), _dp(out.get("disk_rate")),
+                                          _dp(out.get("under_pressure")), _stream_ptr(stream)))
+
+    def ring_ingest(self, ring, seen, window: int, values, series_ids=None, stream=None):
+        t = self.torch
+        _need(ring, t.float32, "ring"); _need(seen, t.int32, "seen"); _need(values, t.float32, "values")
+        n_series, pitch = ring.shape
+        check(self.lib.klm_dev_ring_ingest(_dp(ring), _dp(seen), n_series, window, pitch, values.numel(),
+                                           _dp(series_ids), _dp(values), _stream_ptr(stream)))
+
+    def window_stats(self, ring, seen, window: int, out_min, out_max, out_mean, out_p95,
+                     s0: int = 0, s1: Optional[int] = None, stream=None):
+        t = self.torch
+        _need(ring, t.float32, "ring"); _need(seen, t.int32, "seen")
+        _need(out_min, t.float32, "out_min"); _need(out_max, t.float32, "out_max")
+        _need(out_mean, t.float64, "out_mean"); _need(out_p95, t.float32, "out_p95")
+        n_series, pitch = ring.shape
+        if s1 is None:
+            s1 = n_series
+        check(self.lib.klm_dev_window_stats(_dp(ring), _dp(seen), window, pitch, s0, s1, _dp(out_min),
+                                            _dp(out_max), _dp(out_mean), _dp(out_p95), _stream_ptr(stream)))

@@ -1,0 +1,562 @@
+// Host-buffer half of the C ABI (include/klm.h): a handle that owns device
+// memory and a stream, copies caller arrays in, launches the klm_dev_* kernels
+// and copies results out before returning. No caller pointer is retained.
+//
+// Callers in the reference (Sabre94/k8s-llm-monitor) this layer is shaped for:
+//   internal/scheduler/controller.go:88-110   reconcile: one UAV snapshot, then
+//                                             every pending request (klm_nodes_set
+//                                             + klm_schedule_batch)
+//   internal/metrics/manager.go:195-319       Collect -> calculateClusterMetrics
+//   internal/metrics/manager.go:391-449       UpdateUAVReport (ring ingest)
+// There is no CPU fallback: every entry point needs a live CUDA device.
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <new>
+
+#include "common.cuh"
+
+namespace klm {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+int cuda_fail(cudaError_t e, const char* what) {
+  set_error("CUDA error %d (%s) in %s", (int)e, cudaGetErrorString(e), what);
+  return KLM_ECUDA;
+}
+
+int launch_ring_load(float* ring, uint32_t* seen, int32_t pitch, int64_t s0, int64_t n_rows,
+                     int32_t count, const float* data, cudaStream_t st);
+
+// Grow-only device buffer.
+struct DevBuf {
+  void* p = nullptr;
+  size_t cap = 0;
+  int ensure(size_t bytes) {
+    if (bytes <= cap) return KLM_OK;
+    size_t want = bytes + bytes / 2;
+    want = (want + 255) & ~size_t(255);
+    if (p) {
+      KLM_CUDA(cudaFree(p));
+      p = nullptr;
+      cap = 0;
+    }
+    KLM_CUDA(cudaMalloc(&p, want));
+    cap = want;
+    return KLM_OK;
+  }
+  void release() {
+    if (p) cudaFree(p);
+    p = nullptr;
+    cap = 0;
+  }
+  template <typename T>
+  T* as() const { return static_cast<T*>(p); }
+};
+
+}  // namespace klm
+
+using namespace klm;
+
+struct klm_handle {
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  std::mutex mu;
+
+  // scheduling
+  int64_t n_nodes = -1;  // -1: no snapshot installed yet
+  DevBuf battery, flags, best, best_scratch;
+  DevBuf req_min, req_off, req_ids, res_idx, res_score;
+
+  // aggregation
+  DevBuf agg_cols, agg_pods, agg_gpu, agg_out, agg_scratch;
+  DevBuf rate_in, rate_out, pod_tot;
+  DevBuf fleet_in, fleet_out, fleet_scratch;
+
+  // ring
+  DevBuf ring, seen, ing_ids, ing_vals, stats_out;
+  int64_t n_series = 0;
+  int32_t window = 0, pitch = 0;
+};
+
+namespace {
+
+struct Guard {
+  std::lock_guard<std::mutex> lk;
+  int rc;
+  explicit Guard(klm_handle* h) : lk(h->mu), rc(KLM_OK) {
+    cudaError_t e = cudaSetDevice(h->device);
+    if (e != cudaSuccess) rc = cuda_fail(e, "cudaSetDevice");
+  }
+};
+
+#define KLM_ENTER(h)                       \
+  if (!(h)) {                              \
+    set_error("null handle");              \
+    return KLM_EINVAL;                     \
+  }                                        \
+  Guard klm_guard_(h);                     \
+  if (klm_guard_.rc != KLM_OK) return klm_guard_.rc
+
+#define KLM_TRY(expr)              \
+  do {                             \
+    int klm_rc_ = (expr);          \
+    if (klm_rc_ != KLM_OK) return klm_rc_; \
+  } while (0)
+
+int h2d(void* dst, const void* src, size_t bytes, cudaStream_t st) {
+  if (bytes == 0) return KLM_OK;
+  KLM_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, st));
+  return KLM_OK;
+}
+int d2h(void* dst, const void* src, size_t bytes, cudaStream_t st) {
+  if (bytes == 0) return KLM_OK;
+  KLM_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, st));
+  return KLM_OK;
+}
+int sync(cudaStream_t st) {
+  KLM_CUDA(cudaStreamSynchronize(st));
+  return KLM_OK;
+}
+
+size_t align256(size_t b) { return (b + 255) & ~size_t(255); }
+
+}  // namespace
+
+extern "C" const char* klm_last_error(void) { return g_err; }
+extern "C" int klm_abi_version(void) { return 1000; }
+
+extern "C" int klm_create(const int* device_ids, int n_dev, klm_handle** out) {
+  if (!out) {
+    set_error("klm_create: out is null");
+    return KLM_EINVAL;
+  }
+  *out = nullptr;
+  if (n_dev != 1 && !(n_dev == 0 && !device_ids)) {
+    set_error("klm_create: one device per handle (n_dev == 1); run one handle per GPU");
+    return KLM_EINVAL;
+  }
+  int count = 0;
+  cudaError_t e = cudaGetDeviceCount(&count);
+  if (e != cudaSuccess || count == 0) {
+    set_error("klm_create: no CUDA device (%s); libklm has no CPU fallback",
+              e == cudaSuccess ? "device count is 0" : cudaGetErrorString(e));
+    return KLM_ENODEV;
+  }
+  const int dev = device_ids ? device_ids[0] : 0;
+  if (dev < 0 || dev >= count) {
+    set_error("klm_create: device %d out of range [0, %d)", dev, count);
+    return KLM_EINVAL;
+  }
+  KLM_CUDA(cudaSetDevice(dev));
+  cudaDeviceProp prop;
+  KLM_CUDA(cudaGetDeviceProperties(&prop, dev));
+  if (prop.major != 10) {
+    set_error("klm_create: device %d is sm_%d%d; libklm is built for sm_100a (B200) only", dev,
+              prop.major, prop.minor);
+    return KLM_ENODEV;
+  }
+  klm_handle* h = new (std::nothrow) klm_handle();
+  if (!h) {
+    set_error("klm_create: out of host memory");
+    return KLM_EINVAL;
+  }
+  h->device = dev;
+  e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);
+  if (e != cudaSuccess) {
+    delete h;
+    return cuda_fail(e, "cudaStreamCreateWithFlags");
+  }
+  // scratch areas carry self-resetting tickets that must start at zero
+  int rc = h->best_scratch.ensure((size_t)klm_dev_node_best_scratch_bytes());
+  if (rc == KLM_OK) rc = h->agg_scratch.ensure((size_t)klm_dev_cluster_scratch_bytes());
+  if (rc == KLM_OK) rc = h->best.ensure(2 * sizeof(int64_t));
+  if (rc == KLM_OK) rc = h->agg_out.ensure(sizeof(klm_cluster_out));
+  if (rc == KLM_OK) {
+    e = cudaMemsetAsync(h->best_scratch.p, 0, h->best_scratch.cap, h->stream);
+    if (e == cudaSuccess) e = cudaMemsetAsync(h->agg_scratch.p, 0, h->agg_scratch.cap, h->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
+    if (e != cudaSuccess) rc = cuda_fail(e, "scratch memset");
+  }
+  if (rc != KLM_OK) {
+    klm_destroy(h);
+    return rc;
+  }
+  *out = h;
+  return KLM_OK;
+}
+
+extern "C" void klm_destroy(klm_handle* h) {
+  if (!h) return;
+  cudaSetDevice(h->device);
+  if (h->stream) cudaStreamSynchronize(h->stream);
+  DevBuf* bufs[] = {&h->battery,  &h->flags,    &h->best,       &h->best_scratch, &h->req_min,
+                    &h->req_off,  &h->req_ids,  &h->res_idx,    &h->res_score,    &h->agg_cols,
+                    &h->agg_pods, &h->agg_gpu,  &h->agg_out,    &h->agg_scratch,  &h->rate_in,
+                    &h->rate_out, &h->pod_tot, &h->fleet_in, &h->fleet_out,  &h->fleet_scratch, &h->ring,
+                    &h->seen,     &h->ing_ids,  &h->ing_vals,   &h->stats_out};
+  for (DevBuf* b : bufs) b->release();
+  if (h->stream) cudaStreamDestroy(h->stream);
+  delete h;
+}
+
+// ------------------------------------------------------------ scheduling
+
+extern "C" int klm_nodes_set(klm_handle* h, int64_t n, const double* battery,
+                             const uint8_t* flags) {
+  KLM_ENTER(h);
+  if (n < 0 || n > 0x7fffffff || (n > 0 && (!battery || !flags))) {
+    set_error("klm_nodes_set: bad argument (0 <= n_nodes < 2^31, arrays non-null)");
+    return KLM_EINVAL;
+  }
+  KLM_TRY(h->battery.ensure((size_t)n * sizeof(double)));
+  KLM_TRY(h->flags.ensure((size_t)n));
+  KLM_TRY(h2d(h->battery.p, battery, (size_t)n * sizeof(double), h->stream));
+  KLM_TRY(h2d(h->flags.p, flags, (size_t)n, h->stream));
+  // K1 runs once per snapshot, not once per batch
+  KLM_TRY(klm_dev_node_best(h->battery.as<double>(), h->flags.as<uint8_t>(), n, 0,
+                            h->best.as<int64_t>(), h->best_scratch.p, h->stream));
+  KLM_TRY(sync(h->stream));  // caller may free its arrays after return
+  h->n_nodes = n;
+  return KLM_OK;
+}
+
+extern "C" int klm_schedule_batch(klm_handle* h, int64_t R, const double* min_battery,
+                                  const int32_t* pref_off, const int32_t* pref_ids,
+                                  int32_t* out_idx, double* out_score, int algo) {
+  KLM_ENTER(h);
+  if (h->n_nodes < 0) {
+    set_error("klm_schedule_batch: no node snapshot; call klm_nodes_set first");
+    return KLM_ESTATE;
+  }
+  if (R < 0 || (algo != KLM_ALGO_DECOMPOSED && algo != KLM_ALGO_BRUTEFORCE)) {
+    set_error("klm_schedule_batch: bad argument");
+    return KLM_EINVAL;
+  }
+  if (R == 0) return KLM_OK;
+  if (!min_battery || !pref_off || !out_idx || !out_score) {
+    set_error("klm_schedule_batch: null array");
+    return KLM_EINVAL;
+  }
+  const int64_t n_ids = pref_off[R];
+  if (pref_off[0] != 0 || n_ids < 0 || (n_ids > 0 && !pref_ids)) {
+    set_error("klm_schedule_batch: pref_off must start at 0 and pref_ids be non-null");
+    return KLM_EINVAL;
+  }
+  KLM_TRY(h->req_min.ensure((size_t)R * sizeof(double)));
+  KLM_TRY(h->req_off.ensure((size_t)(R + 1) * sizeof(int32_t)));
+  KLM_TRY(h->req_ids.ensure((size_t)(n_ids > 0 ? n_ids : 1) * sizeof(int32_t)));
+  KLM_TRY(h->res_idx.ensure((size_t)R * sizeof(int32_t)));
+  KLM_TRY(h->res_score.ensure((size_t)R * sizeof(double)));
+  KLM_TRY(h2d(h->req_min.p, min_battery, (size_t)R * sizeof(double), h->stream));
+  KLM_TRY(h2d(h->req_off.p, pref_off, (size_t)(R + 1) * sizeof(int32_t), h->stream));
+  KLM_TRY(h2d(h->req_ids.p, pref_ids, (size_t)n_ids * sizeof(int32_t), h->stream));
+  if (algo == KLM_ALGO_DECOMPOSED) {
+    KLM_TRY(klm_dev_schedule(h->battery.as<double>(), h->flags.as<uint8_t>(), h->n_nodes, 0,
+                             h->best.as<int64_t>(), R, h->req_min.as<double>(),
+                             h->req_off.as<int32_t>(), h->req_ids.as<int32_t>(),
+                             h->res_idx.as<int32_t>(), h->res_score.as<double>(), h->stream));
+  } else {
+    KLM_TRY(klm_dev_schedule_bruteforce(
+        h->battery.as<double>(), h->flags.as<uint8_t>(), h->n_nodes, 0, R,
+        h->req_min.as<double>(), h->req_off.as<int32_t>(), h->req_ids.as<int32_t>(),
+        h->res_idx.as<int32_t>(), h->res_score.as<double>(), h->stream));
+  }
+  KLM_TRY(d2h(out_idx, h->res_idx.p, (size_t)R * sizeof(int32_t), h->stream));
+  KLM_TRY(d2h(out_score, h->res_score.p, (size_t)R * sizeof(double), h->stream));
+  return sync(h->stream);
+}
+
+// ----------------------------------------------------- cluster aggregate
+
+extern "C" int klm_cluster_aggregate(klm_handle* h, const klm_node_cols* c, int64_t n,
+                                     const uint8_t* pod_running, int64_t n_pods,
+                                     klm_cluster_out* out) {
+  KLM_ENTER(h);
+  if (!c || !out || n < 0 || n_pods < 0 || c->n_gpu_usage < 0 ||
+      (n > 0 && (!c->cpu_capacity || !c->cpu_usage || !c->memory_capacity || !c->memory_usage ||
+                 !c->gpu_count || !c->healthy)) ||
+      (n_pods > 0 && !pod_running) || (c->n_gpu_usage > 0 && !c->gpu_usage)) {
+    set_error("klm_cluster_aggregate: bad argument");
+    return KLM_EINVAL;
+  }
+  // one device block, columns at 256-byte aligned offsets
+  const size_t col8 = align256((size_t)n * 8), col4 = align256((size_t)n * 4),
+               col1 = align256((size_t)n);
+  KLM_TRY(h->agg_cols.ensure(4 * col8 + col4 + col1 + 256));
+  KLM_TRY(h->agg_pods.ensure((size_t)n_pods + 256));
+  KLM_TRY(h->agg_gpu.ensure((size_t)c->n_gpu_usage * 8 + 256));
+  char* base = h->agg_cols.as<char>();
+  klm_node_cols d;
+  d.cpu_capacity = reinterpret_cast<int64_t*>(base);
+  d.cpu_usage = reinterpret_cast<int64_t*>(base + col8);
+  d.memory_capacity = reinterpret_cast<int64_t*>(base + 2 * col8);
+  d.memory_usage = reinterpret_cast<int64_t*>(base + 3 * col8);
+  d.gpu_count = reinterpret_cast<int32_t*>(base + 4 * col8);
+  d.healthy = reinterpret_cast<uint8_t*>(base + 4 * col8 + col4);
+  d.gpu_usage = h->agg_gpu.as<double>();
+  d.n_gpu_usage = c->n_gpu_usage;
+  cudaStream_t st = h->stream;
+  KLM_TRY(h2d((void*)d.cpu_capacity, c->cpu_capacity, (size_t)n * 8, st));
+  KLM_TRY(h2d((void*)d.cpu_usage, c->cpu_usage, (size_t)n * 8, st));
+  KLM_TRY(h2d((void*)d.memory_capacity, c->memory_capacity, (size_t)n * 8, st));
+  KLM_TRY(h2d((void*)d.memory_usage, c->memory_usage, (size_t)n * 8, st));
+  KLM_TRY(h2d((void*)d.gpu_count, c->gpu_count, (size_t)n * 4, st));
+  KLM_TRY(h2d((void*)d.healthy, c->healthy, (size_t)n, st));
+  KLM_TRY(h2d((void*)d.gpu_usage, c->gpu_usage, (size_t)c->n_gpu_usage * 8, st));
+  KLM_TRY(h2d(h->agg_pods.p, pod_running, (size_t)n_pods, st));
+  KLM_TRY(klm_dev_cluster_aggregate(&d, n, h->agg_pods.as<uint8_t>(), n_pods,
+                                    h->agg_out.as<klm_cluster_out>(), h->agg_scratch.p, st));
+  KLM_TRY(d2h(out, h->agg_out.p, sizeof(klm_cluster_out), st));
+  return sync(st);
+}
+
+extern "C" int klm_node_rates(klm_handle* h, int64_t n, const int64_t* cpu_cap,
+                              const int64_t* cpu_use, const int64_t* mem_cap,
+                              const int64_t* mem_use, const int64_t* disk_cap,
+                              const int64_t* disk_alloc, double* cpu_rate, double* mem_rate,
+                              int64_t* disk_usage, double* disk_rate, uint8_t* under_pressure) {
+  KLM_ENTER(h);
+  if (n < 0 || (n > 0 && (!cpu_cap || !cpu_use || !mem_cap || !mem_use))) {
+    set_error("klm_node_rates: bad argument");
+    return KLM_EINVAL;
+  }
+  if (n == 0) return KLM_OK;
+  const size_t col = align256((size_t)n * 8);
+  KLM_TRY(h->rate_in.ensure(6 * col));
+  KLM_TRY(h->rate_out.ensure(5 * col));
+  char* in = h->rate_in.as<char>();
+  char* outp = h->rate_out.as<char>();
+  cudaStream_t st = h->stream;
+  const int64_t* src[6] = {cpu_cap, cpu_use, mem_cap, mem_use, disk_cap, disk_alloc};
+  const int64_t* dev[6];
+  for (int k = 0; k < 6; ++k) {
+    dev[k] = src[k] ? reinterpret_cast<const int64_t*>(in + k * col) : nullptr;
+    if (src[k]) KLM_TRY(h2d(in + k * col, src[k], (size_t)n * 8, st));
+  }
+  double* d_cr = reinterpret_cast<double*>(outp);
+  double* d_mr = reinterpret_cast<double*>(outp + col);
+  int64_t* d_du = reinterpret_cast<int64_t*>(outp + 2 * col);
+  double* d_dr = reinterpret_cast<double*>(outp + 3 * col);
+  uint8_t* d_up = reinterpret_cast<uint8_t*>(outp + 4 * col);
+  KLM_TRY(klm_dev_node_rates(n, dev[0], dev[1], dev[2], dev[3], dev[4], dev[5], d_cr, d_mr, d_du,
+                             d_dr, d_up, st));
+  if (cpu_rate) KLM_TRY(d2h(cpu_rate, d_cr, (size_t)n * 8, st));
+  if (mem_rate) KLM_TRY(d2h(mem_rate, d_mr, (size_t)n * 8, st));
+  if (disk_usage) KLM_TRY(d2h(disk_usage, d_du, (size_t)n * 8, st));
+  if (disk_rate) KLM_TRY(d2h(disk_rate, d_dr, (size_t)n * 8, st));
+  if (under_pressure) KLM_TRY(d2h(under_pressure, d_up, (size_t)n, st));
+  return sync(st);
+}
+
+extern "C" int klm_pod_rates(klm_handle* h, int64_t n_pods, const int32_t* ctr_off,
+                             const int64_t* c_cpu_use, const int64_t* c_mem_use,
+                             const int64_t* c_cpu_req, const int64_t* c_cpu_lim,
+                             const int64_t* c_mem_req, const int64_t* c_mem_lim,
+                             int64_t* pod_totals, double* cpu_rate, double* mem_rate,
+                             double* cpu_util, double* mem_util, uint8_t* over_limit) {
+  KLM_ENTER(h);
+  if (n_pods < 0 || (n_pods > 0 && !ctr_off)) {
+    set_error("klm_pod_rates: bad argument");
+    return KLM_EINVAL;
+  }
+  if (n_pods == 0) return KLM_OK;
+  const int64_t n_ctr = ctr_off[n_pods];
+  if (ctr_off[0] != 0 || n_ctr < 0 ||
+      (n_ctr > 0 && (!c_cpu_use || !c_mem_use || !c_cpu_req || !c_cpu_lim || !c_mem_req ||
+                     !c_mem_lim))) {
+    set_error("klm_pod_rates: ctr_off must start at 0 and container columns be non-null");
+    return KLM_EINVAL;
+  }
+  const size_t ccol = align256((size_t)n_ctr * 8), off_b = align256((size_t)(n_pods + 1) * 4);
+  const size_t pcol = align256((size_t)n_pods * 8);
+  KLM_TRY(h->rate_in.ensure(6 * ccol + off_b));
+  KLM_TRY(h->rate_out.ensure(11 * pcol));
+  char* in = h->rate_in.as<char>();
+  char* outp = h->rate_out.as<char>();
+  cudaStream_t st = h->stream;
+  const int64_t* src[6] = {c_cpu_use, c_mem_use, c_cpu_req, c_cpu_lim, c_mem_req, c_mem_lim};
+  for (int k = 0; k < 6; ++k) KLM_TRY(h2d(in + k * ccol, src[k], (size_t)n_ctr * 8, st));
+  KLM_TRY(h2d(in + 6 * ccol, ctr_off, (size_t)(n_pods + 1) * 4, st));
+  auto C = [&](int k) { return reinterpret_cast<const int64_t*>(in + k * ccol); };
+  DevBuf& tot = h->pod_tot;  // [6][P] int64, contiguous like the caller's
+  KLM_TRY(tot.ensure((size_t)6 * n_pods * 8));
+  double* d_cr = reinterpret_cast<double*>(outp);
+  double* d_mr = reinterpret_cast<double*>(outp + pcol);
+  double* d_cu = reinterpret_cast<double*>(outp + 2 * pcol);
+  double* d_mu = reinterpret_cast<double*>(outp + 3 * pcol);
+  uint8_t* d_ov = reinterpret_cast<uint8_t*>(outp + 4 * pcol);
+  KLM_TRY(klm_dev_pod_rates(n_pods, reinterpret_cast<const int32_t*>(in + 6 * ccol), C(0), C(1),
+                            C(2), C(3), C(4), C(5), tot.as<int64_t>(), d_cr, d_mr, d_cu, d_mu,
+                            d_ov, st));
+  if (pod_totals) KLM_TRY(d2h(pod_totals, tot.p, (size_t)6 * n_pods * 8, st));
+  if (cpu_rate) KLM_TRY(d2h(cpu_rate, d_cr, (size_t)n_pods * 8, st));
+  if (mem_rate) KLM_TRY(d2h(mem_rate, d_mr, (size_t)n_pods * 8, st));
+  if (cpu_util) KLM_TRY(d2h(cpu_util, d_cu, (size_t)n_pods * 8, st));
+  if (mem_util) KLM_TRY(d2h(mem_util, d_mu, (size_t)n_pods * 8, st));
+  if (over_limit) KLM_TRY(d2h(over_limit, d_ov, (size_t)n_pods, st));
+  return sync(st);
+}
+
+extern "C" int klm_fleet_scan(klm_handle* h, int64_t n, const uint8_t* status_ok,
+                              const double* pct, double threshold, int64_t* healthy_count,
+                              int32_t* low_idx, int64_t* n_low) {
+  KLM_ENTER(h);
+  if (n < 0 || n > 0x7fffffff || !healthy_count || !n_low ||
+      (n > 0 && (!status_ok || !pct || !low_idx))) {
+    set_error("klm_fleet_scan: bad argument");
+    return KLM_EINVAL;
+  }
+  const size_t pb = align256((size_t)n * 8), sb = align256((size_t)n);
+  KLM_TRY(h->fleet_in.ensure(pb + sb + 256));
+  KLM_TRY(h->fleet_out.ensure(256 + (size_t)n * 4));
+  KLM_TRY(h->fleet_scratch.ensure((size_t)klm_dev_fleet_scan_scratch_bytes(n)));
+  char* in = h->fleet_in.as<char>();
+  char* outp = h->fleet_out.as<char>();
+  cudaStream_t st = h->stream;
+  KLM_TRY(h2d(in, pct, (size_t)n * 8, st));
+  KLM_TRY(h2d(in + pb, status_ok, (size_t)n, st));
+  int64_t* d_cnt = reinterpret_cast<int64_t*>(outp);
+  int32_t* d_idx = reinterpret_cast<int32_t*>(outp + 256);
+  KLM_TRY(klm_dev_fleet_scan(n, reinterpret_cast<uint8_t*>(in + pb),
+                             reinterpret_cast<double*>(in), threshold, d_cnt, d_idx,
+                             h->fleet_scratch.p, st));
+  int64_t cnt[2] = {0, 0};
+  KLM_TRY(d2h(cnt, d_cnt, sizeof(cnt), st));
+  KLM_TRY(sync(st));
+  *healthy_count = cnt[0];
+  *n_low = cnt[1];
+  if (cnt[1] > 0) {
+    KLM_TRY(d2h(low_idx, d_idx, (size_t)cnt[1] * 4, st));
+    KLM_TRY(sync(st));
+  }
+  return KLM_OK;
+}
+
+// ------------------------------------------------------------------ ring
+
+extern "C" int klm_ring_create(klm_handle* h, int64_t n_series, int32_t window) {
+  KLM_ENTER(h);
+  if (n_series < 1 || window < 1) {
+    set_error("klm_ring_create: n_series and window must be positive");
+    return KLM_EINVAL;
+  }
+  const int32_t pitch = (window + 3) & ~3;
+  const size_t bytes = (size_t)n_series * pitch * sizeof(float);
+  KLM_TRY(h->ring.ensure(bytes));
+  KLM_TRY(h->seen.ensure((size_t)n_series * sizeof(uint32_t)));
+  KLM_CUDA(cudaMemsetAsync(h->ring.p, 0, bytes, h->stream));
+  KLM_CUDA(cudaMemsetAsync(h->seen.p, 0, (size_t)n_series * sizeof(uint32_t), h->stream));
+  KLM_TRY(sync(h->stream));
+  h->n_series = n_series;
+  h->window = window;
+  h->pitch = pitch;
+  return KLM_OK;
+}
+
+static int ring_ready(klm_handle* h, const char* who) {
+  if (h->n_series <= 0) {
+    set_error("%s: no ring; call klm_ring_create first", who);
+    return KLM_ESTATE;
+  }
+  return KLM_OK;
+}
+
+extern "C" int klm_ring_ingest(klm_handle* h, int64_t n, const int64_t* series_ids,
+                               const float* values) {
+  KLM_ENTER(h);
+  KLM_TRY(ring_ready(h, "klm_ring_ingest"));
+  if (n < 0 || (n > 0 && (!series_ids || !values))) {
+    set_error("klm_ring_ingest: bad argument");
+    return KLM_EINVAL;
+  }
+  if (n == 0) return KLM_OK;
+  KLM_TRY(h->ing_ids.ensure((size_t)n * 8));
+  KLM_TRY(h->ing_vals.ensure((size_t)n * 4));
+  KLM_TRY(h2d(h->ing_ids.p, series_ids, (size_t)n * 8, h->stream));
+  KLM_TRY(h2d(h->ing_vals.p, values, (size_t)n * 4, h->stream));
+  KLM_TRY(klm_dev_ring_ingest(h->ring.as<float>(), h->seen.as<uint32_t>(), h->n_series,
+                              h->window, h->pitch, n, h->ing_ids.as<int64_t>(),
+                              h->ing_vals.as<float>(), h->stream));
+  return sync(h->stream);
+}
+
+extern "C" int klm_ring_ingest_tick(klm_handle* h, const float* values) {
+  KLM_ENTER(h);
+  KLM_TRY(ring_ready(h, "klm_ring_ingest_tick"));
+  if (!values) {
+    set_error("klm_ring_ingest_tick: values is null");
+    return KLM_EINVAL;
+  }
+  KLM_TRY(h->ing_vals.ensure((size_t)h->n_series * 4));
+  KLM_TRY(h2d(h->ing_vals.p, values, (size_t)h->n_series * 4, h->stream));
+  KLM_TRY(klm_dev_ring_ingest(h->ring.as<float>(), h->seen.as<uint32_t>(), h->n_series,
+                              h->window, h->pitch, h->n_series, nullptr,
+                              h->ing_vals.as<float>(), h->stream));
+  return sync(h->stream);
+}
+
+extern "C" int klm_ring_load(klm_handle* h, int64_t s0, int64_t s1, int32_t count,
+                             const float* data) {
+  KLM_ENTER(h);
+  KLM_TRY(ring_ready(h, "klm_ring_load"));
+  if (s0 < 0 || s1 < s0 || s1 > h->n_series || count < 0 || count > h->window ||
+      (s1 > s0 && count > 0 && !data)) {
+    set_error("klm_ring_load: bad argument");
+    return KLM_EINVAL;
+  }
+  if (s1 == s0) return KLM_OK;
+  const int64_t rows = s1 - s0;
+  cudaStream_t st = h->stream;
+  // stage through device memory in chunks of <= 64 Mi samples (256 MiB)
+  int64_t rows_per_chunk = rows;
+  if (count > 0) {
+    rows_per_chunk = ((int64_t)64 << 20) / count;
+    if (rows_per_chunk < 1) rows_per_chunk = 1;
+  }
+  KLM_TRY(h->ing_vals.ensure((size_t)(rows_per_chunk < rows ? rows_per_chunk : rows) *
+                             (count > 0 ? count : 1) * 4));
+  for (int64_t r = 0; r < rows; r += rows_per_chunk) {
+    const int64_t m = rows - r < rows_per_chunk ? rows - r : rows_per_chunk;
+    KLM_TRY(h2d(h->ing_vals.p, data + r * count, (size_t)m * count * 4, st));
+    KLM_TRY(launch_ring_load(h->ring.as<float>(), h->seen.as<uint32_t>(), h->pitch, s0 + r, m,
+                             count, h->ing_vals.as<float>(), st));
+    KLM_TRY(sync(st));  // the staging buffer is reused by the next chunk
+  }
+  return KLM_OK;
+}
+
+extern "C" int klm_ring_stats(klm_handle* h, int64_t s0, int64_t s1, float* out_min,
+                              float* out_max, double* out_mean, float* out_p95) {
+  KLM_ENTER(h);
+  KLM_TRY(ring_ready(h, "klm_ring_stats"));
+  if (s0 < 0 || s1 < s0 || s1 > h->n_series) {
+    set_error("klm_ring_stats: series range out of bounds");
+    return KLM_EINVAL;
+  }
+  if (s1 == s0) return KLM_OK;
+  const int64_t rows = s1 - s0;
+  const size_t c4 = align256((size_t)rows * 4), c8 = align256((size_t)rows * 8);
+  KLM_TRY(h->stats_out.ensure(3 * c4 + c8));
+  char* o = h->stats_out.as<char>();
+  float* d_min = reinterpret_cast<float*>(o);
+  float* d_max = reinterpret_cast<float*>(o + c4);
+  float* d_p95 = reinterpret_cast<float*>(o + 2 * c4);
+  double* d_mean = reinterpret_cast<double*>(o + 3 * c4);
+  cudaStream_t st = h->stream;
+  KLM_TRY(klm_dev_window_stats(h->ring.as<float>(), h->seen.as<uint32_t>(), h->window, h->pitch,
+                               s0, s1, d_min, d_max, d_mean, out_p95 ? d_p95 : nullptr, st));
+  if (out_min) KLM_TRY(d2h(out_min, d_min, (size_t)rows * 4, st));
+  if (out_max) KLM_TRY(d2h(out_max, d_max, (size_t)rows * 4, st));
+  if (out_mean) KLM_TRY(d2h(out_mean, d_mean, (size_t)rows * 8, st));
+  if (out_p95) KLM_TRY(d2h(out_p95, d_p95, (size_t)rows * 4, st));
+  return sync(st);
+}

@@ -1,0 +1,372 @@
+// Scheduling kernels: K1 node_best_reduce, K2 schedule (decomposed),
+// K2b schedule_bruteforce, K3 merge_partials.
+//
+// Reference semantics (Sabre94/k8s-llm-monitor):
+//   internal/scheduler/controller.go:174-221  buildCandidates (filters + score)
+//   internal/scheduler/controller.go:160-161  stable sort desc, take [0]
+// Selection rule everywhere below: highest score; on equal scores the lowest
+// list index (what a stable descending sort followed by [0] yields).
+// All score arithmetic is IEEE f64, as Go's float64; comparisons are on
+// values, never on bit patterns (so -0.0 == +0.0 like in Go).
+#include "common.cuh"
+
+namespace klm {
+
+// ---------------------------------------------------------------- K1
+
+constexpr int kBestThreads = 256;
+constexpr int kBestNodesPerThread = 16;  // 8 x 16 B of battery + 16 B of flags per trip
+constexpr int kBestMaxBlocks = 2048;
+// scratch layout: [0, 256) ticket (u32, self-resetting); then partial
+// batteries (f64[kBestMaxBlocks]); then partial indices (i64[kBestMaxBlocks]).
+constexpr int64_t kBestScratchBytes = 256 + (int64_t)kBestMaxBlocks * 16;
+
+struct Best {
+  double bat;
+  int64_t idx;  // -1: none
+};
+
+__device__ __forceinline__ Best better(Best a, Best b) {
+  // a wins unless b has a larger battery, or the same battery and a lower index
+  if (b.idx < 0) return a;
+  if (a.idx < 0) return b;
+  if (b.bat > a.bat || (b.bat == a.bat && b.idx < a.idx)) return b;
+  return a;
+}
+
+__device__ __forceinline__ Best warp_best(Best v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    Best w;
+    w.bat = __shfl_xor_sync(0xffffffffu, v.bat, o);
+    w.idx = __shfl_xor_sync(0xffffffffu, v.idx, o);
+    v = better(v, w);
+  }
+  return v;
+}
+
+__device__ __forceinline__ Best block_best(Best v) {
+  __shared__ double s_bat[kBestThreads / 32];
+  __shared__ int64_t s_idx[kBestThreads / 32];
+  v = warp_best(v);
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (lane == 0) {
+    s_bat[warp] = v.bat;
+    s_idx[warp] = v.idx;
+  }
+  __syncthreads();
+  if (warp == 0) {
+    Best w;
+    w.bat = lane < kBestThreads / 32 ? s_bat[lane] : 0.0;
+    w.idx = lane < kBestThreads / 32 ? s_idx[lane] : -1;
+    v = warp_best(w);
+  }
+  return v;  // valid in warp 0
+}
+
+// One pass over the node table: 9 B/node (f64 battery + u8 flags), 128-bit
+// loads when both columns are 16-byte aligned. Block partials go to scratch;
+// the last block to finish (ticket) folds them, so one launch suffices.
+__global__ void __launch_bounds__(kBestThreads)
+node_best_kernel(const double* __restrict__ battery, const uint8_t* __restrict__ flags,
+                 int64_t n, int64_t node_base, int vec_ok, int64_t* __restrict__ best,
+                 unsigned int* __restrict__ ticket, double* __restrict__ part_bat,
+                 int64_t* __restrict__ part_idx) {
+  Best me{0.0, -1};
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t nthreads = (int64_t)gridDim.x * blockDim.x;
+  int64_t done = 0;
+  if (vec_ok) {
+    const int64_t nchunks = n / kBestNodesPerThread;
+    for (int64_t c = tid; c < nchunks; c += nthreads) {
+      const int64_t i0 = c * kBestNodesPerThread;
+      const int4 fw = ld_stream_v4(flags + i0);
+      double2 b[kBestNodesPerThread / 2];
+#pragma unroll
+      for (int k = 0; k < kBestNodesPerThread / 2; ++k) b[k] = ld_stream_d2(battery + i0 + 2 * k);
+      const unsigned int f[4] = {(unsigned)fw.x, (unsigned)fw.y, (unsigned)fw.z, (unsigned)fw.w};
+#pragma unroll
+      for (int k = 0; k < kBestNodesPerThread; ++k) {
+        const unsigned int fl = (f[k >> 2] >> (8 * (k & 3))) & 3u;
+        const double v = (k & 1) ? b[k >> 1].y : b[k >> 1].x;
+        // indices grow within a thread, so a strict > keeps the first maximum
+        if (fl == 3u && (me.idx < 0 || v > me.bat)) {
+          me.bat = v;
+          me.idx = i0 + k;
+        }
+      }
+    }
+    done = nchunks * kBestNodesPerThread;
+  }
+  for (int64_t i = done + tid; i < n; i += nthreads) {
+    const double v = battery[i];
+    if ((flags[i] & 3u) == 3u && (me.idx < 0 || v > me.bat)) {
+      me.bat = v;
+      me.idx = i;
+    }
+  }
+  me = block_best(me);
+
+  __shared__ bool s_last;
+  if (threadIdx.x == 0) {
+    part_bat[blockIdx.x] = me.bat;
+    part_idx[blockIdx.x] = me.idx;
+    __threadfence();
+    const unsigned int t = atomicAdd(ticket, 1u);
+    s_last = (t == gridDim.x - 1);
+  }
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  Best acc{0.0, -1};
+  for (int b = threadIdx.x; b < (int)gridDim.x; b += blockDim.x) {
+    Best p;
+    p.bat = __ldcg(part_bat + b);
+    p.idx = __ldcg(part_idx + b);
+    acc = better(acc, p);
+  }
+  acc = block_best(acc);
+  if (threadIdx.x == 0) {
+    best[0] = acc.idx < 0 ? -1 : acc.idx + node_base;
+    best[1] = __double_as_longlong(acc.idx < 0 ? 0.0 : acc.bat);
+    *ticket = 0;  // ready for the next launch on this scratch
+  }
+}
+
+// ---------------------------------------------------------------- K2
+
+constexpr int kSchedThreads = 256;
+
+// One thread per request. Winner = best of {g} U {preferred nodes that pass
+// every filter}, where g is K1's result: a non-preferred node other than g
+// scores battery <= battery[g] <= score(g) and on equality has a higher index
+// (proved equal to the literal scan by the tests and by K2b).
+// If g fails the battery gate every node does (g has the largest battery).
+__global__ void __launch_bounds__(kSchedThreads)
+schedule_kernel(const double* __restrict__ battery, const uint8_t* __restrict__ flags,
+                int64_t n, int64_t node_base, const int64_t* __restrict__ best,
+                int64_t n_requests, const double* __restrict__ min_battery,
+                const int32_t* __restrict__ pref_off, const int32_t* __restrict__ pref_ids,
+                int32_t* __restrict__ out_idx, double* __restrict__ out_score) {
+  const int64_t g = best[0];
+  const double gb = __longlong_as_double(best[1]);
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; r < n_requests; r += stride) {
+    const double mb = min_battery[r];
+    const bool gate = mb > 0;  // controller.go:194
+    int64_t bi = -1;
+    double bs = 0.0;
+    if (g >= 0 && !(gate && gb < mb)) {
+      bi = g;
+      bs = gb;
+      const int32_t k1 = pref_off[r + 1];
+      for (int32_t k = pref_off[r]; k < k1; ++k) {
+        const int64_t p = pref_ids[k];
+        const int64_t lp = p - node_base;
+        if (lp < 0 || lp >= n) continue;
+        if ((flags[lp] & 3u) != 3u) continue;  // :190, :198
+        const double b = battery[lp];
+        if (gate && b < mb) continue;          // :194
+        const double s = b + 10;               // :205-208
+        if (s > bs || (s == bs && p < bi)) {
+          bs = s;
+          bi = p;
+        }
+      }
+    }
+    out_idx[r] = (int32_t)bi;
+    out_score[r] = bs;
+  }
+}
+
+// ---------------------------------------------------------------- K2b
+
+constexpr int kBruteThreads = 256;
+constexpr int kBruteTile = 2048;  // nodes per shared-memory tile: 16 KB + 2 KB
+constexpr int kBruteRegPrefs = 4;
+
+// The literal loop of controller.go:181-218 for every (request, node) pair:
+// one request per thread, node tiles staged in shared memory and read as
+// warp-wide broadcasts. First strict maximum in index order == stable sort
+// then [0]. On-chip bound by construction (R*N*9 B of shared-memory reads).
+__global__ void __launch_bounds__(kBruteThreads)
+schedule_bruteforce_kernel(const double* __restrict__ battery, const uint8_t* __restrict__ flags,
+                           int64_t n, int64_t node_base, int64_t n_requests,
+                           const double* __restrict__ min_battery,
+                           const int32_t* __restrict__ pref_off,
+                           const int32_t* __restrict__ pref_ids, int32_t* __restrict__ out_idx,
+                           double* __restrict__ out_score) {
+  __shared__ double s_bat[kBruteTile];
+  __shared__ uint8_t s_flag[kBruteTile];
+
+  const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const bool live = r < n_requests;
+  double mb = 0.0;
+  int32_t k0 = 0, k1 = 0;
+  if (live) {
+    mb = min_battery[r];
+    k0 = pref_off[r];
+    k1 = pref_off[r + 1];
+  }
+  const bool gate = mb > 0;
+  const int npref = k1 - k0;
+  int64_t p[kBruteRegPrefs];
+#pragma unroll
+  for (int k = 0; k < kBruteRegPrefs; ++k) p[k] = (k < npref) ? (int64_t)pref_ids[k0 + k] : -2;
+
+  int64_t bi = -1;
+  double bs = 0.0;
+  for (int64_t t0 = 0; t0 < n; t0 += kBruteTile) {
+    const int tn = (int)min((int64_t)kBruteTile, n - t0);
+    __syncthreads();
+    for (int i = threadIdx.x; i < tn; i += blockDim.x) {
+      s_bat[i] = battery[t0 + i];
+      s_flag[i] = flags[t0 + i];
+    }
+    __syncthreads();
+    if (!live) continue;
+#pragma unroll 4
+    for (int i = 0; i < tn; ++i) {
+      if ((s_flag[i] & 3u) != 3u) continue;  // :190, :198
+      const double b = s_bat[i];
+      if (gate && b < mb) continue;          // :194
+      const int64_t gi = node_base + t0 + i;
+      bool pref = false;
+#pragma unroll
+      for (int k = 0; k < kBruteRegPrefs; ++k) pref |= (gi == p[k]);
+      if (npref > kBruteRegPrefs)
+        for (int32_t k = k0 + kBruteRegPrefs; k < k1 && !pref; ++k) pref = (pref_ids[k] == gi);
+      const double s = pref ? b + 10 : b;    // :205-208
+      if (bi < 0 || s > bs) {                // first maximum in list order
+        bs = s;
+        bi = gi;
+      }
+    }
+  }
+  if (live) {
+    out_idx[r] = (int32_t)bi;
+    out_score[r] = bs;
+  }
+}
+
+// ---------------------------------------------------------------- K3
+
+// Per request, fold the partial winners of the node-range shards. Global
+// indices make "lowest index on ties" independent of which rank held the node.
+__global__ void __launch_bounds__(256)
+merge_partials_kernel(int n_parts, int64_t n_requests, const int32_t* __restrict__ part_idx,
+                      const double* __restrict__ part_score, int32_t* __restrict__ out_idx,
+                      double* __restrict__ out_score) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; r < n_requests; r += stride) {
+    int32_t bi = -1;
+    double bs = 0.0;
+    for (int g = 0; g < n_parts; ++g) {
+      const int32_t i = part_idx[(int64_t)g * n_requests + r];
+      if (i < 0) continue;
+      const double s = part_score[(int64_t)g * n_requests + r];
+      if (bi < 0 || s > bs || (s == bs && i < bi)) {
+        bs = s;
+        bi = i;
+      }
+    }
+    out_idx[r] = bi;
+    out_score[r] = bs;
+  }
+}
+
+static int grid_for(int64_t work_items, int threads, int max_waves = 8) {
+  int64_t blocks = ceil_div(work_items, threads);
+  const int64_t cap = (int64_t)kNumSMs * max_waves;
+  if (blocks > cap) blocks = cap;
+  if (blocks < 1) blocks = 1;
+  return (int)blocks;
+}
+
+}  // namespace klm
+
+using namespace klm;
+
+extern "C" int64_t klm_dev_node_best_scratch_bytes(void) { return kBestScratchBytes; }
+
+extern "C" int klm_dev_node_best(const double* battery, const uint8_t* flags, int64_t n_nodes,
+                                 int64_t node_base, int64_t* best, void* scratch, void* stream) {
+  if (n_nodes < 0 || !best || !scratch || (n_nodes > 0 && (!battery || !flags))) {
+    set_error("klm_dev_node_best: bad argument");
+    return KLM_EINVAL;
+  }
+  char* s = static_cast<char*>(scratch);
+  unsigned int* ticket = reinterpret_cast<unsigned int*>(s);
+  double* part_bat = reinterpret_cast<double*>(s + 256);
+  int64_t* part_idx = reinterpret_cast<int64_t*>(s + 256 + (int64_t)kBestMaxBlocks * 8);
+  int64_t blocks = ceil_div(n_nodes, (int64_t)kBestThreads * kBestNodesPerThread);
+  if (blocks < 1) blocks = 1;
+  if (blocks > kBestMaxBlocks) blocks = kBestMaxBlocks;
+  if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
+  const int vec_ok = aligned16(battery) && aligned16(flags);
+  node_best_kernel<<<(int)blocks, kBestThreads, 0, as_stream(stream)>>>(
+      battery, flags, n_nodes, node_base, vec_ok, best, ticket, part_bat, part_idx);
+  KLM_LAUNCH_CHECK("node_best_kernel");
+  return KLM_OK;
+}
+
+extern "C" int klm_dev_schedule(const double* battery, const uint8_t* flags, int64_t n_nodes,
+                                int64_t node_base, const int64_t* best, int64_t n_requests,
+                                const double* min_battery, const int32_t* pref_off,
+                                const int32_t* pref_ids, int32_t* out_idx, double* out_score,
+                                void* stream) {
+  if (n_nodes < 0 || n_requests < 0 || !best) {
+    set_error("klm_dev_schedule: bad argument");
+    return KLM_EINVAL;
+  }
+  if (n_requests == 0) return KLM_OK;
+  if (!min_battery || !pref_off || !out_idx || !out_score) {
+    set_error("klm_dev_schedule: null request array");
+    return KLM_EINVAL;
+  }
+  schedule_kernel<<<grid_for(n_requests, kSchedThreads, 16), kSchedThreads, 0, as_stream(stream)>>>(
+      battery, flags, n_nodes, node_base, best, n_requests, min_battery, pref_off, pref_ids,
+      out_idx, out_score);
+  KLM_LAUNCH_CHECK("schedule_kernel");
+  return KLM_OK;
+}
+
+extern "C" int klm_dev_schedule_bruteforce(const double* battery, const uint8_t* flags,
+                                           int64_t n_nodes, int64_t node_base, int64_t n_requests,
+                                           const double* min_battery, const int32_t* pref_off,
+                                           const int32_t* pref_ids, int32_t* out_idx,
+                                           double* out_score, void* stream) {
+  if (n_nodes < 0 || n_requests < 0) {
+    set_error("klm_dev_schedule_bruteforce: bad argument");
+    return KLM_EINVAL;
+  }
+  if (n_requests == 0) return KLM_OK;
+  if (!min_battery || !pref_off || !out_idx || !out_score) {
+    set_error("klm_dev_schedule_bruteforce: null request array");
+    return KLM_EINVAL;
+  }
+  const int64_t blocks = ceil_div(n_requests, kBruteThreads);
+  if (blocks > 0x7fffffff) {
+    set_error("klm_dev_schedule_bruteforce: too many requests for one launch");
+    return KLM_ELIMIT;
+  }
+  schedule_bruteforce_kernel<<<(unsigned)blocks, kBruteThreads, 0, as_stream(stream)>>>(
+      battery, flags, n_nodes, node_base, n_requests, min_battery, pref_off, pref_ids, out_idx,
+      out_score);
+  KLM_LAUNCH_CHECK("schedule_bruteforce_kernel");
+  return KLM_OK;
+}
+
+extern "C" int klm_dev_merge_partials(int n_parts, int64_t n_requests, const int32_t* part_idx,
+                                      const double* part_score, int32_t* out_idx,
+                                      double* out_score, void* stream) {
+  if (n_parts < 1 || n_requests < 0) {
+    set_error("klm_dev_merge_partials: bad argument");
+    return KLM_EINVAL;
+  }
+  if (n_requests == 0) return KLM_OK;
+  merge_partials_kernel<<<grid_for(n_requests, 256, 16), 256, 0, as_stream(stream)>>>(
+      n_parts, n_requests, part_idx, part_score, out_idx, out_score);
+  KLM_LAUNCH_CHECK("merge_partials_kernel");
+  return KLM_OK;
+}

@@ -1,0 +1,55 @@
+"""CPU: libklm.so loads and exports exactly what include/klm.h declares (no compute calls)."""
+import ctypes
+import os
+import re
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def header_symbols():
+    text = open(os.path.join(ROOT, "include", "klm.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(klm_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_header_declares_symbols():
+    syms = header_symbols()
+    assert "klm_schedule_batch" in syms and "klm_dev_window_stats" in syms and len(syms) >= 30
+
+
+def test_library_exports_every_declared_symbol(pkg):
+    lib = ctypes.CDLL(pkg.binding.LIB_PATH)
+    missing = [s for s in header_symbols() if not hasattr(lib, s)]
+    assert not missing, f"declared in klm.h but not exported: {missing}"
+
+
+def test_binding_covers_header(pkg):
+    assert sorted(pkg.binding.SIGNATURES) == header_symbols()
+    pkg.load()
+
+
+def test_no_cpu_fallback_without_device(pkg):
+    """On a machine without a GPU the handle must fail loudly, not fall back."""
+    import torch
+    if torch.cuda.is_available():
+        return
+    try:
+        pkg.Handle(0)
+    except pkg.KlmError as e:
+        assert e.code == pkg.binding.KLM_ENODEV and "no CPU fallback" in str(e)
+    else:
+        raise AssertionError("klm_create succeeded without a CUDA device")
+
+
+def test_product_does_not_touch_oracle():
+    """Nothing under the package may reference the oracle (it is test infrastructure)."""
+    pkg_dir = os.path.join(ROOT, "k8s-llm-monitor_b200")
+    bad = []
+    for dp, _, files in os.walk(pkg_dir):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".cpp", ".h", ".hpp", "Makefile")):
+                text = open(os.path.join(dp, f), errors="replace").read()
+                # mentions in comments are fine; linking, loading or calling is not
+                if re.search(r"klmo_\w+\s*\(|libklm_oracle|oracle_binding|controller_oracle|-lklm_oracle", text):
+                    bad.append(os.path.join(dp, f))
+    assert not bad, bad
