@@ -1,0 +1,94 @@
+"""GPU parity: cluster aggregate, node/pod rates, fleet scans vs the oracle. Integers
+bit-exact; the f64 rates are single correctly-rounded operations, so bit-exact too."""
+import numpy as np
+import pytest
+
+import oracle_binding as ob
+
+pytestmark = pytest.mark.gpu
+COLS = ("cpu_capacity", "cpu_usage", "memory_capacity", "memory_usage", "gpu_count", "healthy", "gpu_usage",
+        "pod_running")
+
+
+@pytest.mark.parametrize("n,p,g", [(0, 0, 0), (1, 0, 1), (7, 3, 0), (8, 16, 2), (9, 17, 3), (1000, 10_000, 0),
+                                   (5000, 20_000, 2), (100_003, 1_000_001, 1)])
+def test_cluster_aggregate(handle, pkg, n, p, g):
+    snap = pkg.synth.cluster_snapshot(2, n, p, gpus_per_node=g)
+    got = handle.cluster_aggregate(*(snap[k] for k in COLS))
+    assert got == ob.cluster_aggregate(snap)
+
+
+def test_cluster_aggregate_health_cases(handle):
+    G = 1 << 30
+    def run(cap, use, healthy):
+        n = len(cap)
+        return handle.cluster_aggregate(np.array(cap, np.int64), np.array(use, np.int64), np.full(n, G, np.int64),
+                                        np.zeros(n, np.int64), np.zeros(n, np.int32), np.array(healthy, np.uint8),
+                                        np.zeros(0), np.zeros(0, np.uint8))
+    assert run([1000], [800], [1])["health_status"] == 0
+    assert run([1000], [850], [1])["health_status"] == 1
+    assert run([1000], [950], [1])["health_status"] == 2
+    assert run([1000] * 5, [100] * 5, [1, 1, 0, 0, 0])["health_status"] == 1  # 2 < 5//2 false
+    assert run([1000] * 5, [100] * 5, [1, 0, 0, 0, 0])["health_status"] == 2
+    assert run([1000] * 5, [100] * 5, [2, 0, 0, 0, 255])["healthy_nodes"] == 2   # any non-zero byte is true
+
+
+def test_cluster_sums_sharded(dev, pkg):
+    """Node/pod ranges summed per shard then added (what the all-reduce does) == unsharded."""
+    import torch
+    n, p = 10_000, 77_777
+    snap = pkg.synth.cluster_snapshot(4, n, p, gpus_per_node=1)
+    want = ob.cluster_aggregate(snap)
+    tot = torch.zeros(10, dtype=torch.int64, device="cuda")
+    sums = torch.empty(10, dtype=torch.int64, device="cuda")
+    g = 4
+    for k in range(g):
+        lo, hi, plo, phi = n * k // g, n * (k + 1) // g, p * k // g, p * (k + 1) // g
+        cols = {c: torch.from_numpy(snap[c][lo:hi].copy()).cuda() for c in COLS[:7]}
+        pods = torch.from_numpy(snap["pod_running"][plo:phi].copy()).cuda()
+        dev.cluster_sums(cols, pods, sums)
+        tot += sums
+    out = torch.zeros(104, dtype=torch.uint8, device="cuda")
+    dev.cluster_finish(tot, out)
+    torch.cuda.synchronize()
+    rec = out.cpu().numpy().view(pkg.binding.CLUSTER_OUT_DTYPE)[0]
+    assert {k: rec[k].item() for k in rec.dtype.names} == want
+
+
+@pytest.mark.parametrize("n", [0, 1, 1000, 100_001])
+def test_node_rates(handle, pkg, n):
+    snap = pkg.synth.cluster_snapshot(3, n, 0)
+    if n:
+        snap["cpu_capacity"][::7] = 0     # capacity 0 -> rate 0
+        snap["disk_allocatable"][::5] += 1 << 40  # allocatable > capacity -> usage clamps to 0
+    got = handle.node_rates(*(snap[k] for k in ("cpu_capacity", "cpu_usage", "memory_capacity", "memory_usage",
+                                                "disk_capacity", "disk_allocatable")))
+    want = ob.node_rates(snap)
+    for k in want:
+        assert np.array_equal(got[k], want[k]), k
+    got = handle.node_rates(*(snap[k] for k in ("cpu_capacity", "cpu_usage", "memory_capacity", "memory_usage",
+                                                "disk_capacity")))
+    want = ob.node_rates(snap, with_alloc=False)
+    for k in want:
+        assert np.array_equal(got[k], want[k]), k
+
+
+@pytest.mark.parametrize("p", [1, 10_000, 250_000])
+def test_pod_rates(handle, pkg, p):
+    c = pkg.synth.pod_containers(2, p)
+    got = handle.pod_rates(*(c[k] for k in ("ctr_off", "cpu_usage", "memory_usage", "cpu_request", "cpu_limit",
+                                            "memory_request", "memory_limit")))
+    want = ob.pod_rates(c)
+    for k in want:
+        assert np.array_equal(got[k], want[k]), k
+
+
+@pytest.mark.parametrize("n", [0, 1, 1023, 1024, 1025, 5000, 1_000_003])
+def test_fleet_scan(handle, pkg, n):
+    rng = np.random.default_rng(n)
+    ok = (rng.random(n) < 0.9).astype(np.uint8)
+    pct = np.round(rng.random(n) * 100, 1)
+    for thr in (20.0, 0.0, 101.0):
+        h, low = handle.fleet_scan(ok, pct, thr)
+        wh, wlow = ob.fleet_scan(ok, pct, thr)
+        assert h == wh and np.array_equal(low, wlow)

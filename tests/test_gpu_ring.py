@@ -1,0 +1,146 @@
+"""GPU parity: ring ingest and window statistics vs the oracle. min/max/p95 bit-exact
+(they are input elements); mean within rtol 1e-5 (north-star tolerance; the f64 sums differ
+only in association order, ~1e-15)."""
+import numpy as np
+import pytest
+
+import oracle_binding as ob
+
+pytestmark = pytest.mark.gpu
+RTOL = 1e-5
+
+
+def check_stats(got, want, what=""):
+    for k in ("min", "max", "p95"):
+        bad = np.flatnonzero(got[k] != want[k])
+        assert bad.size == 0, f"{what} {k}: {bad.size} mismatches, first at {bad[:5]}: {got[k][bad[:5]]} vs {want[k][bad[:5]]}"
+    assert np.allclose(got["mean"], want["mean"], rtol=RTOL, atol=1e-300), f"{what} mean"
+
+
+def distributions(rng, s, t):
+    rows = np.empty((s, t), np.float32)
+    kinds = 12
+    for i in range(s):
+        k = i % kinds
+        if k == 0: v = rng.random(t) * 100
+        elif k == 1: v = rng.standard_normal(t) * 5
+        elif k == 2: v = np.round(rng.random(t) * 10)              # heavy ties
+        elif k == 3: v = np.full(t, 7.25)                          # constant
+        elif k == 4: v = np.sort(rng.random(t) * 1e6)              # ascending
+        elif k == 5: v = np.sort(rng.random(t))[::-1] - 0.5        # descending, mixed sign
+        elif k == 6: v = np.zeros(t)                               # all zero
+        elif k == 7: v = 39.9042 + 0.001 * np.cos(0.1 * np.arange(t))  # tiny relative variance
+        elif k == 8: v = np.where(rng.random(t) < 0.97, 0.0, rng.random(t) * 1e9)  # sparse spikes
+        elif k == 9: v = -np.abs(rng.standard_normal(t)) * 1e-30   # tiny negatives
+        elif k == 10: v = np.where(rng.random(t) < 0.5, -0.0, 0.0)  # signed zeros
+        else: v = np.maximum(100 - 0.1 * np.arange(t), 0)          # battery drain with a zero plateau
+        rows[i] = v.astype(np.float32)
+    return rows
+
+
+@pytest.mark.parametrize("t", [1, 3, 4, 5, 20, 127, 128, 129, 1000, 3600, 4096, 5000, 20000])
+def test_window_stats_distributions(handle, t):
+    rng = np.random.default_rng(t)
+    s = 48
+    rows = distributions(rng, s, t)
+    handle.ring_create(s, t)
+    handle.ring_load(0, rows)
+    got = handle.ring_stats()
+    pitch = (t + 3) & ~3
+    ring = np.zeros((s, pitch), np.float32)
+    ring[:, :t] = rows
+    want = ob.window_stats(ring, np.full(s, t, np.uint32), t, pitch)
+    check_stats(got, want, f"t={t}")
+
+
+def test_partial_windows_and_ranges(handle):
+    """seen < window (ring still filling), seen == 0, and sub-ranges of series."""
+    rng = np.random.default_rng(9)
+    s, t = 200, 3600
+    ring = np.zeros((s, t), np.float32)
+    seen = np.zeros(s, np.uint32)
+    handle.ring_create(s, t)
+    counts = rng.integers(0, t + 1, size=s)
+    counts[:4] = [0, 1, 2, t]
+    for i in range(s):
+        c = int(counts[i])
+        if c:
+            data = (rng.random((1, c)) * 50 - 10).astype(np.float32)
+            handle.ring_load(i, data)
+            ring[i, :c] = data[0]
+            seen[i] = c
+    want = ob.window_stats(ring, seen, t)
+    check_stats(handle.ring_stats(), want, "partial")
+    sub = handle.ring_stats(17, 93)
+    for k in want:
+        assert np.array_equal(sub[k], want[k][17:93]) or k == "mean"
+    nop = handle.ring_stats(5, 5)
+    assert nop["min"].size == 0
+    assert handle.ring_stats(p95=False)["p95"] is None
+
+
+def test_ingest_matches_oracle_and_wraps(handle):
+    """Tick ingestion and scattered ingestion, past the wrap-around point."""
+    rng = np.random.default_rng(11)
+    s, t = 300, 37
+    ring = np.zeros((s, (t + 3) & ~3), np.float32)
+    seen = np.zeros(s, np.uint32)
+    handle.ring_create(s, t)
+    for tick in range(2 * t + 5):
+        v = (rng.random(s) * 100).astype(np.float32)
+        handle.ring_ingest_tick(v)
+        ob.ring_ingest(ring, seen, t, v)
+        if tick % 9 == 0:
+            ids = rng.choice(s, size=40, replace=False).astype(np.int64)
+            vv = rng.standard_normal(40).astype(np.float32)
+            handle.ring_ingest(ids, vv)
+            ob.ring_ingest(ring, seen, t, vv, series_ids=ids)
+        if tick in (0, 5, t - 1, t, 2 * t + 4):
+            check_stats(handle.ring_stats(), ob.window_stats(ring, seen, t, ring.shape[1]), f"tick {tick}")
+
+
+def test_c2_shape_sample(handle, pkg):
+    """C2 series (pod cpu/memory, node rates) at the real window; a 2k-series slice."""
+    s, t = 2048, 3600
+    scales = pkg.synth.c2_series_scales(1000, 10_000)
+    rows = pkg.synth.c2_ring_rows(2, scales, 19_000, 19_000 + s, t)   # spans pod and node series
+    handle.ring_create(s, t)
+    handle.ring_load(0, rows)
+    check_stats(handle.ring_stats(), ob.window_stats(rows, np.full(s, t, np.uint32), t), "C2")
+
+
+def test_c3_shape_sample(handle, pkg):
+    """C3 UAV channels (simulator waveforms, constants, zero channels) for 24 nodes x 64."""
+    t = 3600
+    rows = pkg.synth.uav_channel_rows(3, 100, 124, t)
+    s = rows.shape[0]
+    handle.ring_create(s, t)
+    handle.ring_load(0, rows)
+    check_stats(handle.ring_stats(), ob.window_stats(rows, np.full(s, t, np.uint32), t), "C3")
+
+
+def test_full_c2_properties(dev, pkg):
+    """Full C2 ring (26k series x 3600) generated on the device: size-independent
+    properties (min <= mean <= max, min <= p95 <= max, exactly ceil(.95 n) elements <= p95
+    and at least n - rank elements >= p95) plus an oracle check of a strided sample."""
+    import torch
+    s, t = 26_000, 3600
+    scales = pkg.synth.c2_series_scales(1000, 10_000)
+    ring = pkg.synth.c2_ring_rows_torch(2, scales, 0, s, t)
+    seen = torch.full((s,), t, dtype=torch.int32, device="cuda")
+    o = {k: torch.empty(s, dtype=torch.float64 if k == "mean" else torch.float32, device="cuda")
+         for k in ("min", "max", "mean", "p95")}
+    dev.window_stats(ring, seen, t, o["min"], o["max"], o["mean"], o["p95"])
+    torch.cuda.synchronize()
+    assert (o["min"].double() <= o["mean"]).all() and (o["mean"] <= o["max"].double()).all()
+    assert (o["min"] <= o["p95"]).all() and (o["p95"] <= o["max"]).all()
+    rank = (19 * t + 19) // 20 - 1
+    le = (ring <= o["p95"][:, None]).sum(1)
+    lt = (ring < o["p95"][:, None]).sum(1)
+    assert (le >= rank + 1).all() and (lt <= rank).all()
+    assert torch.equal(o["min"], ring.min(1).values) and torch.equal(o["max"], ring.max(1).values)
+    pick = torch.arange(0, s, 53, device="cuda")
+    rows = ring[pick].cpu().numpy()
+    want = ob.window_stats(rows, np.full(rows.shape[0], t, np.uint32), t)
+    got = {k: v[pick].cpu().numpy() for k, v in o.items()}
+    check_stats(got, want, "full C2 sample")

@@ -1,0 +1,171 @@
+"""GPU parity, scheduling: CUDA path through the C ABI vs the oracle. Bit-exact on both
+the chosen index and the f64 score."""
+import numpy as np
+import pytest
+
+import controller_oracle as co
+import helpers
+import oracle_binding as ob
+
+pytestmark = pytest.mark.gpu
+KATS = [c for c in helpers.load_kats() if c["name"] != "empty-workload"]
+
+
+def _both(handle, pkg, bat, flags, mb, off, ids):
+    handle.nodes_set(bat, flags)
+    a = handle.schedule_batch(mb, off, ids, algo=pkg.binding.ALGO_DECOMPOSED)
+    b = handle.schedule_batch(mb, off, ids, algo=pkg.binding.ALGO_BRUTEFORCE)
+    return a, b
+
+
+def _eq(got, want, what):
+    assert np.array_equal(got[0], want[0]), f"{what}: index mismatch at {np.flatnonzero(got[0] != want[0])[:5]}"
+    assert np.array_equal(got[1], want[1]), f"{what}: score mismatch"
+
+
+@pytest.mark.parametrize("case", KATS, ids=[c["name"] for c in KATS])
+def test_c1_kats(handle, pkg, case):
+    """Config C1: the reference's example requests against its fixture fleets."""
+    spec = co.decode_spec(case["spec"], apimachinery_ints=False)
+    bat, flags, names = helpers.flatten_items(case["items"])
+    mb, off, ids = helpers.flatten_specs([spec], names)
+    for got in _both(handle, pkg, bat, flags, mb, off, ids):
+        assert got[0][0] == case["expect"]["index"]
+        assert got[1][0] == case["expect"]["score"]
+
+
+def test_c1_batched(handle, pkg):
+    """All KAT requests that share fixture A in one batch (reconcile batches, controller.go:103)."""
+    cases = [c for c in KATS if c["name"].startswith("A/")]
+    bat, flags, names = helpers.flatten_items(cases[0]["items"])
+    specs = [co.decode_spec(c["spec"], apimachinery_ints=False) for c in cases]
+    mb, off, ids = helpers.flatten_specs(specs, names)
+    for got in _both(handle, pkg, bat, flags, mb, off, ids):
+        assert got[0].tolist() == [c["expect"]["index"] for c in cases]
+        assert got[1].tolist() == [c["expect"]["score"] for c in cases]
+
+
+@pytest.mark.parametrize("seed", range(6))
+def test_random_tie_heavy(handle, pkg, seed):
+    rng = np.random.default_rng(100 + seed)
+    n = int(rng.integers(1, 5000))
+    bat, flags, mb, off, ids = helpers.random_problem(rng, n, 2000, kmax=6, grid=rng.choice([0.2, 1.0, 10.0]))
+    want = ob.schedule_literal(bat, flags, mb, off, ids)
+    dec, bru = _both(handle, pkg, bat, flags, mb, off, ids)
+    _eq(dec, want, "decomposed")
+    _eq(bru, want, "bruteforce")
+
+
+def test_edge_shapes(handle, pkg):
+    # no nodes at all
+    e = np.zeros(0)
+    mb, off, ids = np.array([0.0, 50.0]), np.array([0, 1, 1], np.int32), np.array([0], np.int32)
+    for got in _both(handle, pkg, e, e.astype(np.uint8), mb, off, ids):
+        assert got[0].tolist() == [-1, -1] and got[1].tolist() == [0.0, 0.0]
+    # zero requests
+    handle.nodes_set(np.array([1.0]), np.array([3], np.uint8))
+    i, s = handle.schedule_batch(np.zeros(0), np.zeros(1, np.int32), np.zeros(0, np.int32))
+    assert i.size == 0 and s.size == 0
+    # nobody eligible; unaligned sizes around the 16-node vector width
+    for n in (1, 15, 16, 17, 31, 33, 4097):
+        bat = np.linspace(0, 99, n)
+        flags = np.full(n, 1, np.uint8)
+        for got in _both(handle, pkg, bat, flags, np.array([0.0]), np.array([0, 0], np.int32), np.zeros(0, np.int32)):
+            assert got[0][0] == -1
+        flags[n - 1] = 3
+        for got in _both(handle, pkg, bat, flags, np.array([0.0]), np.array([0, 0], np.int32), np.zeros(0, np.int32)):
+            assert got[0][0] == n - 1 and got[1][0] == bat[n - 1]
+    # negative and zero batteries, -0.0 == +0.0 ties go to the lowest index
+    bat = np.array([-5.0, -0.0, 0.0, -1.0])
+    flags = np.full(4, 3, np.uint8)
+    for got in _both(handle, pkg, bat, flags, np.array([0.0, -3.0]), np.array([0, 0, 1], np.int32),
+                     np.array([3], np.int32)):
+        assert got[0].tolist() == [1, 3] and got[1].tolist() == [0.0, 9.0]
+
+
+def test_state_and_errors(pkg):
+    with pkg.Handle(0) as h:
+        with pytest.raises(pkg.KlmError) as ei:
+            h.schedule_batch(np.zeros(1), np.zeros(2, np.int32), np.zeros(0, np.int32))
+        assert ei.value.code == pkg.binding.KLM_ESTATE
+        h.nodes_set(np.array([1.0]), np.array([3], np.uint8))
+        with pytest.raises(pkg.KlmError):
+            h.schedule_batch(np.zeros(1), np.zeros(2, np.int32), np.zeros(0, np.int32), algo=7)
+
+
+@pytest.mark.parametrize("cfg,n,r,k", [(2, 1000, 1, None), (3, 5000, 5000, 2)])
+def test_config_shapes_vs_literal(handle, pkg, cfg, n, r, k):
+    """C2 (1k nodes, single request) and C3 (5k UAV nodes, 5k requests, K=2) at full size."""
+    bat, flags = pkg.synth.node_table(cfg, n)
+    mb, off, ids = pkg.synth.requests(cfg, r, n, k_fixed=k)
+    want = ob.schedule_literal(bat, flags, mb, off, ids)
+    dec, bru = _both(handle, pkg, bat, flags, mb, off, ids)
+    _eq(dec, want, "decomposed")
+    _eq(bru, want, "bruteforce")
+
+
+def test_c4_full_size(handle, pkg):
+    """C4: 100k nodes x 1M requests. The literal oracle checks a 2000-request sample
+    (10^11 evaluations are out of reach on a CPU); the whole batch is checked against the
+    O(N + RK) oracle (proved equal to the literal one in test_oracle_kat.py) and, on the
+    GPU, the brute-force scan of a 200k-request slice must equal the decomposed kernel."""
+    n, r = 100_000, 1_000_000
+    bat, flags = pkg.synth.node_table(4, n)
+    mb, off, ids = pkg.synth.requests(4, r, n)
+    handle.nodes_set(bat, flags)
+    dec = handle.schedule_batch(mb, off, ids)
+    _eq(dec, ob.schedule_decomposed(bat, flags, mb, off, ids), "decomposed vs O(N+RK) oracle")
+    m = 2000
+    sub_off = (off[: m + 1] - off[0]).astype(np.int32)
+    lit = ob.schedule_literal(bat, flags, mb[:m], sub_off, ids[: off[m]])
+    assert np.array_equal(dec[0][:m], lit[0]) and np.array_equal(dec[1][:m], lit[1])
+    m = 200_000
+    bru = handle.schedule_batch(mb[:m], off[: m + 1], ids[: off[m]], algo=pkg.binding.ALGO_BRUTEFORCE)
+    assert np.array_equal(dec[0][:m], bru[0]) and np.array_equal(dec[1][:m], bru[1])
+    # size-independent properties: the winner is eligible, passes the gate, and scores
+    # battery or battery + 10
+    w = dec[0]
+    ok = w >= 0
+    assert ((flags[w[ok]] & 3) == 3).all()
+    gate = mb[ok] > 0
+    assert (bat[w[ok]][gate] >= mb[ok][gate]).all()
+    d = dec[1][ok] - bat[w[ok]]
+    assert np.isin(d, (0.0, 10.0)).all() or np.allclose(d[~np.isin(d, (0.0, 10.0))], 10.0, atol=1e-9)
+
+
+@pytest.mark.parametrize("g", [2, 4, 8])
+def test_c5_node_sharded_merge(dev, pkg, g):
+    """C5: 1M nodes split into g contiguous ranges (one per rank); every rank's partial
+    winners + K3 merge must equal the unsharded result. The ranks are emulated on one GPU
+    (the NCCL all-gather itself is covered by the gloo test and bench.py)."""
+    import torch
+    n, r = 1_000_000, 200_000
+    bat, flags = pkg.synth.node_table(5, n)
+    mb, off, ids = pkg.synth.requests(5, r, n)
+    want = ob.schedule_decomposed(bat, flags, mb, off, ids)
+    t = lambda a: torch.from_numpy(a).cuda()
+    d_bat, d_flags, d_mb, d_off, d_ids = t(bat), t(flags), t(mb), t(off), t(ids)
+    part_idx = torch.empty((g, r), dtype=torch.int32, device="cuda")
+    part_score = torch.empty((g, r), dtype=torch.float64, device="cuda")
+    best = torch.empty(2, dtype=torch.int64, device="cuda")
+    for k in range(g):
+        lo, hi = n * k // g, n * (k + 1) // g
+        dev.node_best(d_bat[lo:hi], d_flags[lo:hi], best, node_base=lo)
+        dev.schedule(d_bat[lo:hi], d_flags[lo:hi], best, d_mb, d_off, d_ids, part_idx[k], part_score[k],
+                     node_base=lo)
+    out_idx = torch.empty(r, dtype=torch.int32, device="cuda")
+    out_score = torch.empty(r, dtype=torch.float64, device="cuda")
+    dev.merge_partials(part_idx, part_score, out_idx, out_score)
+    torch.cuda.synchronize()
+    assert np.array_equal(out_idx.cpu().numpy(), want[0])
+    assert np.array_equal(out_score.cpu().numpy(), want[1])
+
+
+def test_bruteforce_many_prefs(handle, pkg):
+    """More preferred ids than the brute-force kernel keeps in registers."""
+    rng = np.random.default_rng(5)
+    bat, flags, mb, off, ids = helpers.random_problem(rng, 3000, 500, kmax=12, grid=1.0)
+    want = ob.schedule_literal(bat, flags, mb, off, ids)
+    dec, bru = _both(handle, pkg, bat, flags, mb, off, ids)
+    _eq(dec, want, "decomposed")
+    _eq(bru, want, "bruteforce")
