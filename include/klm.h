@@ -297,6 +297,13 @@ int klm_dev_window_stats(const float* ring, const uint32_t* seen,
                          int32_t window, int32_t pitch, int64_t s0, int64_t s1,
                          float* out_min, float* out_max, double* out_mean,
                          float* out_p95, void* stream);
+/* The shared-memory (one CTA per series) variant of K7 that
+ * klm_dev_window_stats uses for windows above 4096 samples, callable directly
+ * for any window up to 51200; same results. */
+int klm_dev_window_stats_block(const float* ring, const uint32_t* seen,
+                               int32_t window, int32_t pitch, int64_t s0,
+                               int64_t s1, float* out_min, float* out_max,
+                               double* out_mean, float* out_p95, void* stream);
 
 #ifdef __cplusplus
 }

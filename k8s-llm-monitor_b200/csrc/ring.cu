@@ -240,17 +240,42 @@ int launch_window_stats_block(const float* ring, const uint32_t* seen, int32_t w
 }
 }  // namespace klm
 
-extern "C" int klm_dev_window_stats(const float* ring, const uint32_t* seen, int32_t window,
-                                    int32_t pitch, int64_t s0, int64_t s1, float* out_min,
-                                    float* out_max, double* out_mean, float* out_p95,
-                                    void* stream) {
+namespace klm {
+int launch_window_stats_warp(const float* ring, const uint32_t* seen, int32_t window,
+                             int32_t pitch, int64_t s0, int64_t s1, float* out_min,
+                             float* out_max, double* out_mean, float* out_p95, cudaStream_t st);
+}
+
+static int window_stats_args_ok(const float* ring, const uint32_t* seen, int32_t window,
+                                int32_t pitch, int64_t s0, int64_t s1) {
   if (!ring || !seen || window < 1 || pitch < window || (pitch & 3) || s0 < 0 || s1 < s0 ||
       !aligned16(ring)) {
     set_error("klm_dev_window_stats: bad argument (pitch must be a multiple of 4 floats and "
               "the ring 16-byte aligned)");
     return KLM_EINVAL;
   }
-  if (s1 == s0) return KLM_OK;
+  return KLM_OK;
+}
+
+extern "C" int klm_dev_window_stats(const float* ring, const uint32_t* seen, int32_t window,
+                                    int32_t pitch, int64_t s0, int64_t s1, float* out_min,
+                                    float* out_max, double* out_mean, float* out_p95,
+                                    void* stream) {
+  const int rc = window_stats_args_ok(ring, seen, window, pitch, s0, s1);
+  if (rc != KLM_OK || s1 == s0) return rc;
+  const int w = launch_window_stats_warp(ring, seen, window, pitch, s0, s1, out_min, out_max,
+                                         out_mean, out_p95, as_stream(stream));
+  if (w != 1) return w;  // handled (or failed) by the register-resident warp kernel
+  return launch_window_stats_block(ring, seen, window, pitch, s0, s1, out_min, out_max, out_mean,
+                                   out_p95, as_stream(stream));
+}
+
+extern "C" int klm_dev_window_stats_block(const float* ring, const uint32_t* seen, int32_t window,
+                                          int32_t pitch, int64_t s0, int64_t s1, float* out_min,
+                                          float* out_max, double* out_mean, float* out_p95,
+                                          void* stream) {
+  const int rc = window_stats_args_ok(ring, seen, window, pitch, s0, s1);
+  if (rc != KLM_OK || s1 == s0) return rc;
   return launch_window_stats_block(ring, seen, window, pitch, s0, s1, out_min, out_max, out_mean,
                                    out_p95, as_stream(stream));
 }

@@ -19,7 +19,7 @@ def check_stats(got, want, what=""):
 
 def distributions(rng, s, t):
     rows = np.empty((s, t), np.float32)
-    kinds = 12
+    kinds = 20
     for i in range(s):
         k = i % kinds
         if k == 0: v = rng.random(t) * 100
@@ -33,7 +33,15 @@ def distributions(rng, s, t):
         elif k == 8: v = np.where(rng.random(t) < 0.97, 0.0, rng.random(t) * 1e9)  # sparse spikes
         elif k == 9: v = -np.abs(rng.standard_normal(t)) * 1e-30   # tiny negatives
         elif k == 10: v = np.where(rng.random(t) < 0.5, -0.0, 0.0)  # signed zeros
-        else: v = np.maximum(100 - 0.1 * np.arange(t), 0)          # battery drain with a zero plateau
+        elif k == 11: v = np.maximum(100 - 0.1 * np.arange(t), 0)  # battery drain with a zero plateau
+        elif k == 12: v = np.floor(8 + 5 * rng.random(t))          # five integer values (satellite count)
+        elif k == 13: v = np.floor(rng.random(t) * 1.05)           # ~5 % ones: p95 sits on the 0/1 edge
+        elif k == 14: v = np.floor(rng.random(t) * 1.02)           # ~2 % ones
+        elif k == 15: v = np.round(rng.random(t) * 100)            # ~100 distinct values
+        elif k == 16: v = np.round(rng.random(t) * 1000) / 10      # 0.1 grid
+        elif k == 17: v = np.where(rng.random(t) < 0.9, 5.0, 5.0 + rng.random(t))  # 90 % tied at the min
+        elif k == 18: v = np.where(rng.random(t) < 0.9, 5.0 - rng.random(t), 5.0)  # 10 % tied at the max
+        else: v = np.exp(rng.standard_normal(t) * 3)               # heavy right tail (lognormal)
         rows[i] = v.astype(np.float32)
     return rows
 
@@ -41,7 +49,7 @@ def distributions(rng, s, t):
 @pytest.mark.parametrize("t", [1, 3, 4, 5, 20, 127, 128, 129, 1000, 3600, 4096, 5000, 20000])
 def test_window_stats_distributions(handle, t):
     rng = np.random.default_rng(t)
-    s = 48
+    s = 80
     rows = distributions(rng, s, t)
     handle.ring_create(s, t)
     handle.ring_load(0, rows)
@@ -144,3 +152,29 @@ def test_full_c2_properties(dev, pkg):
     want = ob.window_stats(rows, np.full(rows.shape[0], t, np.uint32), t)
     got = {k: v[pick].cpu().numpy() for k, v in o.items()}
     check_stats(got, want, "full C2 sample")
+
+
+@pytest.mark.parametrize("t", [100, 1000, 3600, 4096])
+def test_warp_and_block_variants_agree(dev, t):
+    """The register-resident warp kernel (default for windows <= 4096) and the
+    shared-memory block kernel must give identical min/max/p95 and matching means."""
+    import torch
+    rng = np.random.default_rng(1000 + t)
+    s = 400
+    rows = distributions(rng, s, t)
+    pitch = (t + 3) & ~3
+    ring = torch.zeros((s, pitch), dtype=torch.float32, device="cuda")
+    ring[:, :t] = torch.from_numpy(rows).cuda()
+    seen_np = rng.integers(0, 2 * t, size=s)
+    seen_np[:3] = [0, 1, t]
+    seen = torch.from_numpy(seen_np.astype(np.int32)).cuda()
+    res = []
+    for block in (False, True):
+        o = {k: torch.full((s,), -123.0, dtype=torch.float64 if k == "mean" else torch.float32, device="cuda")
+             for k in ("min", "max", "mean", "p95")}
+        dev.window_stats(ring, seen, t, o["min"], o["max"], o["mean"], o["p95"], block_variant=block)
+        torch.cuda.synchronize()
+        res.append({k: v.cpu().numpy() for k, v in o.items()})
+    want = ob.window_stats(ring.cpu().numpy(), seen_np.astype(np.uint32), t, pitch)
+    check_stats(res[0], want, "warp")
+    check_stats(res[1], want, "block")
