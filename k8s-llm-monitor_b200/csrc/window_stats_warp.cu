@@ -8,18 +8,22 @@
 // Per series (n valid samples, k = n - rank95 = how many samples are >= p95):
 //   1. 128-bit streaming loads: lane l takes float4 l + 32 j (j < NV), so a warp
 //      reads its row as NV fully coalesced 512-byte requests. Pads are -inf.
-//   2. 128 samples (4 rows spread over the window) -> their 16 largest, by 16
-//      rounds of warp-wide max (redux) over each lane's sorted four.
+//   2. 128 samples (4 rows spread over the window, one group of 32 per row):
+//      the three largest of each group by three rounds of warp-wide max (redux),
+//      the four groups interleaved. Pivot = the smallest of the four "third
+//      largest" values: about 14 % of the window lies above it and fewer than k
+//      samples do with probability ~0.2 %.
 //   3. ONE fused pass over the registers: min / max / f64 sum, and every element
-//      >= the 16th largest sample (about 12 % of the window; P[fewer than k]
-//      ~ 0.5 %) is appended to a per-lane list in shared memory. The list area
-//      holds a whole window, so the append needs no bounds check.
-//   4. A few counting probes over that list (guided by the sample's ranks, then
-//      interpolation) narrow the bracket to <= 32 candidates, which are ranked
-//      exactly against each other.
-//   Heavy ties (quantised channels, mostly-zero counters) are settled by counting
-//   passes at the tied value; anything the shortcuts cannot place falls back to
-//   an exact bisection over the order-preserving key space.
+//      >= the pivot is appended to a per-lane list in shared memory.
+//   4. The lists are packed into one contiguous array and narrowed by counting
+//      passes that test two pivots at a time (first the sample's own order
+//      statistics, then interpolation on the counts) until <= 32 candidates
+//      remain, which are ranked exactly against each other. Brackets that cannot
+//      shrink because of ties are peeled one distinct value at a time.
+//   Heavy ties at the pivot (quantised channels, mostly-zero counters) are settled
+//   by counting passes over the registers at the tied value; anything the
+//   shortcuts cannot place (list overflow, unlucky pivot) falls back to an exact
+//   bisection over the order-preserving key space.
 // Everything is exact: every branch ends on an input element whose rank has
 // been counted, so the result is bit-identical to sorting.
 #include "common.cuh"
@@ -27,12 +31,19 @@
 
 namespace klm {
 
-constexpr int kWswWarps = 4;               // warps (series) per CTA
+constexpr int kWswWarps = 2;               // warps (series) per CTA: small, so a slow series
+                                           // (bisection fallback) pins few resources
 constexpr int kWswThreads = kWswWarps * 32;
-constexpr int kTopR = 16;                  // sample ranks kept
-constexpr int kTieR = 8;                   // t16 == t8 -> treat as a heavy tie
 constexpr int kSampledMinRows = 7;         // below 7 full rows (896 samples) list everything
 constexpr int kMaxCand = 32;               // candidates ranked exactly at the end
+constexpr int kLaneCap = 64;               // per-lane list entries (wraps beyond: overflow -> bisect)
+constexpr int kLaneListBytes = kLaneCap * 128;  // [entry][lane] f32; power of two, self-aligned
+constexpr int kPackCap = 1024;             // packed list capacity
+// shared memory: first the lane lists (8 KB per warp, each on an 8 KB boundary), then per
+// warp a packed list (4 KB) and 32 candidates + counter (256 B)
+constexpr int kWarpAux = kPackCap * 4 + 256;
+constexpr size_t kWswSmemBytes =
+    (size_t)kWswWarps * (kLaneListBytes + kWarpAux) + kLaneListBytes;  // + alignment slack
 
 #define NEG_INF __int_as_float(0xff800000)
 #define POS_INF __int_as_float(0x7f800000)
@@ -46,7 +57,18 @@ __device__ __forceinline__ float next_down(float x) { // largest float < x (x fi
 __device__ __forceinline__ int warp_max_i32(int v) { return __reduce_max_sync(0xffffffffu, v); }
 __device__ __forceinline__ uint32_t warp_max_u32(uint32_t v) { return __reduce_max_sync(0xffffffffu, v); }
 
-// -1 if a >= b else 0 (FSET); summed with IADD3, two compares per add
+// c += (x >= p) as FSETP + predicated add (ptxas has no cheaper form on sm_100a: a
+// `set` instruction lowers to FSETP + SEL, and `c += (x >= p)` to FSETP + add + move)
+__device__ __forceinline__ void inc_if_ge(int& c, float x, float p) {
+  asm("{\n\t.reg .pred q;\n\tsetp.ge.f32 q, %1, %2;\n\t@q add.s32 %0, %0, 1;\n\t}"
+      : "+r"(c) : "f"(x), "f"(p));
+}
+__device__ __forceinline__ void inc_if_gt(int& c, float x, float p) {
+  asm("{\n\t.reg .pred q;\n\tsetp.gt.f32 q, %1, %2;\n\t@q add.s32 %0, %0, 1;\n\t}"
+      : "+r"(c) : "f"(x), "f"(p));
+}
+
+// -1 if a >= b else 0
 __device__ __forceinline__ int set_ge(float a, float b) {
   int d;
   asm("set.ge.s32.f32 %0, %1, %2;" : "=r"(d) : "f"(a), "f"(b));
@@ -58,16 +80,18 @@ __device__ __forceinline__ int set_gt(float a, float b) {
   return d;
 }
 
-// if (x > lox) { *addr = x; addr += 128; } as three predicated instructions
-__device__ __forceinline__ void append_if_gt(uint32_t& addr, float x, float lox) {
+// if (x > lox) { lane_list[c / 128 mod 64] = x; c += 128; }
+// lb = 8 KB-aligned list base | lane * 4, so the slot address is (c & 0x1F80) | lb.
+// The address lives in a temporary: the store never holds up the counter.
+__device__ __forceinline__ void append_if_gt(uint32_t& c, uint32_t lb, float x, float lox) {
   asm volatile(
-      "{\n\t.reg .pred p;\n\t"
-      "setp.gt.f32 p, %1, %2;\n\t"
-      "@p st.shared.f32 [%0], %1;\n\t"
+      "{\n\t.reg .pred p;\n\t.reg .b32 t;\n\t"
+      "setp.gt.f32 p, %2, %3;\n\t"
+      "lop3.b32 t, %0, 0x1F80, %1, 0xEA;\n\t"
+      "@p st.shared.f32 [t], %2;\n\t"
       "@p add.u32 %0, %0, 128;\n\t}"
-      : "+r"(addr)
-      : "f"(x), "f"(lox)
-      : "memory");
+      : "+r"(c)
+      : "r"(lb), "f"(x), "f"(lox));
 }
 
 template <int NV>
@@ -78,14 +102,16 @@ struct Window {
 
   // number of samples >= p (all lanes get the warp total)
   __device__ __forceinline__ int count_ge(float p) const {
-    int c0 = 0, c1 = 0;
+    int c0 = 0, c1 = 0, c2 = 0, c3 = 0;
 #pragma unroll
     for (int j = 0; j < NV; ++j) {
-      c0 -= set_ge(v[4 * j + 0], p) + set_ge(v[4 * j + 1], p);
-      c1 -= set_ge(v[4 * j + 2], p) + set_ge(v[4 * j + 3], p);
+      inc_if_ge(c0, v[4 * j + 0], p);
+      inc_if_ge(c1, v[4 * j + 1], p);
+      inc_if_ge(c2, v[4 * j + 2], p);
+      inc_if_ge(c3, v[4 * j + 3], p);
     }
-    c0 -= set_ge(tail, p);
-    return warp_sum_i32(c0 + c1);
+    inc_if_ge(c0, tail, p);
+    return warp_sum_i32((c0 + c1) + (c2 + c3));
   }
 
   // exact k-th largest by bisection over keys; needs count_ge(key_f32(lo)) >= k >
@@ -102,25 +128,77 @@ struct Window {
     }
     return key_f32(lo);
   }
+
+  // One pass over the registers: min / max / f64 sum of the valid samples, and append
+  // (x > lox) to the lane's list. FULL: every row but the last is valid in every lane,
+  // so the pass is straight-line code the scheduler can interleave freely.
+  template <bool FULL>
+  __device__ __forceinline__ void fused_pass(int lane, int n, int nfull, int jr, float lox,
+                                             uint32_t lb, uint32_t& c, float& mn, float& mx,
+                                             double& sum) const {
+    float mn0 = POS_INF, mn1 = POS_INF, mx0 = NEG_INF, mx1 = NEG_INF;
+    double sum0 = 0.0, sum1 = 0.0;
+#pragma unroll
+    for (int j = 0; j < NV; ++j) {
+      const float a = v[4 * j], b = v[4 * j + 1], cc = v[4 * j + 2], d = v[4 * j + 3];
+      const bool uniform_valid = FULL ? (j < NV - 1) : (j < jr);
+      if (uniform_valid) {
+        if (j & 1) {
+          mn1 = fminf(fminf(mn1, a), fminf(b, fminf(cc, d)));
+          mx1 = fmaxf(fmaxf(mx1, a), fmaxf(b, fmaxf(cc, d)));
+          sum1 += ((double)a + (double)b) + ((double)cc + (double)d);
+        } else {
+          mn0 = fminf(fminf(mn0, a), fminf(b, fminf(cc, d)));
+          mx0 = fmaxf(fmaxf(mx0, a), fmaxf(b, fmaxf(cc, d)));
+          sum0 += ((double)a + (double)b) + ((double)cc + (double)d);
+        }
+      } else if (lane + 32 * j < nfull) {  // boundary row: some lanes hold data
+        mn0 = fminf(fminf(mn0, a), fminf(b, fminf(cc, d)));
+        mx0 = fmaxf(fmaxf(mx0, a), fmaxf(b, fmaxf(cc, d)));
+        sum0 += ((double)a + (double)b) + ((double)cc + (double)d);
+      }
+      append_if_gt(c, lb, a, lox);  // pads are -inf: never appended
+      append_if_gt(c, lb, b, lox);
+      append_if_gt(c, lb, cc, lox);
+      append_if_gt(c, lb, d, lox);
+    }
+    if (lane < (n & 3)) {
+      mn0 = fminf(mn0, tail);
+      mx0 = fmaxf(mx0, tail);
+      sum0 += (double)tail;
+    }
+    append_if_gt(c, lb, tail, lox);
+    mn = fminf(mn0, mn1);
+    mx = fmaxf(mx0, mx1);
+    sum = sum0 + sum1;
+  }
 };
 
-// count of list entries >= p; list is [entry][lane], padded with -inf up to m4 (multiple of 4)
-__device__ __forceinline__ int list_count_ge(const float* lst, int m4, float p) {
-  int c0 = 0, c1 = 0;
+// Counts of packed-list entries >= p1 and >= p2 (p1 <= p2) in one pass; the list is
+// padded with -inf to a multiple of 128. Returns c1 | c2 << 16.
+__device__ __forceinline__ uint32_t pack_count2(const float4* pk, int nch, float p1, float p2) {
+  int a0 = 0, a1 = 0, b0 = 0, b1 = 0;
 #pragma unroll 2
-  for (int e = 0; e < m4; e += 4) {
-    const float x0 = lst[(e + 0) * 32], x1 = lst[(e + 1) * 32];
-    const float x2 = lst[(e + 2) * 32], x3 = lst[(e + 3) * 32];
-    c0 -= set_ge(x0, p) + set_ge(x1, p);
-    c1 -= set_ge(x2, p) + set_ge(x3, p);
+  for (int c = 0; c < nch; ++c) {
+    const float4 z = pk[c * 32];
+    inc_if_ge(a0, z.x, p1); inc_if_ge(a1, z.y, p1); inc_if_ge(a0, z.z, p1); inc_if_ge(a1, z.w, p1);
+    inc_if_ge(b0, z.x, p2); inc_if_ge(b1, z.y, p2); inc_if_ge(b0, z.z, p2); inc_if_ge(b1, z.w, p2);
   }
-  return warp_sum_i32(c0 + c1);
+  return (uint32_t)warp_sum_i32((a0 + a1) + ((b0 + b1) << 16));
 }
 
-template <int NV>
-constexpr size_t wsw_smem_bytes() {
-  // per warp: a list area of NE + 4 entries x 32 lanes, then 32 candidates + a counter
-  return (size_t)kWswWarps * ((size_t)(NV * 4 + 4) * 128 + 256);
+// Largest packed-list entry < b (or the largest entry if `open`), as a key (0 if none).
+__device__ __forceinline__ uint32_t pack_max_below(const float4* pk, int nch, float b, bool open) {
+  uint32_t m = 0;
+#pragma unroll 1
+  for (int c = 0; c < nch; ++c) {
+    const float4 z = pk[c * 32];
+    const float zz[4] = {z.x, z.y, z.z, z.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+      if (open || zz[i] < b) m = max(m, f32_key(zz[i]));
+  }
+  return warp_max_u32(m);
 }
 
 template <int NV>
@@ -129,9 +207,7 @@ window_stats_warp_kernel(const float* __restrict__ ring, const uint32_t* __restr
                          int32_t window, int32_t pitch, int64_t s0, int64_t n_series,
                          float* __restrict__ out_min, float* __restrict__ out_max,
                          double* __restrict__ out_mean, float* __restrict__ out_p95) {
-  extern __shared__ __align__(128) unsigned char s_raw[];
-  constexpr int kListEntries = NV * 4 + 4;
-  constexpr int kWarpBytes = kListEntries * 128 + 256;
+  extern __shared__ unsigned char s_raw[];
 
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
   const int64_t o = (int64_t)blockIdx.x * kWswWarps + wib;  // output slot
@@ -151,21 +227,39 @@ window_stats_warp_kernel(const float* __restrict__ ring, const uint32_t* __restr
   const float* row = ring + s * (int64_t)pitch;
   const int nfull = n >> 2;   // complete float4 groups
   const int jr = nfull >> 5;  // rows valid in every lane
-  float* lst = reinterpret_cast<float*>(s_raw + (size_t)wib * kWarpBytes) + lane;  // entry e: lst[e * 32]
-  float* fin = reinterpret_cast<float*>(s_raw + (size_t)wib * kWarpBytes + kListEntries * 128);
+  const bool full = jr >= NV - 1;
+
+  // shared memory of this warp; the lane lists must start on a 4 KB boundary
+  const uint32_t raw_s = (uint32_t)__cvta_generic_to_shared(s_raw);
+  const uint32_t base_s = (raw_s + (uint32_t)kLaneListBytes - 1u) & ~((uint32_t)kLaneListBytes - 1u);
+  unsigned char* base_g = s_raw + (base_s - raw_s);
+  const float* lst = reinterpret_cast<const float*>(base_g + wib * kLaneListBytes) + lane;  // entry e: lst[e * 32]
+  unsigned char* aux = base_g + kWswWarps * kLaneListBytes + wib * kWarpAux;
+  float* pack = reinterpret_cast<float*>(aux);
+  float* fin = reinterpret_cast<float*>(aux + kPackCap * 4);
   int* fin_cnt = reinterpret_cast<int*>(fin + 32);
+  const uint32_t lb = (base_s + (uint32_t)wib * kLaneListBytes) | ((uint32_t)lane << 2);
 
   // ---- 1. load
   Window<NV> w;
+  if (full) {
+    const float* p = row + 4 * lane;
 #pragma unroll
-  for (int j = 0; j < NV; ++j) {
-    const int q = lane + 32 * j;
+    for (int j = 0; j < NV - 1; ++j) {
+      const float4 t = ld_stream_f4(p + 128 * j);
+      w.v[4 * j + 0] = t.x; w.v[4 * j + 1] = t.y; w.v[4 * j + 2] = t.z; w.v[4 * j + 3] = t.w;
+    }
     float4 t = make_float4(NEG_INF, NEG_INF, NEG_INF, NEG_INF);
-    if (q < nfull) t = ld_stream_f4(row + 4 * q);
-    w.v[4 * j + 0] = t.x;
-    w.v[4 * j + 1] = t.y;
-    w.v[4 * j + 2] = t.z;
-    w.v[4 * j + 3] = t.w;
+    if (lane + 32 * (NV - 1) < nfull) t = ld_stream_f4(p + 128 * (NV - 1));
+    w.v[4 * NV - 4] = t.x; w.v[4 * NV - 3] = t.y; w.v[4 * NV - 2] = t.z; w.v[4 * NV - 1] = t.w;
+  } else {
+#pragma unroll
+    for (int j = 0; j < NV; ++j) {
+      const int q = lane + 32 * j;
+      float4 t = make_float4(NEG_INF, NEG_INF, NEG_INF, NEG_INF);
+      if (q < nfull) t = ld_stream_f4(row + 4 * q);
+      w.v[4 * j + 0] = t.x; w.v[4 * j + 1] = t.y; w.v[4 * j + 2] = t.z; w.v[4 * j + 3] = t.w;
+    }
   }
   w.tail = (lane < (n & 3)) ? row[4 * nfull + lane] : NEG_INF;
 
@@ -173,15 +267,14 @@ window_stats_warp_kernel(const float* __restrict__ ring, const uint32_t* __restr
   bool bisect = false;             // finish with the exact bisection over the registers
   uint32_t bis_lo = f32_key(NEG_INF), bis_hi = 0, bis_first = 0;
   float lox = POS_INF;             // list predicate: x > lox (+inf: list nothing)
-  uint32_t tkey = 0;               // lane r (1..16) holds the r-th largest sample key
+  float hint_lo = 0.f, hint_hi = 0.f;  // first pair of pivots (sample order statistics)
   const bool want_p95 = out_p95 != nullptr;
   const bool sampled = want_p95 && jr >= kSampledMinRows;
 
-  // ---- 2. sample pivot
+  // ---- 2. sample pivot: four groups of 32 (one sample row each), top three of each
   if (sampled) {
-    // four sample rows spread over the valid rows (all 32 lanes hold data there)
     float sm[4];
-    if (jr >= NV - 1) {  // window (almost) full: the rows are known at compile time
+    if (full) {  // the rows are known at compile time
 #pragma unroll
       for (int q = 0; q < 4; ++q) sm[q] = w.v[4 * (((2 * q + 1) * (NV - 1)) >> 3) + q];
     } else {
@@ -194,28 +287,33 @@ window_stats_warp_kernel(const float* __restrict__ ring, const uint32_t* __restr
         sm[q] = t;
       }
     }
-    uint32_t h0 = f32_key(sm[0]), h1 = f32_key(sm[1]), h2 = f32_key(sm[2]), h3 = f32_key(sm[3]);
-    // sort the lane's four keys descending (5 compare-exchanges)
-#define KLM_CE(a, b) { const uint32_t hi_ = max(a, b), lo_ = min(a, b); a = hi_; b = lo_; }
-    KLM_CE(h0, h1) KLM_CE(h2, h3) KLM_CE(h0, h2) KLM_CE(h1, h3) KLM_CE(h1, h2)
-#undef KLM_CE
+    uint32_t h[4];
+#pragma unroll
+    for (int g = 0; g < 4; ++g) h[g] = f32_key(sm[g]);
     const uint32_t lane_bit = 1u << lane;
-#pragma unroll 1
-    for (int r = 1; r <= kTopR; ++r) {
-      const uint32_t m = warp_max_u32(h0);
-      const unsigned who = __ballot_sync(0xffffffffu, h0 == m);
-      if ((who & (0u - who)) == lane_bit) { h0 = h1; h1 = h2; h2 = h3; h3 = 0u; }  // pop one copy
-      if (lane == r) tkey = m;
+    uint32_t t1 = 0xffffffffu, t2 = 0xffffffffu, t3 = 0xffffffffu;  // min over groups of rank 1/2/3
+#pragma unroll
+    for (int r = 1; r <= 3; ++r) {
+      uint32_t m[4];
+#pragma unroll
+      for (int g = 0; g < 4; ++g) m[g] = warp_max_u32(h[g]);
+#pragma unroll
+      for (int g = 0; g < 4; ++g) {
+        const unsigned who = __ballot_sync(0xffffffffu, h[g] == m[g]);
+        if ((who & (0u - who)) == lane_bit) h[g] = 0u;  // retire one copy
+      }
+      const uint32_t mm = min(min(m[0], m[1]), min(m[2], m[3]));
+      if (r == 1) t1 = mm; else if (r == 2) t2 = mm; else t3 = mm;
     }
-    const uint32_t t16 = __shfl_sync(0xffffffffu, tkey, kTopR);
-    const uint32_t t8 = __shfl_sync(0xffffffffu, tkey, kTieR);
-    const float V = key_f32(t16);
-    if (t16 == t8) {
+    const float V = key_f32(t3);
+    hint_lo = key_f32(t2);
+    hint_hi = key_f32(t1);
+    if (t3 == t2) {
       // heavy tie at V: is the answer above the block of copies of V?
       const int c_gt = w.count_ge(next_up(V));
       if (c_gt < k) {
         // no: it is V itself (found by the first probe) or below it
-        bisect = true; bis_hi = t16 + 1u; bis_first = t16;
+        bisect = true; bis_hi = t3 + 1u; bis_first = t3;
       } else {
         lox = V;  // yes: list the c_gt elements > V
       }
@@ -227,41 +325,12 @@ window_stats_warp_kernel(const float* __restrict__ ring, const uint32_t* __restr
   }
 
   // ---- 3. fused pass: min / max / f64 sum + append(x > lox)
-  float mn0 = POS_INF, mn1 = POS_INF, mx0 = NEG_INF, mx1 = NEG_INF;
-  double sum0 = 0.0, sum1 = 0.0;
-  const uint32_t list_base = (uint32_t)__cvta_generic_to_shared(lst);
-  uint32_t addr = list_base;
-#pragma unroll
-  for (int j = 0; j < NV; ++j) {
-    const float a = w.v[4 * j], b = w.v[4 * j + 1], c = w.v[4 * j + 2], d = w.v[4 * j + 3];
-    if (j < jr) {  // row valid in every lane (warp-uniform)
-      if (j & 1) {
-        mn1 = fminf(fminf(mn1, a), fminf(b, fminf(c, d)));
-        mx1 = fmaxf(fmaxf(mx1, a), fmaxf(b, fmaxf(c, d)));
-        sum1 += ((double)a + (double)b) + ((double)c + (double)d);
-      } else {
-        mn0 = fminf(fminf(mn0, a), fminf(b, fminf(c, d)));
-        mx0 = fmaxf(fmaxf(mx0, a), fmaxf(b, fmaxf(c, d)));
-        sum0 += ((double)a + (double)b) + ((double)c + (double)d);
-      }
-    } else if (lane + 32 * j < nfull) {  // boundary row: some lanes hold data
-      mn0 = fminf(fminf(mn0, a), fminf(b, fminf(c, d)));
-      mx0 = fmaxf(fmaxf(mx0, a), fmaxf(b, fmaxf(c, d)));
-      sum0 += ((double)a + (double)b) + ((double)c + (double)d);
-    }
-    append_if_gt(addr, a, lox);  // pads are -inf: never appended
-    append_if_gt(addr, b, lox);
-    append_if_gt(addr, c, lox);
-    append_if_gt(addr, d, lox);
-  }
-  if (lane < (n & 3)) {
-    mn0 = fminf(mn0, w.tail);
-    mx0 = fmaxf(mx0, w.tail);
-    sum0 += (double)w.tail;
-  }
-  append_if_gt(addr, w.tail, lox);
-  float mn = fminf(mn0, mn1), mx = fmaxf(mx0, mx1);
-  double sum = sum0 + sum1;
+  float mn, mx;
+  double sum;
+  uint32_t c128 = 0;
+  if (full) w.template fused_pass<true>(lane, n, nfull, jr, lox, lb, c128, mn, mx, sum);
+  else w.template fused_pass<false>(lane, n, nfull, jr, lox, lb, c128, mn, mx, sum);
+  asm volatile("" ::: "memory");  // the appends above are plain shared-memory stores
 #pragma unroll
   for (int off = 16; off > 0; off >>= 1) {
     mn = fminf(mn, __shfl_xor_sync(0xffffffffu, mn, off));
@@ -280,68 +349,98 @@ window_stats_warp_kernel(const float* __restrict__ ring, const uint32_t* __restr
   do {  // single-trip block: `break` = result (or the bisect request) is final
     if (bisect) break;
     if (mn == mx) { result = mx; break; }  // constant series
-    const int cnt = (int)((addr - list_base) >> 7);
+    const int cnt = (int)(c128 >> 7);
     const int total = warp_sum_i32(cnt);
     const int maxcnt = warp_max_i32(cnt);
-    if (total < k) {
-      // the sample pivot was too high (or, with lox = -inf, the answer is a -inf sample)
-      if (!sampled) { result = NEG_INF; break; }
+    if (total < k && !sampled) { result = NEG_INF; break; }  // lox = -inf: only -inf samples are unlisted
+    if (total < k || maxcnt > kLaneCap || total > kPackCap) {
+      // unlucky pivot or list overflow: exact bisection over the registers
       bisect = true; bis_hi = f32_key(mx) + 1u; bis_first = 0u;
       break;
     }
-    const int m4 = (maxcnt + 3) & ~3;
-    for (int e = cnt; e < m4; ++e) lst[e * 32] = NEG_INF;  // pad to the common length
+    // pack the lane lists into one contiguous array (exclusive scan of the counts)
+    int incl = cnt;
+#pragma unroll
+    for (int off = 1; off < 32; off <<= 1) {
+      const int u = __shfl_up_sync(0xffffffffu, incl, off);
+      if (lane >= off) incl += u;
+    }
+    float* dst = pack + (incl - cnt);
+    __syncwarp();
+#pragma unroll 1
+    for (int e = 0; e < maxcnt; e += 4) {
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+        if (e + u < cnt) dst[e + u] = lst[(e + u) * 32];
+    }
+    const int nch = (total + 127) >> 7;
+    for (int i = total + lane; i < nch * 128; i += 32) pack[i] = NEG_INF;
     if (lane == 0) *fin_cnt = 0;
     fin[lane] = NEG_INF;
     __syncwarp();
+    const float4* pk = reinterpret_cast<const float4*>(pack) + lane;
 
-    // narrow [a, b): count_ge(a) = ca >= k > cb = count_ge(b)
+    // narrow [a, b): count_ge(a) = ca >= k > cb = count_ge(b); b = +inf with cb = 0 at first
     float a = sampled ? next_up(lox) : mn, b = POS_INF;
     int ca = total, cb = 0;
-    if (sampled) {
-      // sample-guided probes: the answer's expected sample rank is k * 129 / n
-      const int rt = (k * 129) / n;
-      const int r_hi = max(1, rt - 1), r_lo = min(kTopR - 1, rt + 2);
-      const float pb = key_f32(__shfl_sync(0xffffffffu, tkey, r_hi));
-      const float pa = key_f32(__shfl_sync(0xffffffffu, tkey, r_lo));
-      if (pb > a) {
-        const int c = list_count_ge(lst, m4, pb);
-        if (c >= k) { a = pb; ca = c; } else { b = pb; cb = c; }
-      }
-      if (pa > a && pa < b) {
-        const int c = list_count_ge(lst, m4, pa);
-        if (c >= k) { a = pa; ca = c; } else { b = pa; cb = c; }
-      }
-    }
+    bool done = false;
     int it = 0;
 #pragma unroll 1
     while (ca - cb > kMaxCand) {
-      const uint32_t ka = f32_key(a), kb = (b == POS_INF) ? f32_key(mx) + 1u : f32_key(b);
-      if (kb - ka <= 1u) break;  // no key strictly between: every candidate equals a
-      float p;
-      if (it < 3 || (it < 12 && (it & 1))) {
-        // interpolate on the counts towards rank k (value-linear inside the bracket)
-        const float hi = (b == POS_INF) ? mx : b;
-        const float frac = ((float)(ca - k) + 0.5f) / (float)(ca - cb);
-        p = a + (hi - a) * frac;
-        if (!(p > a)) p = next_up(a);
-        if (!(p < b) || !(p <= mx)) p = key_f32(ka + ((kb - ka) >> 1));
+      const uint32_t ka = f32_key(a), kb = (cb == 0) ? f32_key(mx) + 1u : f32_key(b);
+      if (kb - ka <= 1u) { result = a; done = true; break; }  // every candidate equals a
+      float p1, p2;
+      bool snap = false;
+      if (it == 0 && sampled && hint_lo > a && hint_hi > hint_lo) {
+        p1 = hint_lo; p2 = hint_hi;       // sample order statistics around the 5 % point
+      } else if (it < 5) {
+        // interpolate on the counts towards ranks k + dl and k - dl (value-linear inside)
+        const float hi = (cb == 0) ? mx : b;
+        const int span = ca - cb;
+        const int dl = min(max(span >> 3, 6), 40);
+        const float inv = 1.0f / (float)span;
+        p1 = a + (hi - a) * ((float)max(ca - k - dl, 0) + 0.5f) * inv;
+        p2 = a + (hi - a) * ((float)min(ca - k + dl, span) - 0.5f) * inv;
       } else {
-        p = key_f32(ka + ((kb - ka) >> 1));  // guaranteed progress: halve the key range
+        snap = it < 12;
+        p1 = p2 = 0.f;
       }
-      const int c = list_count_ge(lst, m4, p);
-      if (c >= k) { a = p; ca = c; } else { b = p; cb = c; }
+      if (snap) {
+        // ties keep the bracket wide: peel its largest distinct value
+        const uint32_t mk = pack_max_below(pk, nch, b, cb == 0);
+        const float m = key_f32(mk);
+        const int c = (int)(pack_count2(pk, nch, m, m) & 0xffffu);
+        if (c >= k) { result = m; done = true; break; }  // everything above m is >= b
+        b = m; cb = c;
+      } else {
+        // keep both pivots strictly inside (a, b) in key order, p1 <= p2
+        uint32_t k1 = f32_key(p1), k2 = f32_key(p2);
+        if (!(p1 == p1) || !(p2 == p2) || it >= 12 || k1 <= ka || k2 >= kb || k1 > k2) {
+          k1 = ka + max((kb - ka) / 3u, 1u);
+          k2 = max(kb - max((kb - ka) / 3u, 1u), k1);
+          if (it >= 12) k1 = k2 = ka + ((kb - ka) >> 1);  // plain bisection: bounded
+        }
+        p1 = key_f32(k1); p2 = key_f32(k2);
+        const uint32_t cc = pack_count2(pk, nch, p1, p2);
+        const int c1 = (int)(cc & 0xffffu), c2 = (int)(cc >> 16);
+        if (c2 >= k) { a = p2; ca = c2; }
+        else if (c1 >= k) { a = p1; ca = c1; b = p2; cb = c2; }
+        else { b = p1; cb = c1; }
+      }
       ++it;
     }
-    if (ca - cb > kMaxCand) { result = a; break; }  // all candidates are copies of a
+    if (done) break;
 
-    // gather the <= 32 candidates in [a, b) (a smem counter hands out the slots;
-    // only ~1 entry per lane qualifies) and rank them against each other
+    // gather the <= 32 candidates in [a, b) (a shared counter hands out the slots) and
+    // rank them against each other
+    const bool open = cb == 0;  // nothing lies at or above b (b may still be +inf)
 #pragma unroll 1
-    for (int e = 0; e < maxcnt; ++e) {
-      const float x = lst[e * 32];
-      // cb == 0: nothing lies at or above b (b may still be the initial +inf)
-      if (x >= a && (cb == 0 || x < b)) fin[atomicAdd(fin_cnt, 1)] = x;
+    for (int c = 0; c < nch; ++c) {
+      const float4 z = pk[c * 32];
+      const float zz[4] = {z.x, z.y, z.z, z.w};
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+        if (zz[i] >= a && (open || zz[i] < b)) fin[atomicAdd(fin_cnt, 1)] = zz[i];
     }
     __syncwarp();
     const int mcand = ca - cb;   // == *fin_cnt
@@ -352,13 +451,9 @@ window_stats_warp_kernel(const float* __restrict__ ring, const uint32_t* __restr
 #pragma unroll 1
     for (int i = 0; i < mc4; i += 4) {
       const float4 z = *reinterpret_cast<const float4*>(fin + i);
-      gt -= set_gt(z.x, y) + set_gt(z.y, y);
-      ge -= set_ge(z.x, y) + set_ge(z.y, y);
-      gt -= set_gt(z.z, y) + set_gt(z.w, y);
-      ge -= set_ge(z.z, y) + set_ge(z.w, y);
+      inc_if_gt(gt, z.x, y); inc_if_ge(ge, z.x, y); inc_if_gt(gt, z.y, y); inc_if_ge(ge, z.y, y);
+      inc_if_gt(gt, z.z, y); inc_if_ge(ge, z.z, y); inc_if_gt(gt, z.w, y); inc_if_ge(ge, z.w, y);
     }
-    // lanes >= mcand hold y = -inf: every pad compares >= to them, so they can never
-    // satisfy kk <= ge with gt < kk unless kk > mcand, which cannot happen
     const unsigned okm = __ballot_sync(0xffffffffu, lane < mcand && gt < kk && kk <= ge);
     result = __shfl_sync(0xffffffffu, y, __ffs(okm) - 1);
   } while (false);
@@ -375,16 +470,7 @@ static int launch_warp(const float* ring, const uint32_t* seen, int32_t window, 
     set_error("klm_dev_window_stats: too many series for one launch");
     return KLM_ELIMIT;
   }
-  constexpr size_t smem = wsw_smem_bytes<NV>();
-  static bool attr_set[64] = {};
-  int dev = 0;
-  KLM_CUDA(cudaGetDevice(&dev));
-  if (smem > 48 * 1024 && !(dev < 64 && attr_set[dev])) {
-    KLM_CUDA(cudaFuncSetAttribute(window_stats_warp_kernel<NV>,
-                                  cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    if (dev < 64) attr_set[dev] = true;
-  }
-  window_stats_warp_kernel<NV><<<(unsigned)blocks, kWswThreads, smem, st>>>(
+  window_stats_warp_kernel<NV><<<(unsigned)blocks, kWswThreads, kWswSmemBytes, st>>>(
       ring, seen, window, pitch, s0, n_series, out_min, out_max, out_mean, out_p95);
   KLM_LAUNCH_CHECK("window_stats_warp_kernel");
   return KLM_OK;
@@ -394,6 +480,7 @@ static int launch_warp(const float* ring, const uint32_t* seen, int32_t window, 
 int launch_window_stats_warp(const float* ring, const uint32_t* seen, int32_t window,
                              int32_t pitch, int64_t s0, int64_t s1, float* out_min,
                              float* out_max, double* out_mean, float* out_p95, cudaStream_t st) {
+  static_assert(kWswSmemBytes <= 48 * 1024, "dynamic shared memory above 48 KB needs an opt-in");
   const int64_t n = s1 - s0;
   if (window <= 8 * 128) return launch_warp<8>(ring, seen, window, pitch, s0, n, out_min, out_max, out_mean, out_p95, st);
   if (window <= 16 * 128) return launch_warp<16>(ring, seen, window, pitch, s0, n, out_min, out_max, out_mean, out_p95, st);
