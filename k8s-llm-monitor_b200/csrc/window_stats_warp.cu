@@ -31,17 +31,16 @@
 
 namespace klm {
 
-constexpr int kWswWarps = 2;               // warps (series) per CTA: small, so a slow series
-                                           // (bisection fallback) pins few resources
+constexpr int kWswWarps = 4;               // warps (series) per CTA; registers are allocated in
+                                           // units of 4 warps, so smaller CTAs waste them
 constexpr int kWswThreads = kWswWarps * 32;
 constexpr int kSampledMinRows = 7;         // below 7 full rows (896 samples) list everything
-constexpr int kMaxCand = 32;               // candidates ranked exactly at the end
+constexpr int kMaxCand = 64;               // candidates sorted exactly at the end
 constexpr int kLaneCap = 64;               // per-lane list entries (wraps beyond: overflow -> bisect)
 constexpr int kLaneListBytes = kLaneCap * 128;  // [entry][lane] f32; power of two, self-aligned
-constexpr int kPackCap = 1024;             // packed list capacity
 // shared memory: first the lane lists (8 KB per warp, each on an 8 KB boundary), then per
-// warp a packed list (4 KB) and 32 candidates + counter (256 B)
-constexpr int kWarpAux = kPackCap * 4 + 256;
+// warp 64 candidates + a counter (512 B)
+constexpr int kWarpAux = 512;
 constexpr size_t kWswSmemBytes =
     (size_t)kWswWarps * (kLaneListBytes + kWarpAux) + kLaneListBytes;  // + alignment slack
 
@@ -174,31 +173,61 @@ struct Window {
   }
 };
 
-// Counts of packed-list entries >= p1 and >= p2 (p1 <= p2) in one pass; the list is
-// padded with -inf to a multiple of 128. Returns c1 | c2 << 16.
-__device__ __forceinline__ uint32_t pack_count2(const float4* pk, int nch, float p1, float p2) {
+// Counts of list entries >= p1 and >= p2 (p1 <= p2) in one pass over the lane lists
+// ([entry][lane], every lane padded with -inf up to m8, a multiple of 8). The eight
+// loads of a batch are issued together so their latencies overlap. Returns c1 | c2 << 16.
+__device__ __forceinline__ uint32_t list_count2(const float* lst, int m8, float p1, float p2) {
   int a0 = 0, a1 = 0, b0 = 0, b1 = 0;
-#pragma unroll 2
-  for (int c = 0; c < nch; ++c) {
-    const float4 z = pk[c * 32];
-    inc_if_ge(a0, z.x, p1); inc_if_ge(a1, z.y, p1); inc_if_ge(a0, z.z, p1); inc_if_ge(a1, z.w, p1);
-    inc_if_ge(b0, z.x, p2); inc_if_ge(b1, z.y, p2); inc_if_ge(b0, z.z, p2); inc_if_ge(b1, z.w, p2);
+#pragma unroll 1
+  for (int e = 0; e < m8; e += 8) {
+    float x[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) x[u] = lst[(e + u) * 32];
+#pragma unroll
+    for (int u = 0; u < 8; u += 2) {
+      inc_if_ge(a0, x[u], p1); inc_if_ge(a1, x[u + 1], p1);
+      inc_if_ge(b0, x[u], p2); inc_if_ge(b1, x[u + 1], p2);
+    }
   }
   return (uint32_t)warp_sum_i32((a0 + a1) + ((b0 + b1) << 16));
 }
 
-// Largest packed-list entry < b (or the largest entry if `open`), as a key (0 if none).
-__device__ __forceinline__ uint32_t pack_max_below(const float4* pk, int nch, float b, bool open) {
+// Largest list entry < b (or the largest entry if `open`), as a key (0 if none).
+__device__ __forceinline__ uint32_t list_max_below(const float* lst, int m8, float b, bool open) {
   uint32_t m = 0;
 #pragma unroll 1
-  for (int c = 0; c < nch; ++c) {
-    const float4 z = pk[c * 32];
-    const float zz[4] = {z.x, z.y, z.z, z.w};
+  for (int e = 0; e < m8; e += 8) {
+    float x[8];
 #pragma unroll
-    for (int i = 0; i < 4; ++i)
-      if (open || zz[i] < b) m = max(m, f32_key(zz[i]));
+    for (int u = 0; u < 8; ++u) x[u] = lst[(e + u) * 32];
+#pragma unroll
+    for (int u = 0; u < 8; ++u)
+      if (open || x[u] < b) m = max(m, f32_key(x[u]));
   }
   return warp_max_u32(m);
+}
+
+// Bitonic sort of 64 keys, descending, two per lane: element 2 * lane + r is k[r].
+__device__ __forceinline__ void sort64_desc(uint32_t& k0, uint32_t& k1, int lane) {
+#pragma unroll
+  for (int size = 2; size <= 64; size <<= 1) {
+    const bool desc = ((2 * lane) & size) == 0;  // size == 64: every lane descending
+#pragma unroll
+    for (int stride = size >> 1; stride > 0; stride >>= 1) {
+      if (stride == 1) {
+        const uint32_t hi = max(k0, k1), lo = min(k0, k1);
+        k0 = desc ? hi : lo;
+        k1 = desc ? lo : hi;
+      } else {
+        const int ls = stride >> 1;
+        const bool keepmax = (((lane & ls) == 0) == desc);
+        const uint32_t o0 = __shfl_xor_sync(0xffffffffu, k0, ls);
+        const uint32_t o1 = __shfl_xor_sync(0xffffffffu, k1, ls);
+        k0 = keepmax ? max(k0, o0) : min(k0, o0);
+        k1 = keepmax ? max(k1, o1) : min(k1, o1);
+      }
+    }
+  }
 }
 
 template <int NV>
@@ -233,12 +262,22 @@ window_stats_warp_kernel(const float* __restrict__ ring, const uint32_t* __restr
   const uint32_t raw_s = (uint32_t)__cvta_generic_to_shared(s_raw);
   const uint32_t base_s = (raw_s + (uint32_t)kLaneListBytes - 1u) & ~((uint32_t)kLaneListBytes - 1u);
   unsigned char* base_g = s_raw + (base_s - raw_s);
-  const float* lst = reinterpret_cast<const float*>(base_g + wib * kLaneListBytes) + lane;  // entry e: lst[e * 32]
+  float* lst = reinterpret_cast<float*>(base_g + wib * kLaneListBytes) + lane;  // entry e: lst[e * 32]
   unsigned char* aux = base_g + kWswWarps * kLaneListBytes + wib * kWarpAux;
-  float* pack = reinterpret_cast<float*>(aux);
-  float* fin = reinterpret_cast<float*>(aux + kPackCap * 4);
-  int* fin_cnt = reinterpret_cast<int*>(fin + 32);
+  float* fin = reinterpret_cast<float*>(aux);
+  int* fin_cnt = reinterpret_cast<int*>(fin + kMaxCand);
   const uint32_t lb = (base_s + (uint32_t)wib * kLaneListBytes) | ((uint32_t)lane << 2);
+
+  // Ask L2 for the row that a warp will want about one residency later (12 warps per SM
+  // are in flight): one bulk-prefetch instruction covers the whole row.
+  if (lane == 0) {
+    const int64_t later = o + (int64_t)kNumSMs * 12;
+    if (later < n_series) {
+      const uint32_t bytes = ((uint32_t)n * 4u + 15u) & ~15u;
+      asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;"
+                   :: "l"(ring + (s0 + later) * (int64_t)pitch), "r"(bytes) : "memory");
+    }
+  }
 
   // ---- 1. load
   Window<NV> w;
@@ -268,6 +307,8 @@ window_stats_warp_kernel(const float* __restrict__ ring, const uint32_t* __restr
   uint32_t bis_lo = f32_key(NEG_INF), bis_hi = 0, bis_first = 0;
   float lox = POS_INF;             // list predicate: x > lox (+inf: list nothing)
   float hint_lo = 0.f, hint_hi = 0.f;  // first pair of pivots (sample order statistics)
+  bool tie_hit = false;            // the heavy-tie test already found the answer
+  float tie_val = 0.f;
   const bool want_p95 = out_p95 != nullptr;
   const bool sampled = want_p95 && jr >= kSampledMinRows;
 
@@ -309,13 +350,19 @@ window_stats_warp_kernel(const float* __restrict__ ring, const uint32_t* __restr
     hint_lo = key_f32(t2);
     hint_hi = key_f32(t1);
     if (t3 == t2) {
-      // heavy tie at V: is the answer above the block of copies of V?
-      const int c_gt = w.count_ge(next_up(V));
-      if (c_gt < k) {
-        // no: it is V itself (found by the first probe) or below it
-        bisect = true; bis_hi = t3 + 1u; bis_first = t3;
+      // heavy tie at V: place k against the block of copies of V (two counts, one code copy)
+      int c_ge = 0, c_gt = 0;
+#pragma unroll 1
+      for (int t = 0; t < 2; ++t) {
+        const int c = w.count_ge(t ? next_up(V) : V);
+        if (t) c_gt = c; else c_ge = c;
+      }
+      if (c_gt >= k) {
+        lox = V;                       // the answer is above V: list the elements > V
+      } else if (c_ge >= k) {
+        tie_hit = true; tie_val = V;   // the answer is V itself
       } else {
-        lox = V;  // yes: list the c_gt elements > V
+        bisect = true; bis_hi = t3;    // the answer is below V
       }
     } else {
       lox = next_down(V);  // x > lox  <=>  x >= V
@@ -348,37 +395,23 @@ window_stats_warp_kernel(const float* __restrict__ ring, const uint32_t* __restr
   float result = 0.f;
   do {  // single-trip block: `break` = result (or the bisect request) is final
     if (bisect) break;
+    if (tie_hit) { result = tie_val; break; }
     if (mn == mx) { result = mx; break; }  // constant series
     const int cnt = (int)(c128 >> 7);
     const int total = warp_sum_i32(cnt);
     const int maxcnt = warp_max_i32(cnt);
     if (total < k && !sampled) { result = NEG_INF; break; }  // lox = -inf: only -inf samples are unlisted
-    if (total < k || maxcnt > kLaneCap || total > kPackCap) {
+    if (total < k || maxcnt > kLaneCap) {
       // unlucky pivot or list overflow: exact bisection over the registers
       bisect = true; bis_hi = f32_key(mx) + 1u; bis_first = 0u;
       break;
     }
-    // pack the lane lists into one contiguous array (exclusive scan of the counts)
-    int incl = cnt;
-#pragma unroll
-    for (int off = 1; off < 32; off <<= 1) {
-      const int u = __shfl_up_sync(0xffffffffu, incl, off);
-      if (lane >= off) incl += u;
-    }
-    float* dst = pack + (incl - cnt);
-    __syncwarp();
-#pragma unroll 1
-    for (int e = 0; e < maxcnt; e += 4) {
-#pragma unroll
-      for (int u = 0; u < 4; ++u)
-        if (e + u < cnt) dst[e + u] = lst[(e + u) * 32];
-    }
-    const int nch = (total + 127) >> 7;
-    for (int i = total + lane; i < nch * 128; i += 32) pack[i] = NEG_INF;
+    const int m8 = (maxcnt + 7) & ~7;
+    for (int e = cnt; e < m8; ++e) lst[e * 32] = NEG_INF;  // pad to the common length
     if (lane == 0) *fin_cnt = 0;
     fin[lane] = NEG_INF;
+    fin[lane + 32] = NEG_INF;
     __syncwarp();
-    const float4* pk = reinterpret_cast<const float4*>(pack) + lane;
 
     // narrow [a, b): count_ge(a) = ca >= k > cb = count_ge(b); b = +inf with cb = 0 at first
     float a = sampled ? next_up(lox) : mn, b = POS_INF;
@@ -389,30 +422,25 @@ window_stats_warp_kernel(const float* __restrict__ ring, const uint32_t* __restr
     while (ca - cb > kMaxCand) {
       const uint32_t ka = f32_key(a), kb = (cb == 0) ? f32_key(mx) + 1u : f32_key(b);
       if (kb - ka <= 1u) { result = a; done = true; break; }  // every candidate equals a
-      float p1, p2;
-      bool snap = false;
-      if (it == 0 && sampled && hint_lo > a && hint_hi > hint_lo) {
-        p1 = hint_lo; p2 = hint_hi;       // sample order statistics around the 5 % point
-      } else if (it < 5) {
-        // interpolate on the counts towards ranks k + dl and k - dl (value-linear inside)
-        const float hi = (cb == 0) ? mx : b;
-        const int span = ca - cb;
-        const int dl = min(max(span >> 3, 6), 40);
-        const float inv = 1.0f / (float)span;
-        p1 = a + (hi - a) * ((float)max(ca - k - dl, 0) + 0.5f) * inv;
-        p2 = a + (hi - a) * ((float)min(ca - k + dl, span) - 0.5f) * inv;
-      } else {
-        snap = it < 12;
-        p1 = p2 = 0.f;
-      }
-      if (snap) {
+      if (it >= 4 && it < 12) {
         // ties keep the bracket wide: peel its largest distinct value
-        const uint32_t mk = pack_max_below(pk, nch, b, cb == 0);
-        const float m = key_f32(mk);
-        const int c = (int)(pack_count2(pk, nch, m, m) & 0xffffu);
+        const float m = key_f32(list_max_below(lst, m8, b, cb == 0));
+        const int c = (int)(list_count2(lst, m8, m, m) & 0xffffu);
         if (c >= k) { result = m; done = true; break; }  // everything above m is >= b
         b = m; cb = c;
       } else {
+        float p1, p2;
+        if (it == 0 && sampled && hint_lo > a && hint_hi > hint_lo) {
+          p1 = hint_lo; p2 = hint_hi;       // sample order statistics around the 5 % point
+        } else {
+          // interpolate on the counts towards ranks k + dl and k - dl (value-linear inside)
+          const float hi = (cb == 0) ? mx : b;
+          const int span = ca - cb;
+          const int dl = min(max(span / 7, 12), 24);
+          const float inv = 1.0f / (float)span;
+          p1 = a + (hi - a) * ((float)max(ca - k - dl, 0) + 0.5f) * inv;
+          p2 = a + (hi - a) * ((float)min(ca - k + dl, span) - 0.5f) * inv;
+        }
         // keep both pivots strictly inside (a, b) in key order, p1 <= p2
         uint32_t k1 = f32_key(p1), k2 = f32_key(p2);
         if (!(p1 == p1) || !(p2 == p2) || it >= 12 || k1 <= ka || k2 >= kb || k1 > k2) {
@@ -421,7 +449,7 @@ window_stats_warp_kernel(const float* __restrict__ ring, const uint32_t* __restr
           if (it >= 12) k1 = k2 = ka + ((kb - ka) >> 1);  // plain bisection: bounded
         }
         p1 = key_f32(k1); p2 = key_f32(k2);
-        const uint32_t cc = pack_count2(pk, nch, p1, p2);
+        const uint32_t cc = list_count2(lst, m8, p1, p2);
         const int c1 = (int)(cc & 0xffffu), c2 = (int)(cc >> 16);
         if (c2 >= k) { a = p2; ca = c2; }
         else if (c1 >= k) { a = p1; ca = c1; b = p2; cb = c2; }
@@ -431,31 +459,25 @@ window_stats_warp_kernel(const float* __restrict__ ring, const uint32_t* __restr
     }
     if (done) break;
 
-    // gather the <= 32 candidates in [a, b) (a shared counter hands out the slots) and
-    // rank them against each other
+    // gather the <= 64 candidates in [a, b) (a shared counter hands out the slots), sort
+    // them, read off rank k - cb
     const bool open = cb == 0;  // nothing lies at or above b (b may still be +inf)
 #pragma unroll 1
-    for (int c = 0; c < nch; ++c) {
-      const float4 z = pk[c * 32];
-      const float zz[4] = {z.x, z.y, z.z, z.w};
+    for (int e = 0; e < m8; e += 8) {
+      float x[8];
 #pragma unroll
-      for (int i = 0; i < 4; ++i)
-        if (zz[i] >= a && (open || zz[i] < b)) fin[atomicAdd(fin_cnt, 1)] = zz[i];
+      for (int u = 0; u < 8; ++u) x[u] = lst[(e + u) * 32];
+#pragma unroll
+      for (int u = 0; u < 8; ++u)
+        if (x[u] >= a && (open || x[u] < b)) fin[atomicAdd(fin_cnt, 1)] = x[u];
     }
     __syncwarp();
-    const int mcand = ca - cb;   // == *fin_cnt
     const int kk = k - cb;       // rank wanted among the candidates, 1-based from the top
-    const float y = fin[lane];   // -inf beyond mcand
-    int gt = 0, ge = 0;
-    const int mc4 = (mcand + 3) & ~3;
-#pragma unroll 1
-    for (int i = 0; i < mc4; i += 4) {
-      const float4 z = *reinterpret_cast<const float4*>(fin + i);
-      inc_if_gt(gt, z.x, y); inc_if_ge(ge, z.x, y); inc_if_gt(gt, z.y, y); inc_if_ge(ge, z.y, y);
-      inc_if_gt(gt, z.z, y); inc_if_ge(ge, z.z, y); inc_if_gt(gt, z.w, y); inc_if_ge(ge, z.w, y);
-    }
-    const unsigned okm = __ballot_sync(0xffffffffu, lane < mcand && gt < kk && kk <= ge);
-    result = __shfl_sync(0xffffffffu, y, __ffs(okm) - 1);
+    const float2 y = *reinterpret_cast<const float2*>(fin + 2 * lane);  // -inf beyond ca - cb
+    uint32_t k0 = f32_key(y.x), k1 = f32_key(y.y);
+    sort64_desc(k0, k1, lane);
+    const uint32_t pick = ((kk - 1) & 1) ? k1 : k0;
+    result = key_f32(__shfl_sync(0xffffffffu, pick, (kk - 1) >> 1));
   } while (false);
   if (bisect) result = w.select_bisect(bis_lo, bis_hi, k, bis_first);
   if (lane == 0) out_p95[o] = result;
@@ -470,6 +492,18 @@ static int launch_warp(const float* ring, const uint32_t* seen, int32_t window, 
     set_error("klm_dev_window_stats: too many series for one launch");
     return KLM_ELIMIT;
   }
+  static bool attr_set[64] = {};
+  int dev = 0;
+  KLM_CUDA(cudaGetDevice(&dev));
+  if (!(dev < 64 && attr_set[dev])) {
+    // 3 CTAs x 57 KB per SM: opt in above 48 KB and ask for the largest shared-memory carve-out
+    KLM_CUDA(cudaFuncSetAttribute(window_stats_warp_kernel<NV>,
+                                  cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kWswSmemBytes));
+    KLM_CUDA(cudaFuncSetAttribute(window_stats_warp_kernel<NV>,
+                                  cudaFuncAttributePreferredSharedMemoryCarveout,
+                                  (int)cudaSharedmemCarveoutMaxShared));
+    if (dev < 64) attr_set[dev] = true;
+  }
   window_stats_warp_kernel<NV><<<(unsigned)blocks, kWswThreads, kWswSmemBytes, st>>>(
       ring, seen, window, pitch, s0, n_series, out_min, out_max, out_mean, out_p95);
   KLM_LAUNCH_CHECK("window_stats_warp_kernel");
@@ -480,7 +514,7 @@ static int launch_warp(const float* ring, const uint32_t* seen, int32_t window, 
 int launch_window_stats_warp(const float* ring, const uint32_t* seen, int32_t window,
                              int32_t pitch, int64_t s0, int64_t s1, float* out_min,
                              float* out_max, double* out_mean, float* out_p95, cudaStream_t st) {
-  static_assert(kWswSmemBytes <= 48 * 1024, "dynamic shared memory above 48 KB needs an opt-in");
+  static_assert(3 * (kWswSmemBytes + 1024) <= 227 * 1024, "three CTAs per SM must fit");
   const int64_t n = s1 - s0;
   if (window <= 8 * 128) return launch_warp<8>(ring, seen, window, pitch, s0, n, out_min, out_max, out_mean, out_p95, st);
   if (window <= 16 * 128) return launch_warp<16>(ring, seen, window, pitch, s0, n, out_min, out_max, out_mean, out_p95, st);
