@@ -176,7 +176,8 @@ struct Window {
 // Counts of list entries >= p1 and >= p2 (p1 <= p2) in one pass over the lane lists
 // ([entry][lane], every lane padded with -inf up to m8, a multiple of 8). The eight
 // loads of a batch are issued together so their latencies overlap. Returns c1 | c2 << 16.
-__device__ __forceinline__ uint32_t list_count2(const float* lst, int m8, float p1, float p2) {
+__device__ __forceinline__ uint32_t list_count2(const float* lst, int m8, float p1, float p2,
+                                                int& lane_c1, int& lane_c2) {
   int a0 = 0, a1 = 0, b0 = 0, b1 = 0;
 #pragma unroll 1
   for (int e = 0; e < m8; e += 8) {
@@ -189,7 +190,9 @@ __device__ __forceinline__ uint32_t list_count2(const float* lst, int m8, float 
       inc_if_ge(b0, x[u], p2); inc_if_ge(b1, x[u + 1], p2);
     }
   }
-  return (uint32_t)warp_sum_i32((a0 + a1) + ((b0 + b1) << 16));
+  lane_c1 = a0 + a1;
+  lane_c2 = b0 + b1;
+  return (uint32_t)warp_sum_i32(lane_c1 + (lane_c2 << 16));
 }
 
 // Largest list entry < b (or the largest entry if `open`), as a key (0 if none).
@@ -242,7 +245,32 @@ window_stats_warp_kernel(const float* __restrict__ ring, const uint32_t* __restr
   const int64_t o = (int64_t)blockIdx.x * kWswWarps + wib;  // output slot
   if (o >= n_series) return;                                  // no block-wide barrier below
   const int64_t s = s0 + o;
-  const uint32_t sn = seen[s];
+  const float* row = ring + s * (int64_t)pitch;
+  const uint32_t sn = seen[s];  // consumed only after the row loads below are in flight
+
+  // shared memory of this warp; the lane lists must start on their own size boundary
+  const uint32_t raw_s = (uint32_t)__cvta_generic_to_shared(s_raw);
+  const uint32_t base_s = (raw_s + (uint32_t)kLaneListBytes - 1u) & ~((uint32_t)kLaneListBytes - 1u);
+  unsigned char* base_g = s_raw + (base_s - raw_s);
+  float* lst = reinterpret_cast<float*>(base_g + wib * kLaneListBytes) + lane;  // entry e: lst[e * 32]
+  unsigned char* aux = base_g + kWswWarps * kLaneListBytes + wib * kWarpAux;
+  float* fin = reinterpret_cast<float*>(aux);
+  const uint32_t lb = (base_s + (uint32_t)wib * kLaneListBytes) | ((uint32_t)lane << 2);
+
+  // ---- 1. load. The addresses do not depend on seen[s]: every float4 inside the row
+  // pitch is fetched (stale slots beyond n are masked below), so the row loads and the
+  // seen[] load share one memory round trip.
+  Window<NV> w;
+  {
+    const int pfull = pitch >> 2;
+    const float* p = row + 4 * lane;
+#pragma unroll
+    for (int j = 0; j < NV; ++j) {
+      float4 t = make_float4(NEG_INF, NEG_INF, NEG_INF, NEG_INF);
+      if (lane + 32 * j < pfull) t = ld_stream_f4(p + 128 * j);
+      w.v[4 * j + 0] = t.x; w.v[4 * j + 1] = t.y; w.v[4 * j + 2] = t.z; w.v[4 * j + 3] = t.w;
+    }
+  }
   const int n = sn < (uint32_t)window ? (int)sn : window;
   if (n == 0) {
     if (lane == 0) {
@@ -253,21 +281,6 @@ window_stats_warp_kernel(const float* __restrict__ ring, const uint32_t* __restr
     }
     return;
   }
-  const float* row = ring + s * (int64_t)pitch;
-  const int nfull = n >> 2;   // complete float4 groups
-  const int jr = nfull >> 5;  // rows valid in every lane
-  const bool full = jr >= NV - 1;
-
-  // shared memory of this warp; the lane lists must start on a 4 KB boundary
-  const uint32_t raw_s = (uint32_t)__cvta_generic_to_shared(s_raw);
-  const uint32_t base_s = (raw_s + (uint32_t)kLaneListBytes - 1u) & ~((uint32_t)kLaneListBytes - 1u);
-  unsigned char* base_g = s_raw + (base_s - raw_s);
-  float* lst = reinterpret_cast<float*>(base_g + wib * kLaneListBytes) + lane;  // entry e: lst[e * 32]
-  unsigned char* aux = base_g + kWswWarps * kLaneListBytes + wib * kWarpAux;
-  float* fin = reinterpret_cast<float*>(aux);
-  int* fin_cnt = reinterpret_cast<int*>(fin + kMaxCand);
-  const uint32_t lb = (base_s + (uint32_t)wib * kLaneListBytes) | ((uint32_t)lane << 2);
-
   // Ask L2 for the row that a warp will want about one residency later (12 warps per SM
   // are in flight): one bulk-prefetch instruction covers the whole row.
   if (lane == 0) {
@@ -278,27 +291,18 @@ window_stats_warp_kernel(const float* __restrict__ ring, const uint32_t* __restr
                    :: "l"(ring + (s0 + later) * (int64_t)pitch), "r"(bytes) : "memory");
     }
   }
-
-  // ---- 1. load
-  Window<NV> w;
+  const int nfull = n >> 2;   // complete float4 groups
+  const int jr = nfull >> 5;  // rows valid in every lane
+  const bool full = jr >= NV - 1;
+  // mask the slots at and beyond n: rows below jr are valid in every lane
   if (full) {
-    const float* p = row + 4 * lane;
-#pragma unroll
-    for (int j = 0; j < NV - 1; ++j) {
-      const float4 t = ld_stream_f4(p + 128 * j);
-      w.v[4 * j + 0] = t.x; w.v[4 * j + 1] = t.y; w.v[4 * j + 2] = t.z; w.v[4 * j + 3] = t.w;
-    }
-    float4 t = make_float4(NEG_INF, NEG_INF, NEG_INF, NEG_INF);
-    if (lane + 32 * (NV - 1) < nfull) t = ld_stream_f4(p + 128 * (NV - 1));
-    w.v[4 * NV - 4] = t.x; w.v[4 * NV - 3] = t.y; w.v[4 * NV - 2] = t.z; w.v[4 * NV - 1] = t.w;
+    if (!(lane + 32 * (NV - 1) < nfull))
+      w.v[4 * NV - 4] = w.v[4 * NV - 3] = w.v[4 * NV - 2] = w.v[4 * NV - 1] = NEG_INF;
   } else {
 #pragma unroll
-    for (int j = 0; j < NV; ++j) {
-      const int q = lane + 32 * j;
-      float4 t = make_float4(NEG_INF, NEG_INF, NEG_INF, NEG_INF);
-      if (q < nfull) t = ld_stream_f4(row + 4 * q);
-      w.v[4 * j + 0] = t.x; w.v[4 * j + 1] = t.y; w.v[4 * j + 2] = t.z; w.v[4 * j + 3] = t.w;
-    }
+    for (int j = 0; j < NV; ++j)
+      if (j >= jr && !(lane + 32 * j < nfull))
+        w.v[4 * j] = w.v[4 * j + 1] = w.v[4 * j + 2] = w.v[4 * j + 3] = NEG_INF;
   }
   w.tail = (lane < (n & 3)) ? row[4 * nfull + lane] : NEG_INF;
 
@@ -407,8 +411,12 @@ window_stats_warp_kernel(const float* __restrict__ ring, const uint32_t* __restr
       break;
     }
     const int m8 = (maxcnt + 7) & ~7;
-    for (int e = cnt; e < m8; ++e) lst[e * 32] = NEG_INF;  // pad to the common length
-    if (lane == 0) *fin_cnt = 0;
+#pragma unroll 1
+    for (int e = cnt & ~3; e < m8; e += 4) {  // pad every lane's list to the common length
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+        if (e + u >= cnt) lst[(e + u) * 32] = NEG_INF;
+    }
     fin[lane] = NEG_INF;
     fin[lane + 32] = NEG_INF;
     __syncwarp();
@@ -416,6 +424,7 @@ window_stats_warp_kernel(const float* __restrict__ ring, const uint32_t* __restr
     // narrow [a, b): count_ge(a) = ca >= k > cb = count_ge(b); b = +inf with cb = 0 at first
     float a = sampled ? next_up(lox) : mn, b = POS_INF;
     int ca = total, cb = 0;
+    int lane_ca = cnt, lane_cb = 0;  // this lane's share of ca and cb
     bool done = false;
     int it = 0;
 #pragma unroll 1
@@ -425,9 +434,10 @@ window_stats_warp_kernel(const float* __restrict__ ring, const uint32_t* __restr
       if (it >= 4 && it < 12) {
         // ties keep the bracket wide: peel its largest distinct value
         const float m = key_f32(list_max_below(lst, m8, b, cb == 0));
-        const int c = (int)(list_count2(lst, m8, m, m) & 0xffffu);
+        int l1, l2;
+        const int c = (int)(list_count2(lst, m8, m, m, l1, l2) & 0xffffu);
         if (c >= k) { result = m; done = true; break; }  // everything above m is >= b
-        b = m; cb = c;
+        b = m; cb = c; lane_cb = l1;
       } else {
         float p1, p2;
         if (it == 0 && sampled && hint_lo > a && hint_hi > hint_lo) {
@@ -449,27 +459,38 @@ window_stats_warp_kernel(const float* __restrict__ ring, const uint32_t* __restr
           if (it >= 12) k1 = k2 = ka + ((kb - ka) >> 1);  // plain bisection: bounded
         }
         p1 = key_f32(k1); p2 = key_f32(k2);
-        const uint32_t cc = list_count2(lst, m8, p1, p2);
+        int l1, l2;
+        const uint32_t cc = list_count2(lst, m8, p1, p2, l1, l2);
         const int c1 = (int)(cc & 0xffffu), c2 = (int)(cc >> 16);
-        if (c2 >= k) { a = p2; ca = c2; }
-        else if (c1 >= k) { a = p1; ca = c1; b = p2; cb = c2; }
-        else { b = p1; cb = c1; }
+        if (c2 >= k) { a = p2; ca = c2; lane_ca = l2; }
+        else if (c1 >= k) { a = p1; ca = c1; lane_ca = l1; b = p2; cb = c2; lane_cb = l2; }
+        else { b = p1; cb = c1; lane_cb = l1; }
       }
       ++it;
     }
     if (done) break;
 
-    // gather the <= 64 candidates in [a, b) (a shared counter hands out the slots), sort
-    // them, read off rank k - cb
+    // gather the <= 64 candidates in [a, b): each lane already knows how many of them it
+    // holds (lane_ca - lane_cb), so an exclusive scan gives it a private range of slots
     const bool open = cb == 0;  // nothing lies at or above b (b may still be +inf)
+    const int mine = lane_ca - lane_cb;
+    int incl = mine;
+#pragma unroll
+    for (int off = 1; off < 32; off <<= 1) {
+      const int u = __shfl_up_sync(0xffffffffu, incl, off);
+      if (lane >= off) incl += u;
+    }
+    float* dst = fin + (incl - mine);
+    if (mine > 0) {
 #pragma unroll 1
-    for (int e = 0; e < m8; e += 8) {
-      float x[8];
+      for (int e = 0; e < m8; e += 8) {
+        float x[8];
 #pragma unroll
-      for (int u = 0; u < 8; ++u) x[u] = lst[(e + u) * 32];
+        for (int u = 0; u < 8; ++u) x[u] = lst[(e + u) * 32];
 #pragma unroll
-      for (int u = 0; u < 8; ++u)
-        if (x[u] >= a && (open || x[u] < b)) fin[atomicAdd(fin_cnt, 1)] = x[u];
+        for (int u = 0; u < 8; ++u)
+          if (x[u] >= a && (open || x[u] < b)) *dst++ = x[u];
+      }
     }
     __syncwarp();
     const int kk = k - cb;       // rank wanted among the candidates, 1-based from the top
