@@ -264,13 +264,28 @@ window_stats_warp_kernel(const float* __restrict__ ring, const uint32_t* __restr
   {
     const int pfull = pitch >> 2;
     const float* p = row + 4 * lane;
+    if (pfull >= 32 * (NV - 1)) {  // usual case: all rows but the last lie inside the pitch
 #pragma unroll
-    for (int j = 0; j < NV; ++j) {
+      for (int j = 0; j < NV - 1; ++j) {
+        const float4 t = ld_stream_f4(p + 128 * j);
+        w.v[4 * j + 0] = t.x; w.v[4 * j + 1] = t.y; w.v[4 * j + 2] = t.z; w.v[4 * j + 3] = t.w;
+      }
       float4 t = make_float4(NEG_INF, NEG_INF, NEG_INF, NEG_INF);
-      if (lane + 32 * j < pfull) t = ld_stream_f4(p + 128 * j);
-      w.v[4 * j + 0] = t.x; w.v[4 * j + 1] = t.y; w.v[4 * j + 2] = t.z; w.v[4 * j + 3] = t.w;
+      if (lane + 32 * (NV - 1) < pfull) t = ld_stream_f4(p + 128 * (NV - 1));
+      w.v[4 * NV - 4] = t.x; w.v[4 * NV - 3] = t.y; w.v[4 * NV - 2] = t.z; w.v[4 * NV - 1] = t.w;
+    } else {
+#pragma unroll
+      for (int j = 0; j < NV; ++j) {
+        float4 t = make_float4(NEG_INF, NEG_INF, NEG_INF, NEG_INF);
+        if (lane + 32 * j < pfull) t = ld_stream_f4(p + 128 * j);
+        w.v[4 * j + 0] = t.x; w.v[4 * j + 1] = t.y; w.v[4 * j + 2] = t.z; w.v[4 * j + 3] = t.w;
+      }
     }
   }
+  // While the loads are in flight: fill the first 32 entries of this lane's list with -inf,
+  // so the counting passes need no padding later (longer lists are padded when they occur).
+#pragma unroll
+  for (int e = 0; e < 32; ++e) lst[e * 32] = NEG_INF;
   const int n = sn < (uint32_t)window ? (int)sn : window;
   if (n == 0) {
     if (lane == 0) {
@@ -411,12 +426,8 @@ window_stats_warp_kernel(const float* __restrict__ ring, const uint32_t* __restr
       break;
     }
     const int m8 = (maxcnt + 7) & ~7;
-#pragma unroll 1
-    for (int e = cnt & ~3; e < m8; e += 4) {  // pad every lane's list to the common length
-#pragma unroll
-      for (int u = 0; u < 4; ++u)
-        if (e + u >= cnt) lst[(e + u) * 32] = NEG_INF;
-    }
+    // entries below 32 were pre-filled with -inf; pad the rare longer lists here
+    for (int e = max(cnt, 32); e < m8; ++e) lst[e * 32] = NEG_INF;
     fin[lane] = NEG_INF;
     fin[lane + 32] = NEG_INF;
     __syncwarp();
