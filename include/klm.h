@@ -215,6 +215,21 @@ int64_t klm_dev_node_best_scratch_bytes(void);
 int klm_dev_node_best(const double* battery, const uint8_t* flags,
                       int64_t n_nodes, int64_t node_base, int64_t* best,
                       void* scratch, void* stream);
+/* K1 without caller scratch, for hosts that must not allocate device memory (a
+ * process whose HBM is fully reserved by a pool or an MPS memory limit, or a
+ * reconcile loop that forbids cudaMalloc because it synchronises the device).
+ * No counterpart in the reference (it has no GPU path and no allocation contract).
+ * Same result as klm_dev_node_best. The scratch is a 19 200-byte __device__ array
+ * inside libklm.so, held by every GPU that loads the library until exit; it
+ * limits one call to klm_dev_node_best_static_max_nodes() = 4 849 664 nodes
+ * (larger tables: KLM_ELIMIT). All calls on a device share that array, so calls
+ * that could overlap on the GPU race: serialise them. The first call on a device
+ * looks up the array's address; make it before any stream capture. Never calls
+ * cudaMalloc / cudaFree. */
+int64_t klm_dev_node_best_static_max_nodes(void);
+int klm_dev_node_best_static(const double* battery, const uint8_t* flags,
+                             int64_t n_nodes, int64_t node_base, int64_t* best,
+                             void* stream);
 /* K2 schedule_batch (decomposed form of controller.go:174-221 + :160-161).
  * Node arrays hold global indices [node_base, node_base + n_nodes);
  * pref_ids are global; ids outside the local range are skipped, so with

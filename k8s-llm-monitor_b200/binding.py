@@ -80,6 +80,8 @@ SIGNATURES = {
     "klm_ring_stats": (C.c_int, [_P, _I64, _I64, _P, _P, _P, _P]),
     "klm_dev_node_best_scratch_bytes": (_I64, []),
     "klm_dev_node_best": (C.c_int, [_P, _P, _I64, _I64, _P, _P, _P]),
+    "klm_dev_node_best_static_max_nodes": (_I64, []),
+    "klm_dev_node_best_static": (C.c_int, [_P, _P, _I64, _I64, _P, _P]),
     "klm_dev_schedule": (C.c_int, [_P, _P, _I64, _I64, _P, _I64, _P, _P, _P, _P, _P, _P]),
     "klm_dev_schedule_bruteforce": (C.c_int, [_P, _P, _I64, _I64, _I64, _P, _P, _P, _P, _P, _P]),
     "klm_dev_merge_partials": (C.c_int, [C.c_int, _I64, _P, _P, _P, _P, _P]),
