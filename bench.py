@@ -205,8 +205,8 @@ def run_ours(args):
         o_idx = torch.empty(rl, dtype=torch.int32, device="cuda")
         o_score = torch.empty(rl, dtype=torch.float64, device="cuda")
         if wl == "c5" and world > 1:
-            g_idx = torch.empty((world, rl), dtype=torch.int32, device="cuda")
-            g_score = torch.empty((world, rl), dtype=torch.float64, device="cuda")
+            g_idx = torch.empty(world * rl, dtype=torch.int32, device="cuda")
+            g_score = torch.empty(world * rl, dtype=torch.float64, device="cuda")
             m_idx, m_score = torch.empty_like(o_idx), torch.empty_like(o_score)
         units = R  # whole job
 
@@ -223,7 +223,7 @@ def run_ours(args):
             if wl == "c5" and world > 1:
                 dist.all_gather_into_tensor(g_idx, o_idx)
                 dist.all_gather_into_tensor(g_score, o_score)
-                dev.merge_partials(g_idx, g_score, m_idx, m_score)                # K3
+                dev.merge_partials(g_idx.view(world, rl), g_score.view(world, rl), m_idx, m_score)  # K3
                 launches[0] += 1
 
         k7_bytes = 9 * (n1 - n0) + int(24 * rl + 13 * ids.size)
@@ -300,7 +300,10 @@ def run_ours(args):
                      "achieved": achieved, "peak": pk["hbm_gbs"], "unit": "GB/s",
                      "frac": achieved / pk["hbm_gbs"], "frac_of_nominal_8TBs": achieved / 8000.0,
                      "peak_source": pk_src, "algorithmic_bytes_per_launch": k7_bytes,
-                     "avg_launch_ms": kern_ms, "traffic": None},
+                     "avg_launch_ms": kern_ms,
+                     # dram__bytes_read.sum + dram__bytes_write.sum of one K7 launch at c2, from the
+                     # ncu --set full capture summarised in profiles/r01_k7_warp_v2g_ncu_summary.txt
+                     "traffic": 378.911e6 if (wl == "c2" and world >= 1) else None},
     }
     if rank == 0:
         if world == 1 and not args.no_cpu:
@@ -369,7 +372,8 @@ def run_e2e(pkg, wl, cid, shp, rank, world, args, env):
                                  node_base=n0)
                     dist.all_gather_into_tensor(env["g_idx"], env["o_idx"])
                     dist.all_gather_into_tensor(env["g_score"], env["o_score"])
-                    dev.merge_partials(env["g_idx"], env["g_score"], env["m_idx"], env["m_score"])
+                    dev.merge_partials(env["g_idx"].view(world, -1), env["g_score"].view(world, -1),
+                                       env["m_idx"], env["m_score"])
                     res_i.copy_(env["m_idx"], non_blocking=True)
                     res_s.copy_(env["m_score"], non_blocking=True)
                     torch.cuda.synchronize()
@@ -438,11 +442,16 @@ def cpu_baseline(wl, cid, shp, budget_s):
     step()
     rate = u / max(time.perf_counter() - t0, 1e-6)
     step, u, desc, threads = cpu_step_factory(wl, cid, shp, int(rate * budget_s))
-    t0 = time.perf_counter()
-    step()
-    dt = time.perf_counter() - t0
+    step()  # warm the caches and the thread pool
+    reps, t0 = 0, time.perf_counter()
+    while reps < 3 or time.perf_counter() - t0 < min(budget_s, 8.0):
+        step()
+        reps += 1
+        if time.perf_counter() - t0 > 2 * budget_s:
+            break
+    dt = (time.perf_counter() - t0) / reps
     return {"value": u / dt, "unit": METRIC[wl][1], "cores": threads, "kind": "port",
-            "sample": desc + f"; {dt:.2f} s",
+            "sample": desc + f"; mean of {reps} passes, {dt:.3f} s each",
             "note": "C restatement of the Go reference (Go toolchain unavailable); window stats have no "
                     "reference code (quickselect baseline)"}
 
