@@ -286,6 +286,22 @@ def _need(t, dtype, name):
         raise ValueError(f"{name}: need a contiguous CUDA tensor of {dtype}, got {t.dtype} on {t.device}")
 
 
+class _Recorder:
+    """Stands in for the library while a Dev call is being recorded by Dev.prebind()."""
+
+    def __init__(self, lib):
+        self._lib = lib
+        self.calls = []
+
+    def __getattr__(self, name):
+        fn = getattr(self._lib, name)
+
+        def rec(*args):
+            self.calls.append((fn, args))
+            return KLM_OK
+        return rec
+
+
 class Dev:
     """klm_dev_* calls on torch CUDA tensors; only enqueues work on the current stream."""
 
@@ -300,6 +316,27 @@ class Dev:
                                             device=self.device)
             self.cluster_scratch = torch.zeros(self.lib.klm_dev_cluster_scratch_bytes(), dtype=torch.uint8,
                                                device=self.device)
+
+    def prebind(self, method: str, *args, **kwargs):
+        """Validate the arguments of one Dev call now and return a zero-argument callable
+        that just re-issues the C call with the same pointers (hot loops: a launch is then
+        one ctypes call, ~1 us of host time). The tensors must stay alive and in place."""
+        rec = _Recorder(self.lib)
+        real, self.lib = self.lib, rec
+        try:
+            getattr(self, method)(*args, **kwargs)
+        finally:
+            self.lib = real
+        calls = [(fn, tuple(a)) for fn, a in rec.calls if fn.restype is C.c_int]
+        if not calls:
+            raise ValueError(f"{method} issued no launch")
+
+        def issue():
+            for fn, a in calls:
+                rc = fn(*a)
+                if rc != KLM_OK:
+                    raise KlmError(rc, last_error())
+        return issue
 
     def node_best(self, battery, flags, best, node_base: int = 0, stream=None, scratch=None):
         t = self.torch
