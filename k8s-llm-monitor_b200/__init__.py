@@ -8,5 +8,5 @@ and the seeded synthetic-cluster generators used by the tests and bench.py.
 The directory name has a hyphen, so import it through
 `__graft_entry__.load_package()` (registers it as `klm_b200`).
 """
-from . import binding, sharding, synth  # noqa: F401
+from . import binding, hostbinding, sharding, synth  # noqa: F401
 from .binding import Dev, Handle, KlmError, load  # noqa: F401

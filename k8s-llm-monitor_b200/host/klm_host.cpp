@@ -1,0 +1,178 @@
+#include "klm_host.h"
+
+#include <cstdio>
+#include <stdexcept>
+#include <unordered_map>
+
+namespace klmhost {
+
+std::string ToLower(const std::string& s) {
+  std::string o = s;
+  for (char& c : o)
+    if (c >= 'A' && c <= 'Z') c = static_cast<char>(c - 'A' + 'a');
+  return o;
+}
+
+static void check(int rc, const char* what) {
+  if (rc != KLM_OK) throw std::runtime_error(std::string(what) + ": " + klm_last_error());
+}
+
+static std::string sprintf1(const char* fmt, const char* s, double v) {
+  char buf[512];
+  std::snprintf(buf, sizeof(buf), fmt, s, v);
+  return buf;
+}
+
+std::vector<SchedulingRequestStatus> Controller::Reconcile(
+    const std::vector<SchedulingRequest>& requests, const std::vector<UAVMetricItem>& uavs) {
+  // ---- flatten the snapshot once per reconcile (controller.go:181-200 per item)
+  const int64_t n = static_cast<int64_t>(uavs.size());
+  std::vector<double> battery(n);
+  std::vector<uint8_t> flags(n);
+  std::unordered_map<std::string, std::vector<int32_t>> by_name;  // lower(name) -> every index
+  for (int64_t i = 0; i < n; ++i) {
+    const UAVMetricItem& u = uavs[i];
+    const std::string name = u.HasNodeName ? u.NodeName : std::string();
+    battery[i] = u.HasBattery ? u.Battery : 0.0;                                   // :187
+    const std::string st = u.HasStatus ? ToLower(u.CollectionStatus) : std::string();  // :188
+    uint8_t f = 0;
+    if (!name.empty()) f |= KLM_NODE_HAS_NAME;                                    // :190
+    if (st.empty() || st == "active") f |= KLM_NODE_STATUS_OK;                    // :198
+    flags[i] = f;
+    if (!name.empty()) by_name[ToLower(name)].push_back(static_cast<int32_t>(i));  // :206
+  }
+
+  std::vector<SchedulingRequestStatus> out(requests.size());
+  std::vector<size_t> live;  // requests that reach buildCandidates
+  std::vector<double> min_battery;
+  std::vector<int32_t> pref_off{0}, pref_ids;
+  for (size_t r = 0; r < requests.size(); ++r) {
+    const SchedulingRequest& q = requests[r];
+    if (q.HasPhase && !q.Phase.empty() && q.Phase != "Pending") continue;          // :117-119
+    out[r].Updated = true;
+    if (q.Spec.Workload.Name.empty() || q.Spec.Workload.Namespace.empty()) {       // :145-150
+      out[r].Phase = "Failed";
+      out[r].Message = "workload name/namespace 不能为空";
+      continue;
+    }
+    live.push_back(r);
+    min_battery.push_back(q.Spec.MinBatteryPercent);
+    std::unordered_map<std::string, bool> seen;                                    // preferredSet, :175-178
+    for (const std::string& p : q.Spec.PreferredNodes) {
+      const std::string lp = ToLower(p);
+      if (seen.emplace(lp, true).second) {
+        auto it = by_name.find(lp);
+        if (it != by_name.end()) pref_ids.insert(pref_ids.end(), it->second.begin(), it->second.end());
+      }
+    }
+    pref_off.push_back(static_cast<int32_t>(pref_ids.size()));
+  }
+  if (live.empty()) return out;
+
+  // ---- the GPU path: one snapshot, one batch
+  check(klm_nodes_set(h_, n, battery.data(), flags.data()), "klm_nodes_set");
+  std::vector<int32_t> idx(live.size());
+  std::vector<double> score(live.size());
+  if (pref_ids.empty()) pref_ids.push_back(0);
+  check(klm_schedule_batch(h_, static_cast<int64_t>(live.size()), min_battery.data(), pref_off.data(),
+                           pref_ids.data(), idx.data(), score.data(), KLM_ALGO_DECOMPOSED),
+        "klm_schedule_batch");
+
+  for (size_t k = 0; k < live.size(); ++k) {
+    SchedulingRequestStatus& s = out[live[k]];
+    if (idx[k] < 0) {                                                              // :153-158
+      s.Phase = "Failed";
+      s.Message = "无满足要求的 UAV 节点";
+      continue;
+    }
+    const UAVMetricItem& c = uavs[idx[k]];
+    s.Phase = "Assigned";                                                          // :163-169
+    s.AssignedNode = c.NodeName;
+    s.AssignedUAV = c.UAVID;
+    s.Score = score[k];
+    s.Message = sprintf1("选中节点 %s (电量 %.1f%%)", c.NodeName.c_str(), battery[idx[k]]);
+  }
+  return out;
+}
+
+ClusterMetrics Manager::CalculateClusterMetrics(const std::vector<NodeMetrics>& nodes,
+                                                const std::vector<PodMetrics>& pods) {
+  const int64_t n = static_cast<int64_t>(nodes.size()), p = static_cast<int64_t>(pods.size());
+  std::vector<int64_t> cc(n), cu(n), mc(n), mu(n);
+  std::vector<int32_t> gc(n);
+  std::vector<uint8_t> healthy(n), running(p);
+  std::vector<double> gpu;
+  for (int64_t i = 0; i < n; ++i) {
+    cc[i] = nodes[i].CPUCapacity; cu[i] = nodes[i].CPUUsage;
+    mc[i] = nodes[i].MemoryCapacity; mu[i] = nodes[i].MemoryUsage;
+    gc[i] = nodes[i].GPUCount;
+    healthy[i] = nodes[i].Healthy ? 1 : 0;
+    gpu.insert(gpu.end(), nodes[i].GPUUsage.begin(), nodes[i].GPUUsage.end());
+  }
+  for (int64_t i = 0; i < p; ++i) running[i] = pods[i].Phase == "Running" ? 1 : 0;  // manager.go:509
+  klm_node_cols cols{cc.data(), cu.data(), mc.data(), mu.data(), gc.data(), healthy.data(),
+                     gpu.data(), static_cast<int64_t>(gpu.size())};
+  klm_cluster_out o{};
+  check(klm_cluster_aggregate(h_, &cols, n, running.data(), p, &o), "klm_cluster_aggregate");
+
+  ClusterMetrics m;
+  m.TotalNodes = o.total_nodes; m.HealthyNodes = o.healthy_nodes;
+  m.TotalPods = o.total_pods; m.RunningPods = o.running_pods;
+  m.TotalCPU = o.total_cpu; m.UsedCPU = o.used_cpu;
+  m.TotalMemory = o.total_memory; m.UsedMemory = o.used_memory;
+  m.TotalGPUs = o.total_gpus; m.AvailableGPUs = o.available_gpus;
+  m.CPUUsageRate = o.cpu_usage_rate; m.MemoryUsageRate = o.memory_usage_rate;
+  char buf[128];
+  if (o.issues & KLM_ISSUE_UNHEALTHY_NODES) {                                        // manager.go:547-549
+    std::snprintf(buf, sizeof(buf), "%lld nodes are unhealthy",
+                  static_cast<long long>(m.TotalNodes - m.HealthyNodes));
+    m.Issues.push_back(buf);
+  }
+  if (o.issues & KLM_ISSUE_HIGH_CPU) {                                               // :550-552
+    std::snprintf(buf, sizeof(buf), "High CPU usage: %.1f%%", m.CPUUsageRate);
+    m.Issues.push_back(buf);
+  }
+  if (o.issues & KLM_ISSUE_HIGH_MEMORY) {                                            // :553-555
+    std::snprintf(buf, sizeof(buf), "High memory usage: %.1f%%", m.MemoryUsageRate);
+    m.Issues.push_back(buf);
+  }
+  static const char* kStatus[] = {"healthy", "warning", "critical"};                 // :558-564
+  m.HealthStatus = kStatus[o.health_status];
+  return m;
+}
+
+static void fleet_columns(const std::vector<UAVHealth>& fleet, std::vector<uint8_t>& ok,
+                          std::vector<double>& pct) {
+  ok.resize(fleet.size());
+  pct.resize(fleet.size());
+  for (size_t i = 0; i < fleet.size(); ++i) {
+    ok[i] = fleet[i].SystemStatus == "OK" ? 1 : 0;  // uav_metrics.go:207
+    pct[i] = fleet[i].RemainingPercent;
+  }
+}
+
+int64_t Manager::GetHealthyUAVCount(const std::vector<UAVHealth>& fleet) {
+  std::vector<uint8_t> ok;
+  std::vector<double> pct;
+  fleet_columns(fleet, ok, pct);
+  std::vector<int32_t> low(fleet.size() + 1);
+  int64_t healthy = 0, n_low = 0;
+  check(klm_fleet_scan(h_, static_cast<int64_t>(fleet.size()), ok.data(), pct.data(), 0.0, &healthy,
+                       low.data(), &n_low), "klm_fleet_scan");
+  return healthy;
+}
+
+std::vector<std::string> Manager::GetLowBatteryUAVs(const std::vector<UAVHealth>& fleet, double threshold) {
+  std::vector<uint8_t> ok;
+  std::vector<double> pct;
+  fleet_columns(fleet, ok, pct);
+  std::vector<int32_t> low(fleet.size() + 1);
+  int64_t healthy = 0, n_low = 0;
+  check(klm_fleet_scan(h_, static_cast<int64_t>(fleet.size()), ok.data(), pct.data(), threshold,
+                       &healthy, low.data(), &n_low), "klm_fleet_scan");
+  std::vector<std::string> names;
+  for (int64_t i = 0; i < n_low; ++i) names.push_back(fleet[low[i]].NodeName);
+  return names;
+}
+
+}  // namespace klmhost

@@ -1,0 +1,113 @@
+// C++ host layer above the C ABI: the reference's scheduler controller and metrics
+// manager logic that sits around the GPU path, with the reference's names, argument
+// meaning, status strings and failure behaviour (the reference is Go; no Go toolchain
+// exists in this build environment, so the host side is C++ — see INTEGRATION.md for the
+// cgo equivalent). All numeric work goes through libklm.so; nothing here scores,
+// sorts or sums.
+//
+// Reference: internal/scheduler/controller.go, internal/metrics/manager.go,
+// internal/metrics/sources/uav_metrics.go, pkg/models/scheduler.go, pkg/metrics/types.go
+// of Sabre94/k8s-llm-monitor.
+#pragma once
+
+#include <cstdint>
+#include <string>
+#include <vector>
+
+#include "../../include/klm.h"
+
+namespace klmhost {
+
+// ---- pkg/models/scheduler.go:6-29
+struct SchedulingWorkload {
+  std::string Name, Namespace, Type;
+};
+struct SchedulingRequestSpec {
+  SchedulingWorkload Workload;
+  double MinBatteryPercent = 0;  // as decoded at controller.go:133 (0 if the assertion failed)
+  std::vector<std::string> PreferredNodes;
+};
+struct SchedulingRequestStatus {
+  std::string Phase, AssignedNode, AssignedUAV;
+  double Score = 0;
+  std::string Message;
+  bool Updated = false;  // false: request skipped by the phase gate (controller.go:117-119)
+};
+
+// One UAVMetric item as buildCandidates reads it (controller.go:182-188, :252-288).
+struct UAVMetricItem {
+  bool HasNodeName = false;    // spec.node_name present and a string
+  std::string NodeName, UAVID;
+  bool HasBattery = false;     // spec.battery.remaining_percent is float64 / int / int64
+  double Battery = 0;          // readFloat result (0 when missing)
+  bool HasStatus = false;      // status.collection_status present and a string
+  std::string CollectionStatus;
+};
+
+struct SchedulingRequest {
+  bool HasPhase = false;       // status.phase found
+  std::string Phase;
+  SchedulingRequestSpec Spec;
+};
+
+// Go's strings.ToLower for the byte ranges that can occur in Kubernetes object names
+// (ASCII). Non-ASCII bytes pass through unchanged (documented limitation).
+std::string ToLower(const std::string& s);
+
+// internal/scheduler/controller.go Controller: reconcile over one snapshot.
+class Controller {
+ public:
+  explicit Controller(klm_handle* h) : h_(h) {}
+  // controller.go:88-172 for every request against `uavs`: phase gate, workload check,
+  // ONE batched klm_schedule_batch for everything else, status build. Throws
+  // std::runtime_error with klm_last_error() on a library failure ("reconcile failed",
+  // retried next tick by the caller like controller.go:75-77).
+  std::vector<SchedulingRequestStatus> Reconcile(const std::vector<SchedulingRequest>& requests,
+                                                 const std::vector<UAVMetricItem>& uavs);
+
+ private:
+  klm_handle* h_;
+};
+
+// ---- pkg/metrics/types.go (fields calculateClusterMetrics reads)
+struct NodeMetrics {
+  std::string NodeName;
+  int64_t CPUCapacity = 0, CPUUsage = 0, MemoryCapacity = 0, MemoryUsage = 0;
+  int32_t GPUCount = 0;
+  std::vector<double> GPUUsage;
+  bool Healthy = false;
+};
+struct PodMetrics {
+  std::string Phase;
+};
+struct ClusterMetrics {  // types.go:114-139
+  int64_t TotalNodes = 0, HealthyNodes = 0, TotalPods = 0, RunningPods = 0;
+  int64_t TotalCPU = 0, UsedCPU = 0, TotalMemory = 0, UsedMemory = 0, TotalGPUs = 0, AvailableGPUs = 0;
+  double CPUUsageRate = 0, MemoryUsageRate = 0;
+  std::string HealthStatus;
+  std::vector<std::string> Issues;
+};
+
+// One UAV state as the fleet scans read it (uav_metrics.go:197-233).
+struct UAVHealth {
+  std::string NodeName, SystemStatus;
+  double RemainingPercent = 0;
+};
+
+// internal/metrics/manager.go Manager: the aggregation half.
+class Manager {
+ public:
+  explicit Manager(klm_handle* h) : h_(h) {}
+  // manager.go:493-565
+  ClusterMetrics CalculateClusterMetrics(const std::vector<NodeMetrics>& nodes,
+                                         const std::vector<PodMetrics>& pods);
+  // uav_metrics.go:197-214
+  int64_t GetHealthyUAVCount(const std::vector<UAVHealth>& fleet);
+  // uav_metrics.go:216-233; names in fleet order (Go returns map order)
+  std::vector<std::string> GetLowBatteryUAVs(const std::vector<UAVHealth>& fleet, double threshold);
+
+ private:
+  klm_handle* h_;
+};
+
+}  // namespace klmhost

@@ -1,0 +1,157 @@
+// Flat C view of the C++ host layer so the (ctypes) tests can drive it. A session holds the
+// inputs of one reconcile / one Collect and the outputs of the last call.
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "klm_host.h"
+
+using namespace klmhost;
+
+namespace {
+struct Session {
+  explicit Session(klm_handle* handle) : h(handle) {}
+  klm_handle* h;
+  std::vector<UAVMetricItem> uavs;
+  std::vector<SchedulingRequest> requests;
+  std::vector<SchedulingRequestStatus> statuses;
+  std::vector<NodeMetrics> nodes;
+  std::vector<PodMetrics> pods;
+  std::vector<UAVHealth> fleet;
+  ClusterMetrics cluster;
+  std::vector<std::string> names;
+  std::string error;
+};
+void put(char* dst, int cap, const std::string& s) {
+  if (!dst || cap <= 0) return;
+  const size_t n = s.size() < static_cast<size_t>(cap - 1) ? s.size() : static_cast<size_t>(cap - 1);
+  std::memcpy(dst, s.data(), n);
+  dst[n] = 0;
+}
+}  // namespace
+
+extern "C" {
+
+void* klmh_open(klm_handle* h) { return h ? new Session(h) : nullptr; }
+void klmh_close(void* s) { delete static_cast<Session*>(s); }
+const char* klmh_error(void* s) { return static_cast<Session*>(s)->error.c_str(); }
+
+void klmh_clear(void* sv) {
+  Session* s = static_cast<Session*>(sv);
+  s->uavs.clear(); s->requests.clear(); s->statuses.clear();
+  s->nodes.clear(); s->pods.clear(); s->fleet.clear(); s->names.clear();
+}
+
+// node_name / status may be NULL (field absent); battery_kind: 0 missing, 1 number
+void klmh_add_uav(void* sv, const char* node_name, const char* uav_id, int battery_kind,
+                  double battery, const char* status) {
+  UAVMetricItem u;
+  u.HasNodeName = node_name != nullptr;
+  if (node_name) u.NodeName = node_name;
+  if (uav_id) u.UAVID = uav_id;
+  u.HasBattery = battery_kind != 0;
+  u.Battery = battery;
+  u.HasStatus = status != nullptr;
+  if (status) u.CollectionStatus = status;
+  static_cast<Session*>(sv)->uavs.push_back(u);
+}
+
+void klmh_add_request(void* sv, const char* phase, const char* wl_name, const char* wl_ns,
+                      double min_battery, int n_pref, const char** pref) {
+  SchedulingRequest q;
+  q.HasPhase = phase != nullptr;
+  if (phase) q.Phase = phase;
+  if (wl_name) q.Spec.Workload.Name = wl_name;
+  if (wl_ns) q.Spec.Workload.Namespace = wl_ns;
+  q.Spec.MinBatteryPercent = min_battery;
+  for (int i = 0; i < n_pref; ++i) q.Spec.PreferredNodes.push_back(pref[i]);
+  static_cast<Session*>(sv)->requests.push_back(q);
+}
+
+int klmh_reconcile(void* sv) {
+  Session* s = static_cast<Session*>(sv);
+  try {
+    s->statuses = Controller(s->h).Reconcile(s->requests, s->uavs);
+  } catch (const std::exception& e) {
+    s->error = e.what();
+    return -1;
+  }
+  return static_cast<int>(s->statuses.size());
+}
+
+int klmh_status(void* sv, int i, char* phase, char* node, char* uav, double* score, char* message,
+                int cap) {
+  Session* s = static_cast<Session*>(sv);
+  if (i < 0 || i >= static_cast<int>(s->statuses.size())) return -1;
+  const SchedulingRequestStatus& st = s->statuses[i];
+  put(phase, cap, st.Phase); put(node, cap, st.AssignedNode); put(uav, cap, st.AssignedUAV);
+  put(message, cap, st.Message);
+  if (score) *score = st.Score;
+  return st.Updated ? 1 : 0;
+}
+
+void klmh_add_node(void* sv, int64_t cpu_cap, int64_t cpu_use, int64_t mem_cap, int64_t mem_use,
+                   int healthy, int gpu_count, int n_gpu_usage, const double* gpu_usage) {
+  NodeMetrics n;
+  n.CPUCapacity = cpu_cap; n.CPUUsage = cpu_use; n.MemoryCapacity = mem_cap; n.MemoryUsage = mem_use;
+  n.Healthy = healthy != 0; n.GPUCount = gpu_count;
+  n.GPUUsage.assign(gpu_usage, gpu_usage + n_gpu_usage);
+  static_cast<Session*>(sv)->nodes.push_back(n);
+}
+void klmh_add_pod(void* sv, const char* phase) {
+  PodMetrics p;
+  p.Phase = phase ? phase : "";
+  static_cast<Session*>(sv)->pods.push_back(p);
+}
+
+// numeric part -> *out; returns the number of issue strings, or -1
+int klmh_calculate_cluster_metrics(void* sv, klm_cluster_out* out, char* health, int cap) {
+  Session* s = static_cast<Session*>(sv);
+  try {
+    s->cluster = Manager(s->h).CalculateClusterMetrics(s->nodes, s->pods);
+  } catch (const std::exception& e) {
+    s->error = e.what();
+    return -1;
+  }
+  const ClusterMetrics& m = s->cluster;
+  if (out) {
+    *out = klm_cluster_out{m.TotalNodes, m.HealthyNodes, m.TotalPods, m.RunningPods, m.TotalCPU, m.UsedCPU,
+                           m.TotalMemory, m.UsedMemory, m.TotalGPUs, m.AvailableGPUs, m.CPUUsageRate,
+                           m.MemoryUsageRate, 0, 0};
+  }
+  put(health, cap, m.HealthStatus);
+  return static_cast<int>(m.Issues.size());
+}
+int klmh_issue(void* sv, int i, char* dst, int cap) {
+  Session* s = static_cast<Session*>(sv);
+  if (i < 0 || i >= static_cast<int>(s->cluster.Issues.size())) return -1;
+  put(dst, cap, s->cluster.Issues[i]);
+  return 0;
+}
+
+void klmh_add_fleet_uav(void* sv, const char* node_name, const char* system_status, double pct) {
+  UAVHealth u;
+  u.NodeName = node_name ? node_name : "";
+  u.SystemStatus = system_status ? system_status : "";
+  u.RemainingPercent = pct;
+  static_cast<Session*>(sv)->fleet.push_back(u);
+}
+int64_t klmh_healthy_uav_count(void* sv) {
+  Session* s = static_cast<Session*>(sv);
+  try { return Manager(s->h).GetHealthyUAVCount(s->fleet); }
+  catch (const std::exception& e) { s->error = e.what(); return -1; }
+}
+int klmh_low_battery_uavs(void* sv, double threshold) {
+  Session* s = static_cast<Session*>(sv);
+  try { s->names = Manager(s->h).GetLowBatteryUAVs(s->fleet, threshold); }
+  catch (const std::exception& e) { s->error = e.what(); return -1; }
+  return static_cast<int>(s->names.size());
+}
+int klmh_name(void* sv, int i, char* dst, int cap) {
+  Session* s = static_cast<Session*>(sv);
+  if (i < 0 || i >= static_cast<int>(s->names.size())) return -1;
+  put(dst, cap, s->names[i]);
+  return 0;
+}
+
+}  // extern "C"

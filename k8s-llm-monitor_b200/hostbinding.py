@@ -1,0 +1,127 @@
+"""ctypes view of libklm_host.so, the C++ host layer (host/klm_host.h) that mirrors the
+reference's scheduler Controller and metrics Manager around the GPU path. Used by tests."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import List, Optional
+
+from . import binding
+
+LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "libklm_host.so")
+_lib = None
+_CAP = 512
+
+
+def load() -> C.CDLL:
+    global _lib
+    if _lib is None:
+        binding.load()  # libklm.so first (the host library links against it)
+        if not os.path.exists(LIB_PATH):
+            raise ImportError(f"{LIB_PATH} not found: run __graft_entry__.build()")
+        lib = C.CDLL(LIB_PATH)
+        lib.klmh_open.restype = C.c_void_p
+        lib.klmh_open.argtypes = [C.c_void_p]
+        lib.klmh_error.restype = C.c_char_p
+        lib.klmh_error.argtypes = [C.c_void_p]
+        lib.klmh_healthy_uav_count.restype = C.c_int64
+        for name in ("klmh_close", "klmh_clear", "klmh_add_uav", "klmh_add_request", "klmh_reconcile",
+                     "klmh_status", "klmh_add_node", "klmh_add_pod", "klmh_calculate_cluster_metrics",
+                     "klmh_issue", "klmh_add_fleet_uav", "klmh_healthy_uav_count", "klmh_low_battery_uavs",
+                     "klmh_name"):
+            getattr(lib, name)
+        _lib = lib
+    return _lib
+
+
+def _b(s: Optional[str]):
+    return None if s is None else s.encode("utf-8")
+
+
+class HostSession:
+    def __init__(self, handle: "binding.Handle"):
+        self.lib = load()
+        self.s = C.c_void_p(self.lib.klmh_open(handle._h))
+        self._keep = handle
+
+    def close(self):
+        if self.s:
+            self.lib.klmh_close(self.s)
+            self.s = None
+
+    def clear(self):
+        self.lib.klmh_clear(self.s)
+
+    def _err(self):
+        raise RuntimeError(self.lib.klmh_error(self.s).decode("utf-8", "replace"))
+
+    # --- Controller
+    def add_uav(self, node_name: Optional[str], uav_id: str, battery: Optional[float], status: Optional[str]):
+        self.lib.klmh_add_uav(self.s, _b(node_name), _b(uav_id), C.c_int(0 if battery is None else 1),
+                              C.c_double(0.0 if battery is None else float(battery)), _b(status))
+
+    def add_request(self, phase: Optional[str], wl_name: str, wl_ns: str, min_battery: float, preferred: List[str]):
+        arr = (C.c_char_p * max(len(preferred), 1))(*[p.encode("utf-8") for p in preferred])
+        self.lib.klmh_add_request(self.s, _b(phase), _b(wl_name), _b(wl_ns), C.c_double(min_battery),
+                                  C.c_int(len(preferred)), arr)
+
+    def reconcile(self):
+        n = self.lib.klmh_reconcile(self.s)
+        if n < 0:
+            self._err()
+        out = []
+        for i in range(n):
+            bufs = [C.create_string_buffer(_CAP) for _ in range(4)]
+            score = C.c_double(0)
+            upd = self.lib.klmh_status(self.s, i, bufs[0], bufs[1], bufs[2], C.byref(score), bufs[3], _CAP)
+            out.append({"updated": bool(upd), "phase": bufs[0].value.decode(), "node": bufs[1].value.decode(),
+                        "uav": bufs[2].value.decode(), "score": score.value,
+                        "message": bufs[3].value.decode("utf-8")})
+        return out
+
+    # --- Manager
+    def add_node(self, cpu_cap, cpu_use, mem_cap, mem_use, healthy, gpu_usage=()):
+        g = (C.c_double * max(len(gpu_usage), 1))(*gpu_usage)
+        self.lib.klmh_add_node(self.s, C.c_int64(cpu_cap), C.c_int64(cpu_use), C.c_int64(mem_cap),
+                               C.c_int64(mem_use), C.c_int(int(healthy)), C.c_int(len(gpu_usage)),
+                               C.c_int(len(gpu_usage)), g)
+
+    def add_pod(self, phase: str):
+        self.lib.klmh_add_pod(self.s, _b(phase))
+
+    def calculate_cluster_metrics(self):
+        out = binding.ClusterOut()
+        health = C.create_string_buffer(_CAP)
+        n = self.lib.klmh_calculate_cluster_metrics(self.s, C.byref(out), health, _CAP)
+        if n < 0:
+            self._err()
+        issues = []
+        for i in range(n):
+            b = C.create_string_buffer(_CAP)
+            self.lib.klmh_issue(self.s, i, b, _CAP)
+            issues.append(b.value.decode())
+        d = out.as_dict()
+        d.pop("health_status"); d.pop("issues")
+        d["HealthStatus"] = health.value.decode()
+        d["Issues"] = issues
+        return d
+
+    def add_fleet_uav(self, node_name: str, system_status: str, pct: float):
+        self.lib.klmh_add_fleet_uav(self.s, _b(node_name), _b(system_status), C.c_double(pct))
+
+    def healthy_uav_count(self) -> int:
+        n = self.lib.klmh_healthy_uav_count(self.s)
+        if n < 0:
+            self._err()
+        return n
+
+    def low_battery_uavs(self, threshold: float) -> List[str]:
+        n = self.lib.klmh_low_battery_uavs(self.s, C.c_double(threshold))
+        if n < 0:
+            self._err()
+        out = []
+        for i in range(n):
+            b = C.create_string_buffer(_CAP)
+            self.lib.klmh_name(self.s, i, b, _CAP)
+            out.append(b.value.decode())
+        return out

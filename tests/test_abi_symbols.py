@@ -53,3 +53,11 @@ def test_product_does_not_touch_oracle():
                 if re.search(r"klmo_\w+\s*\(|libklm_oracle|oracle_binding|controller_oracle|-lklm_oracle", text):
                     bad.append(os.path.join(dp, f))
     assert not bad, bad
+
+
+def test_host_layer_loads(pkg):
+    """libklm_host.so (C++ Controller / Manager mirror) loads and exports its C view."""
+    lib = pkg.hostbinding.load()
+    for name in ("klmh_open", "klmh_reconcile", "klmh_status", "klmh_calculate_cluster_metrics",
+                 "klmh_low_battery_uavs"):
+        assert hasattr(lib, name)

@@ -1,0 +1,103 @@
+"""GPU: the C++ host layer (k8s-llm-monitor_b200/host) that mirrors the reference's
+Controller and Manager around the C ABI, checked against the string-level oracle: same
+phase, node, UAV id, score and status message as internal/scheduler/controller.go would
+write, same ClusterMetrics issues and health strings as internal/metrics/manager.go."""
+import pytest
+
+import controller_oracle as co
+import helpers
+
+pytestmark = pytest.mark.gpu
+KATS = helpers.load_kats()
+
+
+@pytest.fixture(scope="module")
+def host(pkg, handle):
+    s = pkg.hostbinding.HostSession(handle)
+    yield s
+    s.close()
+
+
+def _add_items(host, items):
+    for it in items:
+        spec, st = it.get("spec", {}), it.get("status", {})
+        name = spec.get("node_name") if isinstance(spec.get("node_name"), str) else None
+        bat = spec.get("battery", {}).get("remaining_percent") if isinstance(spec.get("battery"), dict) else None
+        status = st.get("collection_status") if isinstance(st.get("collection_status"), str) else None
+        host.add_uav(name, spec.get("uav_id", ""), bat, status)
+
+
+def _add_request(host, raw_spec, phase=None):
+    spec = co.decode_spec(raw_spec, apimachinery_ints=False)
+    host.add_request(phase, spec.workload.name, spec.workload.namespace, spec.min_battery_percent,
+                     spec.preferred_nodes)
+    return spec
+
+
+@pytest.mark.parametrize("case", KATS, ids=[c["name"] for c in KATS])
+def test_controller_kats(host, case):
+    host.clear()
+    _add_items(host, case["items"])
+    spec = _add_request(host, case["spec"])
+    (got,) = host.reconcile()
+    want = co.process_request(spec, case["items"])
+    assert got["updated"]
+    assert (got["phase"], got["node"], got["uav"], got["score"], got["message"]) == \
+        (want.phase, want.assigned_node, want.assigned_uav, want.score, want.message)
+    assert got["message"] == case["expect"]["message"]
+
+
+def test_controller_batch_and_phase_gate(host):
+    """One reconcile over fixture A with every example request plus requests the phase gate
+    skips (controller.go:117-119): one GPU batch, statuses in request order."""
+    a = [c for c in KATS if c["name"].startswith("A/")]
+    host.clear()
+    _add_items(host, a[0]["items"])
+    specs = []
+    for c in a:
+        specs.append(_add_request(host, c["spec"]))
+    _add_request(host, a[0]["spec"], phase="Assigned")    # already handled -> skipped
+    _add_request(host, a[0]["spec"], phase="Pending")     # explicit Pending -> processed
+    _add_request(host, a[0]["spec"], phase="")            # empty phase -> processed
+    _add_request(host, {"workload": {"name": "x"}})        # namespace missing -> Failed
+    got = host.reconcile()
+    assert len(got) == len(a) + 4
+    for g, c, sp in zip(got, a, specs):
+        w = co.process_request(sp, c["items"])
+        assert (g["phase"], g["node"], g["score"], g["message"]) == (w.phase, w.assigned_node, w.score, w.message)
+    assert got[len(a)]["updated"] is False and got[len(a)]["phase"] == ""
+    for g in got[len(a) + 1:len(a) + 3]:
+        assert g["updated"] and g["node"] == a[0]["expect"]["node"]
+    assert got[-1]["phase"] == "Failed" and got[-1]["message"] == "workload name/namespace 不能为空"
+
+
+def test_manager_cluster_metrics(host):
+    G = 1 << 30
+    host.clear()
+    for cap, use, mu, healthy, gpus in [(4000, 1000, 1 * G, 1, [10.0, 50.0]), (4000, 2000, 2 * G, 1, []),
+                                        (8000, 3000, 3 * G, 1, [49.9]), (8000, 4000, 4 * G, 0, [])]:
+        host.add_node(cap, use, 8 * G, mu, healthy, gpus)
+    for ph in ("Running", "Running", "Pending"):
+        host.add_pod(ph)
+    m = host.calculate_cluster_metrics()
+    assert (m["total_nodes"], m["healthy_nodes"], m["total_pods"], m["running_pods"]) == (4, 3, 3, 2)
+    assert (m["total_gpus"], m["available_gpus"]) == (3, 2)
+    assert m["cpu_usage_rate"] == 10000 / 24000 * 100.0 and m["memory_usage_rate"] == 31.25
+    assert m["Issues"] == ["1 nodes are unhealthy"] and m["HealthStatus"] == "warning"   # manager.go:548, :563
+    host.clear()
+    host.add_node(1000, 950, G, G, 1)
+    m = host.calculate_cluster_metrics()
+    assert m["Issues"] == ["High CPU usage: 95.0%", "High memory usage: 100.0%"] and m["HealthStatus"] == "critical"
+    host.clear()
+    m = host.calculate_cluster_metrics()
+    assert m["Issues"] == [] and m["HealthStatus"] == "healthy" and m["total_nodes"] == 0
+
+
+def test_manager_fleet_scans(host):
+    host.clear()
+    fleet = [("n0", "OK", 19.9), ("n1", "WARNING", 20.0), ("n2", "OK", 5.0), ("n3", "OK", 50.0), ("n4", "ok", 1.0)]
+    for f in fleet:
+        host.add_fleet_uav(*f)
+    assert host.healthy_uav_count() == 3                      # exact match on "OK" (uav_metrics.go:207)
+    assert host.low_battery_uavs(20.0) == ["n0", "n2", "n4"]  # strict < (uav_metrics.go:226)
+    assert host.low_battery_uavs(0.0) == []
