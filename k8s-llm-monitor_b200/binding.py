@@ -95,6 +95,8 @@ SIGNATURES = {
     "klm_dev_fleet_scan": (C.c_int, [_I64, _P, _P, _F64, _P, _P, _P, _P]),
     "klm_dev_ring_ingest": (C.c_int, [_P, _P, _I64, _I32, _I32, _I64, _P, _P, _P]),
     "klm_dev_window_stats": (C.c_int, [_P, _P, _I32, _I32, _I64, _I64, _P, _P, _P, _P, _P]),
+    "klm_dev_window_stats_pipe": (C.c_int, [_P, _P, _I32, _I32, _I64, _I64, _P, _P, _P, _P, _P]),
+    "klm_dev_window_stats_warp": (C.c_int, [_P, _P, _I32, _I32, _I64, _I64, _P, _P, _P, _P, _P]),
     "klm_dev_window_stats_block": (C.c_int, [_P, _P, _I32, _I32, _I64, _I64, _P, _P, _P, _P, _P]),
 }
 
@@ -408,7 +410,8 @@ class Dev:
                                            _dp(series_ids), _dp(values), _stream_ptr(stream)))
 
     def window_stats(self, ring, seen, window: int, out_min, out_max, out_mean, out_p95,
-                     s0: int = 0, s1: Optional[int] = None, stream=None, block_variant: bool = False):
+                     s0: int = 0, s1: Optional[int] = None, stream=None, block_variant: bool = False,
+                     variant: Optional[str] = None):
         t = self.torch
         _need(ring, t.float32, "ring"); _need(seen, t.int32, "seen")
         _need(out_min, t.float32, "out_min"); _need(out_max, t.float32, "out_max")
@@ -416,6 +419,9 @@ class Dev:
         n_series, pitch = ring.shape
         if s1 is None:
             s1 = n_series
-        fn = self.lib.klm_dev_window_stats_block if block_variant else self.lib.klm_dev_window_stats
+        if block_variant:
+            variant = "block"
+        fn = {None: self.lib.klm_dev_window_stats, "pipe": self.lib.klm_dev_window_stats_pipe,
+              "warp": self.lib.klm_dev_window_stats_warp, "block": self.lib.klm_dev_window_stats_block}[variant]
         check(fn(_dp(ring), _dp(seen), window, pitch, s0, s1, _dp(out_min), _dp(out_max), _dp(out_mean),
                  _dp(out_p95), _stream_ptr(stream)))

@@ -3,6 +3,8 @@
 
 #include <stdint.h>
 
+#include "common.cuh"
+
 namespace klm {
 
 // Nearest-rank 95th percentile: 0-based index ceil(0.95 n) - 1 into the
@@ -18,6 +20,201 @@ __device__ __forceinline__ uint32_t f32_key(float x) {
 __device__ __forceinline__ float key_f32(uint32_t k) {
   return __uint_as_float((k & 0x80000000u) ? (k ^ 0x80000000u) : ~k);
 }
-#endif
+
+#define NEG_INF __int_as_float(0xff800000)
+#define POS_INF __int_as_float(0x7f800000)
+
+__device__ __forceinline__ float next_up(float x) {   // smallest float > x (x finite or -inf)
+  return key_f32(f32_key(x) + 1u);
+}
+__device__ __forceinline__ float next_down(float x) { // largest float < x (x finite or +inf)
+  return key_f32(f32_key(x) - 1u);
+}
+__device__ __forceinline__ int warp_max_i32(int v) { return __reduce_max_sync(0xffffffffu, v); }
+__device__ __forceinline__ uint32_t warp_max_u32(uint32_t v) { return __reduce_max_sync(0xffffffffu, v); }
+
+// c += (x >= p) as FSETP + predicated add (ptxas has no cheaper form on sm_100a: a
+// `set` instruction lowers to FSETP + SEL, and `c += (x >= p)` to FSETP + add + move)
+__device__ __forceinline__ void inc_if_ge(int& c, float x, float p) {
+  asm("{\n\t.reg .pred q;\n\tsetp.ge.f32 q, %1, %2;\n\t@q add.s32 %0, %0, 1;\n\t}"
+      : "+r"(c) : "f"(x), "f"(p));
+}
+__device__ __forceinline__ void inc_if_gt(int& c, float x, float p) {
+  asm("{\n\t.reg .pred q;\n\tsetp.gt.f32 q, %1, %2;\n\t@q add.s32 %0, %0, 1;\n\t}"
+      : "+r"(c) : "f"(x), "f"(p));
+}
+
+// -1 if a >= b else 0
+__device__ __forceinline__ int set_ge(float a, float b) {
+  int d;
+  asm("set.ge.s32.f32 %0, %1, %2;" : "=r"(d) : "f"(a), "f"(b));
+  return d;
+}
+__device__ __forceinline__ int set_gt(float a, float b) {
+  int d;
+  asm("set.gt.s32.f32 %0, %1, %2;" : "=r"(d) : "f"(a), "f"(b));
+  return d;
+}
+
+// Counts of list entries >= p1 and >= p2 (p1 <= p2) in one pass over the lane lists
+// ([entry][lane], every lane padded with -inf up to m8, a multiple of 8). The eight
+// loads of a batch are issued together so their latencies overlap. Returns c1 | c2 << 16.
+__device__ __forceinline__ uint32_t list_count2(const float* lst, int m8, float p1, float p2,
+                                                int& lane_c1, int& lane_c2) {
+  int a0 = 0, a1 = 0, b0 = 0, b1 = 0;
+#pragma unroll 1
+  for (int e = 0; e < m8; e += 8) {
+    float x[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) x[u] = lst[(e + u) * 32];
+#pragma unroll
+    for (int u = 0; u < 8; u += 2) {
+      inc_if_ge(a0, x[u], p1); inc_if_ge(a1, x[u + 1], p1);
+      inc_if_ge(b0, x[u], p2); inc_if_ge(b1, x[u + 1], p2);
+    }
+  }
+  lane_c1 = a0 + a1;
+  lane_c2 = b0 + b1;
+  return (uint32_t)warp_sum_i32(lane_c1 + (lane_c2 << 16));
+}
+
+// Largest list entry < b (or the largest entry if `open`), as a key (0 if none).
+__device__ __forceinline__ uint32_t list_max_below(const float* lst, int m8, float b, bool open) {
+  uint32_t m = 0;
+#pragma unroll 1
+  for (int e = 0; e < m8; e += 8) {
+    float x[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) x[u] = lst[(e + u) * 32];
+#pragma unroll
+    for (int u = 0; u < 8; ++u)
+      if (open || x[u] < b) m = max(m, f32_key(x[u]));
+  }
+  return warp_max_u32(m);
+}
+
+// Bitonic sort of 64 keys, descending, two per lane: element 2 * lane + r is k[r].
+__device__ __forceinline__ void sort64_desc(uint32_t& k0, uint32_t& k1, int lane) {
+#pragma unroll
+  for (int size = 2; size <= 64; size <<= 1) {
+    const bool desc = ((2 * lane) & size) == 0;  // size == 64: every lane descending
+#pragma unroll
+    for (int stride = size >> 1; stride > 0; stride >>= 1) {
+      if (stride == 1) {
+        const uint32_t hi = max(k0, k1), lo = min(k0, k1);
+        k0 = desc ? hi : lo;
+        k1 = desc ? lo : hi;
+      } else {
+        const int ls = stride >> 1;
+        const bool keepmax = (((lane & ls) == 0) == desc);
+        const uint32_t o0 = __shfl_xor_sync(0xffffffffu, k0, ls);
+        const uint32_t o1 = __shfl_xor_sync(0xffffffffu, k1, ls);
+        k0 = keepmax ? max(k0, o0) : min(k0, o0);
+        k1 = keepmax ? max(k1, o1) : min(k1, o1);
+      }
+    }
+  }
+}
+
+constexpr int kMaxCand = 64;  // candidates sorted exactly at the end of select_from_lists
+
+// The k-th largest of the elements held in the lane lists (lst = this lane's list, entry e at
+// lst[e * 32]; entries below 32 beyond the lane's count already hold -inf). `a` is a value
+// with count_ge(a) == total >= k (every listed element is >= a); mx is the window maximum.
+// `fin` is 64 floats of scratch owned by the warp. Counting passes test two pivots at a
+// time (first the sample hints, then interpolation on the counts) until <= 64 candidates
+// remain; each lane knows its share, an exclusive scan hands out slots, a bitonic sort
+// finishes. Brackets held wide by ties are peeled one distinct value at a time; after 12
+// passes plain key-space bisection bounds the work. Exact: the result is a listed element
+// whose rank has been counted.
+__device__ __forceinline__ float select_from_lists(float* lst, float* fin, int lane, int cnt,
+                                                   int total, int maxcnt, int k, float a, float mx,
+                                                   bool have_hints, float hint_lo, float hint_hi) {
+  const int m8 = (maxcnt + 7) & ~7;
+  // entries below 32 were pre-filled with -inf; pad the rare longer lists here
+  for (int e = max(cnt, 32); e < m8; ++e) lst[e * 32] = NEG_INF;
+  fin[lane] = NEG_INF;
+  fin[lane + 32] = NEG_INF;
+  __syncwarp();
+
+  // narrow [a, b): count_ge(a) = ca >= k > cb = count_ge(b); b = +inf with cb = 0 at first
+  float b = POS_INF;
+  int ca = total, cb = 0;
+  int lane_ca = cnt, lane_cb = 0;  // this lane's share of ca and cb
+  int it = 0;
+#pragma unroll 1
+  while (ca - cb > kMaxCand) {
+    const uint32_t ka = f32_key(a), kb = (cb == 0) ? f32_key(mx) + 1u : f32_key(b);
+    if (kb - ka <= 1u) return a;  // every candidate equals a
+    if (it >= 4 && it < 12) {
+      // ties keep the bracket wide: peel its largest distinct value
+      const float m = key_f32(list_max_below(lst, m8, b, cb == 0));
+      int l1, l2;
+      const int c = (int)(list_count2(lst, m8, m, m, l1, l2) & 0xffffu);
+      if (c >= k) return m;  // everything above m is >= b
+      b = m; cb = c; lane_cb = l1;
+    } else {
+      float p1, p2;
+      if (it == 0 && have_hints && hint_lo > a && hint_hi > hint_lo) {
+        p1 = hint_lo; p2 = hint_hi;       // sample order statistics around the 5 % point
+      } else {
+        // interpolate on the counts towards ranks k + dl and k - dl (value-linear inside)
+        const float hi = (cb == 0) ? mx : b;
+        const int span = ca - cb;
+        const int dl = min(max(span / 7, 12), 24);
+        const float inv = 1.0f / (float)span;
+        p1 = a + (hi - a) * ((float)max(ca - k - dl, 0) + 0.5f) * inv;
+        p2 = a + (hi - a) * ((float)min(ca - k + dl, span) - 0.5f) * inv;
+      }
+      // keep both pivots strictly inside (a, b) in key order, p1 <= p2
+      uint32_t k1 = f32_key(p1), k2 = f32_key(p2);
+      if (!(p1 == p1) || !(p2 == p2) || it >= 12 || k1 <= ka || k2 >= kb || k1 > k2) {
+        k1 = ka + max((kb - ka) / 3u, 1u);
+        k2 = max(kb - max((kb - ka) / 3u, 1u), k1);
+        if (it >= 12) k1 = k2 = ka + ((kb - ka) >> 1);  // plain bisection: bounded
+      }
+      p1 = key_f32(k1); p2 = key_f32(k2);
+      int l1, l2;
+      const uint32_t cc = list_count2(lst, m8, p1, p2, l1, l2);
+      const int c1 = (int)(cc & 0xffffu), c2 = (int)(cc >> 16);
+      if (c2 >= k) { a = p2; ca = c2; lane_ca = l2; }
+      else if (c1 >= k) { a = p1; ca = c1; lane_ca = l1; b = p2; cb = c2; lane_cb = l2; }
+      else { b = p1; cb = c1; lane_cb = l1; }
+    }
+    ++it;
+  }
+
+  // gather the <= 64 candidates in [a, b): each lane already knows how many of them it
+  // holds (lane_ca - lane_cb), so an exclusive scan gives it a private range of slots
+  const bool open = cb == 0;  // nothing lies at or above b (b may still be +inf)
+  const int mine = lane_ca - lane_cb;
+  int incl = mine;
+#pragma unroll
+  for (int off = 1; off < 32; off <<= 1) {
+    const int u = __shfl_up_sync(0xffffffffu, incl, off);
+    if (lane >= off) incl += u;
+  }
+  float* dst = fin + (incl - mine);
+  if (mine > 0) {
+#pragma unroll 1
+    for (int e = 0; e < m8; e += 8) {
+      float x[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) x[u] = lst[(e + u) * 32];
+#pragma unroll
+      for (int u = 0; u < 8; ++u)
+        if (x[u] >= a && (open || x[u] < b)) *dst++ = x[u];
+    }
+  }
+  __syncwarp();
+  const int kk = k - cb;       // rank wanted among the candidates, 1-based from the top
+  const float2 y = *reinterpret_cast<const float2*>(fin + 2 * lane);  // -inf beyond ca - cb
+  uint32_t k0 = f32_key(y.x), k1 = f32_key(y.y);
+  sort64_desc(k0, k1, lane);
+  const uint32_t pick = ((kk - 1) & 1) ? k1 : k0;
+  return key_f32(__shfl_sync(0xffffffffu, pick, (kk - 1) >> 1));
+}
+
+#endif  // __CUDACC__
 
 }  // namespace klm

@@ -31,11 +31,13 @@
 
 namespace klm {
 
+#ifndef KLM_WSW_MIN_BLOCKS
+#define KLM_WSW_MIN_BLOCKS 3
+#endif
 constexpr int kWswWarps = 4;               // warps (series) per CTA; registers are allocated in
                                            // units of 4 warps, so smaller CTAs waste them
 constexpr int kWswThreads = kWswWarps * 32;
 constexpr int kSampledMinRows = 7;         // below 7 full rows (896 samples) list everything
-constexpr int kMaxCand = 64;               // candidates sorted exactly at the end
 constexpr int kLaneCap = 64;               // per-lane list entries (wraps beyond: overflow -> bisect)
 constexpr int kLaneListBytes = kLaneCap * 128;  // [entry][lane] f32; power of two, self-aligned
 // shared memory: first the lane lists (8 KB per warp, each on an 8 KB boundary), then per
@@ -43,41 +45,6 @@ constexpr int kLaneListBytes = kLaneCap * 128;  // [entry][lane] f32; power of t
 constexpr int kWarpAux = 512;
 constexpr size_t kWswSmemBytes =
     (size_t)kWswWarps * (kLaneListBytes + kWarpAux) + kLaneListBytes;  // + alignment slack
-
-#define NEG_INF __int_as_float(0xff800000)
-#define POS_INF __int_as_float(0x7f800000)
-
-__device__ __forceinline__ float next_up(float x) {   // smallest float > x (x finite or -inf)
-  return key_f32(f32_key(x) + 1u);
-}
-__device__ __forceinline__ float next_down(float x) { // largest float < x (x finite or +inf)
-  return key_f32(f32_key(x) - 1u);
-}
-__device__ __forceinline__ int warp_max_i32(int v) { return __reduce_max_sync(0xffffffffu, v); }
-__device__ __forceinline__ uint32_t warp_max_u32(uint32_t v) { return __reduce_max_sync(0xffffffffu, v); }
-
-// c += (x >= p) as FSETP + predicated add (ptxas has no cheaper form on sm_100a: a
-// `set` instruction lowers to FSETP + SEL, and `c += (x >= p)` to FSETP + add + move)
-__device__ __forceinline__ void inc_if_ge(int& c, float x, float p) {
-  asm("{\n\t.reg .pred q;\n\tsetp.ge.f32 q, %1, %2;\n\t@q add.s32 %0, %0, 1;\n\t}"
-      : "+r"(c) : "f"(x), "f"(p));
-}
-__device__ __forceinline__ void inc_if_gt(int& c, float x, float p) {
-  asm("{\n\t.reg .pred q;\n\tsetp.gt.f32 q, %1, %2;\n\t@q add.s32 %0, %0, 1;\n\t}"
-      : "+r"(c) : "f"(x), "f"(p));
-}
-
-// -1 if a >= b else 0
-__device__ __forceinline__ int set_ge(float a, float b) {
-  int d;
-  asm("set.ge.s32.f32 %0, %1, %2;" : "=r"(d) : "f"(a), "f"(b));
-  return d;
-}
-__device__ __forceinline__ int set_gt(float a, float b) {
-  int d;
-  asm("set.gt.s32.f32 %0, %1, %2;" : "=r"(d) : "f"(a), "f"(b));
-  return d;
-}
 
 // if (x > lox) { lane_list[c / 128 mod 64] = x; c += 128; }
 // lb = 8 KB-aligned list base | lane * 4, so the slot address is (c & 0x1F80) | lb.
@@ -128,6 +95,13 @@ struct Window {
     return key_f32(lo);
   }
 
+  // append(x > lox) only: the retry after a pivot that listed fewer than k elements
+  __device__ __forceinline__ void append_pass(float lox, uint32_t lb, uint32_t& c) const {
+#pragma unroll
+    for (int i = 0; i < NE; ++i) append_if_gt(c, lb, v[i], lox);
+    append_if_gt(c, lb, tail, lox);
+  }
+
   // One pass over the registers: min / max / f64 sum of the valid samples, and append
   // (x > lox) to the lane's list. FULL: every row but the last is valid in every lane,
   // so the pass is straight-line code the scheduler can interleave freely.
@@ -173,68 +147,8 @@ struct Window {
   }
 };
 
-// Counts of list entries >= p1 and >= p2 (p1 <= p2) in one pass over the lane lists
-// ([entry][lane], every lane padded with -inf up to m8, a multiple of 8). The eight
-// loads of a batch are issued together so their latencies overlap. Returns c1 | c2 << 16.
-__device__ __forceinline__ uint32_t list_count2(const float* lst, int m8, float p1, float p2,
-                                                int& lane_c1, int& lane_c2) {
-  int a0 = 0, a1 = 0, b0 = 0, b1 = 0;
-#pragma unroll 1
-  for (int e = 0; e < m8; e += 8) {
-    float x[8];
-#pragma unroll
-    for (int u = 0; u < 8; ++u) x[u] = lst[(e + u) * 32];
-#pragma unroll
-    for (int u = 0; u < 8; u += 2) {
-      inc_if_ge(a0, x[u], p1); inc_if_ge(a1, x[u + 1], p1);
-      inc_if_ge(b0, x[u], p2); inc_if_ge(b1, x[u + 1], p2);
-    }
-  }
-  lane_c1 = a0 + a1;
-  lane_c2 = b0 + b1;
-  return (uint32_t)warp_sum_i32(lane_c1 + (lane_c2 << 16));
-}
-
-// Largest list entry < b (or the largest entry if `open`), as a key (0 if none).
-__device__ __forceinline__ uint32_t list_max_below(const float* lst, int m8, float b, bool open) {
-  uint32_t m = 0;
-#pragma unroll 1
-  for (int e = 0; e < m8; e += 8) {
-    float x[8];
-#pragma unroll
-    for (int u = 0; u < 8; ++u) x[u] = lst[(e + u) * 32];
-#pragma unroll
-    for (int u = 0; u < 8; ++u)
-      if (open || x[u] < b) m = max(m, f32_key(x[u]));
-  }
-  return warp_max_u32(m);
-}
-
-// Bitonic sort of 64 keys, descending, two per lane: element 2 * lane + r is k[r].
-__device__ __forceinline__ void sort64_desc(uint32_t& k0, uint32_t& k1, int lane) {
-#pragma unroll
-  for (int size = 2; size <= 64; size <<= 1) {
-    const bool desc = ((2 * lane) & size) == 0;  // size == 64: every lane descending
-#pragma unroll
-    for (int stride = size >> 1; stride > 0; stride >>= 1) {
-      if (stride == 1) {
-        const uint32_t hi = max(k0, k1), lo = min(k0, k1);
-        k0 = desc ? hi : lo;
-        k1 = desc ? lo : hi;
-      } else {
-        const int ls = stride >> 1;
-        const bool keepmax = (((lane & ls) == 0) == desc);
-        const uint32_t o0 = __shfl_xor_sync(0xffffffffu, k0, ls);
-        const uint32_t o1 = __shfl_xor_sync(0xffffffffu, k1, ls);
-        k0 = keepmax ? max(k0, o0) : min(k0, o0);
-        k1 = keepmax ? max(k1, o1) : min(k1, o1);
-      }
-    }
-  }
-}
-
 template <int NV>
-__global__ void __launch_bounds__(kWswThreads, 3)
+__global__ void __launch_bounds__(kWswThreads, KLM_WSW_MIN_BLOCKS)
 window_stats_warp_kernel(const float* __restrict__ ring, const uint32_t* __restrict__ seen,
                          int32_t window, int32_t pitch, int64_t s0, int64_t n_series,
                          float* __restrict__ out_min, float* __restrict__ out_max,
@@ -326,6 +240,8 @@ window_stats_warp_kernel(const float* __restrict__ ring, const uint32_t* __restr
   uint32_t bis_lo = f32_key(NEG_INF), bis_hi = 0, bis_first = 0;
   float lox = POS_INF;             // list predicate: x > lox (+inf: list nothing)
   float hint_lo = 0.f, hint_hi = 0.f;  // first pair of pivots (sample order statistics)
+  float lox_retry = POS_INF;       // lower pivot for one retry of the append (+inf: none)
+  bool tie_mode = false, retried = false;
   bool tie_hit = false;            // the heavy-tie test already found the answer
   float tie_val = 0.f;
   const bool want_p95 = out_p95 != nullptr;
@@ -365,10 +281,14 @@ window_stats_warp_kernel(const float* __restrict__ ring, const uint32_t* __restr
       const uint32_t mm = min(min(m[0], m[1]), min(m[2], m[3]));
       if (r == 1) t1 = mm; else if (r == 2) t2 = mm; else t3 = mm;
     }
-    const float V = key_f32(t3);
+    // pivot: the smallest "second largest" (about 10 % of the window above it; fewer than k
+    // with probability ~5 %, in which case the append is redone from the "third largest")
+    const float V = key_f32(t2);
     hint_lo = key_f32(t2);
     hint_hi = key_f32(t1);
-    if (t3 == t2) {
+    if (t3 < t2) lox_retry = next_down(key_f32(t3));
+    if (t1 == t2 || t2 == t3) {
+      tie_mode = true;
       // heavy tie at V: place k against the block of copies of V (two counts, one code copy)
       int c_ge = 0, c_gt = 0;
 #pragma unroll 1
@@ -380,8 +300,11 @@ window_stats_warp_kernel(const float* __restrict__ ring, const uint32_t* __restr
         lox = V;                       // the answer is above V: list the elements > V
       } else if (c_ge >= k) {
         tie_hit = true; tie_val = V;   // the answer is V itself
+      } else if (t3 < t2) {
+        lox = lox_retry;               // below V: list from the next sample statistic down
+        lox_retry = POS_INF;
       } else {
-        bisect = true; bis_hi = t3;    // the answer is below V
+        bisect = true; bis_hi = t2;    // the answer is below V
       }
     } else {
       lox = next_down(V);  // x > lox  <=>  x >= V
@@ -416,100 +339,30 @@ window_stats_warp_kernel(const float* __restrict__ ring, const uint32_t* __restr
     if (bisect) break;
     if (tie_hit) { result = tie_val; break; }
     if (mn == mx) { result = mx; break; }  // constant series
-    const int cnt = (int)(c128 >> 7);
-    const int total = warp_sum_i32(cnt);
-    const int maxcnt = warp_max_i32(cnt);
+    int cnt = (int)(c128 >> 7);
+    int total = warp_sum_i32(cnt);
+    int maxcnt = warp_max_i32(cnt);
     if (total < k && !sampled) { result = NEG_INF; break; }  // lox = -inf: only -inf samples are unlisted
+    if (total < k && !tie_mode && lox_retry != POS_INF) {
+      // the pivot was too high: redo the append (only) from the next sample statistic down
+#pragma unroll
+      for (int e = 0; e < 32; ++e) lst[e * 32] = NEG_INF;
+      lox = lox_retry;
+      c128 = 0;
+      w.append_pass(lox, lb, c128);
+      asm volatile("" ::: "memory");
+      cnt = (int)(c128 >> 7);
+      total = warp_sum_i32(cnt);
+      maxcnt = warp_max_i32(cnt);
+      retried = true;
+    }
     if (total < k || maxcnt > kLaneCap) {
       // unlucky pivot or list overflow: exact bisection over the registers
       bisect = true; bis_hi = f32_key(mx) + 1u; bis_first = 0u;
       break;
     }
-    const int m8 = (maxcnt + 7) & ~7;
-    // entries below 32 were pre-filled with -inf; pad the rare longer lists here
-    for (int e = max(cnt, 32); e < m8; ++e) lst[e * 32] = NEG_INF;
-    fin[lane] = NEG_INF;
-    fin[lane + 32] = NEG_INF;
-    __syncwarp();
-
-    // narrow [a, b): count_ge(a) = ca >= k > cb = count_ge(b); b = +inf with cb = 0 at first
-    float a = sampled ? next_up(lox) : mn, b = POS_INF;
-    int ca = total, cb = 0;
-    int lane_ca = cnt, lane_cb = 0;  // this lane's share of ca and cb
-    bool done = false;
-    int it = 0;
-#pragma unroll 1
-    while (ca - cb > kMaxCand) {
-      const uint32_t ka = f32_key(a), kb = (cb == 0) ? f32_key(mx) + 1u : f32_key(b);
-      if (kb - ka <= 1u) { result = a; done = true; break; }  // every candidate equals a
-      if (it >= 4 && it < 12) {
-        // ties keep the bracket wide: peel its largest distinct value
-        const float m = key_f32(list_max_below(lst, m8, b, cb == 0));
-        int l1, l2;
-        const int c = (int)(list_count2(lst, m8, m, m, l1, l2) & 0xffffu);
-        if (c >= k) { result = m; done = true; break; }  // everything above m is >= b
-        b = m; cb = c; lane_cb = l1;
-      } else {
-        float p1, p2;
-        if (it == 0 && sampled && hint_lo > a && hint_hi > hint_lo) {
-          p1 = hint_lo; p2 = hint_hi;       // sample order statistics around the 5 % point
-        } else {
-          // interpolate on the counts towards ranks k + dl and k - dl (value-linear inside)
-          const float hi = (cb == 0) ? mx : b;
-          const int span = ca - cb;
-          const int dl = min(max(span / 7, 12), 24);
-          const float inv = 1.0f / (float)span;
-          p1 = a + (hi - a) * ((float)max(ca - k - dl, 0) + 0.5f) * inv;
-          p2 = a + (hi - a) * ((float)min(ca - k + dl, span) - 0.5f) * inv;
-        }
-        // keep both pivots strictly inside (a, b) in key order, p1 <= p2
-        uint32_t k1 = f32_key(p1), k2 = f32_key(p2);
-        if (!(p1 == p1) || !(p2 == p2) || it >= 12 || k1 <= ka || k2 >= kb || k1 > k2) {
-          k1 = ka + max((kb - ka) / 3u, 1u);
-          k2 = max(kb - max((kb - ka) / 3u, 1u), k1);
-          if (it >= 12) k1 = k2 = ka + ((kb - ka) >> 1);  // plain bisection: bounded
-        }
-        p1 = key_f32(k1); p2 = key_f32(k2);
-        int l1, l2;
-        const uint32_t cc = list_count2(lst, m8, p1, p2, l1, l2);
-        const int c1 = (int)(cc & 0xffffu), c2 = (int)(cc >> 16);
-        if (c2 >= k) { a = p2; ca = c2; lane_ca = l2; }
-        else if (c1 >= k) { a = p1; ca = c1; lane_ca = l1; b = p2; cb = c2; lane_cb = l2; }
-        else { b = p1; cb = c1; lane_cb = l1; }
-      }
-      ++it;
-    }
-    if (done) break;
-
-    // gather the <= 64 candidates in [a, b): each lane already knows how many of them it
-    // holds (lane_ca - lane_cb), so an exclusive scan gives it a private range of slots
-    const bool open = cb == 0;  // nothing lies at or above b (b may still be +inf)
-    const int mine = lane_ca - lane_cb;
-    int incl = mine;
-#pragma unroll
-    for (int off = 1; off < 32; off <<= 1) {
-      const int u = __shfl_up_sync(0xffffffffu, incl, off);
-      if (lane >= off) incl += u;
-    }
-    float* dst = fin + (incl - mine);
-    if (mine > 0) {
-#pragma unroll 1
-      for (int e = 0; e < m8; e += 8) {
-        float x[8];
-#pragma unroll
-        for (int u = 0; u < 8; ++u) x[u] = lst[(e + u) * 32];
-#pragma unroll
-        for (int u = 0; u < 8; ++u)
-          if (x[u] >= a && (open || x[u] < b)) *dst++ = x[u];
-      }
-    }
-    __syncwarp();
-    const int kk = k - cb;       // rank wanted among the candidates, 1-based from the top
-    const float2 y = *reinterpret_cast<const float2*>(fin + 2 * lane);  // -inf beyond ca - cb
-    uint32_t k0 = f32_key(y.x), k1 = f32_key(y.y);
-    sort64_desc(k0, k1, lane);
-    const uint32_t pick = ((kk - 1) & 1) ? k1 : k0;
-    result = key_f32(__shfl_sync(0xffffffffu, pick, (kk - 1) >> 1));
+    result = select_from_lists(lst, fin, lane, cnt, total, maxcnt, k, sampled ? next_up(lox) : mn, mx,
+                               retried, hint_lo, hint_hi);
   } while (false);
   if (bisect) result = w.select_bisect(bis_lo, bis_hi, k, bis_first);
   if (lane == 0) out_p95[o] = result;
@@ -546,7 +399,7 @@ static int launch_warp(const float* ring, const uint32_t* seen, int32_t window, 
 int launch_window_stats_warp(const float* ring, const uint32_t* seen, int32_t window,
                              int32_t pitch, int64_t s0, int64_t s1, float* out_min,
                              float* out_max, double* out_mean, float* out_p95, cudaStream_t st) {
-  static_assert(3 * (kWswSmemBytes + 1024) <= 227 * 1024, "three CTAs per SM must fit");
+  static_assert(KLM_WSW_MIN_BLOCKS * (kWswSmemBytes + 1024) <= 227 * 1024, "the CTAs per SM must fit");
   const int64_t n = s1 - s0;
   if (window <= 8 * 128) return launch_warp<8>(ring, seen, window, pitch, s0, n, out_min, out_max, out_mean, out_p95, st);
   if (window <= 16 * 128) return launch_warp<16>(ring, seen, window, pitch, s0, n, out_min, out_max, out_mean, out_p95, st);

@@ -155,9 +155,9 @@ def test_full_c2_properties(dev, pkg):
 
 
 @pytest.mark.parametrize("t", [100, 1000, 3600, 4096])
-def test_warp_and_block_variants_agree(dev, t):
-    """The register-resident warp kernel (default for windows <= 4096) and the
-    shared-memory block kernel must give identical min/max/p95 and matching means."""
+def test_k7_variants_agree(dev, t):
+    """The pipelined kernel (default for windows <= 4096), the register-resident warp kernel
+    and the shared-memory block kernel must all match the oracle."""
     import torch
     rng = np.random.default_rng(1000 + t)
     s = 400
@@ -168,13 +168,10 @@ def test_warp_and_block_variants_agree(dev, t):
     seen_np = rng.integers(0, 2 * t, size=s)
     seen_np[:3] = [0, 1, t]
     seen = torch.from_numpy(seen_np.astype(np.int32)).cuda()
-    res = []
-    for block in (False, True):
+    want = ob.window_stats(ring.cpu().numpy(), seen_np.astype(np.uint32), t, pitch)
+    for variant in ("pipe", "warp", "block"):
         o = {k: torch.full((s,), -123.0, dtype=torch.float64 if k == "mean" else torch.float32, device="cuda")
              for k in ("min", "max", "mean", "p95")}
-        dev.window_stats(ring, seen, t, o["min"], o["max"], o["mean"], o["p95"], block_variant=block)
+        dev.window_stats(ring, seen, t, o["min"], o["max"], o["mean"], o["p95"], variant=variant)
         torch.cuda.synchronize()
-        res.append({k: v.cpu().numpy() for k, v in o.items()})
-    want = ob.window_stats(ring.cpu().numpy(), seen_np.astype(np.uint32), t, pitch)
-    check_stats(res[0], want, "warp")
-    check_stats(res[1], want, "block")
+        check_stats({k: v.cpu().numpy() for k, v in o.items()}, want, variant)
