@@ -321,7 +321,8 @@ def run_ours(args):
                    **extra},
         "clocks": clocks,
         "e2e": {"value": e2e_value, "unit": METRIC[wl][1], "h2d_bytes_per_step": e2e["h2d"],
-                "d2h_bytes_per_step": e2e["d2h"], "timing": "host wall clock around synchronous klm_* calls"},
+                "d2h_bytes_per_step": e2e["d2h"], "timing": "host wall clock around synchronous klm_* calls",
+                "calls_per_step": "klm_collect + klm_nodes_set + klm_schedule_batch" if weak else "klm_nodes_set + klm_schedule_batch"},
         "gpu_launches": n_launch,
         "roofline": {"bound": "hbm", "kernel": "window_stats" if weak else "node_best+schedule",
                      "achieved": achieved, "peak": pk["hbm_gbs"], "unit": "GB/s",
@@ -329,8 +330,8 @@ def run_ours(args):
                      "peak_source": pk_src, "algorithmic_bytes_per_launch": k7_bytes,
                      "avg_launch_ms": kern_ms,
                      # dram__bytes_read.sum + dram__bytes_write.sum of one K7 launch at c2, from the
-                     # ncu --set full capture summarised in profiles/r01_k7_warp_v2g_ncu_summary.txt
-                     "traffic": 378.911e6 if (wl == "c2" and world >= 1) else None},
+                     # ncu --set full capture summarised in profiles/r01_k7_warp_v2h_ncu_summary.txt
+                     "traffic": 378.747e6 if (wl == "c2" and world >= 1) else None},
     }
     if rank == 0:
         if world == 1 and not args.no_cpu:
@@ -362,20 +363,24 @@ def run_e2e(pkg, wl, cid, shp, rank, world, args, env):
             bat, flags, mb, off = pin(env["bat"]), pin(env["flags"]), pin(env["mb"]), pin(env["off"])
             ids = pin(env["ids"] if env["ids"].size else np.zeros(1, np.int32))
             snap = {k: pin(v) for k, v in env["snap"].items()}
-            ccols = [snap[k] for k in ("cpu_capacity", "cpu_usage", "memory_capacity", "memory_usage",
-                                       "gpu_count", "healthy", "gpu_usage", "pod_running")]
-            rcols = [snap[k] for k in ("cpu_capacity", "cpu_usage", "memory_capacity", "memory_usage",
-                                       "disk_capacity", "disk_allocatable")]
+            snap_h = dict(snap)
+            snap_h["gpu_usage"] = np.zeros(0)   # the C2 / C3 nodes carry no GPUs
+            outs = {"cpu_rate": pin(np.empty(N)), "memory_rate": pin(np.empty(N)),
+                    "disk_usage": pin(np.empty(N, np.int64)), "disk_rate": pin(np.empty(N)),
+                    "under_pressure": pin(np.empty(N, np.uint8)), "min": pin(np.empty(S, np.float32)),
+                    "max": pin(np.empty(S, np.float32)), "mean": pin(np.empty(S)),
+                    "p95": pin(np.empty(S, np.float32))}
+            col_keys = ("cpu_capacity", "cpu_usage", "memory_capacity", "memory_usage", "gpu_count", "healthy",
+                        "pod_running", "disk_capacity", "disk_allocatable")
             h2d = tick.nbytes + bat.nbytes + flags.nbytes + mb.nbytes + off.nbytes + env["ids"].nbytes + \
-                sum(c.nbytes for c in ccols) + sum(c.nbytes for c in rcols)
+                sum(snap[k].nbytes for k in col_keys)
             d2h = S * 20 + 104 + N * 33 + mb.size * 12
 
             def step():
-                h.ring_ingest_tick(ticks_h[e2e_tick[0] % ticks_h.shape[0]])
+                # the metrics manager's cycle (Manager.Collect): one call, one synchronisation
+                h.collect(ticks_h[e2e_tick[0] % ticks_h.shape[0]], snap_h, outs)
                 e2e_tick[0] += 1
-                h.ring_stats()
-                h.node_rates(*rcols)
-                h.cluster_aggregate(*ccols)
+                # the scheduler's reconcile: snapshot + batch
                 h.nodes_set(bat, flags)
                 h.schedule_batch(mb, off, ids)
         else:

@@ -197,6 +197,36 @@ int klm_ring_load(klm_handle* h, int64_t s0, int64_t s1, int32_t count,
 int klm_ring_stats(klm_handle* h, int64_t s0, int64_t s1, float* out_min,
                    float* out_max, double* out_mean, float* out_p95);
 
+/* One collection cycle in one call — Manager.Collect (manager.go:195-319): append the
+ * tick to the ring (if tick_values != NULL), compute the window statistics of every
+ * series, the per-node rates (node_metrics.go:116-140) and calculateClusterMetrics
+ * (manager.go:493-565) from the same node columns. Everything is enqueued on the
+ * handle's stream and synchronised once, so a cycle costs one host round trip
+ * instead of four. Any output pointer may be NULL; disk_capacity / disk_allocatable
+ * may be NULL (rates then use 0). Results are identical to the separate calls. */
+typedef struct klm_collect_in {
+  const float* tick_values;        /* [n_series] or NULL: no ingest this cycle */
+  const klm_node_cols* nodes;      /* may be NULL with n_nodes == 0 */
+  int64_t n_nodes;
+  const int64_t* disk_capacity;    /* [n_nodes] or NULL */
+  const int64_t* disk_allocatable; /* [n_nodes] or NULL */
+  const uint8_t* pod_running;      /* [n_pods] */
+  int64_t n_pods;
+} klm_collect_in;
+typedef struct klm_collect_out {
+  klm_cluster_out* cluster;
+  double* cpu_rate;      /* [n_nodes] */
+  double* memory_rate;   /* [n_nodes] */
+  int64_t* disk_usage;   /* [n_nodes] */
+  double* disk_rate;     /* [n_nodes] */
+  uint8_t* under_pressure; /* [n_nodes] */
+  float* win_min;        /* [n_series] */
+  float* win_max;
+  double* win_mean;
+  float* win_p95;
+} klm_collect_out;
+int klm_collect(klm_handle* h, const klm_collect_in* in, const klm_collect_out* out);
+
 /* ================================================= device-pointer layer */
 /* All pointers below are DEVICE pointers; nothing is allocated or freed;
  * work is enqueued on `stream` and the call returns without synchronising.

@@ -51,6 +51,19 @@ class ClusterOut(C.Structure):  # klm_cluster_out
         return {name: getattr(self, name) for name, _ in self._fields_}
 
 
+class CollectIn(C.Structure):  # klm_collect_in
+    _fields_ = [("tick_values", C.c_void_p), ("nodes", C.POINTER(NodeCols)), ("n_nodes", C.c_int64),
+                ("disk_capacity", C.c_void_p), ("disk_allocatable", C.c_void_p),
+                ("pod_running", C.c_void_p), ("n_pods", C.c_int64)]
+
+
+class CollectOut(C.Structure):  # klm_collect_out
+    _fields_ = [("cluster", C.POINTER(ClusterOut)), ("cpu_rate", C.c_void_p), ("memory_rate", C.c_void_p),
+                ("disk_usage", C.c_void_p), ("disk_rate", C.c_void_p), ("under_pressure", C.c_void_p),
+                ("win_min", C.c_void_p), ("win_max", C.c_void_p), ("win_mean", C.c_void_p),
+                ("win_p95", C.c_void_p)]
+
+
 CLUSTER_OUT_DTYPE = np.dtype([
     ("total_nodes", "<i8"), ("healthy_nodes", "<i8"), ("total_pods", "<i8"), ("running_pods", "<i8"),
     ("total_cpu", "<i8"), ("used_cpu", "<i8"), ("total_memory", "<i8"), ("used_memory", "<i8"),
@@ -78,6 +91,7 @@ SIGNATURES = {
     "klm_ring_ingest_tick": (C.c_int, [_P, _P]),
     "klm_ring_load": (C.c_int, [_P, _I64, _I64, _I32, _P]),
     "klm_ring_stats": (C.c_int, [_P, _I64, _I64, _P, _P, _P, _P]),
+    "klm_collect": (C.c_int, [_P, C.POINTER(CollectIn), C.POINTER(CollectOut)]),
     "klm_dev_node_best_scratch_bytes": (_I64, []),
     "klm_dev_node_best": (C.c_int, [_P, _P, _I64, _I64, _P, _P, _P]),
     "klm_dev_node_best_static_max_nodes": (_I64, []),
@@ -254,6 +268,36 @@ class Handle:
         if d.ndim != 2:
             raise ValueError("data must be [rows, count]")
         check(self._lib.klm_ring_load(self._h, s0, s0 + d.shape[0], d.shape[1], _ptr(d)))
+
+    def collect(self, tick_values, snap: dict, out: Optional[dict] = None) -> dict:
+        """One Manager.Collect cycle (klm_collect): tick ingest + window stats + node rates +
+        cluster aggregate, one synchronisation. `snap` holds the node / pod columns
+        (cluster_snapshot layout); `out` may carry preallocated (e.g. pinned) arrays."""
+        cols = [_np(snap[k], dt) for k, dt in (("cpu_capacity", np.int64), ("cpu_usage", np.int64),
+                                               ("memory_capacity", np.int64), ("memory_usage", np.int64),
+                                               ("gpu_count", np.int32), ("healthy", np.uint8))]
+        gu = _np(snap.get("gpu_usage", np.zeros(0)), np.float64)
+        pr = _np(snap["pod_running"], np.uint8)
+        dc = None if snap.get("disk_capacity") is None else _np(snap["disk_capacity"], np.int64)
+        da = None if snap.get("disk_allocatable") is None else _np(snap["disk_allocatable"], np.int64)
+        tick = None if tick_values is None else _np(tick_values, np.float32)
+        n, s = cols[0].size, self._ring_shape[0]
+        nc = NodeCols(*[a.ctypes.data if a.size else None for a in cols], gu.ctypes.data if gu.size else None,
+                      gu.size)
+        o = out if out is not None else {}
+        o.setdefault("cpu_rate", np.empty(n, np.float64)); o.setdefault("memory_rate", np.empty(n, np.float64))
+        o.setdefault("disk_usage", np.empty(n, np.int64)); o.setdefault("disk_rate", np.empty(n, np.float64))
+        o.setdefault("under_pressure", np.empty(n, np.uint8))
+        o.setdefault("min", np.empty(s, np.float32)); o.setdefault("max", np.empty(s, np.float32))
+        o.setdefault("mean", np.empty(s, np.float64)); o.setdefault("p95", np.empty(s, np.float32))
+        cl = ClusterOut()
+        cin = CollectIn(_ptr(tick), C.pointer(nc), n, _ptr(dc), _ptr(da), _ptr(pr) if pr.size else None, pr.size)
+        cout = CollectOut(C.pointer(cl), *[_ptr(o[k]) for k in ("cpu_rate", "memory_rate", "disk_usage",
+                                                                  "disk_rate", "under_pressure", "min", "max",
+                                                                  "mean", "p95")])
+        check(self._lib.klm_collect(self._h, C.byref(cin), C.byref(cout)))
+        o["cluster"] = cl.as_dict()
+        return o
 
     def ring_stats(self, s0: int = 0, s1: Optional[int] = None, p95: bool = True) -> dict:
         if s1 is None:

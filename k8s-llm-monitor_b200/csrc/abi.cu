@@ -560,3 +560,113 @@ extern "C" int klm_ring_stats(klm_handle* h, int64_t s0, int64_t s1, float* out_
   if (out_p95) KLM_TRY(d2h(out_p95, d_p95, (size_t)rows * 4, st));
   return sync(st);
 }
+
+// ------------------------------------------------------------- collect cycle
+
+extern "C" int klm_collect(klm_handle* h, const klm_collect_in* in, const klm_collect_out* out) {
+  KLM_ENTER(h);
+  if (!in || !out || in->n_nodes < 0 || in->n_pods < 0 || (in->n_nodes > 0 && !in->nodes) ||
+      (in->n_pods > 0 && !in->pod_running)) {
+    set_error("klm_collect: bad argument");
+    return KLM_EINVAL;
+  }
+  cudaStream_t st = h->stream;
+  const bool want_win = out->win_min || out->win_max || out->win_mean || out->win_p95;
+  if ((in->tick_values || want_win) && h->n_series <= 0) {
+    set_error("klm_collect: no ring; call klm_ring_create first");
+    return KLM_ESTATE;
+  }
+  // ---- ring: tick ingest, then the window statistics of every series
+  const int64_t S = h->n_series;
+  float *d_min = nullptr, *d_max = nullptr, *d_p95 = nullptr;
+  double* d_mean = nullptr;
+  if (in->tick_values) {
+    KLM_TRY(h->ing_vals.ensure((size_t)S * 4));
+    KLM_TRY(h2d(h->ing_vals.p, in->tick_values, (size_t)S * 4, st));
+    KLM_TRY(klm_dev_ring_ingest(h->ring.as<float>(), h->seen.as<uint32_t>(), S, h->window, h->pitch, S,
+                                nullptr, h->ing_vals.as<float>(), st));
+  }
+  if (want_win) {
+    const size_t c4 = align256((size_t)S * 4), c8 = align256((size_t)S * 8);
+    KLM_TRY(h->stats_out.ensure(3 * c4 + c8));
+    char* o = h->stats_out.as<char>();
+    d_min = reinterpret_cast<float*>(o);
+    d_max = reinterpret_cast<float*>(o + c4);
+    d_p95 = reinterpret_cast<float*>(o + 2 * c4);
+    d_mean = reinterpret_cast<double*>(o + 3 * c4);
+    KLM_TRY(klm_dev_window_stats(h->ring.as<float>(), h->seen.as<uint32_t>(), h->window, h->pitch, 0, S,
+                                 d_min, d_max, d_mean, out->win_p95 ? d_p95 : nullptr, st));
+  }
+  // ---- node snapshot: one upload of the columns serves the rates and the aggregate
+  const int64_t n = in->n_nodes, np = in->n_pods;
+  const size_t col8 = align256((size_t)n * 8), col4 = align256((size_t)n * 4), col1 = align256((size_t)n);
+  klm_node_cols d{};
+  const bool want_rates = out->cpu_rate || out->memory_rate || out->disk_usage || out->disk_rate ||
+                          out->under_pressure;
+  char* rout = nullptr;
+  if (n > 0 || np > 0) {
+    const klm_node_cols* c = in->nodes;
+    const int64_t ng = (n > 0 && c) ? c->n_gpu_usage : 0;
+    if (n > 0 && (!c->cpu_capacity || !c->cpu_usage || !c->memory_capacity || !c->memory_usage ||
+                  !c->gpu_count || !c->healthy || ng < 0 || (ng > 0 && !c->gpu_usage))) {
+      set_error("klm_collect: null node column");
+      return KLM_EINVAL;
+    }
+    KLM_TRY(h->agg_cols.ensure(6 * col8 + col4 + col1 + 256));
+    KLM_TRY(h->agg_pods.ensure((size_t)np + 256));
+    KLM_TRY(h->agg_gpu.ensure((size_t)ng * 8 + 256));
+    char* base = h->agg_cols.as<char>();
+    d.cpu_capacity = reinterpret_cast<int64_t*>(base);
+    d.cpu_usage = reinterpret_cast<int64_t*>(base + col8);
+    d.memory_capacity = reinterpret_cast<int64_t*>(base + 2 * col8);
+    d.memory_usage = reinterpret_cast<int64_t*>(base + 3 * col8);
+    int64_t* d_dcap = reinterpret_cast<int64_t*>(base + 4 * col8);
+    int64_t* d_dalloc = reinterpret_cast<int64_t*>(base + 5 * col8);
+    d.gpu_count = reinterpret_cast<int32_t*>(base + 6 * col8);
+    d.healthy = reinterpret_cast<uint8_t*>(base + 6 * col8 + col4);
+    d.gpu_usage = h->agg_gpu.as<double>();
+    d.n_gpu_usage = ng;
+    if (n > 0) {
+      KLM_TRY(h2d((void*)d.cpu_capacity, c->cpu_capacity, (size_t)n * 8, st));
+      KLM_TRY(h2d((void*)d.cpu_usage, c->cpu_usage, (size_t)n * 8, st));
+      KLM_TRY(h2d((void*)d.memory_capacity, c->memory_capacity, (size_t)n * 8, st));
+      KLM_TRY(h2d((void*)d.memory_usage, c->memory_usage, (size_t)n * 8, st));
+      KLM_TRY(h2d((void*)d.gpu_count, c->gpu_count, (size_t)n * 4, st));
+      KLM_TRY(h2d((void*)d.healthy, c->healthy, (size_t)n, st));
+      KLM_TRY(h2d((void*)d.gpu_usage, c->gpu_usage, (size_t)ng * 8, st));
+      if (in->disk_capacity) KLM_TRY(h2d(d_dcap, in->disk_capacity, (size_t)n * 8, st));
+      if (in->disk_allocatable) KLM_TRY(h2d(d_dalloc, in->disk_allocatable, (size_t)n * 8, st));
+    }
+    KLM_TRY(h2d(h->agg_pods.p, in->pod_running, (size_t)np, st));
+    if (want_rates && n > 0) {
+      KLM_TRY(h->rate_out.ensure(5 * col8));
+      rout = h->rate_out.as<char>();
+      KLM_TRY(klm_dev_node_rates(n, d.cpu_capacity, d.cpu_usage, d.memory_capacity, d.memory_usage,
+                                 in->disk_capacity ? d_dcap : nullptr,
+                                 in->disk_allocatable ? d_dalloc : nullptr,
+                                 reinterpret_cast<double*>(rout), reinterpret_cast<double*>(rout + col8),
+                                 reinterpret_cast<int64_t*>(rout + 2 * col8),
+                                 reinterpret_cast<double*>(rout + 3 * col8),
+                                 reinterpret_cast<uint8_t*>(rout + 4 * col8), st));
+    }
+  }
+  if (out->cluster) {
+    KLM_TRY(klm_dev_cluster_aggregate(&d, n, h->agg_pods.as<uint8_t>(), np,
+                                      h->agg_out.as<klm_cluster_out>(), h->agg_scratch.p, st));
+    KLM_TRY(d2h(out->cluster, h->agg_out.p, sizeof(klm_cluster_out), st));
+  }
+  if (rout) {
+    if (out->cpu_rate) KLM_TRY(d2h(out->cpu_rate, rout, (size_t)n * 8, st));
+    if (out->memory_rate) KLM_TRY(d2h(out->memory_rate, rout + col8, (size_t)n * 8, st));
+    if (out->disk_usage) KLM_TRY(d2h(out->disk_usage, rout + 2 * col8, (size_t)n * 8, st));
+    if (out->disk_rate) KLM_TRY(d2h(out->disk_rate, rout + 3 * col8, (size_t)n * 8, st));
+    if (out->under_pressure) KLM_TRY(d2h(out->under_pressure, rout + 4 * col8, (size_t)n, st));
+  }
+  if (want_win) {
+    if (out->win_min) KLM_TRY(d2h(out->win_min, d_min, (size_t)S * 4, st));
+    if (out->win_max) KLM_TRY(d2h(out->win_max, d_max, (size_t)S * 4, st));
+    if (out->win_mean) KLM_TRY(d2h(out->win_mean, d_mean, (size_t)S * 8, st));
+    if (out->win_p95) KLM_TRY(d2h(out->win_p95, d_p95, (size_t)S * 4, st));
+  }
+  return sync(st);
+}

@@ -286,7 +286,11 @@ window_stats_pipe_kernel(const float* __restrict__ ring, const uint32_t* __restr
         asm volatile("ld.acquire.cta.shared.u32 %0, [%1];" : "=r"(d) : "r"(drained_s + 4 * slot) : "memory");
         if (d >= round) break;
         __nanosleep(20);
-        if (clock64() - t0 > kSpinCycles) { const uint32_t bar = drained_s + 4 * slot, parity = round; KLM_PIPE_FAIL(300 + (int)q); }
+        if (clock64() - t0 > kSpinCycles) {
+          const uint32_t bar = drained_s + 4 * slot, parity = round;
+          (void)bar; (void)parity;
+          KLM_PIPE_FAIL(300 + (int)q);
+        }
       }
     }
     mbar_wait_warp(full_s + 8 * slot, round & 1u, lane, 200 + (int)q);

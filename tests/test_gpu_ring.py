@@ -175,3 +175,30 @@ def test_k7_variants_agree(dev, t):
         dev.window_stats(ring, seen, t, o["min"], o["max"], o["mean"], o["p95"], variant=variant)
         torch.cuda.synchronize()
         check_stats({k: v.cpu().numpy() for k, v in o.items()}, want, variant)
+
+
+def test_collect_cycle_matches_separate_calls(handle, pkg):
+    """klm_collect (one Manager.Collect cycle in one call) == ingest + stats + rates +
+    aggregate done separately, and == the oracle."""
+    rng = np.random.default_rng(77)
+    s, t, n, p = 700, 1200, 333, 2111
+    rows = distributions(rng, s, t)
+    snap = pkg.synth.cluster_snapshot(2, n, p, gpus_per_node=1)
+    ring = np.ascontiguousarray(rows)
+    seen = np.full(s, t - 1, np.uint32)
+    handle.ring_create(s, t)
+    handle.ring_load(0, rows[:, : t - 1])
+    ring_o = np.zeros((s, t), np.float32)
+    ring_o[:, : t - 1] = rows[:, : t - 1]
+    for cycle in range(3):
+        tick = (rng.random(s) * 100).astype(np.float32)
+        got = handle.collect(tick, snap)
+        ob.ring_ingest(ring_o, seen, t, tick)
+        check_stats(got, ob.window_stats(ring_o, seen, t), f"collect cycle {cycle}")
+        assert got["cluster"] == ob.cluster_aggregate(snap)
+        want = ob.node_rates(snap)
+        for k in want:
+            assert np.array_equal(got[k], want[k]), k
+    again = handle.collect(None, snap)      # no tick: statistics unchanged
+    for k in ("min", "max", "p95", "mean"):
+        assert np.array_equal(again[k], got[k])
