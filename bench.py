@@ -225,10 +225,30 @@ def run_ours(args):
         best = torch.empty(2, dtype=torch.int64, device="cuda")
         o_idx = torch.empty(rl, dtype=torch.int32, device="cuda")
         o_score = torch.empty(rl, dtype=torch.float64, device="cuda")
+        peer = None
         if wl == "c5" and world > 1:
             g_idx = torch.empty(world * rl, dtype=torch.int32, device="cuda")
             g_score = torch.empty(world * rl, dtype=torch.float64, device="cuda")
             m_idx, m_score = torch.empty_like(o_idx), torch.empty_like(o_score)
+            if not args.nccl_merge:
+                # partial winners live in symmetric memory: K3 reads the peers' arrays in place
+                # over NVLink and merges only this rank's slice of the requests
+                try:
+                    import torch.distributed._symmetric_memory as symm_mem
+                    o_idx = symm_mem.empty(rl, dtype=torch.int32, device="cuda")
+                    o_score = symm_mem.empty(rl, dtype=torch.float64, device="cuda")
+                    h_i = symm_mem.rendezvous(o_idx, dist.group.WORLD)
+                    h_s = symm_mem.rendezvous(o_score, dist.group.WORLD)
+                    q0, q1 = R * rank // world, R * (rank + 1) // world
+                    p_idx = torch.empty(q1 - q0, dtype=torch.int32, device="cuda")
+                    p_score = torch.empty(q1 - q0, dtype=torch.float64, device="cuda")
+                    k3p = dev.prebind("merge_partials_peer", [int(x) for x in h_i.buffer_ptrs],
+                                      [int(x) for x in h_s.buffer_ptrs], q0, q1, p_idx, p_score)
+                    peer = (h_i, k3p)
+                except Exception as e:  # fall back to the NCCL all-gather + K3 path, and say so
+                    extra["peer_merge_unavailable"] = str(e)[:200]
+            extra["merge"] = ("K3 over symmetric (peer) memory, result sharded by request" if peer
+                              else "NCCL all-gather + K3, result replicated")
         units = R  # whole job
         k1 = dev.prebind("node_best", d_bat, d_flags, best, node_base=n0)                     # K1
         k2 = dev.prebind("schedule", d_bat, d_flags, best, d_mb, d_off, d_ids, o_idx, o_score, node_base=n0)  # K2
@@ -245,13 +265,37 @@ def run_ours(args):
                 e1.record()
                 k7_events.append((e0, e1))
             launches[0] += 2
-            if wl == "c5" and world > 1:
+            if peer is not None:
+                peer[0].barrier()   # every rank's partials are complete
+                peer[1]()           # K3 over peer memory
+                peer[0].barrier()   # nobody still reads the buffers the next step overwrites
+                launches[0] += 1
+            elif wl == "c5" and world > 1:
                 dist.all_gather_into_tensor(g_idx, o_idx)
                 dist.all_gather_into_tensor(g_score, o_score)
                 dev.merge_partials(g_idx.view(world, rl), g_score.view(world, rl), m_idx, m_score)  # K3
                 launches[0] += 1
 
         k7_bytes = 9 * (n1 - n0) + int(24 * rl + 13 * ids.size)
+
+    if wl == "c5" and world > 1:
+        # self-check (untimed): this rank's merged slice == the unsharded kernels on the whole table
+        step(False)
+        torch.cuda.synchronize()
+        fb, ff = cu(bat), cu(flags)
+        fbest = torch.empty(2, dtype=torch.int64, device="cuda")
+        fi, fs = torch.empty(rl, dtype=torch.int32, device="cuda"), torch.empty(rl, dtype=torch.float64, device="cuda")
+        dev.node_best(fb, ff, fbest)
+        dev.schedule(fb, ff, fbest, d_mb, d_off, d_ids, fi, fs)
+        torch.cuda.synchronize()
+        if peer is not None:
+            ok = bool(torch.equal(p_idx, fi[q0:q1]) and torch.equal(p_score, fs[q0:q1]))
+        else:
+            ok = bool(torch.equal(m_idx, fi) and torch.equal(m_score, fs))
+        extra["sharded_equals_unsharded"] = ok
+        if not ok:
+            raise SystemExit("c5: node-sharded result differs from the unsharded one")
+        del fb, ff, fi, fs
 
     # L2 hygiene: c2/c3 inputs (374 MB / 4.6 GB) exceed the 126 MB L2; c4/c5 inputs (~45 MB)
     # do not, so those workloads flush L2 between steps.
@@ -389,7 +433,27 @@ def run_e2e(pkg, wl, cid, shp, rank, world, args, env):
             mb, off, ids = pin(env["mb"]), pin(env["off"]), pin(env["ids"])
             h2d = bat.nbytes + flags.nbytes + mb.nbytes + off.nbytes + ids.nbytes
             d2h = mb.size * 12
-            if wl == "c5" and world > 1:
+            if wl == "c5" and world > 1 and env.get("peer") is not None:
+                dev = env["dev"]
+                hb = [torch.from_numpy(x) for x in (bat, flags, mb, off, ids)]
+                db = [torch.empty_like(x, device="cuda") for x in hb]
+                res_i = torch.empty(env["p_idx"].numel(), dtype=torch.int32).pin_memory()
+                res_s = torch.empty(env["p_idx"].numel(), dtype=torch.float64).pin_memory()
+                d2h = res_i.numel() * 12
+
+                def step():
+                    for d, s_ in zip(db, hb):
+                        d.copy_(s_, non_blocking=True)
+                    dev.node_best(db[0], db[1], env["best"], node_base=n0)
+                    dev.schedule(db[0], db[1], env["best"], db[2], db[3], db[4], env["o_idx"], env["o_score"],
+                                 node_base=n0)
+                    env["peer"][0].barrier()
+                    env["peer"][1]()
+                    env["peer"][0].barrier()
+                    res_i.copy_(env["p_idx"], non_blocking=True)
+                    res_s.copy_(env["p_score"], non_blocking=True)
+                    torch.cuda.synchronize()
+            elif wl == "c5" and world > 1:
                 # node-range sharding needs the device-pointer layer + NCCL; its e2e adds
                 # the H2D of the rank's inputs and the D2H of the merged result
                 import torch.distributed as dist
@@ -534,6 +598,8 @@ def main():
     ap.add_argument("--workload", choices=sorted(SHAPES), default="c2")
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--nccl-merge", action="store_true",
+                    help="c5, N > 1: merge through an NCCL all-gather instead of peer memory")
     args = ap.parse_args()
     if args.impl == "reference":
         args.steps = args.steps or 5

@@ -285,6 +285,17 @@ int klm_dev_merge_partials(int n_parts, int64_t n_requests,
                            const int32_t* part_idx, const double* part_score,
                            int32_t* out_idx, double* out_score, void* stream);
 
+/* K3 over peer memory: part_idx[g] / part_score[g] (HOST arrays of n_parts DEVICE
+ * pointers, at most 16) are rank g's partial winners for ALL requests, readable from this
+ * device (its own memory, or a peer's mapped over NVLink / NVSwitch: CUDA IPC, symmetric
+ * memory). Merges requests [r0, r1) only and writes out[r - r0]: with one slice per rank
+ * the exchange and the merge are a single kernel and nothing is staged through an
+ * all-gather. The caller orders it after every rank's K2 (a cross-rank barrier). */
+int klm_dev_merge_partials_peer(int n_parts, const int32_t* const* part_idx,
+                                const double* const* part_score, int64_t r0,
+                                int64_t r1, int32_t* out_idx, double* out_score,
+                                void* stream);
+
 int64_t klm_dev_cluster_scratch_bytes(void);
 /* K4 cluster_aggregate (manager.go:493-565). `out` is a device
  * klm_cluster_out. node_cols members are device pointers. */

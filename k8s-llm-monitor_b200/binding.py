@@ -99,6 +99,7 @@ SIGNATURES = {
     "klm_dev_schedule": (C.c_int, [_P, _P, _I64, _I64, _P, _I64, _P, _P, _P, _P, _P, _P]),
     "klm_dev_schedule_bruteforce": (C.c_int, [_P, _P, _I64, _I64, _I64, _P, _P, _P, _P, _P, _P]),
     "klm_dev_merge_partials": (C.c_int, [C.c_int, _I64, _P, _P, _P, _P, _P]),
+    "klm_dev_merge_partials_peer": (C.c_int, [C.c_int, _P, _P, _I64, _I64, _P, _P, _P]),
     "klm_dev_cluster_scratch_bytes": (_I64, []),
     "klm_dev_cluster_aggregate": (C.c_int, [C.POINTER(NodeCols), _I64, _P, _I64, _P, _P, _P]),
     "klm_dev_cluster_sums": (C.c_int, [C.POINTER(NodeCols), _I64, _P, _I64, _P, _P, _P]),
@@ -414,6 +415,14 @@ class Dev:
         n_parts, r = part_idx.shape
         check(self.lib.klm_dev_merge_partials(n_parts, r, _dp(part_idx), _dp(part_score), _dp(out_idx),
                                               _dp(out_score), _stream_ptr(stream)))
+
+    def merge_partials_peer(self, idx_ptrs, score_ptrs, r0: int, r1: int, out_idx, out_score, stream=None):
+        """idx_ptrs / score_ptrs: device addresses (ints) of every rank's partial arrays."""
+        n = len(idx_ptrs)
+        ai = (C.c_void_p * n)(*idx_ptrs)
+        asc = (C.c_void_p * n)(*score_ptrs)
+        check(self.lib.klm_dev_merge_partials_peer(n, ai, asc, r0, r1, _dp(out_idx), _dp(out_score),
+                                                   _stream_ptr(stream)))
 
     def _cols(self, cols: dict) -> NodeCols:
         gu = cols.get("gpu_usage")

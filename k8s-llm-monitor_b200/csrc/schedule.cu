@@ -275,6 +275,45 @@ merge_partials_kernel(int n_parts, int64_t n_requests, const int32_t* __restrict
   }
 }
 
+// K3 over peer memory: rank-local merge of requests [r0, r1) reading every rank's partial
+// arrays where they live (peer pointers over NVLink / NVSwitch, or local ones). Each rank
+// merges only its own slice, so every partial crosses the fabric at most once and no
+// staging copy (all-gather) is made: exchange and merge are one kernel.
+constexpr int kMaxPeerParts = 16;
+struct PeerParts {
+  const int32_t* idx[kMaxPeerParts];
+  const double* score[kMaxPeerParts];
+};
+
+__global__ void __launch_bounds__(256)
+merge_partials_peer_kernel(PeerParts parts, int n_parts, int64_t r0, int64_t r1,
+                           int32_t* __restrict__ out_idx, double* __restrict__ out_score) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t r = r0 + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; r < r1; r += stride) {
+    // issue every rank's loads before comparing: the peer reads overlap
+    int32_t pi[kMaxPeerParts];
+    double ps[kMaxPeerParts];
+#pragma unroll
+    for (int g = 0; g < kMaxPeerParts; ++g) {
+      if (g < n_parts) {
+        pi[g] = parts.idx[g][r];
+        ps[g] = parts.score[g][r];
+      }
+    }
+    int32_t bi = -1;
+    double bs = 0.0;
+#pragma unroll
+    for (int g = 0; g < kMaxPeerParts; ++g) {
+      if (g < n_parts && pi[g] >= 0 && (bi < 0 || ps[g] > bs || (ps[g] == bs && pi[g] < bi))) {
+        bs = ps[g];
+        bi = pi[g];
+      }
+    }
+    out_idx[r - r0] = bi;
+    out_score[r - r0] = bs;
+  }
+}
+
 static int grid_for(int64_t work_items, int threads, int max_waves = 8) {
   int64_t blocks = ceil_div(work_items, threads);
   const int64_t cap = (int64_t)kNumSMs * max_waves;
@@ -368,5 +407,32 @@ extern "C" int klm_dev_merge_partials(int n_parts, int64_t n_requests, const int
   merge_partials_kernel<<<grid_for(n_requests, 256, 16), 256, 0, as_stream(stream)>>>(
       n_parts, n_requests, part_idx, part_score, out_idx, out_score);
   KLM_LAUNCH_CHECK("merge_partials_kernel");
+  return KLM_OK;
+}
+
+extern "C" int klm_dev_merge_partials_peer(int n_parts, const int32_t* const* part_idx,
+                                           const double* const* part_score, int64_t r0, int64_t r1,
+                                           int32_t* out_idx, double* out_score, void* stream) {
+  if (n_parts < 1 || n_parts > kMaxPeerParts || !part_idx || !part_score || r0 < 0 || r1 < r0) {
+    set_error("klm_dev_merge_partials_peer: bad argument (1 <= n_parts <= %d)", kMaxPeerParts);
+    return n_parts > kMaxPeerParts ? KLM_ELIMIT : KLM_EINVAL;
+  }
+  if (r1 == r0) return KLM_OK;
+  if (!out_idx || !out_score) {
+    set_error("klm_dev_merge_partials_peer: null output");
+    return KLM_EINVAL;
+  }
+  PeerParts p{};
+  for (int g = 0; g < n_parts; ++g) {
+    if (!part_idx[g] || !part_score[g]) {
+      set_error("klm_dev_merge_partials_peer: null partial array for part %d", g);
+      return KLM_EINVAL;
+    }
+    p.idx[g] = part_idx[g];
+    p.score[g] = part_score[g];
+  }
+  merge_partials_peer_kernel<<<grid_for(r1 - r0, 256, 16), 256, 0, as_stream(stream)>>>(
+      p, n_parts, r0, r1, out_idx, out_score);
+  KLM_LAUNCH_CHECK("merge_partials_peer_kernel");
   return KLM_OK;
 }

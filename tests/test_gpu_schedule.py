@@ -159,6 +159,18 @@ def test_c5_node_sharded_merge(dev, pkg, g):
     torch.cuda.synchronize()
     assert np.array_equal(out_idx.cpu().numpy(), want[0])
     assert np.array_equal(out_score.cpu().numpy(), want[1])
+    # the peer-memory form: every "rank" merges only its slice of the requests, reading the
+    # partial arrays through per-rank pointers (all local here; peers over NVLink in bench.py)
+    ip = [part_idx[k].data_ptr() for k in range(g)]
+    sp = [part_score[k].data_ptr() for k in range(g)]
+    for k in range(g):
+        r0, r1 = r * k // g, r * (k + 1) // g
+        oi = torch.full((r1 - r0,), -5, dtype=torch.int32, device="cuda")
+        os_ = torch.zeros(r1 - r0, dtype=torch.float64, device="cuda")
+        dev.merge_partials_peer(ip, sp, r0, r1, oi, os_)
+        torch.cuda.synchronize()
+        assert np.array_equal(oi.cpu().numpy(), want[0][r0:r1])
+        assert np.array_equal(os_.cpu().numpy(), want[1][r0:r1])
 
 
 def test_bruteforce_many_prefs(handle, pkg):
