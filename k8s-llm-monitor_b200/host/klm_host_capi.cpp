@@ -5,6 +5,7 @@
 #include <vector>
 
 #include "klm_host.h"
+#include "klm_wire.h"
 
 using namespace klmhost;
 
@@ -32,7 +33,8 @@ void put(char* dst, int cap, const std::string& s) {
 
 extern "C" {
 
-void* klmh_open(klm_handle* h) { return h ? new Session(h) : nullptr; }
+// h may be NULL for a decode / encode only session (no GPU call is possible then)
+void* klmh_open(klm_handle* h) { return new Session(h); }
 void klmh_close(void* s) { delete static_cast<Session*>(s); }
 const char* klmh_error(void* s) { return static_cast<Session*>(s)->error.c_str(); }
 
@@ -68,8 +70,51 @@ void klmh_add_request(void* sv, const char* phase, const char* wl_name, const ch
   static_cast<Session*>(sv)->requests.push_back(q);
 }
 
+// wire format in: replace the session's UAV items / requests with the decoded lists
+int klmh_load_uavs_json(void* sv, const char* json) {
+  Session* s = static_cast<Session*>(sv);
+  try { s->uavs = DecodeUAVMetricList(json); }
+  catch (const std::exception& e) { s->error = e.what(); return -1; }
+  return static_cast<int>(s->uavs.size());
+}
+int klmh_load_requests_json(void* sv, const char* json, int apimachinery_ints) {
+  Session* s = static_cast<Session*>(sv);
+  try { s->requests = DecodeSchedulingRequestList(json, apimachinery_ints != 0); }
+  catch (const std::exception& e) { s->error = e.what(); return -1; }
+  return static_cast<int>(s->requests.size());
+}
+// decoded request i: min battery, number of preferred nodes, workload name (for the tests)
+int klmh_request_info(void* sv, int i, double* min_battery, int* n_pref, char* wl_name, char* phase, int cap) {
+  Session* s = static_cast<Session*>(sv);
+  if (i < 0 || i >= static_cast<int>(s->requests.size())) return -1;
+  const SchedulingRequest& q = s->requests[i];
+  if (min_battery) *min_battery = q.Spec.MinBatteryPercent;
+  if (n_pref) *n_pref = static_cast<int>(q.Spec.PreferredNodes.size());
+  put(wl_name, cap, q.Spec.Workload.Name);
+  put(phase, cap, q.Phase);
+  return q.HasPhase ? 1 : 0;
+}
+int klmh_uav_info(void* sv, int i, double* battery, int* has_battery, char* name, char* status, int cap) {
+  Session* s = static_cast<Session*>(sv);
+  if (i < 0 || i >= static_cast<int>(s->uavs.size())) return -1;
+  const UAVMetricItem& u = s->uavs[i];
+  if (battery) *battery = u.Battery;
+  if (has_battery) *has_battery = u.HasBattery ? 1 : 0;
+  put(name, cap, u.NodeName);
+  put(status, cap, u.CollectionStatus);
+  return (u.HasNodeName ? 1 : 0) | (u.HasStatus ? 2 : 0);
+}
+// wire format out: status i of the last reconcile as the JSON map controller.go:229-236 writes
+int klmh_status_json(void* sv, int i, const char* last_updated, char* dst, int cap) {
+  Session* s = static_cast<Session*>(sv);
+  if (i < 0 || i >= static_cast<int>(s->statuses.size())) return -1;
+  put(dst, cap, EncodeStatus(s->statuses[i], last_updated ? last_updated : ""));
+  return s->statuses[i].Updated ? 1 : 0;
+}
+
 int klmh_reconcile(void* sv) {
   Session* s = static_cast<Session*>(sv);
+  if (!s->h) { s->error = "no GPU handle in this session"; return -1; }
   try {
     s->statuses = Controller(s->h).Reconcile(s->requests, s->uavs);
   } catch (const std::exception& e) {

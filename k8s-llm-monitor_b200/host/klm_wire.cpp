@@ -1,0 +1,269 @@
+#include "klm_wire.h"
+
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <map>
+#include <memory>
+#include <stdexcept>
+
+namespace klmhost {
+namespace {
+
+struct JValue;
+using JPtr = std::shared_ptr<JValue>;
+struct JValue {
+  enum Kind { Null, Bool, Int, Float, String, Array, Object } kind = Null;
+  bool b = false;
+  double num = 0;  // Int and Float both carry the value here
+  std::string str;
+  std::vector<JPtr> arr;
+  std::map<std::string, JPtr> obj;
+  const JValue* get(const std::string& k) const {
+    if (kind != Object) return nullptr;
+    auto it = obj.find(k);
+    return it == obj.end() ? nullptr : it->second.get();
+  }
+};
+
+class Parser {
+ public:
+  explicit Parser(const std::string& s) : s_(s) {}
+  JPtr parse() {
+    JPtr v = value();
+    ws();
+    if (i_ != s_.size()) fail("trailing characters");
+    return v;
+  }
+
+ private:
+  const std::string& s_;
+  size_t i_ = 0;
+  [[noreturn]] void fail(const char* what) const {
+    throw std::runtime_error("JSON: " + std::string(what) + " at offset " + std::to_string(i_));
+  }
+  void ws() {
+    while (i_ < s_.size() && (s_[i_] == ' ' || s_[i_] == '\n' || s_[i_] == '\t' || s_[i_] == '\r')) ++i_;
+  }
+  bool eat(const char* lit) {
+    size_t n = std::char_traits<char>::length(lit);
+    if (s_.compare(i_, n, lit) == 0) { i_ += n; return true; }
+    return false;
+  }
+  static void utf8(std::string& out, unsigned cp) {
+    if (cp < 0x80) out += static_cast<char>(cp);
+    else if (cp < 0x800) { out += static_cast<char>(0xC0 | (cp >> 6)); out += static_cast<char>(0x80 | (cp & 0x3F)); }
+    else if (cp < 0x10000) {
+      out += static_cast<char>(0xE0 | (cp >> 12)); out += static_cast<char>(0x80 | ((cp >> 6) & 0x3F));
+      out += static_cast<char>(0x80 | (cp & 0x3F));
+    } else {
+      out += static_cast<char>(0xF0 | (cp >> 18)); out += static_cast<char>(0x80 | ((cp >> 12) & 0x3F));
+      out += static_cast<char>(0x80 | ((cp >> 6) & 0x3F)); out += static_cast<char>(0x80 | (cp & 0x3F));
+    }
+  }
+  unsigned hex4() {
+    if (i_ + 4 > s_.size()) fail("short \\u escape");
+    unsigned v = 0;
+    for (int k = 0; k < 4; ++k) {
+      char c = s_[i_++];
+      v <<= 4;
+      if (c >= '0' && c <= '9') v |= c - '0';
+      else if (c >= 'a' && c <= 'f') v |= c - 'a' + 10;
+      else if (c >= 'A' && c <= 'F') v |= c - 'A' + 10;
+      else fail("bad \\u escape");
+    }
+    return v;
+  }
+  std::string string() {
+    if (s_[i_] != '"') fail("expected string");
+    ++i_;
+    std::string out;
+    while (i_ < s_.size() && s_[i_] != '"') {
+      char c = s_[i_++];
+      if (c != '\\') { out += c; continue; }
+      if (i_ >= s_.size()) fail("short escape");
+      char e = s_[i_++];
+      switch (e) {
+        case '"': out += '"'; break;
+        case '\\': out += '\\'; break;
+        case '/': out += '/'; break;
+        case 'b': out += '\b'; break;
+        case 'f': out += '\f'; break;
+        case 'n': out += '\n'; break;
+        case 'r': out += '\r'; break;
+        case 't': out += '\t'; break;
+        case 'u': {
+          unsigned cp = hex4();
+          if (cp >= 0xD800 && cp < 0xDC00 && s_.compare(i_, 2, "\\u") == 0) {
+            i_ += 2;
+            unsigned lo = hex4();
+            cp = 0x10000 + ((cp - 0xD800) << 10) + (lo - 0xDC00);
+          }
+          utf8(out, cp);
+          break;
+        }
+        default: fail("bad escape");
+      }
+    }
+    if (i_ >= s_.size()) fail("unterminated string");
+    ++i_;
+    return out;
+  }
+  JPtr value() {
+    ws();
+    if (i_ >= s_.size()) fail("unexpected end");
+    auto v = std::make_shared<JValue>();
+    char c = s_[i_];
+    if (c == '{') {
+      v->kind = JValue::Object;
+      ++i_;
+      ws();
+      if (i_ < s_.size() && s_[i_] == '}') { ++i_; return v; }
+      for (;;) {
+        ws();
+        std::string k = string();
+        ws();
+        if (i_ >= s_.size() || s_[i_] != ':') fail("expected ':'");
+        ++i_;
+        v->obj[k] = value();
+        ws();
+        if (i_ < s_.size() && s_[i_] == ',') { ++i_; continue; }
+        if (i_ < s_.size() && s_[i_] == '}') { ++i_; return v; }
+        fail("expected ',' or '}'");
+      }
+    }
+    if (c == '[') {
+      v->kind = JValue::Array;
+      ++i_;
+      ws();
+      if (i_ < s_.size() && s_[i_] == ']') { ++i_; return v; }
+      for (;;) {
+        v->arr.push_back(value());
+        ws();
+        if (i_ < s_.size() && s_[i_] == ',') { ++i_; continue; }
+        if (i_ < s_.size() && s_[i_] == ']') { ++i_; return v; }
+        fail("expected ',' or ']'");
+      }
+    }
+    if (c == '"') { v->kind = JValue::String; v->str = string(); return v; }
+    if (eat("true")) { v->kind = JValue::Bool; v->b = true; return v; }
+    if (eat("false")) { v->kind = JValue::Bool; return v; }
+    if (eat("null")) return v;
+    // number: integral text (no '.', 'e', 'E') is an int64 for apimachinery's decoder
+    size_t st = i_;
+    bool integral = true;
+    if (s_[i_] == '-') ++i_;
+    while (i_ < s_.size()) {
+      char d = s_[i_];
+      if (d >= '0' && d <= '9') { ++i_; continue; }
+      if (d == '.' || d == 'e' || d == 'E' || d == '+' || d == '-') { integral = false; ++i_; continue; }
+      break;
+    }
+    if (i_ == st) fail("unexpected character");
+    v->kind = integral ? JValue::Int : JValue::Float;
+    v->num = std::strtod(s_.substr(st, i_ - st).c_str(), nullptr);
+    return v;
+  }
+};
+
+const std::vector<JPtr>& items_of(const JValue& root) {
+  if (root.kind == JValue::Array) return root.arr;
+  const JValue* it = root.get("items");
+  if (!it || it->kind != JValue::Array) throw std::runtime_error("JSON: no \"items\" array");
+  return it->arr;
+}
+
+}  // namespace
+
+std::vector<UAVMetricItem> DecodeUAVMetricList(const std::string& json) {
+  JPtr root = Parser(json).parse();
+  std::vector<UAVMetricItem> out;
+  for (const JPtr& it : items_of(*root)) {
+    UAVMetricItem u;
+    const JValue* spec = it->get("spec");      // NestedMap(item, "spec"), controller.go:182
+    const JValue* status = it->get("status");  // :183
+    if (spec) {
+      if (const JValue* v = spec->get("node_name"); v && v->kind == JValue::String) {  // :185
+        u.HasNodeName = true;
+        u.NodeName = v->str;
+      }
+      if (const JValue* v = spec->get("uav_id"); v && v->kind == JValue::String) u.UAVID = v->str;  // :186
+      if (const JValue* b = spec->get("battery"))  // readFloat(spec, "battery", "remaining_percent"), :187
+        if (const JValue* v = b->get("remaining_percent"); v && (v->kind == JValue::Int || v->kind == JValue::Float)) {
+          u.HasBattery = true;  // float64 / int64 cases of the type switch, :262-271
+          u.Battery = v->num;
+        }
+    }
+    if (status)
+      if (const JValue* v = status->get("collection_status"); v && v->kind == JValue::String) {  // :188
+        u.HasStatus = true;
+        u.CollectionStatus = v->str;
+      }
+    out.push_back(u);
+  }
+  return out;
+}
+
+std::vector<SchedulingRequest> DecodeSchedulingRequestList(const std::string& json, bool apimachinery_ints) {
+  JPtr root = Parser(json).parse();
+  std::vector<SchedulingRequest> out;
+  for (const JPtr& it : items_of(*root)) {
+    SchedulingRequest q;
+    if (const JValue* st = it->get("status"))
+      if (const JValue* v = st->get("phase"); v && v->kind == JValue::String) {  // NestedString, :113
+        q.HasPhase = true;
+        q.Phase = v->str;
+      }
+    if (const JValue* spec = it->get("spec")) {
+      if (const JValue* wl = spec->get("workload"); wl && wl->kind == JValue::Object) {  // :127-131
+        if (const JValue* v = wl->get("name"); v && v->kind == JValue::String) q.Spec.Workload.Name = v->str;
+        if (const JValue* v = wl->get("namespace"); v && v->kind == JValue::String) q.Spec.Workload.Namespace = v->str;
+        if (const JValue* v = wl->get("type"); v && v->kind == JValue::String) q.Spec.Workload.Type = v->str;
+      }
+      if (const JValue* v = spec->get("minBatteryPercent"))  // .(float64) only, :133
+        if (v->kind == JValue::Float || (v->kind == JValue::Int && !apimachinery_ints)) q.Spec.MinBatteryPercent = v->num;
+      if (const JValue* v = spec->get("preferredNodes"); v && v->kind == JValue::Array)  // :137-143
+        for (const JPtr& e : v->arr)
+          if (e->kind == JValue::String) q.Spec.PreferredNodes.push_back(e->str);
+    }
+    out.push_back(q);
+  }
+  return out;
+}
+
+static std::string quote(const std::string& s) {
+  std::string o = "\"";
+  for (unsigned char c : s) {
+    switch (c) {
+      case '"': o += "\\\""; break;
+      case '\\': o += "\\\\"; break;
+      case '\n': o += "\\n"; break;
+      case '\r': o += "\\r"; break;
+      case '\t': o += "\\t"; break;
+      default:
+        if (c < 0x20) { char b[8]; std::snprintf(b, sizeof(b), "\\u%04x", c); o += b; }
+        else o += static_cast<char>(c);
+    }
+  }
+  return o + "\"";
+}
+
+std::string EncodeStatus(const SchedulingRequestStatus& st, const std::string& last_updated) {
+  // Go's encoding/json prints float64 with strconv 'g'-like shortest form; integral scores
+  // print without a fraction (90 -> 90), others with the shortest round-trip digits.
+  char score[40];
+  if (st.Score == std::floor(st.Score) && std::fabs(st.Score) < 1e15) std::snprintf(score, sizeof(score), "%.0f", st.Score);
+  else std::snprintf(score, sizeof(score), "%.17g", st.Score);
+  double back = std::strtod(score, nullptr);
+  for (int p = 1; p < 17 && back == st.Score && score[0]; ++p) {  // shortest digits that round-trip
+    char t[40];
+    std::snprintf(t, sizeof(t), "%.*g", p, st.Score);
+    if (std::strtod(t, nullptr) == st.Score) { std::snprintf(score, sizeof(score), "%s", t); break; }
+  }
+  const std::string phase = st.Phase.empty() ? "Pending" : st.Phase;  // controller.go:238-240
+  return "{\"phase\":" + quote(phase) + ",\"assignedNode\":" + quote(st.AssignedNode) +
+         ",\"assignedUAV\":" + quote(st.AssignedUAV) + ",\"score\":" + score + ",\"message\":" +
+         quote(st.Message) + ",\"lastUpdated\":" + quote(last_updated) + "}";
+}
+
+}  // namespace klmhost

@@ -28,7 +28,8 @@ def load() -> C.CDLL:
         for name in ("klmh_close", "klmh_clear", "klmh_add_uav", "klmh_add_request", "klmh_reconcile",
                      "klmh_status", "klmh_add_node", "klmh_add_pod", "klmh_calculate_cluster_metrics",
                      "klmh_issue", "klmh_add_fleet_uav", "klmh_healthy_uav_count", "klmh_low_battery_uavs",
-                     "klmh_name"):
+                     "klmh_name", "klmh_load_uavs_json", "klmh_load_requests_json", "klmh_request_info",
+                     "klmh_uav_info", "klmh_status_json"):
             getattr(lib, name)
         _lib = lib
     return _lib
@@ -39,9 +40,10 @@ def _b(s: Optional[str]):
 
 
 class HostSession:
-    def __init__(self, handle: "binding.Handle"):
+    def __init__(self, handle: Optional["binding.Handle"]):
+        """handle=None gives a decode / encode only session (usable without a GPU)."""
         self.lib = load()
-        self.s = C.c_void_p(self.lib.klmh_open(handle._h))
+        self.s = C.c_void_p(self.lib.klmh_open(handle._h if handle is not None else None))
         self._keep = handle
 
     def close(self):
@@ -64,6 +66,38 @@ class HostSession:
         arr = (C.c_char_p * max(len(preferred), 1))(*[p.encode("utf-8") for p in preferred])
         self.lib.klmh_add_request(self.s, _b(phase), _b(wl_name), _b(wl_ns), C.c_double(min_battery),
                                   C.c_int(len(preferred)), arr)
+
+    # --- wire format (host/klm_wire.h)
+    def load_uavs_json(self, text: str) -> int:
+        n = self.lib.klmh_load_uavs_json(self.s, text.encode("utf-8"))
+        if n < 0:
+            self._err()
+        return n
+
+    def load_requests_json(self, text: str, apimachinery_ints: bool = True) -> int:
+        n = self.lib.klmh_load_requests_json(self.s, text.encode("utf-8"), C.c_int(int(apimachinery_ints)))
+        if n < 0:
+            self._err()
+        return n
+
+    def request_info(self, i: int) -> dict:
+        mb, npref = C.c_double(0), C.c_int(0)
+        name, phase = C.create_string_buffer(_CAP), C.create_string_buffer(_CAP)
+        hp = self.lib.klmh_request_info(self.s, i, C.byref(mb), C.byref(npref), name, phase, _CAP)
+        return {"min_battery": mb.value, "n_pref": npref.value, "workload": name.value.decode(),
+                "has_phase": hp == 1, "phase": phase.value.decode()}
+
+    def uav_info(self, i: int) -> dict:
+        bat, hb = C.c_double(0), C.c_int(0)
+        name, status = C.create_string_buffer(_CAP), C.create_string_buffer(_CAP)
+        f = self.lib.klmh_uav_info(self.s, i, C.byref(bat), C.byref(hb), name, status, _CAP)
+        return {"battery": bat.value, "has_battery": bool(hb.value), "name": name.value.decode(),
+                "has_name": bool(f & 1), "status": status.value.decode(), "has_status": bool(f & 2)}
+
+    def status_json(self, i: int, last_updated: str) -> str:
+        buf = C.create_string_buffer(2048)
+        self.lib.klmh_status_json(self.s, i, last_updated.encode(), buf, 2048)
+        return buf.value.decode("utf-8")
 
     def reconcile(self):
         n = self.lib.klmh_reconcile(self.s)

@@ -101,3 +101,28 @@ def test_manager_fleet_scans(host):
     assert host.healthy_uav_count() == 3                      # exact match on "OK" (uav_metrics.go:207)
     assert host.low_battery_uavs(20.0) == ["n0", "n2", "n4"]  # strict < (uav_metrics.go:226)
     assert host.low_battery_uavs(0.0) == []
+
+
+def test_wire_in_wire_out(host):
+    """JSON lists in (the API server's view) -> one GPU reconcile -> the status maps
+    controller.go:229-236 writes, for fixture A with every example request."""
+    import json
+    a = [c for c in KATS if c["name"].startswith("A/")]
+    reqs = [{"spec": c["spec"]} for c in a] + [{"spec": a[0]["spec"], "status": {"phase": "Assigned"}}]
+    host.clear()
+    assert host.load_uavs_json(json.dumps({"items": a[0]["items"]}, ensure_ascii=False)) == 3
+    assert host.load_requests_json(json.dumps({"items": reqs}), apimachinery_ints=False) == len(reqs)
+    got = host.reconcile()
+    stamp = "2025-10-17T00:00:00Z"
+    for i, c in enumerate(a):
+        spec = co.decode_spec(c["spec"], apimachinery_ints=False)
+        w = co.process_request(spec, c["items"])
+        m = json.loads(host.status_json(i, stamp))
+        assert m == {"phase": w.phase, "assignedNode": w.assigned_node, "assignedUAV": w.assigned_uav,
+                     "score": w.score, "message": w.message, "lastUpdated": stamp}
+    assert got[-1]["updated"] is False
+    # with apimachinery's decoder the integral minBatteryPercent of the examples is dropped
+    # (controller.go:133): edge-task (min 80) then also accepts agent-0 at 75 -> same winner
+    host.load_requests_json(json.dumps({"items": reqs}), apimachinery_ints=True)
+    got2 = host.reconcile()
+    assert [g["node"] for g in got2[:3]] == [g["node"] for g in got[:3]]
