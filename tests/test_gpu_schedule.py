@@ -181,3 +181,47 @@ def test_bruteforce_many_prefs(handle, pkg):
     dec, bru = _both(handle, pkg, bat, flags, mb, off, ids)
     _eq(dec, want, "decomposed")
     _eq(bru, want, "bruteforce")
+
+
+def test_handle_is_thread_safe(pkg):
+    """The reference's callers are concurrent goroutines on arbitrary OS threads (reconcile
+    loop, Collect loop, HTTP handlers - SURVEY.md §8b): many threads share one handle, each
+    call must see a consistent snapshot and return its own results."""
+    import threading
+    rng = np.random.default_rng(3)
+    problems = [helpers.random_problem(rng, 2000 + 37 * i, 500, kmax=3, grid=1.0) for i in range(6)]
+    wants = [ob.schedule_literal(*p) for p in problems]
+    snap = pkg.synth.cluster_snapshot(2, 1500, 4000, gpus_per_node=1)
+    want_cluster = ob.cluster_aggregate(snap)
+    errors = []
+    with pkg.Handle(0) as h:
+        lock = threading.Lock()   # nodes_set + schedule_batch form one reconcile: keep them together
+
+        def scheduler(i):
+            try:
+                for _ in range(15):
+                    bat, flags, mb, off, ids = problems[i]
+                    with lock:
+                        h.nodes_set(bat, flags)
+                        got = h.schedule_batch(mb, off, ids)
+                    assert np.array_equal(got[0], wants[i][0]) and np.array_equal(got[1], wants[i][1])
+            except Exception as e:  # noqa: BLE001
+                errors.append(repr(e))
+
+        def collector():
+            try:
+                for _ in range(40):
+                    got = h.cluster_aggregate(*(snap[k] for k in ("cpu_capacity", "cpu_usage", "memory_capacity",
+                                                                  "memory_usage", "gpu_count", "healthy",
+                                                                  "gpu_usage", "pod_running")))
+                    assert got == want_cluster
+            except Exception as e:  # noqa: BLE001
+                errors.append(repr(e))
+
+        threads = [threading.Thread(target=scheduler, args=(i,)) for i in range(6)] + \
+                  [threading.Thread(target=collector) for _ in range(3)]
+        for t in threads:
+            t.start()
+        for t in threads:
+            t.join()
+    assert not errors, errors[:3]
