@@ -62,6 +62,31 @@ struct DevBuf {
   T* as() const { return static_cast<T*>(p); }
 };
 
+// Grow-only page-locked host buffer: staging for the small-copy paths below. A call that
+// moves only a few KB per array pays ~5 us of copy-engine latency per cudaMemcpyAsync, so
+// such arrays are gathered here with memcpy and cross PCIe as one transfer each way.
+struct PinBuf {
+  void* p = nullptr;
+  size_t cap = 0;
+  int ensure(size_t bytes) {
+    if (bytes <= cap) return KLM_OK;
+    release();
+    KLM_CUDA(cudaHostAlloc(&p, bytes, cudaHostAllocDefault));
+    cap = bytes;
+    return KLM_OK;
+  }
+  void release() {
+    if (p) cudaFreeHost(p);
+    p = nullptr;
+    cap = 0;
+  }
+  char* at(size_t off) const { return static_cast<char*>(p) + off; }
+};
+
+// Arrays up to this many bytes in total go through the staging block; above it the
+// memcpy would cost more than the extra copy submissions and the arrays are sent directly.
+constexpr size_t kStageMax = 256 << 10;
+
 }  // namespace klm
 
 using namespace klm;
@@ -69,12 +94,23 @@ using namespace klm;
 struct klm_handle {
   int device = 0;
   cudaStream_t stream = nullptr;
+  cudaStream_t stream2 = nullptr;  // klm_collect: node-snapshot branch beside the ring branch
   std::mutex mu;
+
+  // staging (host, page-locked) and the events that say the last transfer out of each
+  // block has been read, i.e. the block may be overwritten
+  PinBuf sched_pin, snap_pin;
+  cudaEvent_t sched_read = nullptr;
 
   // scheduling
   int64_t n_nodes = -1;  // -1: no snapshot installed yet
-  DevBuf battery, flags, best, best_scratch;
+  DevBuf node_tab;       // battery f64[n] | flags u8[n] (256-byte aligned parts)
+  double* d_battery = nullptr;
+  uint8_t* d_flags = nullptr;
+  DevBuf req_blk, res_blk;  // small batches: min | off | ids and score | idx as single blocks
+  DevBuf best, best_scratch;
   DevBuf req_min, req_off, req_ids, res_idx, res_score;
+  DevBuf snap_out;  // klm_collect, small snapshots: cluster_out | the five rate columns
 
   // aggregation
   DevBuf agg_cols, agg_pods, agg_gpu, agg_out, agg_scratch;
@@ -171,9 +207,11 @@ extern "C" int klm_create(const int* device_ids, int n_dev, klm_handle** out) {
   }
   h->device = dev;
   e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);
+  if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->stream2, cudaStreamNonBlocking);
+  if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->sched_read, cudaEventDisableTiming);
   if (e != cudaSuccess) {
-    delete h;
-    return cuda_fail(e, "cudaStreamCreateWithFlags");
+    klm_destroy(h);
+    return cuda_fail(e, "cudaStreamCreateWithFlags / cudaEventCreateWithFlags");
   }
   // scratch areas carry self-resetting tickets that must start at zero
   int rc = h->best_scratch.ensure((size_t)klm_dev_node_best_scratch_bytes());
@@ -198,12 +236,18 @@ extern "C" void klm_destroy(klm_handle* h) {
   if (!h) return;
   cudaSetDevice(h->device);
   if (h->stream) cudaStreamSynchronize(h->stream);
-  DevBuf* bufs[] = {&h->battery,  &h->flags,    &h->best,       &h->best_scratch, &h->req_min,
+  if (h->stream2) cudaStreamSynchronize(h->stream2);
+  DevBuf* bufs[] = {&h->node_tab, &h->req_blk,  &h->res_blk,    &h->snap_out,
+                    &h->best,     &h->best_scratch, &h->req_min,
                     &h->req_off,  &h->req_ids,  &h->res_idx,    &h->res_score,    &h->agg_cols,
                     &h->agg_pods, &h->agg_gpu,  &h->agg_out,    &h->agg_scratch,  &h->rate_in,
                     &h->rate_out, &h->pod_tot, &h->fleet_in, &h->fleet_out,  &h->fleet_scratch, &h->ring,
                     &h->seen,     &h->ing_ids,  &h->ing_vals,   &h->stats_out};
   for (DevBuf* b : bufs) b->release();
+  h->sched_pin.release();
+  h->snap_pin.release();
+  if (h->sched_read) cudaEventDestroy(h->sched_read);
+  if (h->stream2) cudaStreamDestroy(h->stream2);
   if (h->stream) cudaStreamDestroy(h->stream);
   delete h;
 }
@@ -217,14 +261,33 @@ extern "C" int klm_nodes_set(klm_handle* h, int64_t n, const double* battery,
     set_error("klm_nodes_set: bad argument (0 <= n_nodes < 2^31, arrays non-null)");
     return KLM_EINVAL;
   }
-  KLM_TRY(h->battery.ensure((size_t)n * sizeof(double)));
-  KLM_TRY(h->flags.ensure((size_t)n));
-  KLM_TRY(h2d(h->battery.p, battery, (size_t)n * sizeof(double), h->stream));
-  KLM_TRY(h2d(h->flags.p, flags, (size_t)n, h->stream));
+  const size_t bat_bytes = (size_t)n * sizeof(double), flag_off = align256(bat_bytes);
+  const size_t tab_bytes = flag_off + (size_t)n;
+  h->n_nodes = -1;  // no snapshot until this one is in place
+  KLM_TRY(h->node_tab.ensure(tab_bytes + 256));
+  h->d_battery = h->node_tab.as<double>();
+  h->d_flags = h->node_tab.as<uint8_t>() + flag_off;
+  const bool staged = tab_bytes <= kStageMax;
+  if (staged) {
+    // Small table: gather both columns in the staging block and send one transfer. The
+    // caller's arrays are consumed by the memcpy, so the call returns without waiting
+    // for the GPU; a device-side failure is reported by the next call that synchronises.
+    KLM_TRY(h->sched_pin.ensure(kStageMax));
+    KLM_CUDA(cudaEventSynchronize(h->sched_read));  // previous transfer out of the block
+    if (n > 0) {
+      std::memcpy(h->sched_pin.at(0), battery, bat_bytes);
+      std::memcpy(h->sched_pin.at(flag_off), flags, (size_t)n);
+    }
+    KLM_TRY(h2d(h->node_tab.p, h->sched_pin.p, tab_bytes, h->stream));
+    KLM_CUDA(cudaEventRecord(h->sched_read, h->stream));
+  } else {
+    KLM_TRY(h2d(h->d_battery, battery, bat_bytes, h->stream));
+    KLM_TRY(h2d(h->d_flags, flags, (size_t)n, h->stream));
+  }
   // K1 runs once per snapshot, not once per batch
-  KLM_TRY(klm_dev_node_best(h->battery.as<double>(), h->flags.as<uint8_t>(), n, 0,
-                            h->best.as<int64_t>(), h->best_scratch.p, h->stream));
-  KLM_TRY(sync(h->stream));  // caller may free its arrays after return
+  KLM_TRY(klm_dev_node_best(h->d_battery, h->d_flags, n, 0, h->best.as<int64_t>(),
+                            h->best_scratch.p, h->stream));
+  if (!staged) KLM_TRY(sync(h->stream));  // caller may free its arrays after return
   h->n_nodes = n;
   return KLM_OK;
 }
@@ -251,27 +314,65 @@ extern "C" int klm_schedule_batch(klm_handle* h, int64_t R, const double* min_ba
     set_error("klm_schedule_batch: pref_off must start at 0 and pref_ids be non-null");
     return KLM_EINVAL;
   }
-  KLM_TRY(h->req_min.ensure((size_t)R * sizeof(double)));
-  KLM_TRY(h->req_off.ensure((size_t)(R + 1) * sizeof(int32_t)));
-  KLM_TRY(h->req_ids.ensure((size_t)(n_ids > 0 ? n_ids : 1) * sizeof(int32_t)));
-  KLM_TRY(h->res_idx.ensure((size_t)R * sizeof(int32_t)));
-  KLM_TRY(h->res_score.ensure((size_t)R * sizeof(double)));
-  KLM_TRY(h2d(h->req_min.p, min_battery, (size_t)R * sizeof(double), h->stream));
-  KLM_TRY(h2d(h->req_off.p, pref_off, (size_t)(R + 1) * sizeof(int32_t), h->stream));
-  KLM_TRY(h2d(h->req_ids.p, pref_ids, (size_t)n_ids * sizeof(int32_t), h->stream));
-  if (algo == KLM_ALGO_DECOMPOSED) {
-    KLM_TRY(klm_dev_schedule(h->battery.as<double>(), h->flags.as<uint8_t>(), h->n_nodes, 0,
-                             h->best.as<int64_t>(), R, h->req_min.as<double>(),
-                             h->req_off.as<int32_t>(), h->req_ids.as<int32_t>(),
-                             h->res_idx.as<int32_t>(), h->res_score.as<double>(), h->stream));
+  const size_t min_bytes = (size_t)R * sizeof(double), off_bytes = (size_t)(R + 1) * sizeof(int32_t);
+  const size_t ids_bytes = (size_t)n_ids * sizeof(int32_t), idx_bytes = (size_t)R * sizeof(int32_t);
+  // block layouts of the small path (each part 256-byte aligned)
+  const size_t in_off = align256(min_bytes), in_ids = in_off + align256(off_bytes);
+  const size_t in_bytes = in_ids + align256(ids_bytes), out_idx_at = align256(min_bytes);
+  const size_t out_bytes = out_idx_at + idx_bytes;
+  const bool staged = in_bytes + out_bytes <= kStageMax;
+  double *d_min, *d_score;
+  int32_t *d_off, *d_ids, *d_idx;
+  if (staged) {
+    // A reconcile with a handful of pending requests: three arrays in and two out would be
+    // five copy submissions for a few hundred bytes; stage them and move one block each way.
+    KLM_TRY(h->req_blk.ensure(in_bytes + 256));
+    KLM_TRY(h->res_blk.ensure(out_bytes + 256));
+    KLM_TRY(h->sched_pin.ensure(kStageMax));
+    KLM_CUDA(cudaEventSynchronize(h->sched_read));
+    char* blk = h->req_blk.as<char>();
+    d_min = reinterpret_cast<double*>(blk);
+    d_off = reinterpret_cast<int32_t*>(blk + in_off);
+    d_ids = reinterpret_cast<int32_t*>(blk + in_ids);
+    d_score = h->res_blk.as<double>();
+    d_idx = reinterpret_cast<int32_t*>(h->res_blk.as<char>() + out_idx_at);
+    std::memcpy(h->sched_pin.at(0), min_battery, min_bytes);
+    std::memcpy(h->sched_pin.at(in_off), pref_off, off_bytes);
+    if (ids_bytes) std::memcpy(h->sched_pin.at(in_ids), pref_ids, ids_bytes);
+    KLM_TRY(h2d(blk, h->sched_pin.p, in_bytes, h->stream));
   } else {
-    KLM_TRY(klm_dev_schedule_bruteforce(
-        h->battery.as<double>(), h->flags.as<uint8_t>(), h->n_nodes, 0, R,
-        h->req_min.as<double>(), h->req_off.as<int32_t>(), h->req_ids.as<int32_t>(),
-        h->res_idx.as<int32_t>(), h->res_score.as<double>(), h->stream));
+    KLM_TRY(h->req_min.ensure(min_bytes));
+    KLM_TRY(h->req_off.ensure(off_bytes));
+    KLM_TRY(h->req_ids.ensure(ids_bytes ? ids_bytes : sizeof(int32_t)));
+    KLM_TRY(h->res_idx.ensure(idx_bytes));
+    KLM_TRY(h->res_score.ensure(min_bytes));
+    d_min = h->req_min.as<double>();
+    d_off = h->req_off.as<int32_t>();
+    d_ids = h->req_ids.as<int32_t>();
+    d_idx = h->res_idx.as<int32_t>();
+    d_score = h->res_score.as<double>();
+    KLM_TRY(h2d(d_min, min_battery, min_bytes, h->stream));
+    KLM_TRY(h2d(d_off, pref_off, off_bytes, h->stream));
+    KLM_TRY(h2d(d_ids, pref_ids, ids_bytes, h->stream));
   }
-  KLM_TRY(d2h(out_idx, h->res_idx.p, (size_t)R * sizeof(int32_t), h->stream));
-  KLM_TRY(d2h(out_score, h->res_score.p, (size_t)R * sizeof(double), h->stream));
+  if (algo == KLM_ALGO_DECOMPOSED) {
+    KLM_TRY(klm_dev_schedule(h->d_battery, h->d_flags, h->n_nodes, 0, h->best.as<int64_t>(), R, d_min,
+                             d_off, d_ids, d_idx, d_score, h->stream));
+  } else {
+    KLM_TRY(klm_dev_schedule_bruteforce(h->d_battery, h->d_flags, h->n_nodes, 0, R, d_min, d_off, d_ids,
+                                        d_idx, d_score, h->stream));
+  }
+  if (staged) {
+    // results come back into the same staging block (the inputs have been read by then:
+    // same stream), then out to the caller's arrays
+    KLM_TRY(d2h(h->sched_pin.p, d_score, out_bytes, h->stream));
+    KLM_TRY(sync(h->stream));
+    std::memcpy(out_score, h->sched_pin.at(0), min_bytes);
+    std::memcpy(out_idx, h->sched_pin.at(out_idx_at), idx_bytes);
+    return KLM_OK;
+  }
+  KLM_TRY(d2h(out_idx, d_idx, idx_bytes, h->stream));
+  KLM_TRY(d2h(out_score, d_score, min_bytes, h->stream));
   return sync(h->stream);
 }
 
@@ -563,20 +664,33 @@ extern "C" int klm_ring_stats(klm_handle* h, int64_t s0, int64_t s1, float* out_
 
 // ------------------------------------------------------------- collect cycle
 
-extern "C" int klm_collect(klm_handle* h, const klm_collect_in* in, const klm_collect_out* out) {
-  KLM_ENTER(h);
+namespace {
+
+// The two branches of a collect cycle share no data, so they run on two streams: the ring
+// branch (tick upload, K6, K7, statistics download) on `stream`, the node-snapshot branch
+// (column upload, K5, K4, small downloads) on `stream2`, where its copies and kernels hide
+// behind K7. Both streams are joined before the call returns.
+int collect_impl(klm_handle* h, const klm_collect_in* in, const klm_collect_out* out) {
   if (!in || !out || in->n_nodes < 0 || in->n_pods < 0 || (in->n_nodes > 0 && !in->nodes) ||
       (in->n_pods > 0 && !in->pod_running)) {
     set_error("klm_collect: bad argument");
     return KLM_EINVAL;
   }
-  cudaStream_t st = h->stream;
+  cudaStream_t st = h->stream, st2 = h->stream2;
   const bool want_win = out->win_min || out->win_max || out->win_mean || out->win_p95;
   if ((in->tick_values || want_win) && h->n_series <= 0) {
     set_error("klm_collect: no ring; call klm_ring_create first");
     return KLM_ESTATE;
   }
-  // ---- ring: tick ingest, then the window statistics of every series
+  const int64_t n = in->n_nodes, np = in->n_pods;
+  const klm_node_cols* c = in->nodes;
+  const int64_t ng = (n > 0 && c) ? c->n_gpu_usage : 0;
+  if (n > 0 && (!c->cpu_capacity || !c->cpu_usage || !c->memory_capacity || !c->memory_usage ||
+                !c->gpu_count || !c->healthy || ng < 0 || (ng > 0 && !c->gpu_usage))) {
+    set_error("klm_collect: null node column");
+    return KLM_EINVAL;
+  }
+  // ---- ring branch: tick ingest, then the window statistics of every series
   const int64_t S = h->n_series;
   float *d_min = nullptr, *d_max = nullptr, *d_p95 = nullptr;
   double* d_mean = nullptr;
@@ -597,76 +711,133 @@ extern "C" int klm_collect(klm_handle* h, const klm_collect_in* in, const klm_co
     KLM_TRY(klm_dev_window_stats(h->ring.as<float>(), h->seen.as<uint32_t>(), h->window, h->pitch, 0, S,
                                  d_min, d_max, d_mean, out->win_p95 ? d_p95 : nullptr, st));
   }
-  // ---- node snapshot: one upload of the columns serves the rates and the aggregate
-  const int64_t n = in->n_nodes, np = in->n_pods;
+  // ---- snapshot branch: one upload of the columns serves the rates and the aggregate
   const size_t col8 = align256((size_t)n * 8), col4 = align256((size_t)n * 4), col1 = align256((size_t)n);
+  const size_t o_gc = 6 * col8, o_hl = o_gc + col4, o_pod = o_hl + col1;
+  const size_t o_gu = o_pod + align256((size_t)np), in_bytes = o_gu + align256((size_t)ng * 8);
+  const size_t out_bytes = 256 + 5 * col8;  // cluster_out | cpu, memory, disk usage, disk rate, pressure
+  const bool want_rates = (out->cpu_rate || out->memory_rate || out->disk_usage || out->disk_rate ||
+                           out->under_pressure) && n > 0;
+  const bool staged = in_bytes <= kStageMax && out_bytes <= kStageMax;
   klm_node_cols d{};
-  const bool want_rates = out->cpu_rate || out->memory_rate || out->disk_usage || out->disk_rate ||
-                          out->under_pressure;
   char* rout = nullptr;
+  klm_cluster_out* d_cluster = h->agg_out.as<klm_cluster_out>();
   if (n > 0 || np > 0) {
-    const klm_node_cols* c = in->nodes;
-    const int64_t ng = (n > 0 && c) ? c->n_gpu_usage : 0;
-    if (n > 0 && (!c->cpu_capacity || !c->cpu_usage || !c->memory_capacity || !c->memory_usage ||
-                  !c->gpu_count || !c->healthy || ng < 0 || (ng > 0 && !c->gpu_usage))) {
-      set_error("klm_collect: null node column");
-      return KLM_EINVAL;
-    }
-    KLM_TRY(h->agg_cols.ensure(6 * col8 + col4 + col1 + 256));
-    KLM_TRY(h->agg_pods.ensure((size_t)np + 256));
-    KLM_TRY(h->agg_gpu.ensure((size_t)ng * 8 + 256));
+    uint8_t* d_pods;
+    KLM_TRY(h->agg_cols.ensure((staged ? in_bytes : o_pod) + 256));
     char* base = h->agg_cols.as<char>();
+    if (staged) {
+      d_pods = reinterpret_cast<uint8_t*>(base + o_pod);
+      d.gpu_usage = reinterpret_cast<double*>(base + o_gu);
+    } else {
+      KLM_TRY(h->agg_pods.ensure((size_t)np + 256));
+      KLM_TRY(h->agg_gpu.ensure((size_t)ng * 8 + 256));
+      d_pods = h->agg_pods.as<uint8_t>();
+      d.gpu_usage = h->agg_gpu.as<double>();
+    }
     d.cpu_capacity = reinterpret_cast<int64_t*>(base);
     d.cpu_usage = reinterpret_cast<int64_t*>(base + col8);
     d.memory_capacity = reinterpret_cast<int64_t*>(base + 2 * col8);
     d.memory_usage = reinterpret_cast<int64_t*>(base + 3 * col8);
     int64_t* d_dcap = reinterpret_cast<int64_t*>(base + 4 * col8);
     int64_t* d_dalloc = reinterpret_cast<int64_t*>(base + 5 * col8);
-    d.gpu_count = reinterpret_cast<int32_t*>(base + 6 * col8);
-    d.healthy = reinterpret_cast<uint8_t*>(base + 6 * col8 + col4);
-    d.gpu_usage = h->agg_gpu.as<double>();
+    d.gpu_count = reinterpret_cast<int32_t*>(base + o_gc);
+    d.healthy = reinterpret_cast<uint8_t*>(base + o_hl);
     d.n_gpu_usage = ng;
+    // the same layout on the host side of the staged path; `put` is a memcpy there and a
+    // copy submission otherwise
+    if (staged) KLM_TRY(h->snap_pin.ensure(2 * kStageMax));
+    auto put = [&](size_t off, void* dev, const void* src, size_t bytes) -> int {
+      if (bytes == 0 || !src) return KLM_OK;
+      if (staged) {
+        std::memcpy(h->snap_pin.at(off), src, bytes);
+        return KLM_OK;
+      }
+      return h2d(dev, src, bytes, st2);
+    };
     if (n > 0) {
-      KLM_TRY(h2d((void*)d.cpu_capacity, c->cpu_capacity, (size_t)n * 8, st));
-      KLM_TRY(h2d((void*)d.cpu_usage, c->cpu_usage, (size_t)n * 8, st));
-      KLM_TRY(h2d((void*)d.memory_capacity, c->memory_capacity, (size_t)n * 8, st));
-      KLM_TRY(h2d((void*)d.memory_usage, c->memory_usage, (size_t)n * 8, st));
-      KLM_TRY(h2d((void*)d.gpu_count, c->gpu_count, (size_t)n * 4, st));
-      KLM_TRY(h2d((void*)d.healthy, c->healthy, (size_t)n, st));
-      KLM_TRY(h2d((void*)d.gpu_usage, c->gpu_usage, (size_t)ng * 8, st));
-      if (in->disk_capacity) KLM_TRY(h2d(d_dcap, in->disk_capacity, (size_t)n * 8, st));
-      if (in->disk_allocatable) KLM_TRY(h2d(d_dalloc, in->disk_allocatable, (size_t)n * 8, st));
+      KLM_TRY(put(0, (void*)d.cpu_capacity, c->cpu_capacity, (size_t)n * 8));
+      KLM_TRY(put(col8, (void*)d.cpu_usage, c->cpu_usage, (size_t)n * 8));
+      KLM_TRY(put(2 * col8, (void*)d.memory_capacity, c->memory_capacity, (size_t)n * 8));
+      KLM_TRY(put(3 * col8, (void*)d.memory_usage, c->memory_usage, (size_t)n * 8));
+      KLM_TRY(put(4 * col8, d_dcap, in->disk_capacity, (size_t)n * 8));
+      KLM_TRY(put(5 * col8, d_dalloc, in->disk_allocatable, (size_t)n * 8));
+      KLM_TRY(put(o_gc, (void*)d.gpu_count, c->gpu_count, (size_t)n * 4));
+      KLM_TRY(put(o_hl, (void*)d.healthy, c->healthy, (size_t)n));
+      KLM_TRY(put(o_gu, (void*)d.gpu_usage, c->gpu_usage, (size_t)ng * 8));
     }
-    KLM_TRY(h2d(h->agg_pods.p, in->pod_running, (size_t)np, st));
-    if (want_rates && n > 0) {
-      KLM_TRY(h->rate_out.ensure(5 * col8));
-      rout = h->rate_out.as<char>();
+    KLM_TRY(put(o_pod, d_pods, in->pod_running, (size_t)np));
+    if (staged) KLM_TRY(h2d(base, h->snap_pin.p, in_bytes, st2));
+    if (staged) {
+      KLM_TRY(h->snap_out.ensure(out_bytes));
+      d_cluster = h->snap_out.as<klm_cluster_out>();
+    }
+    if (want_rates) {
+      if (staged) {
+        rout = h->snap_out.as<char>() + 256;
+      } else {
+        KLM_TRY(h->rate_out.ensure(5 * col8));
+        rout = h->rate_out.as<char>();
+      }
       KLM_TRY(klm_dev_node_rates(n, d.cpu_capacity, d.cpu_usage, d.memory_capacity, d.memory_usage,
                                  in->disk_capacity ? d_dcap : nullptr,
                                  in->disk_allocatable ? d_dalloc : nullptr,
                                  reinterpret_cast<double*>(rout), reinterpret_cast<double*>(rout + col8),
                                  reinterpret_cast<int64_t*>(rout + 2 * col8),
                                  reinterpret_cast<double*>(rout + 3 * col8),
-                                 reinterpret_cast<uint8_t*>(rout + 4 * col8), st));
+                                 reinterpret_cast<uint8_t*>(rout + 4 * col8), st2));
+    }
+    if (out->cluster) {
+      KLM_TRY(klm_dev_cluster_aggregate(&d, n, d_pods, np, d_cluster, h->agg_scratch.p, st2));
+    }
+  } else if (out->cluster) {
+    KLM_TRY(klm_dev_cluster_aggregate(&d, 0, nullptr, 0, d_cluster, h->agg_scratch.p, st2));
+  }
+  const bool staged_out = staged && (n > 0 || np > 0);
+  char* hout = staged_out ? h->snap_pin.at(kStageMax) : nullptr;
+  if (staged_out) {
+    KLM_TRY(d2h(hout, h->snap_out.p, rout ? out_bytes : 256, st2));
+  } else {
+    if (out->cluster) KLM_TRY(d2h(out->cluster, d_cluster, sizeof(klm_cluster_out), st2));
+    if (rout) {
+      if (out->cpu_rate) KLM_TRY(d2h(out->cpu_rate, rout, (size_t)n * 8, st2));
+      if (out->memory_rate) KLM_TRY(d2h(out->memory_rate, rout + col8, (size_t)n * 8, st2));
+      if (out->disk_usage) KLM_TRY(d2h(out->disk_usage, rout + 2 * col8, (size_t)n * 8, st2));
+      if (out->disk_rate) KLM_TRY(d2h(out->disk_rate, rout + 3 * col8, (size_t)n * 8, st2));
+      if (out->under_pressure) KLM_TRY(d2h(out->under_pressure, rout + 4 * col8, (size_t)n, st2));
     }
   }
-  if (out->cluster) {
-    KLM_TRY(klm_dev_cluster_aggregate(&d, n, h->agg_pods.as<uint8_t>(), np,
-                                      h->agg_out.as<klm_cluster_out>(), h->agg_scratch.p, st));
-    KLM_TRY(d2h(out->cluster, h->agg_out.p, sizeof(klm_cluster_out), st));
-  }
-  if (rout) {
-    if (out->cpu_rate) KLM_TRY(d2h(out->cpu_rate, rout, (size_t)n * 8, st));
-    if (out->memory_rate) KLM_TRY(d2h(out->memory_rate, rout + col8, (size_t)n * 8, st));
-    if (out->disk_usage) KLM_TRY(d2h(out->disk_usage, rout + 2 * col8, (size_t)n * 8, st));
-    if (out->disk_rate) KLM_TRY(d2h(out->disk_rate, rout + 3 * col8, (size_t)n * 8, st));
-    if (out->under_pressure) KLM_TRY(d2h(out->under_pressure, rout + 4 * col8, (size_t)n, st));
-  }
+  // ---- ring branch, second half: the statistics go straight to the caller's arrays
   if (want_win) {
     if (out->win_min) KLM_TRY(d2h(out->win_min, d_min, (size_t)S * 4, st));
     if (out->win_max) KLM_TRY(d2h(out->win_max, d_max, (size_t)S * 4, st));
     if (out->win_mean) KLM_TRY(d2h(out->win_mean, d_mean, (size_t)S * 8, st));
     if (out->win_p95) KLM_TRY(d2h(out->win_p95, d_p95, (size_t)S * 4, st));
   }
+  // ---- join; the snapshot branch finishes first, so its host-side scatter overlaps K7
+  KLM_TRY(sync(st2));
+  if (staged_out) {
+    if (out->cluster) std::memcpy(out->cluster, hout, sizeof(klm_cluster_out));
+    if (rout) {
+      const char* r = hout + 256;
+      if (out->cpu_rate) std::memcpy(out->cpu_rate, r, (size_t)n * 8);
+      if (out->memory_rate) std::memcpy(out->memory_rate, r + col8, (size_t)n * 8);
+      if (out->disk_usage) std::memcpy(out->disk_usage, r + 2 * col8, (size_t)n * 8);
+      if (out->disk_rate) std::memcpy(out->disk_rate, r + 3 * col8, (size_t)n * 8);
+      if (out->under_pressure) std::memcpy(out->under_pressure, r + 4 * col8, (size_t)n);
+    }
+  }
   return sync(st);
+}
+
+}  // namespace
+
+extern "C" int klm_collect(klm_handle* h, const klm_collect_in* in, const klm_collect_out* out) {
+  KLM_ENTER(h);
+  const int rc = collect_impl(h, in, out);
+  if (rc != KLM_OK) {  // leave nothing in flight that still reads or writes the staging blocks
+    cudaStreamSynchronize(h->stream);
+    cudaStreamSynchronize(h->stream2);
+  }
+  return rc;
 }

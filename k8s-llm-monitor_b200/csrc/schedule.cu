@@ -136,6 +136,8 @@ node_best_kernel(const double* __restrict__ battery, const uint8_t* __restrict__
 // ---------------------------------------------------------------- K2
 
 constexpr int kSchedThreads = 256;
+constexpr int kSchedUnroll = 4;  // requests per thread per pass
+constexpr int kSchedSlots = 2;   // preferred ids fetched up front (the common list lengths)
 
 // One thread per request. Winner = best of {g} U {preferred nodes that pass
 // every filter}, where g is K1's result: a non-preferred node other than g
@@ -150,32 +152,75 @@ schedule_kernel(const double* __restrict__ battery, const uint8_t* __restrict__ 
                 int32_t* __restrict__ out_idx, double* __restrict__ out_score) {
   const int64_t g = best[0];
   const double gb = __longlong_as_double(best[1]);
-  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-  for (int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; r < n_requests; r += stride) {
-    const double mb = min_battery[r];
-    const bool gate = mb > 0;  // controller.go:194
-    int64_t bi = -1;
-    double bs = 0.0;
-    if (g >= 0 && !(gate && gb < mb)) {
-      bi = g;
-      bs = gb;
-      const int32_t k1 = pref_off[r + 1];
-      for (int32_t k = pref_off[r]; k < k1; ++k) {
-        const int64_t p = pref_ids[k];
-        const int64_t lp = p - node_base;
-        if (lp < 0 || lp >= n) continue;
-        if ((flags[lp] & 3u) != 3u) continue;  // :190, :198
-        const double b = battery[lp];
-        if (gate && b < mb) continue;          // :194
-        const double s = b + 10;               // :205-208
-        if (s > bs || (s == bs && p < bi)) {
-          bs = s;
-          bi = p;
+  // A request is a chain of dependent loads (offsets -> ids -> node columns), each level an
+  // L2 or DRAM round trip, so one request per thread leaves the kernel waiting on latency.
+  // Every thread therefore carries kSchedUnroll requests and issues each level's loads for
+  // all of them (and for the first kSchedSlots preferred ids of each) before using any.
+  const int64_t tile = (int64_t)blockDim.x * kSchedUnroll;
+  for (int64_t base = (int64_t)blockIdx.x * tile; base < n_requests; base += (int64_t)gridDim.x * tile) {
+    double mb[kSchedUnroll];
+    int32_t k0[kSchedUnroll], k1[kSchedUnroll];
+#pragma unroll
+    for (int j = 0; j < kSchedUnroll; ++j) {
+      const int64_t r = base + (int64_t)j * blockDim.x + threadIdx.x;
+      const bool live = r < n_requests;
+      mb[j] = live ? min_battery[r] : 0.0;
+      k0[j] = live ? pref_off[r] : 0;
+      k1[j] = live ? pref_off[r + 1] : 0;
+    }
+    int32_t p[kSchedUnroll][kSchedSlots];
+#pragma unroll
+    for (int j = 0; j < kSchedUnroll; ++j)
+#pragma unroll
+      for (int q = 0; q < kSchedSlots; ++q) p[j][q] = k0[j] + q < k1[j] ? pref_ids[k0[j] + q] : -1;
+    uint8_t f[kSchedUnroll][kSchedSlots];
+    double b[kSchedUnroll][kSchedSlots];
+#pragma unroll
+    for (int j = 0; j < kSchedUnroll; ++j)
+#pragma unroll
+      for (int q = 0; q < kSchedSlots; ++q) {
+        const int64_t lp = (int64_t)p[j][q] - node_base;
+        const bool in = p[j][q] >= 0 && lp >= 0 && lp < n;
+        f[j][q] = in ? flags[lp] : (uint8_t)0;  // 0 fails the name/status test below
+        b[j][q] = in ? battery[lp] : 0.0;
+      }
+#pragma unroll
+    for (int j = 0; j < kSchedUnroll; ++j) {
+      const int64_t r = base + (int64_t)j * blockDim.x + threadIdx.x;
+      if (r >= n_requests) continue;
+      const bool gate = mb[j] > 0;  // controller.go:194
+      int64_t bi = -1;
+      double bs = 0.0;
+      if (g >= 0 && !(gate && gb < mb[j])) {
+        bi = g;
+        bs = gb;
+#pragma unroll
+        for (int q = 0; q < kSchedSlots; ++q) {
+          if ((f[j][q] & 3u) != 3u) continue;     // :190, :198
+          if (gate && b[j][q] < mb[j]) continue;  // :194
+          const double s = b[j][q] + 10;          // :205-208
+          if (s > bs || (s == bs && p[j][q] < bi)) {
+            bs = s;
+            bi = p[j][q];
+          }
+        }
+        for (int32_t k = k0[j] + kSchedSlots; k < k1[j]; ++k) {  // longer preferred lists
+          const int64_t pk = pref_ids[k];
+          const int64_t lp = pk - node_base;
+          if (lp < 0 || lp >= n) continue;
+          if ((flags[lp] & 3u) != 3u) continue;
+          const double bk = battery[lp];
+          if (gate && bk < mb[j]) continue;
+          const double s = bk + 10;
+          if (s > bs || (s == bs && pk < bi)) {
+            bs = s;
+            bi = pk;
+          }
         }
       }
+      out_idx[r] = (int32_t)bi;
+      out_score[r] = bs;
     }
-    out_idx[r] = (int32_t)bi;
-    out_score[r] = bs;
   }
 }
 
@@ -363,7 +408,8 @@ extern "C" int klm_dev_schedule(const double* battery, const uint8_t* flags, int
     set_error("klm_dev_schedule: null request array");
     return KLM_EINVAL;
   }
-  schedule_kernel<<<grid_for(n_requests, kSchedThreads, 16), kSchedThreads, 0, as_stream(stream)>>>(
+  schedule_kernel<<<grid_for(ceil_div(n_requests, (int64_t)kSchedUnroll), kSchedThreads, 8), kSchedThreads, 0,
+                    as_stream(stream)>>>(
       battery, flags, n_nodes, node_base, best, n_requests, min_battery, pref_off, pref_ids,
       out_idx, out_score);
   KLM_LAUNCH_CHECK("schedule_kernel");

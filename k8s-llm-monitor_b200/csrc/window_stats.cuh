@@ -117,9 +117,10 @@ __device__ __forceinline__ void sort64_desc(uint32_t& k0, uint32_t& k1, int lane
 }
 
 constexpr int kMaxCand = 64;  // candidates sorted exactly at the end of select_from_lists
+constexpr int kListPrefill = 24;  // list entries per lane the kernels pre-fill with -inf
 
 // The k-th largest of the elements held in the lane lists (lst = this lane's list, entry e at
-// lst[e * 32]; entries below 32 beyond the lane's count already hold -inf). `a` is a value
+// lst[e * 32]; entries below kListPrefill beyond the lane's count already hold -inf). `a` is a value
 // with count_ge(a) == total >= k (every listed element is >= a); mx is the window maximum.
 // `fin` is 64 floats of scratch owned by the warp. Counting passes test two pivots at a
 // time (first the sample hints, then interpolation on the counts) until <= 64 candidates
@@ -131,8 +132,8 @@ __device__ __forceinline__ float select_from_lists(float* lst, float* fin, int l
                                                    int total, int maxcnt, int k, float a, float mx,
                                                    bool have_hints, float hint_lo, float hint_hi) {
   const int m8 = (maxcnt + 7) & ~7;
-  // entries below 32 were pre-filled with -inf; pad the rare longer lists here
-  for (int e = max(cnt, 32); e < m8; ++e) lst[e * 32] = NEG_INF;
+  // entries below kListPrefill were pre-filled with -inf; pad the rare longer lists here
+  for (int e = max(cnt, kListPrefill); e < m8; ++e) lst[e * 32] = NEG_INF;
   fin[lane] = NEG_INF;
   fin[lane + 32] = NEG_INF;
   __syncwarp();

@@ -275,7 +275,7 @@ window_stats_pipe_kernel(const float* __restrict__ ring, const uint32_t* __restr
     // while the row is on its way: fill this lane's list with -inf (entries a pass does not
     // overwrite must compare below every pivot)
 #pragma unroll
-    for (int e = 0; e < kPipeLaneCap; ++e) lst[e * 32] = NEG_INF;
+    for (int e = 0; e < kListPrefill; ++e) lst[e * 32] = NEG_INF;
 
     const int slot = (int)(q % n_slots);
     const uint32_t round = (uint32_t)(q / n_slots);
@@ -381,7 +381,7 @@ window_stats_pipe_kernel(const float* __restrict__ ring, const uint32_t* __restr
         else if (!tie_mode && total < k && t3 < t2) lox2 = next_down(key_f32(t3));
         if (lox2 != POS_INF) {
 #pragma unroll
-          for (int e = 0; e < kPipeLaneCap; ++e) lst[e * 32] = NEG_INF;
+          for (int e = 0; e < kListPrefill; ++e) lst[e * 32] = NEG_INF;
           lox = lox2;
           c128 = 0;
           float d0, d1;

@@ -196,10 +196,10 @@ window_stats_warp_kernel(const float* __restrict__ ring, const uint32_t* __restr
       }
     }
   }
-  // While the loads are in flight: fill the first 32 entries of this lane's list with -inf,
+  // While the loads are in flight: fill the first kListPrefill entries of this lane's list with -inf,
   // so the counting passes need no padding later (longer lists are padded when they occur).
 #pragma unroll
-  for (int e = 0; e < 32; ++e) lst[e * 32] = NEG_INF;
+  for (int e = 0; e < kListPrefill; ++e) lst[e * 32] = NEG_INF;
   const int n = sn < (uint32_t)window ? (int)sn : window;
   if (n == 0) {
     if (lane == 0) {
@@ -346,7 +346,7 @@ window_stats_warp_kernel(const float* __restrict__ ring, const uint32_t* __restr
     if (total < k && !tie_mode && lox_retry != POS_INF) {
       // the pivot was too high: redo the append (only) from the next sample statistic down
 #pragma unroll
-      for (int e = 0; e < 32; ++e) lst[e * 32] = NEG_INF;
+      for (int e = 0; e < kListPrefill; ++e) lst[e * 32] = NEG_INF;
       lox = lox_retry;
       c128 = 0;
       w.append_pass(lox, lb, c128);

@@ -177,11 +177,14 @@ def test_k7_variants_agree(dev, t):
         check_stats({k: v.cpu().numpy() for k, v in o.items()}, want, variant)
 
 
-def test_collect_cycle_matches_separate_calls(handle, pkg):
+@pytest.mark.parametrize("n,p", [(333, 2111), (40_000, 90_001), (0, 17), (5, 0)],
+                         ids=["staged", "direct", "no_nodes", "no_pods"])
+def test_collect_cycle_matches_separate_calls(handle, pkg, n, p):
     """klm_collect (one Manager.Collect cycle in one call) == ingest + stats + rates +
-    aggregate done separately, and == the oracle."""
+    aggregate done separately, and == the oracle. Small snapshots cross PCIe as one staged
+    block each way, large ones column by column; both run beside the ring branch."""
     rng = np.random.default_rng(77)
-    s, t, n, p = 700, 1200, 333, 2111
+    s, t = 700, 1200
     rows = distributions(rng, s, t)
     snap = pkg.synth.cluster_snapshot(2, n, p, gpus_per_node=1)
     ring = np.ascontiguousarray(rows)

@@ -56,6 +56,23 @@ def test_random_tie_heavy(handle, pkg, seed):
     _eq(bru, want, "bruteforce")
 
 
+@pytest.mark.parametrize("n,r", [(300, 40), (300, 30_000), (60_000, 40), (60_000, 30_000)],
+                         ids=["staged/staged", "staged/direct", "direct/staged", "direct/direct"])
+def test_staged_and_direct_copy_paths(handle, pkg, n, r):
+    """Small node tables and small batches cross PCIe as one staged block each way, large
+    ones array by array (abi.cu, kStageMax); every combination gives the oracle's answer.
+    Two snapshots are installed back to back first: a staged klm_nodes_set returns before
+    the GPU has read the staging block, and the next one must wait for that."""
+    rng = np.random.default_rng(n * 7 + r)
+    stale = helpers.random_problem(rng, n, 1, kmax=1, grid=1.0)
+    handle.nodes_set(stale[0], stale[1])
+    bat, flags, mb, off, ids = helpers.random_problem(rng, n, r, kmax=3, grid=0.5)
+    want = ob.schedule_scan(bat, flags, mb, off, ids, threads=8)  # the literal loop, threaded
+    handle.nodes_set(bat, flags)
+    for _ in range(2):
+        _eq(handle.schedule_batch(mb, off, ids), want, "decomposed")
+
+
 def test_edge_shapes(handle, pkg):
     # no nodes at all
     e = np.zeros(0)
