@@ -300,6 +300,75 @@ class Handle:
         o["cluster"] = cl.as_dict()
         return o
 
+    # -- prepared calls: argument structs built once, then only the C call per cycle. This is
+    #    what a compiled caller (the cgo shim) pays; the convenience wrappers above spend
+    #    ~30 us per call on array coercion and struct building. Arrays are used in place, so
+    #    they must already be contiguous, of the exact dtype, and stay alive and unmoved.
+    @staticmethod
+    def _exact(a, dtype, name):
+        if not isinstance(a, np.ndarray) or a.dtype != dtype or not a.flags["C_CONTIGUOUS"]:
+            raise ValueError(f"{name}: prepared calls need a C-contiguous numpy array of {np.dtype(dtype)}")
+        return a.ctypes.data if a.size else None
+
+    def collect_prepared(self, snap: dict, out: dict):
+        """Returns call(tick) -> ClusterOut dict; fills `out` (keys as collect()) in place."""
+        ex = self._exact
+        cols = [ex(snap[k], dt, k) for k, dt in (("cpu_capacity", np.int64), ("cpu_usage", np.int64),
+                                                 ("memory_capacity", np.int64), ("memory_usage", np.int64),
+                                                 ("gpu_count", np.int32), ("healthy", np.uint8))]
+        gu = snap.get("gpu_usage")
+        n_gu = 0 if gu is None else gu.size
+        nc = NodeCols(*cols, ex(gu, np.float64, "gpu_usage") if n_gu else None, n_gu)
+        n, p = snap["cpu_capacity"].size, snap["pod_running"].size
+        cl = ClusterOut()
+        cin = CollectIn(None, C.pointer(nc), n, ex(snap["disk_capacity"], np.int64, "disk_capacity"),
+                        ex(snap["disk_allocatable"], np.int64, "disk_allocatable"),
+                        ex(snap["pod_running"], np.uint8, "pod_running"), p)
+        dts = (("cpu_rate", np.float64), ("memory_rate", np.float64), ("disk_usage", np.int64),
+               ("disk_rate", np.float64), ("under_pressure", np.uint8), ("min", np.float32),
+               ("max", np.float32), ("mean", np.float64), ("p95", np.float32))
+        cout = CollectOut(C.pointer(cl), *[ex(out[k], dt, k) for k, dt in dts])
+        fn, h, pin_, pout = self._lib.klm_collect, self._h, C.byref(cin), C.byref(cout)
+        keep = (nc, cl, cin, cout, snap, out)
+        s = self._ring_shape[0]
+
+        def call(tick):
+            if tick is not None:
+                if tick.dtype != np.float32 or tick.size != s or not tick.flags["C_CONTIGUOUS"]:
+                    raise ValueError("tick: need float32[n_series], C-contiguous")
+                cin.tick_values = tick.ctypes.data
+            else:
+                cin.tick_values = None
+            rc = fn(h, pin_, pout)
+            if rc != KLM_OK:
+                raise KlmError(rc, last_error())
+            return cl
+        call.keep = keep
+        return call
+
+    def reconcile_prepared(self, battery, flags, min_battery, pref_off, pref_ids, out_idx, out_score,
+                           algo: int = ALGO_DECOMPOSED):
+        """Returns call(): klm_nodes_set + klm_schedule_batch on the given arrays, results in
+        out_idx / out_score (one reconcile: snapshot, then every pending request)."""
+        ex = self._exact
+        n, r = battery.size, min_battery.size
+        if flags.size != n or pref_off.size != r + 1 or out_idx.size != r or out_score.size != r:
+            raise ValueError("reconcile_prepared: array lengths disagree")
+        a = [ex(battery, np.float64, "battery"), ex(flags, np.uint8, "flags"),
+             ex(min_battery, np.float64, "min_battery"), ex(pref_off, np.int32, "pref_off"),
+             ex(pref_ids, np.int32, "pref_ids"), ex(out_idx, np.int32, "out_idx"),
+             ex(out_score, np.float64, "out_score")]
+        set_fn, batch_fn, h = self._lib.klm_nodes_set, self._lib.klm_schedule_batch, self._h
+
+        def call():
+            rc = set_fn(h, n, a[0], a[1])
+            if rc == KLM_OK:
+                rc = batch_fn(h, r, a[2], a[3], a[4], a[5], a[6], algo)
+            if rc != KLM_OK:
+                raise KlmError(rc, last_error())
+        call.keep = (battery, flags, min_battery, pref_off, pref_ids, out_idx, out_score)
+        return call
+
     def ring_stats(self, s0: int = 0, s1: Optional[int] = None, p95: bool = True) -> dict:
         if s1 is None:
             s1 = self._ring_shape[0]

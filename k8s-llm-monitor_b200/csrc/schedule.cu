@@ -298,6 +298,7 @@ schedule_bruteforce_kernel(const double* __restrict__ battery, const uint8_t* __
 
 // Per request, fold the partial winners of the node-range shards. Global
 // indices make "lowest index on ties" independent of which rank held the node.
+constexpr int kMergeChunk = 8;  // parts whose loads are in flight together
 __global__ void __launch_bounds__(256)
 merge_partials_kernel(int n_parts, int64_t n_requests, const int32_t* __restrict__ part_idx,
                       const double* __restrict__ part_score, int32_t* __restrict__ out_idx,
@@ -306,13 +307,23 @@ merge_partials_kernel(int n_parts, int64_t n_requests, const int32_t* __restrict
   for (int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; r < n_requests; r += stride) {
     int32_t bi = -1;
     double bs = 0.0;
-    for (int g = 0; g < n_parts; ++g) {
-      const int32_t i = part_idx[(int64_t)g * n_requests + r];
-      if (i < 0) continue;
-      const double s = part_score[(int64_t)g * n_requests + r];
-      if (bi < 0 || s > bs || (s == bs && i < bi)) {
-        bs = s;
-        bi = i;
+    // all loads of a chunk of parts are issued before the first compare (the score is read
+    // whether or not the index is valid), so a request costs one memory round trip per chunk
+    for (int g0 = 0; g0 < n_parts; g0 += kMergeChunk) {
+      int32_t pi[kMergeChunk];
+      double ps[kMergeChunk];
+#pragma unroll
+      for (int j = 0; j < kMergeChunk; ++j) {
+        const bool live = g0 + j < n_parts;
+        pi[j] = live ? __ldcs(part_idx + (int64_t)(g0 + j) * n_requests + r) : -1;
+        ps[j] = live ? __ldcs(part_score + (int64_t)(g0 + j) * n_requests + r) : 0.0;
+      }
+#pragma unroll
+      for (int j = 0; j < kMergeChunk; ++j) {
+        if (pi[j] >= 0 && (bi < 0 || ps[j] > bs || (ps[j] == bs && pi[j] < bi))) {
+          bs = ps[j];
+          bi = pi[j];
+        }
       }
     }
     out_idx[r] = bi;
@@ -450,7 +461,7 @@ extern "C" int klm_dev_merge_partials(int n_parts, int64_t n_requests, const int
     return KLM_EINVAL;
   }
   if (n_requests == 0) return KLM_OK;
-  merge_partials_kernel<<<grid_for(n_requests, 256, 16), 256, 0, as_stream(stream)>>>(
+  merge_partials_kernel<<<grid_for(n_requests, 256, 1 << 16), 256, 0, as_stream(stream)>>>(
       n_parts, n_requests, part_idx, part_score, out_idx, out_score);
   KLM_LAUNCH_CHECK("merge_partials_kernel");
   return KLM_OK;

@@ -205,3 +205,37 @@ def test_collect_cycle_matches_separate_calls(handle, pkg, n, p):
     again = handle.collect(None, snap)      # no tick: statistics unchanged
     for k in ("min", "max", "p95", "mean"):
         assert np.array_equal(again[k], got[k])
+
+
+def test_prepared_calls_match_wrappers(pkg):
+    """collect_prepared / reconcile_prepared (structs built once, bare C calls per cycle, what
+    bench.py's e2e leg times) give exactly what the convenience wrappers give."""
+    rng = np.random.default_rng(5)
+    s, t, n, p, r = 300, 500, 120, 900, 7
+    rows = distributions(rng, s, t)
+    snap = pkg.synth.cluster_snapshot(2, n, p, gpus_per_node=2)
+    bat, flags = pkg.synth.node_table(2, n)
+    mb, off, ids = pkg.synth.requests(2, r, n, k_fixed=2)
+    with pkg.Handle(0) as a, pkg.Handle(0) as b:
+        for h in (a, b):
+            h.ring_create(s, t)
+            h.ring_load(0, rows[:, : t - 1])
+        out = {"cpu_rate": np.empty(n), "memory_rate": np.empty(n), "disk_usage": np.empty(n, np.int64),
+               "disk_rate": np.empty(n), "under_pressure": np.empty(n, np.uint8), "min": np.empty(s, np.float32),
+               "max": np.empty(s, np.float32), "mean": np.empty(s), "p95": np.empty(s, np.float32)}
+        res_i, res_s = np.empty(r, np.int32), np.empty(r)
+        collect = b.collect_prepared(snap, out)
+        reconcile = b.reconcile_prepared(bat, flags, mb, off, ids, res_i, res_s)
+        for cycle in range(3):
+            tick = (rng.random(s) * 100).astype(np.float32)
+            want = a.collect(tick, snap)
+            cl = collect(tick)
+            assert cl.as_dict() == want["cluster"]
+            for k in out:
+                assert np.array_equal(out[k], want[k]), (cycle, k)
+            a.nodes_set(bat, flags)
+            wi, ws = a.schedule_batch(mb, off, ids)
+            reconcile()
+            assert np.array_equal(res_i, wi) and np.array_equal(res_s, ws)
+        with pytest.raises(ValueError):
+            b.collect_prepared(snap, dict(out, min=np.empty(s, np.float64)))  # wrong dtype: refused
