@@ -110,7 +110,11 @@ int klm_abi_version(void);
 
 /* Install the UAV snapshot of one reconcile (controller.go:96-98): one entry
  * per UAVMetric item in list order. battery = readFloat(spec, "battery",
- * "remaining_percent") (controller.go:187, :252-272; missing -> 0). */
+ * "remaining_percent") (controller.go:187, :252-272; missing -> 0).
+ * The arrays are consumed before the call returns. For tables up to 256 KB
+ * the call does not wait for the GPU (the table is staged in page-locked
+ * memory owned by the handle), so a device fault raised by this upload is
+ * reported by the next call that synchronises, klm_schedule_batch included. */
 int klm_nodes_set(klm_handle* h, int64_t n_nodes, const double* battery,
                   const uint8_t* flags);
 
