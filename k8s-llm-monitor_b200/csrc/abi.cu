@@ -9,6 +9,7 @@
 //   internal/metrics/manager.go:195-319       Collect -> calculateClusterMetrics
 //   internal/metrics/manager.go:391-449       UpdateUAVReport (ring ingest)
 // There is no CPU fallback: every entry point needs a live CUDA device.
+#include <algorithm>
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
@@ -87,6 +88,11 @@ struct PinBuf {
 // memcpy would cost more than the extra copy submissions and the arrays are sent directly.
 constexpr size_t kStageMax = 256 << 10;
 
+// klm_schedule_batch pipelines batches of at least 2 * kChunkRequests requests over two
+// streams, in at most kMaxChunks chunks of at least kChunkRequests requests.
+constexpr int64_t kChunkRequests = 128 << 10;
+constexpr int64_t kMaxChunks = 8;
+
 }  // namespace klm
 
 using namespace klm;
@@ -101,6 +107,7 @@ struct klm_handle {
   // block has been read, i.e. the block may be overwritten
   PinBuf sched_pin, snap_pin;
   cudaEvent_t sched_read = nullptr;
+  cudaEvent_t ev_fork = nullptr, ev_chain[2] = {nullptr, nullptr};  // chunked klm_schedule_batch
 
   // scheduling
   int64_t n_nodes = -1;  // -1: no snapshot installed yet
@@ -209,6 +216,9 @@ extern "C" int klm_create(const int* device_ids, int n_dev, klm_handle** out) {
   e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);
   if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->stream2, cudaStreamNonBlocking);
   if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->sched_read, cudaEventDisableTiming);
+  if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming);
+  if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->ev_chain[0], cudaEventDisableTiming);
+  if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->ev_chain[1], cudaEventDisableTiming);
   if (e != cudaSuccess) {
     klm_destroy(h);
     return cuda_fail(e, "cudaStreamCreateWithFlags / cudaEventCreateWithFlags");
@@ -247,6 +257,9 @@ extern "C" void klm_destroy(klm_handle* h) {
   h->sched_pin.release();
   h->snap_pin.release();
   if (h->sched_read) cudaEventDestroy(h->sched_read);
+  if (h->ev_fork) cudaEventDestroy(h->ev_fork);
+  for (cudaEvent_t ev : h->ev_chain)
+    if (ev) cudaEventDestroy(ev);
   if (h->stream2) cudaStreamDestroy(h->stream2);
   if (h->stream) cudaStreamDestroy(h->stream);
   delete h;
@@ -351,6 +364,45 @@ extern "C" int klm_schedule_batch(klm_handle* h, int64_t R, const double* min_ba
     d_ids = h->req_ids.as<int32_t>();
     d_idx = h->res_idx.as<int32_t>();
     d_score = h->res_score.as<double>();
+    if (algo == KLM_ALGO_DECOMPOSED && R >= 2 * kChunkRequests) {
+      // A large batch is PCIe time, not kernel time (C4: 17 MB in, 12 MB out, 16 us of K2),
+      // so it is cut into chunks that alternate between the two streams: chunk c's download
+      // runs while chunk c+1 uploads (separate copy engines) and K2 disappears between them.
+      // With pageable caller arrays the driver stages every copy synchronously and the
+      // chunks simply run back to back.
+      const int64_t n_chunks = std::min<int64_t>(kMaxChunks, R / kChunkRequests);
+      for (int64_t c = 0; c < n_chunks; ++c) {  // before anything is in flight
+        const int64_t i0 = pref_off[R * c / n_chunks], i1 = pref_off[R * (c + 1) / n_chunks];
+        if (i0 < 0 || i1 < i0 || i1 > n_ids) {
+          set_error("klm_schedule_batch: pref_off is not non-decreasing within [0, pref_off[R]]");
+          return KLM_EINVAL;
+        }
+      }
+      cudaStream_t ss[2] = {h->stream, h->stream2};
+      // stream2 has not seen the node table or K1's result (a staged klm_nodes_set does not
+      // synchronise)
+      KLM_CUDA(cudaEventRecord(h->ev_fork, h->stream));
+      KLM_CUDA(cudaStreamWaitEvent(h->stream2, h->ev_fork, 0));
+      for (int64_t c = 0; c < n_chunks; ++c) {
+        const int64_t r0 = R * c / n_chunks, r1 = R * (c + 1) / n_chunks;
+        const int64_t i0 = pref_off[r0], i1 = pref_off[r1];
+        cudaStream_t st = ss[c & 1];
+        // offsets (r0, r1]: entry r0 came with the previous chunk (entry 0 with the first)
+        const int64_t o0 = c == 0 ? 0 : r0 + 1;
+        KLM_TRY(h2d(d_min + r0, min_battery + r0, (size_t)(r1 - r0) * sizeof(double), st));
+        KLM_TRY(h2d(d_off + o0, pref_off + o0, (size_t)(r1 + 1 - o0) * sizeof(int32_t), st));
+        KLM_TRY(h2d(d_ids + i0, pref_ids + i0, (size_t)(i1 - i0) * sizeof(int32_t), st));
+        KLM_CUDA(cudaEventRecord(h->ev_chain[c & 1], st));
+        // ... which is why this chunk's kernel waits for the previous chunk's upload
+        if (c > 0) KLM_CUDA(cudaStreamWaitEvent(st, h->ev_chain[(c - 1) & 1], 0));
+        KLM_TRY(klm_dev_schedule(h->d_battery, h->d_flags, h->n_nodes, 0, h->best.as<int64_t>(), r1 - r0,
+                                 d_min + r0, d_off + r0, d_ids, d_idx + r0, d_score + r0, st));
+        KLM_TRY(d2h(out_idx + r0, d_idx + r0, (size_t)(r1 - r0) * sizeof(int32_t), st));
+        KLM_TRY(d2h(out_score + r0, d_score + r0, (size_t)(r1 - r0) * sizeof(double), st));
+      }
+      KLM_TRY(sync(h->stream2));
+      return sync(h->stream);
+    }
     KLM_TRY(h2d(d_min, min_battery, min_bytes, h->stream));
     KLM_TRY(h2d(d_off, pref_off, off_bytes, h->stream));
     KLM_TRY(h2d(d_ids, pref_ids, ids_bytes, h->stream));

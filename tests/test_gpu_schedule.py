@@ -73,6 +73,34 @@ def test_staged_and_direct_copy_paths(handle, pkg, n, r):
         _eq(handle.schedule_batch(mb, off, ids), want, "decomposed")
 
 
+@pytest.mark.parametrize("r", [262_144, 300_001, 1_100_000])
+def test_chunked_batch_with_pinned_arrays(pkg, r):
+    """Batches of >= 256 k requests are cut into chunks that alternate between two streams
+    (abi.cu, kChunkRequests). With page-locked caller arrays every copy is truly asynchronous,
+    so this is the case where a missing dependency between the chunks would show."""
+    import torch
+    pin = lambda a: torch.from_numpy(np.ascontiguousarray(a)).pin_memory().numpy()
+    rng = np.random.default_rng(r)
+    n = 20_000
+    bat, flags, mb, off, ids = helpers.random_problem(rng, n, r, kmax=4, grid=0.5)
+    want = ob.schedule_decomposed(bat, flags, mb, off, ids)
+    lit = ob.schedule_scan(bat, flags, mb[:2000], off[:2001], ids[: off[2000]], threads=8)
+    assert np.array_equal(lit[0], want[0][:2000]) and np.array_equal(lit[1], want[1][:2000])
+    bat, flags, mb, off, ids = map(pin, (bat, flags, mb, off, ids))
+    res_i, res_s = pin(np.empty(r, np.int32)), pin(np.empty(r))
+    with pkg.Handle(0) as h:
+        call = h.reconcile_prepared(bat, flags, mb, off, ids, res_i, res_s)
+        for _ in range(3):
+            res_i.fill(-7)
+            res_s.fill(np.nan)
+            call()
+            _eq((res_i, res_s), want, f"chunked R={r}")
+        bad = off.copy()
+        bad[r // 2] = bad[-1] + 5          # a chunk boundary beyond pref_off[R]
+        with pytest.raises(pkg.binding.KlmError):
+            h.schedule_batch(mb, bad, ids)
+
+
 def test_edge_shapes(handle, pkg):
     # no nodes at all
     e = np.zeros(0)
