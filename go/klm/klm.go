@@ -204,3 +204,19 @@ func (k *Handle) RingStats(s0, s1 int64) (*WindowStats, error) {
 	}
 	return w, nil
 }
+
+// HostFloat64s returns a slice of n float64 backed by page-locked C memory
+// (klm_host_alloc). Arrays passed to the klm_* calls may be ordinary Go
+// slices, but the driver stages those synchronously; page-locked arrays make
+// the copies asynchronous, which lets klm_collect overlap its two branches and
+// klm_schedule_batch pipeline a large batch over PCIe. Release with HostFree.
+func HostFloat64s(n int) ([]float64, error) {
+	var p unsafe.Pointer
+	if rc := C.klm_host_alloc(C.size_t(n*8), &p); rc != 0 {
+		return nil, lastErr("klm_host_alloc")
+	}
+	return unsafe.Slice((*float64)(p), n), nil
+}
+
+// HostFree releases a slice obtained from a Host* allocator.
+func HostFree(p unsafe.Pointer) { C.klm_host_free(p) }

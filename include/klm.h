@@ -28,6 +28,7 @@
 #ifndef KLM_H_
 #define KLM_H_
 
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
@@ -105,6 +106,16 @@ void klm_destroy(klm_handle* h);
 const char* klm_last_error(void);
 /* ABI version of this header: major*1000 + minor. */
 int klm_abi_version(void);
+
+/* Page-locked host memory for the caller's arrays (no reference counterpart).
+ * Every klm_* call accepts ordinary pageable arrays, but the CUDA driver
+ * stages those synchronously; with arrays from klm_host_alloc the copies are
+ * asynchronous, which is what lets klm_collect overlap its two branches and
+ * klm_schedule_batch pipeline a large batch over PCIe. From Go: wrap the
+ * pointer with unsafe.Slice; it is C memory, so the cgo pointer rules do not
+ * restrict it. Free with klm_host_free (NULL is a no-op). */
+int klm_host_alloc(size_t bytes, void** out);
+int klm_host_free(void* p);
 
 /* ------------------------------------------------------------ scheduling */
 

@@ -80,6 +80,8 @@ SIGNATURES = {
     "klm_destroy": (None, [_P]),
     "klm_last_error": (C.c_char_p, []),
     "klm_abi_version": (C.c_int, []),
+    "klm_host_alloc": (C.c_int, [C.c_size_t, C.POINTER(_P)]),
+    "klm_host_free": (C.c_int, [_P]),
     "klm_nodes_set": (C.c_int, [_P, _I64, _P, _P]),
     "klm_schedule_batch": (C.c_int, [_P, _I64, _P, _P, _P, _P, _P, C.c_int]),
     "klm_cluster_aggregate": (C.c_int, [_P, C.POINTER(NodeCols), _I64, _P, _I64, C.POINTER(ClusterOut)]),
@@ -134,6 +136,21 @@ def load() -> C.CDLL:
         fn.argtypes = args
     _lib = lib
     return lib
+
+
+def host_array(shape, dtype) -> np.ndarray:
+    """numpy array on page-locked memory from klm_host_alloc (freed when the array dies)."""
+    import weakref
+    lib = load()
+    dt = np.dtype(dtype)
+    n = int(np.prod(shape))
+    p = _P()
+    rc = lib.klm_host_alloc(max(1, n * dt.itemsize), C.byref(p))
+    if rc != KLM_OK:
+        raise KlmError(rc, last_error())
+    buf = (C.c_char * max(1, n * dt.itemsize)).from_address(p.value)
+    weakref.finalize(buf, lib.klm_host_free, p.value)
+    return np.frombuffer(buf, dtype=dt, count=n).reshape(shape)
 
 
 def last_error() -> str:

@@ -31,6 +31,9 @@ void set_error(const char* fmt, ...) {
 
 int cuda_fail(cudaError_t e, const char* what) {
   set_error("CUDA error %d (%s) in %s", (int)e, cudaGetErrorString(e), what);
+  // reset the runtime's per-thread last error: a recoverable failure (an allocation that
+  // did not fit) must not be reported again by the next launch check
+  (void)cudaGetLastError();
   return KLM_ECUDA;
 }
 
@@ -175,7 +178,24 @@ size_t align256(size_t b) { return (b + 255) & ~size_t(255); }
 }  // namespace
 
 extern "C" const char* klm_last_error(void) { return g_err; }
-extern "C" int klm_abi_version(void) { return 1000; }
+extern "C" int klm_abi_version(void) { return 1001; }
+
+extern "C" int klm_host_alloc(size_t bytes, void** out) {
+  if (!out || bytes == 0) {
+    set_error("klm_host_alloc: bad argument");
+    return KLM_EINVAL;
+  }
+  *out = nullptr;
+  // portable: usable with every handle of the process, whichever device it drives
+  KLM_CUDA(cudaHostAlloc(out, bytes, cudaHostAllocPortable));
+  return KLM_OK;
+}
+
+extern "C" int klm_host_free(void* p) {
+  if (!p) return KLM_OK;
+  KLM_CUDA(cudaFreeHost(p));
+  return KLM_OK;
+}
 
 extern "C" int klm_create(const int* device_ids, int n_dev, klm_handle** out) {
   if (!out) {

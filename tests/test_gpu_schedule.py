@@ -101,6 +101,31 @@ def test_chunked_batch_with_pinned_arrays(pkg, r):
             h.schedule_batch(mb, bad, ids)
 
 
+def test_host_alloc_arrays(pkg):
+    """klm_host_alloc gives page-locked arrays a caller can fill and pass to any klm_* call."""
+    b = pkg.binding
+    rng = np.random.default_rng(3)
+    n, r = 4000, 300_000
+    prob = helpers.random_problem(rng, n, r, kmax=2, grid=1.0)
+    want = ob.schedule_decomposed(*prob)
+    arrs = []
+    for a in prob:
+        ha = b.host_array(a.shape, a.dtype)
+        ha[...] = a
+        arrs.append(ha)
+    res_i, res_s = b.host_array(r, np.int32), b.host_array(r, np.float64)
+    with pkg.Handle(0) as h:
+        call = h.reconcile_prepared(*arrs, res_i, res_s)
+        call()
+        _eq((res_i, res_s), want, "host_alloc arrays")
+        assert b.load().klm_host_free(None) == 0
+        with pytest.raises(b.KlmError):
+            b.host_array(1 << 50, np.uint8)   # beyond host memory: a clean error, not a crash
+        res_i.fill(-7)
+        call()                                 # and it does not poison the calls that follow
+        _eq((res_i, res_s), want, "after a failed allocation")
+
+
 def test_edge_shapes(handle, pkg):
     # no nodes at all
     e = np.zeros(0)
