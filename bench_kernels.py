@@ -113,7 +113,7 @@ def main():
     timeit(f"K5 node_rates N={n}", k5, (48 + 33) * n)
 
     # ---- K6 / K7
-    s, t = 26_000, 3600
+    s, t = 26_000, int(os.environ.get("KLM_BK_WINDOW", "3600"))
     ring = (torch.rand((s, t), device="cuda") * 100).float()
     seen = torch.full((s,), t, dtype=torch.int32, device="cuda")
     tick = torch.rand(s, device="cuda")

@@ -13,7 +13,8 @@ from typing import Optional, Tuple
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libklm.so")
+# KLM_LIB_NAME picks a sibling build (tools/build_variant.sh: ablation / tuning experiments)
+LIB_PATH = os.path.join(_HERE, os.environ.get("KLM_LIB_NAME", "libklm.so"))
 
 KLM_OK, KLM_EINVAL, KLM_ECUDA, KLM_ENODEV, KLM_ESTATE, KLM_ELIMIT = 0, -1, -2, -3, -4, -5
 NODE_HAS_NAME, NODE_STATUS_OK, NODE_ELIGIBLE = 1, 2, 3

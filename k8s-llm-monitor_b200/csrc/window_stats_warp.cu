@@ -43,13 +43,19 @@ constexpr int kLaneListBytes = kLaneCap * 128;  // [entry][lane] f32; power of t
 // shared memory: first the lane lists (8 KB per warp, each on an 8 KB boundary), then per
 // warp 64 candidates + a counter (512 B)
 constexpr int kWarpAux = 512;
+#ifndef KLM_WSW_EXTRA_SMEM  // experiments: unused shared memory per CTA, to lower the occupancy
+#define KLM_WSW_EXTRA_SMEM 0
+#endif
 constexpr size_t kWswSmemBytes =
-    (size_t)kWswWarps * (kLaneListBytes + kWarpAux) + kLaneListBytes;  // + alignment slack
+    (size_t)kWswWarps * (kLaneListBytes + kWarpAux) + kLaneListBytes + KLM_WSW_EXTRA_SMEM;  // + alignment slack
 
 // if (x > lox) { lane_list[c / 128 mod 64] = x; c += 128; }
 // lb = 8 KB-aligned list base | lane * 4, so the slot address is (c & 0x1F80) | lb.
 // The address lives in a temporary: the store never holds up the counter.
 __device__ __forceinline__ void append_if_gt(uint32_t& c, uint32_t lb, float x, float lox) {
+#ifdef KLM_ABL_NOAPPEND
+  return;
+#endif
   asm volatile(
       "{\n\t.reg .pred p;\n\t.reg .b32 t;\n\t"
       "setp.gt.f32 p, %2, %3;\n\t"
@@ -60,21 +66,56 @@ __device__ __forceinline__ void append_if_gt(uint32_t& c, uint32_t lb, float x, 
       : "r"(lb), "f"(x), "f"(lox));
 }
 
-template <int NV>
+// Ablation switches (tools/build_variant.sh; timing experiments only, the results are then
+// wrong): each removes one phase so that its cost can be read off as a difference.
+#if defined(KLM_ABL_NOSUM)
+#define KLM_SUM4(acc, a, b, c, d) ((void)0)
+#elif defined(KLM_ABL_F32SUM)
+#define KLM_SUM4(acc, a, b, c, d) acc += (double)(((a) + (b)) + ((c) + (d)))
+#else
+#define KLM_SUM4(acc, a, b, c, d) acc += ((double)(a) + (double)(b)) + ((double)(c) + (double)(d))
+#endif
+
+// The window of one series, spread over a warp: row j (j < NV) is float4 l + 32 j of lane
+// l. Rows below NR live in registers, the other NS = NV - NR rows in shared memory, each
+// lane reading back only the float4 it loaded itself (no cross-lane traffic, so no
+// barrier). NR == NV keeps everything in registers (166 registers at NV = 29: 3 CTAs per
+// SM); NR = 19 fits 128 registers, i.e. a fourth CTA per SM, and the kernel is bound by the
+// latency the resident warps can hide, not by issue slots ("K7 in detail").
+template <int NV, int NR>
 struct Window {
-  static constexpr int NE = NV * 4;
-  float v[NE];   // element 4 j + c = sample 4 (lane + 32 j) + c, or -inf
-  float tail;    // lane c < (n & 3) holds sample 4 (n / 4) + c, else -inf
+  static constexpr int NS = NV - NR;
+  float v[4 * NR];  // element 4 j + c = sample 4 (lane + 32 j) + c, or -inf
+  float tail;       // lane c < (n & 3) holds sample 4 (n / 4) + c, else -inf
+  uint32_t srow;    // shared address of this lane's float4 of row NR (row j: + 512 (j - NR))
+
+  __device__ __forceinline__ float4 row(int j) const {
+    if (j < NR) return make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+    float4 t;
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
+                 : "=f"(t.x), "=f"(t.y), "=f"(t.z), "=f"(t.w)
+                 : "r"(srow + (uint32_t)((j - NR) * 512)));
+    return t;
+  }
+  __device__ __forceinline__ void set_row_neg_inf(int j) {
+    if (j < NR) {
+      v[4 * j] = v[4 * j + 1] = v[4 * j + 2] = v[4 * j + 3] = NEG_INF;
+    } else {
+      asm volatile("st.shared.v4.f32 [%0], {%1, %1, %1, %1};"
+                   :: "r"(srow + (uint32_t)((j - NR) * 512)), "f"(NEG_INF) : "memory");
+    }
+  }
 
   // number of samples >= p (all lanes get the warp total)
   __device__ __forceinline__ int count_ge(float p) const {
     int c0 = 0, c1 = 0, c2 = 0, c3 = 0;
 #pragma unroll
     for (int j = 0; j < NV; ++j) {
-      inc_if_ge(c0, v[4 * j + 0], p);
-      inc_if_ge(c1, v[4 * j + 1], p);
-      inc_if_ge(c2, v[4 * j + 2], p);
-      inc_if_ge(c3, v[4 * j + 3], p);
+      const float4 t = row(j);
+      inc_if_ge(c0, t.x, p);
+      inc_if_ge(c1, t.y, p);
+      inc_if_ge(c2, t.z, p);
+      inc_if_ge(c3, t.w, p);
     }
     inc_if_ge(c0, tail, p);
     return warp_sum_i32((c0 + c1) + (c2 + c3));
@@ -98,7 +139,13 @@ struct Window {
   // append(x > lox) only: the retry after a pivot that listed fewer than k elements
   __device__ __forceinline__ void append_pass(float lox, uint32_t lb, uint32_t& c) const {
 #pragma unroll
-    for (int i = 0; i < NE; ++i) append_if_gt(c, lb, v[i], lox);
+    for (int j = 0; j < NV; ++j) {
+      const float4 t = row(j);
+      append_if_gt(c, lb, t.x, lox);
+      append_if_gt(c, lb, t.y, lox);
+      append_if_gt(c, lb, t.z, lox);
+      append_if_gt(c, lb, t.w, lox);
+    }
     append_if_gt(c, lb, tail, lox);
   }
 
@@ -113,22 +160,23 @@ struct Window {
     double sum0 = 0.0, sum1 = 0.0;
 #pragma unroll
     for (int j = 0; j < NV; ++j) {
-      const float a = v[4 * j], b = v[4 * j + 1], cc = v[4 * j + 2], d = v[4 * j + 3];
+      const float4 t4 = row(j);
+      const float a = t4.x, b = t4.y, cc = t4.z, d = t4.w;
       const bool uniform_valid = FULL ? (j < NV - 1) : (j < jr);
       if (uniform_valid) {
         if (j & 1) {
           mn1 = fminf(fminf(mn1, a), fminf(b, fminf(cc, d)));
           mx1 = fmaxf(fmaxf(mx1, a), fmaxf(b, fmaxf(cc, d)));
-          sum1 += ((double)a + (double)b) + ((double)cc + (double)d);
+          KLM_SUM4(sum1, a, b, cc, d);
         } else {
           mn0 = fminf(fminf(mn0, a), fminf(b, fminf(cc, d)));
           mx0 = fmaxf(fmaxf(mx0, a), fmaxf(b, fmaxf(cc, d)));
-          sum0 += ((double)a + (double)b) + ((double)cc + (double)d);
+          KLM_SUM4(sum0, a, b, cc, d);
         }
       } else if (lane + 32 * j < nfull) {  // boundary row: some lanes hold data
         mn0 = fminf(fminf(mn0, a), fminf(b, fminf(cc, d)));
         mx0 = fmaxf(fmaxf(mx0, a), fmaxf(b, fmaxf(cc, d)));
-        sum0 += ((double)a + (double)b) + ((double)cc + (double)d);
+        KLM_SUM4(sum0, a, b, cc, d);
       }
       append_if_gt(c, lb, a, lox);  // pads are -inf: never appended
       append_if_gt(c, lb, b, lox);
@@ -147,8 +195,8 @@ struct Window {
   }
 };
 
-template <int NV>
-__global__ void __launch_bounds__(kWswThreads, KLM_WSW_MIN_BLOCKS)
+template <int NV, int NR, int MINB>
+__global__ void __launch_bounds__(kWswThreads, MINB)
 window_stats_warp_kernel(const float* __restrict__ ring, const uint32_t* __restrict__ seen,
                          int32_t window, int32_t pitch, int64_t s0, int64_t n_series,
                          float* __restrict__ out_min, float* __restrict__ out_max,
@@ -163,38 +211,56 @@ window_stats_warp_kernel(const float* __restrict__ ring, const uint32_t* __restr
   const uint32_t sn = seen[s];  // consumed only after the row loads below are in flight
 
   // shared memory of this warp; the lane lists must start on their own size boundary
+  constexpr int NS = NV - NR;
   const uint32_t raw_s = (uint32_t)__cvta_generic_to_shared(s_raw);
   const uint32_t base_s = (raw_s + (uint32_t)kLaneListBytes - 1u) & ~((uint32_t)kLaneListBytes - 1u);
   unsigned char* base_g = s_raw + (base_s - raw_s);
   float* lst = reinterpret_cast<float*>(base_g + wib * kLaneListBytes) + lane;  // entry e: lst[e * 32]
-  unsigned char* aux = base_g + kWswWarps * kLaneListBytes + wib * kWarpAux;
-  float* fin = reinterpret_cast<float*>(aux);
   const uint32_t lb = (base_s + (uint32_t)wib * kLaneListBytes) | ((uint32_t)lane << 2);
+  unsigned char* aux;
+  uint32_t rows_s = 0;  // shared address of this warp's window rows (NS > 0)
+  if (NS == 0) {
+    aux = base_g + kWswWarps * kLaneListBytes + wib * kWarpAux;
+  } else {
+    // Dynamic shared memory starts 1 KB into the CTA's window (the system reserve), so 7 KB
+    // precede the first 8 KB boundary: they take the four aux areas and warp 0's rows, the
+    // rows of warps 1..3 follow the lists. Nothing is lost to alignment, 4 CTAs fit per SM.
+    if (base_s - raw_s < (uint32_t)(kWswWarps * kWarpAux + NS * 512)) __trap();  // host checked
+    aux = s_raw + wib * kWarpAux;
+    rows_s = wib == 0 ? raw_s + (uint32_t)(kWswWarps * kWarpAux)
+                      : base_s + (uint32_t)(kWswWarps * kLaneListBytes + (wib - 1) * NS * 512);
+  }
+  float* fin = reinterpret_cast<float*>(aux);
 
   // ---- 1. load. The addresses do not depend on seen[s]: every float4 inside the row
   // pitch is fetched (stale slots beyond n are masked below), so the row loads and the
   // seen[] load share one memory round trip.
-  Window<NV> w;
+  Window<NV, NR> w;
+  w.srow = rows_s + ((uint32_t)lane << 4);
   {
     const int pfull = pitch >> 2;
     const float* p = row + 4 * lane;
+    // rows kept in shared memory arrive by asynchronous 16-byte copies, every lane its own
+    // float4 (slots outside the pitch stay unwritten and are overwritten with -inf below)
+    auto fetch = [&](int j, bool pred) {
+      if (j < NR) {
+        float4 t = make_float4(NEG_INF, NEG_INF, NEG_INF, NEG_INF);
+        if (pred) t = ld_stream_f4(p + 128 * j);
+        w.v[4 * j + 0] = t.x; w.v[4 * j + 1] = t.y; w.v[4 * j + 2] = t.z; w.v[4 * j + 3] = t.w;
+      } else if (pred) {
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;"
+                     :: "r"(w.srow + (uint32_t)((j - NR) * 512)), "l"(p + 128 * j) : "memory");
+      }
+    };
     if (pfull >= 32 * (NV - 1)) {  // usual case: all rows but the last lie inside the pitch
 #pragma unroll
-      for (int j = 0; j < NV - 1; ++j) {
-        const float4 t = ld_stream_f4(p + 128 * j);
-        w.v[4 * j + 0] = t.x; w.v[4 * j + 1] = t.y; w.v[4 * j + 2] = t.z; w.v[4 * j + 3] = t.w;
-      }
-      float4 t = make_float4(NEG_INF, NEG_INF, NEG_INF, NEG_INF);
-      if (lane + 32 * (NV - 1) < pfull) t = ld_stream_f4(p + 128 * (NV - 1));
-      w.v[4 * NV - 4] = t.x; w.v[4 * NV - 3] = t.y; w.v[4 * NV - 2] = t.z; w.v[4 * NV - 1] = t.w;
+      for (int j = 0; j < NV - 1; ++j) fetch(j, true);
+      fetch(NV - 1, lane + 32 * (NV - 1) < pfull);
     } else {
 #pragma unroll
-      for (int j = 0; j < NV; ++j) {
-        float4 t = make_float4(NEG_INF, NEG_INF, NEG_INF, NEG_INF);
-        if (lane + 32 * j < pfull) t = ld_stream_f4(p + 128 * j);
-        w.v[4 * j + 0] = t.x; w.v[4 * j + 1] = t.y; w.v[4 * j + 2] = t.z; w.v[4 * j + 3] = t.w;
-      }
+      for (int j = 0; j < NV; ++j) fetch(j, lane + 32 * j < pfull);
     }
+    if (NS > 0) asm volatile("cp.async.commit_group;" ::: "memory");
   }
   // While the loads are in flight: fill the first kListPrefill entries of this lane's list with -inf,
   // so the counting passes need no padding later (longer lists are padded when they occur).
@@ -224,14 +290,13 @@ window_stats_warp_kernel(const float* __restrict__ ring, const uint32_t* __restr
   const int jr = nfull >> 5;  // rows valid in every lane
   const bool full = jr >= NV - 1;
   // mask the slots at and beyond n: rows below jr are valid in every lane
+  if (NS > 0) asm volatile("cp.async.wait_group 0;" ::: "memory");  // this lane's own copies
   if (full) {
-    if (!(lane + 32 * (NV - 1) < nfull))
-      w.v[4 * NV - 4] = w.v[4 * NV - 3] = w.v[4 * NV - 2] = w.v[4 * NV - 1] = NEG_INF;
+    if (!(lane + 32 * (NV - 1) < nfull)) w.set_row_neg_inf(NV - 1);
   } else {
 #pragma unroll
     for (int j = 0; j < NV; ++j)
-      if (j >= jr && !(lane + 32 * j < nfull))
-        w.v[4 * j] = w.v[4 * j + 1] = w.v[4 * j + 2] = w.v[4 * j + 3] = NEG_INF;
+      if (j >= jr && !(lane + 32 * j < nfull)) w.set_row_neg_inf(j);
   }
   w.tail = (lane < (n & 3)) ? row[4 * nfull + lane] : NEG_INF;
 
@@ -245,21 +310,30 @@ window_stats_warp_kernel(const float* __restrict__ ring, const uint32_t* __restr
   bool tie_hit = false;            // the heavy-tie test already found the answer
   float tie_val = 0.f;
   const bool want_p95 = out_p95 != nullptr;
+#ifdef KLM_ABL_NOPIVOT
+  const bool sampled = false;
+#else
   const bool sampled = want_p95 && jr >= kSampledMinRows;
+#endif
 
   // ---- 2. sample pivot: four groups of 32 (one sample row each), top three of each
   if (sampled) {
     float sm[4];
     if (full) {  // the rows are known at compile time
 #pragma unroll
-      for (int q = 0; q < 4; ++q) sm[q] = w.v[4 * (((2 * q + 1) * (NV - 1)) >> 3) + q];
+      for (int q = 0; q < 4; ++q) sm[q] = w.v[4 * (((2 * q + 1) * (NR - 1)) >> 3) + q];  // register rows
     } else {
 #pragma unroll
       for (int q = 0; q < 4; ++q) {
         const int jq = ((2 * q + 1) * jr) >> 3;
         float t = NEG_INF;
 #pragma unroll
-        for (int j = 0; j < NV; ++j) t = (j == jq) ? w.v[4 * j + q] : t;
+        for (int j = 0; j < NV; ++j) {
+          if (j == jq) {  // warp-uniform
+            const float4 r4 = w.row(j);
+            t = q == 0 ? r4.x : q == 1 ? r4.y : q == 2 ? r4.z : r4.w;
+          }
+        }
         sm[q] = t;
       }
     }
@@ -339,6 +413,9 @@ window_stats_warp_kernel(const float* __restrict__ ring, const uint32_t* __restr
     if (bisect) break;
     if (tie_hit) { result = tie_val; break; }
     if (mn == mx) { result = mx; break; }  // constant series
+#ifdef KLM_ABL_NOSELECT
+    result = lox; break;
+#endif
     int cnt = (int)(c128 >> 7);
     int total = warp_sum_i32(cnt);
     int maxcnt = warp_max_i32(cnt);
@@ -368,10 +445,23 @@ window_stats_warp_kernel(const float* __restrict__ ring, const uint32_t* __restr
   if (lane == 0) out_p95[o] = result;
 }
 
-template <int NV>
+// dynamic shared memory of one CTA: NR == NV: lists (with alignment slack) then aux; else the
+// layout described in the kernel, which counts on the 1 KB system reserve before it
+template <int NV, int NR>
+constexpr size_t wsw_smem_bytes() {
+  return NR == NV ? kWswSmemBytes
+                  : (size_t)(kLaneListBytes - 1024) + (size_t)kWswWarps * kLaneListBytes +
+                        (size_t)(kWswWarps - 1) * (NV - NR) * 512 + KLM_WSW_EXTRA_SMEM;
+}
+
+template <int NV, int NR, int MINB>
 static int launch_warp(const float* ring, const uint32_t* seen, int32_t window, int32_t pitch,
                        int64_t s0, int64_t n_series, float* out_min, float* out_max,
                        double* out_mean, float* out_p95, cudaStream_t st) {
+  static_assert(KLM_WSW_EXTRA_SMEM != 0 || MINB * (wsw_smem_bytes<NV, NR>() + 1024) <= 227 * 1024,
+                "the CTAs per SM must fit");
+  static_assert(NR == NV || kWswWarps * kWarpAux + (NV - NR) * 512 <= kLaneListBytes - 1024,
+                "aux areas + one warp's rows must fit below the first list boundary");
   const int64_t blocks = ceil_div(n_series, kWswWarps);
   if (blocks > 0x7fffffff) {
     set_error("klm_dev_window_stats: too many series for one launch");
@@ -381,30 +471,50 @@ static int launch_warp(const float* ring, const uint32_t* seen, int32_t window, 
   int dev = 0;
   KLM_CUDA(cudaGetDevice(&dev));
   if (!(dev < 64 && attr_set[dev])) {
-    // 3 CTAs x 57 KB per SM: opt in above 48 KB and ask for the largest shared-memory carve-out
-    KLM_CUDA(cudaFuncSetAttribute(window_stats_warp_kernel<NV>,
-                                  cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kWswSmemBytes));
-    KLM_CUDA(cudaFuncSetAttribute(window_stats_warp_kernel<NV>,
+    // opt in above 48 KB and ask for the largest shared-memory carve-out
+    KLM_CUDA(cudaFuncSetAttribute(window_stats_warp_kernel<NV, NR, MINB>,
+                                  cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  (int)wsw_smem_bytes<NV, NR>()));
+    KLM_CUDA(cudaFuncSetAttribute(window_stats_warp_kernel<NV, NR, MINB>,
                                   cudaFuncAttributePreferredSharedMemoryCarveout,
                                   (int)cudaSharedmemCarveoutMaxShared));
     if (dev < 64) attr_set[dev] = true;
   }
-  window_stats_warp_kernel<NV><<<(unsigned)blocks, kWswThreads, kWswSmemBytes, st>>>(
+  window_stats_warp_kernel<NV, NR, MINB><<<(unsigned)blocks, kWswThreads, wsw_smem_bytes<NV, NR>(), st>>>(
       ring, seen, window, pitch, s0, n_series, out_min, out_max, out_mean, out_p95);
   KLM_LAUNCH_CHECK("window_stats_warp_kernel");
   return KLM_OK;
+}
+
+// The split layout needs dynamic shared memory to start exactly 1 KB into the CTA's window.
+static bool split_layout_ok() {
+  static int cached = -1;
+  if (cached < 0) {
+    int dev = 0, reserved = 0;
+    cached = cudaGetDevice(&dev) == cudaSuccess &&
+             cudaDeviceGetAttribute(&reserved, cudaDevAttrReservedSharedMemoryPerBlock, dev) == cudaSuccess &&
+             reserved == 1024;
+  }
+  return cached == 1;
 }
 
 // Windows up to 4096 samples take the warp kernel; returns 1 if it did not handle the call.
 int launch_window_stats_warp(const float* ring, const uint32_t* seen, int32_t window,
                              int32_t pitch, int64_t s0, int64_t s1, float* out_min,
                              float* out_max, double* out_mean, float* out_p95, cudaStream_t st) {
-  static_assert(KLM_WSW_MIN_BLOCKS * (kWswSmemBytes + 1024) <= 227 * 1024, "the CTAs per SM must fit");
   const int64_t n = s1 - s0;
-  if (window <= 8 * 128) return launch_warp<8>(ring, seen, window, pitch, s0, n, out_min, out_max, out_mean, out_p95, st);
-  if (window <= 16 * 128) return launch_warp<16>(ring, seen, window, pitch, s0, n, out_min, out_max, out_mean, out_p95, st);
-  if (window <= 29 * 128) return launch_warp<29>(ring, seen, window, pitch, s0, n, out_min, out_max, out_mean, out_p95, st);
-  if (window <= 32 * 128) return launch_warp<32>(ring, seen, window, pitch, s0, n, out_min, out_max, out_mean, out_p95, st);
+#define KLM_WSW_GO(NV, NR, MINB) \
+  return launch_warp<NV, NR, MINB>(ring, seen, window, pitch, s0, n, out_min, out_max, out_mean, out_p95, st)
+  if (window <= 8 * 128) KLM_WSW_GO(8, 8, KLM_WSW_MIN_BLOCKS);
+  if (window <= 16 * 128) KLM_WSW_GO(16, 16, KLM_WSW_MIN_BLOCKS);
+  if (window <= 29 * 128) {
+#ifndef KLM_WSW_NO_SPLIT
+    if (split_layout_ok()) KLM_WSW_GO(29, 19, 4);  // 19 rows in registers, 10 in shared memory
+#endif
+    KLM_WSW_GO(29, 29, KLM_WSW_MIN_BLOCKS);
+  }
+  if (window <= 32 * 128) KLM_WSW_GO(32, 32, KLM_WSW_MIN_BLOCKS);
+#undef KLM_WSW_GO
   return 1;
 }
 

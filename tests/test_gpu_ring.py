@@ -46,7 +46,10 @@ def distributions(rng, s, t):
     return rows
 
 
-@pytest.mark.parametrize("t", [1, 3, 4, 5, 20, 127, 128, 129, 1000, 3600, 4096, 5000, 20000])
+# 2049..3712 is the split instantiation of the warp kernel (19 rows of 128 samples in
+# registers, up to 10 in shared memory): sizes around each of its row boundaries
+@pytest.mark.parametrize("t", [1, 3, 4, 5, 20, 127, 128, 129, 1000, 2048, 2049, 2431, 2432, 2433, 2560, 3583,
+                               3584, 3585, 3600, 3711, 3712, 3713, 4096, 5000, 20000])
 def test_window_stats_distributions(handle, t):
     rng = np.random.default_rng(t)
     s = 80
@@ -70,6 +73,7 @@ def test_partial_windows_and_ranges(handle):
     handle.ring_create(s, t)
     counts = rng.integers(0, t + 1, size=s)
     counts[:4] = [0, 1, 2, t]
+    counts[4:12] = [2431, 2432, 2433, 2436, 2559, 2560, 2561, 3599]   # around the register / shared split
     for i in range(s):
         c = int(counts[i])
         if c:
