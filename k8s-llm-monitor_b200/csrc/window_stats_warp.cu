@@ -160,6 +160,7 @@ struct Window {
     double sum0 = 0.0, sum1 = 0.0;
 #pragma unroll
     for (int j = 0; j < NV; ++j) {
+      if (!FULL && j > jr) break;  // rows beyond the boundary row hold only pads (warp-uniform)
       const float4 t4 = row(j);
       const float a = t4.x, b = t4.y, cc = t4.z, d = t4.w;
       const bool uniform_valid = FULL ? (j < NV - 1) : (j < jr);
@@ -505,8 +506,11 @@ int launch_window_stats_warp(const float* ring, const uint32_t* seen, int32_t wi
   const int64_t n = s1 - s0;
 #define KLM_WSW_GO(NV, NR, MINB) \
   return launch_warp<NV, NR, MINB>(ring, seen, window, pitch, s0, n, out_min, out_max, out_mean, out_p95, st)
-  if (window <= 8 * 128) KLM_WSW_GO(8, 8, KLM_WSW_MIN_BLOCKS);
-  if (window <= 16 * 128) KLM_WSW_GO(16, 16, KLM_WSW_MIN_BLOCKS);
+  // shorter windows need fewer registers: 92 at NV = 8 (5 CTAs per SM fit anyway); NV = 16 is
+  // held to 128 for a fourth CTA (2048 samples: 76 -> 66 us at C2's series count; a fifth
+  // CTA would need 96 registers and spills)
+  if (window <= 8 * 128) KLM_WSW_GO(8, 8, 5);
+  if (window <= 16 * 128) KLM_WSW_GO(16, 16, 4);
   if (window <= 29 * 128) {
 #ifndef KLM_WSW_NO_SPLIT
     if (split_layout_ok()) KLM_WSW_GO(29, 19, 4);  // 19 rows in registers, 10 in shared memory
