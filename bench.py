@@ -374,8 +374,8 @@ def run_ours(args):
                      "peak_source": pk_src, "algorithmic_bytes_per_launch": k7_bytes,
                      "avg_launch_ms": kern_ms,
                      # dram__bytes_read.sum + dram__bytes_write.sum of one K7 launch at c2, from the
-                     # ncu --set full capture summarised in profiles/r01_k7_warp_v2h_ncu_summary.txt
-                     "traffic": 378.747e6 if (wl == "c2" and world >= 1) else None},
+                     # ncu --set full capture summarised in profiles/r01_k7_warp_v3_split_ncu_summary.txt
+                     "traffic": 379.089e6 if (wl == "c2" and world >= 1) else None},
     }
     if rank == 0:
         if world == 1 and not args.no_cpu:

@@ -265,8 +265,15 @@ window_stats_warp_kernel(const float* __restrict__ ring, const uint32_t* __restr
   }
   // While the loads are in flight: fill the first kListPrefill entries of this lane's list with -inf,
   // so the counting passes need no padding later (longer lists are padded when they occur).
+  // The first kListPrefill entries of all 32 lists are one contiguous block, written as
+  // 128-bit stores across the warp (a quarter of the store instructions; the memory
+  // instruction queue is what throttles this phase).
+  static_assert(kListPrefill % 4 == 0, "whole 512-byte warp stores");
+  float4* const lst4 = reinterpret_cast<float4*>(base_g + wib * kLaneListBytes) + lane;
 #pragma unroll
-  for (int e = 0; e < kListPrefill; ++e) lst[e * 32] = NEG_INF;
+  for (int e = 0; e < kListPrefill / 4; ++e)
+    lst4[e * 32] = make_float4(NEG_INF, NEG_INF, NEG_INF, NEG_INF);
+  __syncwarp();  // lanes append into slots another lane has just filled
   const int n = sn < (uint32_t)window ? (int)sn : window;
   if (n == 0) {
     if (lane == 0) {
@@ -423,8 +430,11 @@ window_stats_warp_kernel(const float* __restrict__ ring, const uint32_t* __restr
     if (total < k && !sampled) { result = NEG_INF; break; }  // lox = -inf: only -inf samples are unlisted
     if (total < k && !tie_mode && lox_retry != POS_INF) {
       // the pivot was too high: redo the append (only) from the next sample statistic down
+      __syncwarp();
 #pragma unroll
-      for (int e = 0; e < kListPrefill; ++e) lst[e * 32] = NEG_INF;
+      for (int e = 0; e < kListPrefill / 4; ++e)
+        lst4[e * 32] = make_float4(NEG_INF, NEG_INF, NEG_INF, NEG_INF);
+      __syncwarp();
       lox = lox_retry;
       c128 = 0;
       w.append_pass(lox, lb, c128);
