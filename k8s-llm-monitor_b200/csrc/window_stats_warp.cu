@@ -1,5 +1,5 @@
-// K7 window_stats, warp variant: one warp per series, the whole window held in
-// registers (windows <= 4096 samples), selection without sorting.
+// K7 window_stats, warp variant: one warp per series, the whole window resident on chip
+// (windows <= 4096 samples), selection without sorting.
 //
 // No reference code exists for this (the reference keeps only the latest
 // snapshot, internal/metrics/manager.go:29, :289-290); definition in
@@ -7,21 +7,26 @@
 //
 // Per series (n valid samples, k = n - rank95 = how many samples are >= p95):
 //   1. 128-bit streaming loads: lane l takes float4 l + 32 j (j < NV), so a warp
-//      reads its row as NV fully coalesced 512-byte requests. Pads are -inf.
-//   2. 128 samples (4 rows spread over the window, one group of 32 per row):
-//      the three largest of each group by three rounds of warp-wide max (redux),
-//      the four groups interleaved. Pivot = the smallest of the four "third
-//      largest" values: about 14 % of the window lies above it and fewer than k
-//      samples do with probability ~0.2 %.
-//   3. ONE fused pass over the registers: min / max / f64 sum, and every element
+//      reads its row as NV fully coalesced 512-byte requests. Pads are -inf. The
+//      first NR rows land in registers, the other NV - NR in shared memory
+//      (cp.async, each lane its own 16 bytes): at NV = 29 the split 19 + 10 fits
+//      128 registers and a fourth CTA per SM; this kernel is bound by the latency
+//      its resident warps can hide ("K7 in detail").
+//   2. 128 samples (4 register rows, one group of 32 per row): the three largest of
+//      each group by three rounds of warp-wide max (redux), the four groups
+//      interleaved. Pivot = the smallest of the four "second largest" values:
+//      about 10 % of the window lies above it; fewer than k samples do with
+//      probability ~5 %, and then the append alone is redone from the smallest
+//      "third largest" (~14.5 % above).
+//   3. ONE fused pass over the window: min / max / f64 sum, and every element
 //      >= the pivot is appended to a per-lane list in shared memory.
-//   4. The lists are packed into one contiguous array and narrowed by counting
-//      passes that test two pivots at a time (first the sample's own order
-//      statistics, then interpolation on the counts) until <= 32 candidates
-//      remain, which are ranked exactly against each other. Brackets that cannot
-//      shrink because of ties are peeled one distinct value at a time.
+//   4. select_from_lists (window_stats.cuh): counting passes over the lists, two
+//      pivots at a time, until <= 64 candidates remain; those are gathered (each
+//      lane knows its share, an exclusive scan hands out slots) and sorted by a
+//      64-key warp bitonic network. Brackets that cannot shrink because of ties
+//      are peeled one distinct value at a time.
 //   Heavy ties at the pivot (quantised channels, mostly-zero counters) are settled
-//   by counting passes over the registers at the tied value; anything the
+//   by counting passes over the window at the tied value; anything the
 //   shortcuts cannot place (list overflow, unlucky pivot) falls back to an exact
 //   bisection over the order-preserving key space.
 // Everything is exact: every branch ends on an input element whose rank has
