@@ -285,6 +285,20 @@ int klm_dev_schedule(const double* battery, const uint8_t* flags,
                      int64_t n_requests, const double* min_battery,
                      const int32_t* pref_off, const int32_t* pref_ids,
                      int32_t* out_idx, double* out_score, void* stream);
+/* K2 launched to overlap the kernel before it on `stream` (no reference
+ * counterpart; same result as klm_dev_schedule). Meant for the pair
+ * klm_dev_node_best -> this call: K2 starts while K1 is still running, issues
+ * all of its loads, and waits for K1 only before it reads `best` (programmatic
+ * dependent launch). CONTRACT: if the operation enqueued on `stream` just
+ * before this call is a kernel, it must write nothing this call reads except
+ * `best` -- the node columns and the request arrays must have been complete
+ * before that kernel started. Otherwise use klm_dev_schedule. */
+int klm_dev_schedule_after_best(const double* battery, const uint8_t* flags,
+                                int64_t n_nodes, int64_t node_base,
+                                const int64_t* best, int64_t n_requests,
+                                const double* min_battery, const int32_t* pref_off,
+                                const int32_t* pref_ids, int32_t* out_idx,
+                                double* out_score, void* stream);
 /* K2b schedule_bruteforce: same result, every request scans every node
  * through shared-memory tiles — the literal loop of controller.go:181-218. */
 int klm_dev_schedule_bruteforce(const double* battery, const uint8_t* flags,

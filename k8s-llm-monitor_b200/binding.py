@@ -100,6 +100,7 @@ SIGNATURES = {
     "klm_dev_node_best_static_max_nodes": (_I64, []),
     "klm_dev_node_best_static": (C.c_int, [_P, _P, _I64, _I64, _P, _P]),
     "klm_dev_schedule": (C.c_int, [_P, _P, _I64, _I64, _P, _I64, _P, _P, _P, _P, _P, _P]),
+    "klm_dev_schedule_after_best": (C.c_int, [_P, _P, _I64, _I64, _P, _I64, _P, _P, _P, _P, _P, _P]),
     "klm_dev_schedule_bruteforce": (C.c_int, [_P, _P, _I64, _I64, _I64, _P, _P, _P, _P, _P, _P]),
     "klm_dev_merge_partials": (C.c_int, [C.c_int, _I64, _P, _P, _P, _P, _P]),
     "klm_dev_merge_partials_peer": (C.c_int, [C.c_int, _P, _P, _I64, _I64, _P, _P, _P]),
@@ -480,12 +481,15 @@ class Dev:
                                          _dp(sc), _stream_ptr(stream)))
 
     def schedule(self, battery, flags, best, min_battery, pref_off, pref_ids, out_idx, out_score,
-                 node_base: int = 0, stream=None):
+                 node_base: int = 0, stream=None, after_best: bool = False):
+        """after_best=True: klm_dev_schedule_after_best (overlaps the node_best launched just
+        before it on the same stream; see the contract in klm.h)."""
         t = self.torch
         _need(min_battery, t.float64, "min_battery"); _need(pref_off, t.int32, "pref_off")
         _need(pref_ids, t.int32, "pref_ids"); _need(out_idx, t.int32, "out_idx")
         _need(out_score, t.float64, "out_score")
-        check(self.lib.klm_dev_schedule(_dp(battery), _dp(flags), battery.numel(), node_base, _dp(best),
+        fn = self.lib.klm_dev_schedule_after_best if after_best else self.lib.klm_dev_schedule
+        check(fn(_dp(battery), _dp(flags), battery.numel(), node_base, _dp(best),
                                         min_battery.numel(), _dp(min_battery), _dp(pref_off), _dp(pref_ids),
                                         _dp(out_idx), _dp(out_score), _stream_ptr(stream)))
 

@@ -72,6 +72,10 @@ node_best_kernel(const double* __restrict__ battery, const uint8_t* __restrict__
                  int64_t n, int64_t node_base, int vec_ok, int64_t* __restrict__ best,
                  unsigned int* __restrict__ ticket, double* __restrict__ part_bat,
                  int64_t* __restrict__ part_idx) {
+  // A kernel launched behind this one with programmatic stream serialisation
+  // (klm_dev_schedule_after_best) may start now: K1 occupies a fraction of the SMs and its
+  // result is needed only at the end of K2. Without such a dependent this is a no-op.
+  asm volatile("griddepcontrol.launch_dependents;");
   Best me{0.0, -1};
   const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   const int64_t nthreads = (int64_t)gridDim.x * blockDim.x;
@@ -144,14 +148,22 @@ constexpr int kSchedSlots = 2;   // preferred ids fetched up front (the common l
 // scores battery <= battery[g] <= score(g) and on equality has a higher index
 // (proved equal to the literal scan by the tests and by K2b).
 // If g fails the battery gate every node does (g has the largest battery).
+// AFTER_BEST: launched with programmatic stream serialisation right behind K1; `best` may be
+// read only after griddepcontrol.wait (K1 complete and visible), everything else before.
+template <bool AFTER_BEST>
 __global__ void __launch_bounds__(kSchedThreads)
 schedule_kernel(const double* __restrict__ battery, const uint8_t* __restrict__ flags,
                 int64_t n, int64_t node_base, const int64_t* __restrict__ best,
                 int64_t n_requests, const double* __restrict__ min_battery,
                 const int32_t* __restrict__ pref_off, const int32_t* __restrict__ pref_ids,
                 int32_t* __restrict__ out_idx, double* __restrict__ out_score) {
-  const int64_t g = best[0];
-  const double gb = __longlong_as_double(best[1]);
+  int64_t g = 0;
+  double gb = 0.0;
+  if (!AFTER_BEST) {
+    g = best[0];
+    gb = __longlong_as_double(best[1]);
+  }
+  bool have_best = !AFTER_BEST;
   // A request is a chain of dependent loads (offsets -> ids -> node columns), each level an
   // L2 or DRAM round trip, so one request per thread leaves the kernel waiting on latency.
   // Every thread therefore carries kSchedUnroll requests and issues each level's loads for
@@ -184,6 +196,12 @@ schedule_kernel(const double* __restrict__ battery, const uint8_t* __restrict__ 
         f[j][q] = in ? flags[lp] : (uint8_t)0;  // 0 fails the name/status test below
         b[j][q] = in ? battery[lp] : 0.0;
       }
+    if (!have_best) {  // first tile only: every load of this tile is in flight by now
+      asm volatile("griddepcontrol.wait;" ::: "memory");
+      g = __ldcg(best);
+      gb = __longlong_as_double(__ldcg(best + 1));
+      have_best = true;
+    }
 #pragma unroll
     for (int j = 0; j < kSchedUnroll; ++j) {
       const int64_t r = base + (int64_t)j * blockDim.x + threadIdx.x;
@@ -405,26 +423,57 @@ extern "C" int klm_dev_node_best(const double* battery, const uint8_t* flags, in
   return KLM_OK;
 }
 
+static int launch_schedule(bool after_best, const double* battery, const uint8_t* flags, int64_t n_nodes,
+                           int64_t node_base, const int64_t* best, int64_t n_requests,
+                           const double* min_battery, const int32_t* pref_off, const int32_t* pref_ids,
+                           int32_t* out_idx, double* out_score, void* stream, const char* who) {
+  if (n_nodes < 0 || n_requests < 0 || !best) {
+    set_error("%s: bad argument", who);
+    return KLM_EINVAL;
+  }
+  if (n_requests == 0) return KLM_OK;
+  if (!min_battery || !pref_off || !out_idx || !out_score) {
+    set_error("%s: null request array", who);
+    return KLM_EINVAL;
+  }
+  const int grid = grid_for(ceil_div(n_requests, (int64_t)kSchedUnroll), kSchedThreads, 8);
+  if (!after_best) {
+    schedule_kernel<false><<<grid, kSchedThreads, 0, as_stream(stream)>>>(
+        battery, flags, n_nodes, node_base, best, n_requests, min_battery, pref_off, pref_ids, out_idx,
+        out_score);
+  } else {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)grid);
+    cfg.blockDim = dim3(kSchedThreads);
+    cfg.stream = as_stream(stream);
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    KLM_CUDA(cudaLaunchKernelEx(&cfg, schedule_kernel<true>, battery, flags, n_nodes, node_base, best,
+                                n_requests, min_battery, pref_off, pref_ids, out_idx, out_score));
+  }
+  KLM_LAUNCH_CHECK("schedule_kernel");
+  return KLM_OK;
+}
+
 extern "C" int klm_dev_schedule(const double* battery, const uint8_t* flags, int64_t n_nodes,
                                 int64_t node_base, const int64_t* best, int64_t n_requests,
                                 const double* min_battery, const int32_t* pref_off,
                                 const int32_t* pref_ids, int32_t* out_idx, double* out_score,
                                 void* stream) {
-  if (n_nodes < 0 || n_requests < 0 || !best) {
-    set_error("klm_dev_schedule: bad argument");
-    return KLM_EINVAL;
-  }
-  if (n_requests == 0) return KLM_OK;
-  if (!min_battery || !pref_off || !out_idx || !out_score) {
-    set_error("klm_dev_schedule: null request array");
-    return KLM_EINVAL;
-  }
-  schedule_kernel<<<grid_for(ceil_div(n_requests, (int64_t)kSchedUnroll), kSchedThreads, 8), kSchedThreads, 0,
-                    as_stream(stream)>>>(
-      battery, flags, n_nodes, node_base, best, n_requests, min_battery, pref_off, pref_ids,
-      out_idx, out_score);
-  KLM_LAUNCH_CHECK("schedule_kernel");
-  return KLM_OK;
+  return launch_schedule(false, battery, flags, n_nodes, node_base, best, n_requests, min_battery,
+                         pref_off, pref_ids, out_idx, out_score, stream, "klm_dev_schedule");
+}
+
+extern "C" int klm_dev_schedule_after_best(const double* battery, const uint8_t* flags, int64_t n_nodes,
+                                           int64_t node_base, const int64_t* best, int64_t n_requests,
+                                           const double* min_battery, const int32_t* pref_off,
+                                           const int32_t* pref_ids, int32_t* out_idx,
+                                           double* out_score, void* stream) {
+  return launch_schedule(true, battery, flags, n_nodes, node_base, best, n_requests, min_battery,
+                         pref_off, pref_ids, out_idx, out_score, stream, "klm_dev_schedule_after_best");
 }
 
 extern "C" int klm_dev_schedule_bruteforce(const double* battery, const uint8_t* flags,

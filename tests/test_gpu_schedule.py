@@ -243,6 +243,36 @@ def test_c5_node_sharded_merge(dev, pkg, g):
         assert np.array_equal(os_.cpu().numpy(), want[1][r0:r1])
 
 
+@pytest.mark.parametrize("n,r", [(1000, 5), (100_000, 300_000), (1_000_000, 1_000_000)])
+def test_schedule_after_best_overlaps_k1(dev, pkg, n, r):
+    """klm_dev_schedule_after_best starts while the node_best launched just before it is still
+    running and may read `best` only once that kernel is complete. Two node tables with
+    different winners alternate, back to back and without synchronisation, so a K2 that read
+    `best` early would answer with the previous table's winner."""
+    import torch
+    rng = np.random.default_rng(n + r)
+    mb, off, ids = pkg.synth.requests(4, r, n)
+    t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()
+    d_mb, d_off, d_ids = t(mb), t(off), t(ids if ids.size else np.zeros(1, np.int32))
+    tables, wants = [], []
+    for k in range(2):
+        bat, flags = pkg.synth.node_table(4 + k, n)
+        bat = bat.copy()
+        bat[rng.integers(0, n)] = 99.95 + k * 0.01          # a distinct winner per table
+        tables.append((t(bat), t(flags)))
+        wants.append(ob.schedule_decomposed(bat, flags, mb, off, ids))
+    best = torch.zeros(2, dtype=torch.int64, device="cuda")
+    outs = [(torch.empty(r, dtype=torch.int32, device="cuda"), torch.empty(r, dtype=torch.float64, device="cuda"))
+            for _ in range(6)]
+    for i, (oi, os_) in enumerate(outs):
+        d_bat, d_flags = tables[i & 1]
+        dev.node_best(d_bat, d_flags, best)
+        dev.schedule(d_bat, d_flags, best, d_mb, d_off, d_ids, oi, os_, after_best=True)
+    torch.cuda.synchronize()
+    for i, (oi, os_) in enumerate(outs):
+        _eq((oi.cpu().numpy(), os_.cpu().numpy()), wants[i & 1], f"launch {i}")
+
+
 def test_bruteforce_many_prefs(handle, pkg):
     """More preferred ids than the brute-force kernel keeps in registers."""
     rng = np.random.default_rng(5)
