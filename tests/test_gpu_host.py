@@ -126,3 +126,41 @@ def test_wire_in_wire_out(host):
     host.load_requests_json(json.dumps({"items": reqs}), apimachinery_ints=True)
     got2 = host.reconcile()
     assert [g["node"] for g in got2[:3]] == [g["node"] for g in got[:3]]
+
+
+def test_wire_path_at_scale(host):
+    """A 3000-item fleet and 600 requests as JSON (mixed-case names, empty names, stale
+    statuses, missing batteries, integral and fractional minBatteryPercent): decode, one GPU
+    reconcile, and every status map equals the string-level oracle's."""
+    import json
+
+    import numpy as np
+    rng = np.random.default_rng(8)
+    n, r = 3000, 600
+    items = []
+    for i in range(n):
+        spec = {"uav_id": f"uav-{i}", "node_name": f"Node-{i:04d}" if rng.random() > 0.02 else ""}
+        if rng.random() > 0.01:
+            spec["battery"] = {"remaining_percent": round(float(rng.random() * 100), 1)}
+        st = {"collection_status": "active" if rng.random() > 0.05 else "Stale"}
+        if rng.random() < 0.1:
+            st = {}                                   # missing status counts as ok (controller.go:198)
+        items.append({"spec": spec, "status": st})
+    reqs = []
+    for q in range(r):
+        pref = [f"node-{int(rng.integers(0, n)):04d}" for _ in range(int(rng.integers(0, 4)))]
+        mbp = rng.choice([0, 20, 50.5, 80, 99.9])
+        reqs.append({"spec": {"workload": {"name": f"job-{q}", "namespace": "default"},
+                              "minBatteryPercent": float(mbp) if mbp != int(mbp) or q % 2 else int(mbp),
+                              "preferredNodes": pref}})
+    for ints in (False, True):
+        host.clear()
+        assert host.load_uavs_json(json.dumps({"items": items})) == n
+        assert host.load_requests_json(json.dumps({"items": reqs}), apimachinery_ints=ints) == r
+        host.reconcile()
+        stamp = "2025-10-17T00:00:00Z"
+        for q in range(r):
+            w = co.process_request(co.decode_spec(reqs[q]["spec"], apimachinery_ints=ints), items)
+            m = json.loads(host.status_json(q, stamp))
+            assert m == {"phase": w.phase, "assignedNode": w.assigned_node, "assignedUAV": w.assigned_uav,
+                         "score": w.score, "message": w.message, "lastUpdated": stamp}, (ints, q)
