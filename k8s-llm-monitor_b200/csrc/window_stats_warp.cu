@@ -36,6 +36,9 @@
 
 namespace klm {
 
+#ifndef KLM_WSW_NR  // register rows of the 29-row split instantiation (tuning builds)
+#define KLM_WSW_NR 19
+#endif
 #ifndef KLM_WSW_MIN_BLOCKS
 #define KLM_WSW_MIN_BLOCKS 3
 #endif
@@ -46,8 +49,8 @@ constexpr int kSampledMinRows = 7;         // below 7 full rows (896 samples) li
 constexpr int kLaneCap = 64;               // per-lane list entries (wraps beyond: overflow -> bisect)
 constexpr int kLaneListBytes = kLaneCap * 128;  // [entry][lane] f32; power of two, self-aligned
 // shared memory: first the lane lists (8 KB per warp, each on an 8 KB boundary), then per
-// warp 64 candidates + a counter (512 B)
-constexpr int kWarpAux = 512;
+// warp 64 candidates (256 B)
+constexpr int kWarpAux = 256;                  // per warp: the 64 candidates of the final sort
 #ifndef KLM_WSW_EXTRA_SMEM  // experiments: unused shared memory per CTA, to lower the occupancy
 #define KLM_WSW_EXTRA_SMEM 0
 #endif
@@ -528,7 +531,7 @@ int launch_window_stats_warp(const float* ring, const uint32_t* seen, int32_t wi
   if (window <= 16 * 128) KLM_WSW_GO(16, 16, 4);
   if (window <= 29 * 128) {
 #ifndef KLM_WSW_NO_SPLIT
-    if (split_layout_ok()) KLM_WSW_GO(29, 19, 4);  // 19 rows in registers, 10 in shared memory
+    if (split_layout_ok()) KLM_WSW_GO(29, KLM_WSW_NR, 4);  // rows in registers; the rest in shared memory
 #endif
     KLM_WSW_GO(29, 29, KLM_WSW_MIN_BLOCKS);
   }
