@@ -399,29 +399,37 @@ extern "C" int klm_schedule_batch(klm_handle* h, int64_t R, const double* min_ba
         }
       }
       cudaStream_t ss[2] = {h->stream, h->stream2};
-      // stream2 has not seen the node table or K1's result (a staged klm_nodes_set does not
-      // synchronise)
-      KLM_CUDA(cudaEventRecord(h->ev_fork, h->stream));
-      KLM_CUDA(cudaStreamWaitEvent(h->stream2, h->ev_fork, 0));
-      for (int64_t c = 0; c < n_chunks; ++c) {
-        const int64_t r0 = R * c / n_chunks, r1 = R * (c + 1) / n_chunks;
-        const int64_t i0 = pref_off[r0], i1 = pref_off[r1];
-        cudaStream_t st = ss[c & 1];
-        // offsets (r0, r1]: entry r0 came with the previous chunk (entry 0 with the first)
-        const int64_t o0 = c == 0 ? 0 : r0 + 1;
-        KLM_TRY(h2d(d_min + r0, min_battery + r0, (size_t)(r1 - r0) * sizeof(double), st));
-        KLM_TRY(h2d(d_off + o0, pref_off + o0, (size_t)(r1 + 1 - o0) * sizeof(int32_t), st));
-        KLM_TRY(h2d(d_ids + i0, pref_ids + i0, (size_t)(i1 - i0) * sizeof(int32_t), st));
-        KLM_CUDA(cudaEventRecord(h->ev_chain[c & 1], st));
-        // ... which is why this chunk's kernel waits for the previous chunk's upload
-        if (c > 0) KLM_CUDA(cudaStreamWaitEvent(st, h->ev_chain[(c - 1) & 1], 0));
-        KLM_TRY(klm_dev_schedule(h->d_battery, h->d_flags, h->n_nodes, 0, h->best.as<int64_t>(), r1 - r0,
-                                 d_min + r0, d_off + r0, d_ids, d_idx + r0, d_score + r0, st));
-        KLM_TRY(d2h(out_idx + r0, d_idx + r0, (size_t)(r1 - r0) * sizeof(int32_t), st));
-        KLM_TRY(d2h(out_score + r0, d_score + r0, (size_t)(r1 - r0) * sizeof(double), st));
+      auto pipeline = [&]() -> int {
+        // stream2 has not seen the node table or K1's result (a staged klm_nodes_set does not
+        // synchronise)
+        KLM_CUDA(cudaEventRecord(h->ev_fork, h->stream));
+        KLM_CUDA(cudaStreamWaitEvent(h->stream2, h->ev_fork, 0));
+        for (int64_t c = 0; c < n_chunks; ++c) {
+          const int64_t r0 = R * c / n_chunks, r1 = R * (c + 1) / n_chunks;
+          const int64_t i0 = pref_off[r0], i1 = pref_off[r1];
+          cudaStream_t st = ss[c & 1];
+          // offsets (r0, r1]: entry r0 came with the previous chunk (entry 0 with the first)
+          const int64_t o0 = c == 0 ? 0 : r0 + 1;
+          KLM_TRY(h2d(d_min + r0, min_battery + r0, (size_t)(r1 - r0) * sizeof(double), st));
+          KLM_TRY(h2d(d_off + o0, pref_off + o0, (size_t)(r1 + 1 - o0) * sizeof(int32_t), st));
+          KLM_TRY(h2d(d_ids + i0, pref_ids + i0, (size_t)(i1 - i0) * sizeof(int32_t), st));
+          KLM_CUDA(cudaEventRecord(h->ev_chain[c & 1], st));
+          // ... which is why this chunk's kernel waits for the previous chunk's upload
+          if (c > 0) KLM_CUDA(cudaStreamWaitEvent(st, h->ev_chain[(c - 1) & 1], 0));
+          KLM_TRY(klm_dev_schedule(h->d_battery, h->d_flags, h->n_nodes, 0, h->best.as<int64_t>(), r1 - r0,
+                                   d_min + r0, d_off + r0, d_ids, d_idx + r0, d_score + r0, st));
+          KLM_TRY(d2h(out_idx + r0, d_idx + r0, (size_t)(r1 - r0) * sizeof(int32_t), st));
+          KLM_TRY(d2h(out_score + r0, d_score + r0, (size_t)(r1 - r0) * sizeof(double), st));
+        }
+        KLM_TRY(sync(h->stream2));
+        return sync(h->stream);
+      };
+      const int rc = pipeline();
+      if (rc != KLM_OK) {  // earlier chunks may still be writing the caller's arrays
+        cudaStreamSynchronize(h->stream);
+        cudaStreamSynchronize(h->stream2);
       }
-      KLM_TRY(sync(h->stream2));
-      return sync(h->stream);
+      return rc;
     }
     KLM_TRY(h2d(d_min, min_battery, min_bytes, h->stream));
     KLM_TRY(h2d(d_off, pref_off, off_bytes, h->stream));
