@@ -524,18 +524,31 @@ int launch_window_stats_warp(const float* ring, const uint32_t* seen, int32_t wi
   const int64_t n = s1 - s0;
 #define KLM_WSW_GO(NV, NR, MINB) \
   return launch_warp<NV, NR, MINB>(ring, seen, window, pitch, s0, n, out_min, out_max, out_mean, out_p95, st)
-  // shorter windows need fewer registers: 92 at NV = 8 (5 CTAs per SM fit anyway); NV = 16 is
-  // held to 128 for a fourth CTA (2048 samples: 76 -> 66 us at C2's series count; a fifth
-  // CTA would need 96 registers and spills)
+  // The pass is straight-line only when the window fills all rows but the last of its
+  // instantiation, so there is one per common size class (300, 600, 900, 1500, 1800, 2048,
+  // 2500, 3000, 3600 and 4096 samples land in the top row of theirs); other sizes take the
+  // generic pass of the next one up. Up to 16 rows fit 128 registers (4 CTAs per SM; 5 at
+  // <= 8 rows); from 20 rows on the window is split between registers and shared memory.
+#define KLM_WSW_SPLIT_OR_3(NV)                              \
+  do {                                                      \
+    if (split_layout_ok()) KLM_WSW_GO(NV, KLM_WSW_NR, 4);   \
+    KLM_WSW_GO(NV, NV, KLM_WSW_MIN_BLOCKS);                 \
+  } while (0)
+  if (window <= 3 * 128) KLM_WSW_GO(3, 3, 5);
+  if (window <= 5 * 128) KLM_WSW_GO(5, 5, 5);
   if (window <= 8 * 128) KLM_WSW_GO(8, 8, 5);
+  if (window <= 12 * 128) KLM_WSW_GO(12, 12, 4);
+  if (window <= 15 * 128) KLM_WSW_GO(15, 15, 4);
   if (window <= 16 * 128) KLM_WSW_GO(16, 16, 4);
-  if (window <= 29 * 128) {
 #ifndef KLM_WSW_NO_SPLIT
-    if (split_layout_ok()) KLM_WSW_GO(29, KLM_WSW_NR, 4);  // rows in registers; the rest in shared memory
+  if (window <= 20 * 128) KLM_WSW_SPLIT_OR_3(20);
+  if (window <= 24 * 128) KLM_WSW_SPLIT_OR_3(24);
+  if (window <= 29 * 128) KLM_WSW_SPLIT_OR_3(29);
+#else
+  if (window <= 29 * 128) KLM_WSW_GO(29, 29, KLM_WSW_MIN_BLOCKS);
 #endif
-    KLM_WSW_GO(29, 29, KLM_WSW_MIN_BLOCKS);
-  }
   if (window <= 32 * 128) KLM_WSW_GO(32, 32, KLM_WSW_MIN_BLOCKS);
+#undef KLM_WSW_SPLIT_OR_3
 #undef KLM_WSW_GO
   return 1;
 }

@@ -46,10 +46,13 @@ def distributions(rng, s, t):
     return rows
 
 
-# 2049..3712 is the split instantiation of the warp kernel (19 rows of 128 samples in
-# registers, up to 10 in shared memory): sizes around each of its row boundaries
-@pytest.mark.parametrize("t", [1, 3, 4, 5, 20, 127, 128, 129, 1000, 2048, 2049, 2431, 2432, 2433, 2560, 3583,
-                               3584, 3585, 3600, 3711, 3712, 3713, 4096, 5000, 20000])
+# The warp kernel has one instantiation per size class (3, 5, 8, 12, 15, 16, 20, 24, 29, 32 rows of
+# 128 samples; from 20 rows on split between registers and shared memory): sizes around each
+# class boundary, plus sizes that fall in the middle of a class (generic pass)
+@pytest.mark.parametrize("t", [1, 3, 4, 5, 20, 127, 128, 129, 300, 384, 385, 600, 640, 641, 900, 1000, 1024, 1025,
+                               1200, 1536, 1537, 1800, 1920, 1921, 2048, 2049, 2431, 2432, 2433, 2500, 2560,
+                               2561, 3000, 3072, 3073, 3583, 3584, 3585, 3600, 3711, 3712, 3713, 4096, 5000,
+                               20000])
 def test_window_stats_distributions(handle, t):
     rng = np.random.default_rng(t)
     s = 80
