@@ -130,10 +130,19 @@ constexpr int kListPrefill = 24;  // list entries per lane the kernels pre-fill 
 // whose rank has been counted.
 __device__ __forceinline__ float select_from_lists(float* lst, float* fin, int lane, int cnt,
                                                    int total, int maxcnt, int k, float a, float mx,
-                                                   bool have_hints, float hint_lo, float hint_hi) {
+                                                   bool have_hints, float hint_lo, float hint_hi,
+                                                   int prefilled) {
   const int m8 = (maxcnt + 7) & ~7;
-  // entries below kListPrefill were pre-filled with -inf; pad the rare longer lists here
-  for (int e = max(cnt, kListPrefill); e < m8; ++e) lst[e * 32] = NEG_INF;
+  // entries below `prefilled` beyond the lane's count already hold -inf (pre-filled by the
+  // caller); pad the rest up to m8 here. prefilled == 0: the usual lengths as straight-line
+  // predicated stores, the rare longer lists in a loop.
+  if (prefilled == 0) {
+#pragma unroll
+    for (int e = 0; e < kListPrefill; ++e)
+      if (e >= cnt && e < m8) lst[e * 32] = NEG_INF;
+    prefilled = kListPrefill;
+  }
+  for (int e = max(cnt, prefilled); e < m8; ++e) lst[e * 32] = NEG_INF;
   fin[lane] = NEG_INF;
   fin[lane + 32] = NEG_INF;
   __syncwarp();

@@ -422,7 +422,8 @@ window_stats_pipe_kernel(const float* __restrict__ ring, const uint32_t* __restr
         // t1 (about 6 % of the window above it) is the hint for the first counting pass
         const float hint = sampled ? key_f32(t1) : 0.f;
         result = select_from_lists(lst, fin, lane, cnt, total, maxcnt, k,
-                                   sampled ? next_up(lox) : mn, mx, sampled && !tie_mode, hint, hint);
+                                   sampled ? next_up(lox) : mn, mx, sampled && !tie_mode, hint, hint,
+                                   kListPrefill);
       }
     } else if (state == kBisect) {
       result = pipe_bisect_global(ring + s * (int64_t)pitch, n, lane, f32_key(NEG_INF),

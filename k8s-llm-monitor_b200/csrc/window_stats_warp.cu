@@ -90,7 +90,13 @@ __device__ __forceinline__ void append_if_gt(uint32_t& c, uint32_t lb, float x, 
 // barrier). NR == NV keeps everything in registers (166 registers at NV = 29: 3 CTAs per
 // SM); NR = 19 fits 128 registers, i.e. a fourth CTA per SM, and the kernel is bound by the
 // latency the resident warps can hide, not by issue slots ("K7 in detail").
-template <int NV, int NR>
+// OVL: the lane lists overlay the shared-memory rows (NS * 512 == kLaneListBytes). The passes
+// then visit the shared rows first and in order: after row r has been read, the 4 (r + 1)
+// elements seen so far can have produced at most that many list entries, i.e. 512 (r + 1)
+// bytes from the start of the block -- only rows that every lane has already read (a warp's
+// shared-memory instructions execute in order). Anything that needs the rows again
+// afterwards (append retry, bisection) reloads them.
+template <int NV, int NR, bool OVL = false>
 struct Window {
   static constexpr int NS = NV - NR;
   float v[4 * NR];  // element 4 j + c = sample 4 (lane + 32 j) + c, or -inf
@@ -144,16 +150,35 @@ struct Window {
     return key_f32(lo);
   }
 
+  // calls f(j, row j) for every row; OVL: shared rows first, the next one fetched before the
+  // current one is used (its slot is not yet written by the appends of the current one)
+  template <typename F>
+  __device__ __forceinline__ void for_rows(F&& f) const {
+    if (OVL) {
+      float4 cur = row(NR);
+#pragma unroll
+      for (int j = NR; j < NV; ++j) {
+        float4 nxt = cur;
+        if (j + 1 < NV) nxt = row(j + 1);
+        f(j, cur);
+        cur = nxt;
+      }
+#pragma unroll
+      for (int j = 0; j < NR; ++j) f(j, row(j));
+    } else {
+#pragma unroll
+      for (int j = 0; j < NV; ++j) f(j, row(j));
+    }
+  }
+
   // append(x > lox) only: the retry after a pivot that listed fewer than k elements
   __device__ __forceinline__ void append_pass(float lox, uint32_t lb, uint32_t& c) const {
-#pragma unroll
-    for (int j = 0; j < NV; ++j) {
-      const float4 t = row(j);
+    for_rows([&](int, float4 t) {
       append_if_gt(c, lb, t.x, lox);
       append_if_gt(c, lb, t.y, lox);
       append_if_gt(c, lb, t.z, lox);
       append_if_gt(c, lb, t.w, lox);
-    }
+    });
     append_if_gt(c, lb, tail, lox);
   }
 
@@ -166,10 +191,8 @@ struct Window {
                                              double& sum) const {
     float mn0 = POS_INF, mn1 = POS_INF, mx0 = NEG_INF, mx1 = NEG_INF;
     double sum0 = 0.0, sum1 = 0.0;
-#pragma unroll
-    for (int j = 0; j < NV; ++j) {
-      if (!FULL && j > jr) break;  // rows beyond the boundary row hold only pads (warp-uniform)
-      const float4 t4 = row(j);
+    for_rows([&](int j, float4 t4) {
+      if (!FULL && j > jr) return;  // rows beyond the boundary row hold only pads (warp-uniform)
       const float a = t4.x, b = t4.y, cc = t4.z, d = t4.w;
       const bool uniform_valid = FULL ? (j < NV - 1) : (j < jr);
       if (uniform_valid) {
@@ -191,7 +214,7 @@ struct Window {
       append_if_gt(c, lb, b, lox);
       append_if_gt(c, lb, cc, lox);
       append_if_gt(c, lb, d, lox);
-    }
+    });
     if (lane < (n & 3)) {
       mn0 = fminf(mn0, tail);
       mx0 = fmaxf(mx0, tail);
@@ -204,7 +227,7 @@ struct Window {
   }
 };
 
-template <int NV, int NR, int MINB>
+template <int NV, int NR, int MINB, bool OVL>
 __global__ void __launch_bounds__(kWswThreads, MINB)
 window_stats_warp_kernel(const float* __restrict__ ring, const uint32_t* __restrict__ seen,
                          int32_t window, int32_t pitch, int64_t s0, int64_t n_series,
@@ -230,6 +253,12 @@ window_stats_warp_kernel(const float* __restrict__ ring, const uint32_t* __restr
   uint32_t rows_s = 0;  // shared address of this warp's window rows (NS > 0)
   if (NS == 0) {
     aux = base_g + kWswWarps * kLaneListBytes + wib * kWarpAux;
+  } else if (OVL) {
+    // the rows share the 8 KB list block of the warp; the aux areas sit below the first block
+    static_assert(!OVL || NS * 512 == kLaneListBytes, "overlay: the shared rows are exactly the list block");
+    if (base_s - raw_s < (uint32_t)(kWswWarps * kWarpAux)) __trap();  // host checked
+    aux = s_raw + wib * kWarpAux;
+    rows_s = base_s + (uint32_t)(wib * kLaneListBytes);
   } else {
     // Dynamic shared memory starts 1 KB into the CTA's window (the system reserve), so 7 KB
     // precede the first 8 KB boundary: they take the four aux areas and warp 0's rows, the
@@ -244,11 +273,11 @@ window_stats_warp_kernel(const float* __restrict__ ring, const uint32_t* __restr
   // ---- 1. load. The addresses do not depend on seen[s]: every float4 inside the row
   // pitch is fetched (stale slots beyond n are masked below), so the row loads and the
   // seen[] load share one memory round trip.
-  Window<NV, NR> w;
+  Window<NV, NR, OVL> w;
   w.srow = rows_s + ((uint32_t)lane << 4);
+  const int pfull = pitch >> 2;
+  const float* p = row + 4 * lane;
   {
-    const int pfull = pitch >> 2;
-    const float* p = row + 4 * lane;
     // rows kept in shared memory arrive by asynchronous 16-byte copies, every lane its own
     // float4 (slots outside the pitch stay unwritten and are overwritten with -inf below)
     auto fetch = [&](int j, bool pred) {
@@ -278,10 +307,12 @@ window_stats_warp_kernel(const float* __restrict__ ring, const uint32_t* __restr
   // instruction queue is what throttles this phase).
   static_assert(kListPrefill % 4 == 0, "whole 512-byte warp stores");
   float4* const lst4 = reinterpret_cast<float4*>(base_g + wib * kLaneListBytes) + lane;
+  if (!OVL) {  // (overlay: the block still holds the rows; the lists are padded after the pass)
 #pragma unroll
-  for (int e = 0; e < kListPrefill / 4; ++e)
-    lst4[e * 32] = make_float4(NEG_INF, NEG_INF, NEG_INF, NEG_INF);
-  __syncwarp();  // lanes append into slots another lane has just filled
+    for (int e = 0; e < kListPrefill / 4; ++e)
+      lst4[e * 32] = make_float4(NEG_INF, NEG_INF, NEG_INF, NEG_INF);
+    __syncwarp();  // lanes append into slots another lane has just filled
+  }
   const int n = sn < (uint32_t)window ? (int)sn : window;
   if (n == 0) {
     if (lane == 0) {
@@ -292,10 +323,10 @@ window_stats_warp_kernel(const float* __restrict__ ring, const uint32_t* __restr
     }
     return;
   }
-  // Ask L2 for the row that a warp will want about one residency later (12 warps per SM
-  // are in flight): one bulk-prefetch instruction covers the whole row.
+  // Ask L2 for the row that a warp will want about one residency later (MINB CTAs of
+  // kWswWarps warps per SM are in flight): one bulk-prefetch instruction covers the whole row.
   if (lane == 0) {
-    const int64_t later = o + (int64_t)kNumSMs * 12;
+    const int64_t later = o + (int64_t)kNumSMs * MINB * kWswWarps;
     if (later < n_series) {
       const uint32_t bytes = ((uint32_t)n * 4u + 15u) & ~15u;
       asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;"
@@ -314,6 +345,22 @@ window_stats_warp_kernel(const float* __restrict__ ring, const uint32_t* __restr
     for (int j = 0; j < NV; ++j)
       if (j >= jr && !(lane + 32 * j < nfull)) w.set_row_neg_inf(j);
   }
+  // overlay only: the appends overwrite the shared rows, so the rare paths that need the
+  // window again fetch and mask those rows once more (they are still in L2)
+  auto reload_shared_rows = [&]() {
+#pragma unroll
+    for (int j = NR; j < NV; ++j) {
+      if (lane + 32 * j < pfull)
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;"
+                     :: "r"(w.srow + (uint32_t)((j - NR) * 512)), "l"(p + 128 * j) : "memory");
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+#pragma unroll
+    for (int j = NR; j < NV; ++j)
+      if (j >= jr && !(lane + 32 * j < nfull)) w.set_row_neg_inf(j);
+    __syncwarp();
+  };
   w.tail = (lane < (n & 3)) ? row[4 * nfull + lane] : NEG_INF;
 
   const int k = n - p95_rank(n);
@@ -439,10 +486,14 @@ window_stats_warp_kernel(const float* __restrict__ ring, const uint32_t* __restr
     if (total < k && !tie_mode && lox_retry != POS_INF) {
       // the pivot was too high: redo the append (only) from the next sample statistic down
       __syncwarp();
+      if (OVL) {
+        reload_shared_rows();
+      } else {
 #pragma unroll
-      for (int e = 0; e < kListPrefill / 4; ++e)
-        lst4[e * 32] = make_float4(NEG_INF, NEG_INF, NEG_INF, NEG_INF);
-      __syncwarp();
+        for (int e = 0; e < kListPrefill / 4; ++e)
+          lst4[e * 32] = make_float4(NEG_INF, NEG_INF, NEG_INF, NEG_INF);
+        __syncwarp();
+      }
       lox = lox_retry;
       c128 = 0;
       w.append_pass(lox, lb, c128);
@@ -458,28 +509,32 @@ window_stats_warp_kernel(const float* __restrict__ ring, const uint32_t* __restr
       break;
     }
     result = select_from_lists(lst, fin, lane, cnt, total, maxcnt, k, sampled ? next_up(lox) : mn, mx,
-                               retried, hint_lo, hint_hi);
+                               retried, hint_lo, hint_hi, OVL ? 0 : kListPrefill);
   } while (false);
-  if (bisect) result = w.select_bisect(bis_lo, bis_hi, k, bis_first);
+  if (bisect) {
+    if (OVL) reload_shared_rows();
+    result = w.select_bisect(bis_lo, bis_hi, k, bis_first);
+  }
   if (lane == 0) out_p95[o] = result;
 }
 
 // dynamic shared memory of one CTA: NR == NV: lists (with alignment slack) then aux; else the
 // layout described in the kernel, which counts on the 1 KB system reserve before it
-template <int NV, int NR>
+template <int NV, int NR, bool OVL>
 constexpr size_t wsw_smem_bytes() {
   return NR == NV ? kWswSmemBytes
+         : OVL    ? (size_t)(kLaneListBytes - 1024) + (size_t)kWswWarps * kLaneListBytes + KLM_WSW_EXTRA_SMEM
                   : (size_t)(kLaneListBytes - 1024) + (size_t)kWswWarps * kLaneListBytes +
                         (size_t)(kWswWarps - 1) * (NV - NR) * 512 + KLM_WSW_EXTRA_SMEM;
 }
 
-template <int NV, int NR, int MINB>
+template <int NV, int NR, int MINB, bool OVL = false>
 static int launch_warp(const float* ring, const uint32_t* seen, int32_t window, int32_t pitch,
                        int64_t s0, int64_t n_series, float* out_min, float* out_max,
                        double* out_mean, float* out_p95, cudaStream_t st) {
-  static_assert(KLM_WSW_EXTRA_SMEM != 0 || MINB * (wsw_smem_bytes<NV, NR>() + 1024) <= 227 * 1024,
+  static_assert(KLM_WSW_EXTRA_SMEM != 0 || MINB * (wsw_smem_bytes<NV, NR, OVL>() + 1024) <= 227 * 1024,
                 "the CTAs per SM must fit");
-  static_assert(NR == NV || kWswWarps * kWarpAux + (NV - NR) * 512 <= kLaneListBytes - 1024,
+  static_assert(NR == NV || OVL || kWswWarps * kWarpAux + (NV - NR) * 512 <= kLaneListBytes - 1024,
                 "aux areas + one warp's rows must fit below the first list boundary");
   const int64_t blocks = ceil_div(n_series, kWswWarps);
   if (blocks > 0x7fffffff) {
@@ -491,16 +546,17 @@ static int launch_warp(const float* ring, const uint32_t* seen, int32_t window, 
   KLM_CUDA(cudaGetDevice(&dev));
   if (!(dev < 64 && attr_set[dev])) {
     // opt in above 48 KB and ask for the largest shared-memory carve-out
-    KLM_CUDA(cudaFuncSetAttribute(window_stats_warp_kernel<NV, NR, MINB>,
+    KLM_CUDA(cudaFuncSetAttribute(window_stats_warp_kernel<NV, NR, MINB, OVL>,
                                   cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                  (int)wsw_smem_bytes<NV, NR>()));
-    KLM_CUDA(cudaFuncSetAttribute(window_stats_warp_kernel<NV, NR, MINB>,
+                                  (int)wsw_smem_bytes<NV, NR, OVL>()));
+    KLM_CUDA(cudaFuncSetAttribute(window_stats_warp_kernel<NV, NR, MINB, OVL>,
                                   cudaFuncAttributePreferredSharedMemoryCarveout,
                                   (int)cudaSharedmemCarveoutMaxShared));
     if (dev < 64) attr_set[dev] = true;
   }
-  window_stats_warp_kernel<NV, NR, MINB><<<(unsigned)blocks, kWswThreads, wsw_smem_bytes<NV, NR>(), st>>>(
-      ring, seen, window, pitch, s0, n_series, out_min, out_max, out_mean, out_p95);
+  window_stats_warp_kernel<NV, NR, MINB, OVL>
+      <<<(unsigned)blocks, kWswThreads, wsw_smem_bytes<NV, NR, OVL>(), st>>>(
+          ring, seen, window, pitch, s0, n_series, out_min, out_max, out_mean, out_p95);
   KLM_LAUNCH_CHECK("window_stats_warp_kernel");
   return KLM_OK;
 }
@@ -543,6 +599,10 @@ int launch_window_stats_warp(const float* ring, const uint32_t* seen, int32_t wi
 #ifndef KLM_WSW_NO_SPLIT
   if (window <= 20 * 128) KLM_WSW_SPLIT_OR_3(20);
   if (window <= 24 * 128) KLM_WSW_SPLIT_OR_3(24);
+#ifdef KLM_WSW_OVERLAY  // 13 rows in registers, 16 in the list block: 96 registers, 5 CTAs per SM
+  if (window <= 29 * 128 && split_layout_ok())
+    return launch_warp<29, 13, 5, true>(ring, seen, window, pitch, s0, n, out_min, out_max, out_mean, out_p95, st);
+#endif
   if (window <= 29 * 128) KLM_WSW_SPLIT_OR_3(29);
 #else
   if (window <= 29 * 128) KLM_WSW_GO(29, 29, KLM_WSW_MIN_BLOCKS);
