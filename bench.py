@@ -365,7 +365,7 @@ def run_ours(args):
         "dtype": "f32 samples, f64 sums and scores, int64 aggregates", "data": "synthetic",
         "config": {"workload": f"{wl}: " + ", ".join(f"{k}={v}" for k, v in shp.items()),
                    "per_rank": "own series shard" if weak else ("request shard" if wl == "c4" else "node-range shard"),
-                   "l2": "inputs exceed L2 (374 MB+ per step)" if flush is None else "256 MiB L2 flush between steps",
+                   "l2": f"inputs exceed L2 ({k7_bytes / 1e6:.0f} MB of ring per step)" if flush is None else "256 MiB L2 flush between steps",
                    **extra},
         "clocks": clocks,
         "e2e": {"value": e2e_value, "unit": METRIC[wl][1], "h2d_bytes_per_step": e2e["h2d"],

@@ -89,8 +89,22 @@ def main():
     d_bat, d_flags, d_mb, d_off, d_ids = cu(bat), cu(flags), cu(mb), cu(off), cu(ids)
     k2b = dev.prebind("schedule_bruteforce", d_bat, d_flags, d_mb, d_off, d_ids, oi[:rb], os_[:rb])
     timeit(f"K2b bruteforce R={rb} N={nb}", k2b, 9 * nb + 24 * rb + 13 * ids.size,
-           "on-chip bound by construction (R*N*9 B of shared-memory reads)", iters=5,
-           units=("node_evaluations/s", rb * nb))
+           "on-chip bound by construction: smem_read_GB/s = R*N*9 B of shared-memory reads / time", iters=5,
+           units=("smem_read_GB/s", rb * nb * 9 / 1e9))
+    # C5 with a single request: what one decision costs when the nodes are sharded
+    n1, g1 = 1_000_000, 8
+    bat, flags = syn.node_table(5, n1)
+    mb, off, ids = syn.requests(5, 1, n1, k_fixed=2)
+    d_bat, d_flags, d_mb, d_off, d_ids = cu(bat), cu(flags), cu(mb), cu(off), cu(ids)
+    k1 = dev.prebind("node_best", d_bat[: n1 // g1], d_flags[: n1 // g1], best)
+    k2 = dev.prebind("schedule", d_bat[: n1 // g1], d_flags[: n1 // g1], best, d_mb, d_off, d_ids, oi[:1], os_[:1],
+                     after_best=True)
+    k3 = dev.prebind("merge_partials", pi[:, :1].contiguous(), ps[:, :1].contiguous(), oi[:1], os_[:1])
+
+    def one_decision():
+        k1(); k2(); k3()
+    timeit(f"C5 R=1: K1+K2 on one of {g1} node shards + K3", one_decision, 9 * (n1 // g1) + 50 + 16 * g1,
+           "latency of one sharded decision, exchange excluded")
 
     # ---- K4 / K5 / fleet scan
     n, pods = 100_000, 1_000_000
@@ -119,6 +133,14 @@ def main():
     tick = torch.rand(s, device="cuda")
     k6 = dev.prebind("ring_ingest", ring, seen, t, tick)
     timeit(f"K6 ring_ingest S={s}", k6, 8 * s, "one 32 B sector per sample in DRAM", do_flush=False)
+    if t == 3600:  # C3's ingest tick: 5000 nodes x 64 channels (rows of a larger ring; same scatter)
+        s3 = 320_000
+        ring3 = torch.empty((s3, t), dtype=torch.float32, device="cuda")
+        seen3 = torch.full((s3,), t, dtype=torch.int32, device="cuda")
+        k63 = dev.prebind("ring_ingest", ring3, seen3, t, torch.rand(s3, device="cuda"))
+        timeit(f"K6 ring_ingest S={s3} (C3 tick)", k63, 8 * s3, "sector traffic 36 B/sample (4 read + 32 written)",
+               do_flush=False, units=("samples/s", s3))
+        del ring3, seen3
     o = [torch.empty(s, dtype=torch.float32, device="cuda") for _ in range(3)]
     om = torch.empty(s, dtype=torch.float64, device="cuda")
     for variant in ("warp", "pipe", "block"):
