@@ -150,30 +150,44 @@ struct Window {
     return key_f32(lo);
   }
 
-  // calls f(j, row j) for every row; OVL: shared rows first, the next one fetched before the
-  // current one is used (its slot is not yet written by the appends of the current one)
+  __device__ __forceinline__ float4 shared_row(int r) const {  // r may be a run-time value
+    float4 t;
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
+                 : "=f"(t.x), "=f"(t.y), "=f"(t.z), "=f"(t.w)
+                 : "r"(srow + (uint32_t)(r * 512)));
+    return t;
+  }
+
+  // calls f(j, row j, j & 1) for every row. OVL: shared rows first, the next one fetched
+  // before the current one is used (its slot is not yet written by the appends of the
+  // current one), and as a LOOP of four rows per trip: with 20 warps per SM in different
+  // phases the instruction caches, not the issue slots, are what a longer straight line costs.
   template <typename F>
   __device__ __forceinline__ void for_rows(F&& f) const {
     if (OVL) {
-      float4 cur = row(NR);
+      static_assert(!OVL || NS % 4 == 0, "overlay: four shared rows per trip");
+      float4 cur = shared_row(0);
+#pragma unroll 1
+      for (int i = 0; i < NS; i += 4) {
 #pragma unroll
-      for (int j = NR; j < NV; ++j) {
-        float4 nxt = cur;
-        if (j + 1 < NV) nxt = row(j + 1);
-        f(j, cur);
-        cur = nxt;
+        for (int u = 0; u < 4; ++u) {
+          float4 nxt = cur;
+          if (i + u + 1 < NS) nxt = shared_row(i + u + 1);
+          f(NR + i + u, cur, (NR + u) & 1);  // i is a multiple of 4
+          cur = nxt;
+        }
       }
 #pragma unroll
-      for (int j = 0; j < NR; ++j) f(j, row(j));
+      for (int j = 0; j < NR; ++j) f(j, row(j), j & 1);
     } else {
 #pragma unroll
-      for (int j = 0; j < NV; ++j) f(j, row(j));
+      for (int j = 0; j < NV; ++j) f(j, row(j), j & 1);
     }
   }
 
   // append(x > lox) only: the retry after a pivot that listed fewer than k elements
   __device__ __forceinline__ void append_pass(float lox, uint32_t lb, uint32_t& c) const {
-    for_rows([&](int, float4 t) {
+    for_rows([&](int, float4 t, int) {
       append_if_gt(c, lb, t.x, lox);
       append_if_gt(c, lb, t.y, lox);
       append_if_gt(c, lb, t.z, lox);
@@ -191,12 +205,12 @@ struct Window {
                                              double& sum) const {
     float mn0 = POS_INF, mn1 = POS_INF, mx0 = NEG_INF, mx1 = NEG_INF;
     double sum0 = 0.0, sum1 = 0.0;
-    for_rows([&](int j, float4 t4) {
+    for_rows([&](int j, float4 t4, int odd) {
       if (!FULL && j > jr) return;  // rows beyond the boundary row hold only pads (warp-uniform)
       const float a = t4.x, b = t4.y, cc = t4.z, d = t4.w;
       const bool uniform_valid = FULL ? (j < NV - 1) : (j < jr);
       if (uniform_valid) {
-        if (j & 1) {
+        if (odd) {
           mn1 = fminf(fminf(mn1, a), fminf(b, fminf(cc, d)));
           mx1 = fmaxf(fmaxf(mx1, a), fmaxf(b, fmaxf(cc, d)));
           KLM_SUM4(sum1, a, b, cc, d);
