@@ -160,22 +160,18 @@ struct Window {
 
   // calls f(j, row j, j & 1) for every row. OVL: shared rows first, the next one fetched
   // before the current one is used (its slot is not yet written by the appends of the
-  // current one), and as a LOOP of four rows per trip: with 20 warps per SM in different
-  // phases the instruction caches, not the issue slots, are what a longer straight line costs.
+  // current one). Fully unrolled: rolling the shared rows into a loop of four per trip
+  // shrinks the code by 1300 instructions but runs 10 % slower (111 vs 101 us at C2).
   template <typename F>
   __device__ __forceinline__ void for_rows(F&& f) const {
     if (OVL) {
-      static_assert(!OVL || NS % 4 == 0, "overlay: four shared rows per trip");
       float4 cur = shared_row(0);
-#pragma unroll 1
-      for (int i = 0; i < NS; i += 4) {
 #pragma unroll
-        for (int u = 0; u < 4; ++u) {
-          float4 nxt = cur;
-          if (i + u + 1 < NS) nxt = shared_row(i + u + 1);
-          f(NR + i + u, cur, (NR + u) & 1);  // i is a multiple of 4
-          cur = nxt;
-        }
+      for (int r = 0; r < NS; ++r) {
+        float4 nxt = cur;
+        if (r + 1 < NS) nxt = shared_row(r + 1);
+        f(NR + r, cur, (NR + r) & 1);
+        cur = nxt;
       }
 #pragma unroll
       for (int j = 0; j < NR; ++j) f(j, row(j), j & 1);
