@@ -427,7 +427,7 @@ def run_e2e(pkg, wl, cid, shp, rank, world, args, env):
             # argument structs built once: the timed region is the C ABI calls themselves, as a
             # compiled (cgo) caller issues them, not the Python wrapper's array coercions
             res_i, res_s = pin(np.empty(mb.size, np.int32)), pin(np.empty(mb.size))
-            collect = h.collect_prepared(snap_h, outs)
+            collect = h.collect_prepared(snap_h, outs, packed=True)   # one download for the four statistics
             reconcile = h.reconcile_prepared(bat, flags, mb, off, ids, res_i, res_s)
 
             def step():

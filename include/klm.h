@@ -239,8 +239,16 @@ typedef struct klm_collect_out {
   float* win_max;
   double* win_mean;
   float* win_p95;
+  /* Optional: all four window statistics as ONE block of klm_collect_packed_bytes(n_series)
+   * bytes, fetched with a single device-to-host copy (each separate array above costs its
+   * own copy, ~6 us of fixed latency): with c = n_series * 4 rounded up to 256,
+   * min f32[n_series] at byte 0, max at c, p95 at 2 c, mean f64[n_series] at 3 c.
+   * When non-NULL the four win_* pointers above must be NULL. */
+  void* win_packed;
 } klm_collect_out;
 int klm_collect(klm_handle* h, const klm_collect_in* in, const klm_collect_out* out);
+/* size of the win_packed block for n_series series (0 if n_series <= 0) */
+int64_t klm_collect_packed_bytes(int64_t n_series);
 
 /* ================================================= device-pointer layer */
 /* All pointers below are DEVICE pointers; nothing is allocated or freed;

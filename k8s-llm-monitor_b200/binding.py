@@ -62,7 +62,7 @@ class CollectOut(C.Structure):  # klm_collect_out
     _fields_ = [("cluster", C.POINTER(ClusterOut)), ("cpu_rate", C.c_void_p), ("memory_rate", C.c_void_p),
                 ("disk_usage", C.c_void_p), ("disk_rate", C.c_void_p), ("under_pressure", C.c_void_p),
                 ("win_min", C.c_void_p), ("win_max", C.c_void_p), ("win_mean", C.c_void_p),
-                ("win_p95", C.c_void_p)]
+                ("win_p95", C.c_void_p), ("win_packed", C.c_void_p)]
 
 
 CLUSTER_OUT_DTYPE = np.dtype([
@@ -81,6 +81,7 @@ SIGNATURES = {
     "klm_destroy": (None, [_P]),
     "klm_last_error": (C.c_char_p, []),
     "klm_abi_version": (C.c_int, []),
+    "klm_collect_packed_bytes": (_I64, [_I64]),
     "klm_host_alloc": (C.c_int, [C.c_size_t, C.POINTER(_P)]),
     "klm_host_free": (C.c_int, [_P]),
     "klm_nodes_set": (C.c_int, [_P, _I64, _P, _P]),
@@ -329,8 +330,11 @@ class Handle:
             raise ValueError(f"{name}: prepared calls need a C-contiguous numpy array of {np.dtype(dtype)}")
         return a.ctypes.data if a.size else None
 
-    def collect_prepared(self, snap: dict, out: dict):
-        """Returns call(tick) -> ClusterOut dict; fills `out` (keys as collect()) in place."""
+    def collect_prepared(self, snap: dict, out: dict, packed: bool = False):
+        """Returns call(tick) -> ClusterOut dict; fills `out` (keys as collect()) in place.
+        packed=True: the four window statistics come back as one page-locked block
+        (klm_collect_out.win_packed, a single download); out["min"/"max"/"p95"/"mean"] are
+        then replaced by views into it."""
         ex = self._exact
         cols = [ex(snap[k], dt, k) for k, dt in (("cpu_capacity", np.int64), ("cpu_usage", np.int64),
                                                  ("memory_capacity", np.int64), ("memory_usage", np.int64),
@@ -346,10 +350,22 @@ class Handle:
         dts = (("cpu_rate", np.float64), ("memory_rate", np.float64), ("disk_usage", np.int64),
                ("disk_rate", np.float64), ("under_pressure", np.uint8), ("min", np.float32),
                ("max", np.float32), ("mean", np.float64), ("p95", np.float32))
-        cout = CollectOut(C.pointer(cl), *[ex(out[k], dt, k) for k, dt in dts])
-        fn, h, pin_, pout = self._lib.klm_collect, self._h, C.byref(cin), C.byref(cout)
-        keep = (nc, cl, cin, cout, snap, out)
         s = self._ring_shape[0]
+        block = None
+        if packed:
+            nbytes = self._lib.klm_collect_packed_bytes(s)
+            block = host_array(nbytes, np.uint8)
+            c4 = (s * 4 + 255) & ~255
+            out["min"] = block[0:s * 4].view(np.float32)
+            out["max"] = block[c4:c4 + s * 4].view(np.float32)
+            out["p95"] = block[2 * c4:2 * c4 + s * 4].view(np.float32)
+            out["mean"] = block[3 * c4:3 * c4 + s * 8].view(np.float64)
+            ptrs = [ex(out[k], dt, k) for k, dt in dts[:5]] + [None] * 4 + [block.ctypes.data]
+        else:
+            ptrs = [ex(out[k], dt, k) for k, dt in dts]
+        cout = CollectOut(C.pointer(cl), *ptrs)
+        fn, h, pin_, pout = self._lib.klm_collect, self._h, C.byref(cin), C.byref(cout)
+        keep = (nc, cl, cin, cout, snap, out, block)
 
         def call(tick):
             if tick is not None:

@@ -178,7 +178,7 @@ size_t align256(size_t b) { return (b + 255) & ~size_t(255); }
 }  // namespace
 
 extern "C" const char* klm_last_error(void) { return g_err; }
-extern "C" int klm_abi_version(void) { return 1001; }
+extern "C" int klm_abi_version(void) { return 1002; }
 
 extern "C" int klm_host_alloc(size_t bytes, void** out) {
   if (!out || bytes == 0) {
@@ -757,7 +757,11 @@ int collect_impl(klm_handle* h, const klm_collect_in* in, const klm_collect_out*
     return KLM_EINVAL;
   }
   cudaStream_t st = h->stream, st2 = h->stream2;
-  const bool want_win = out->win_min || out->win_max || out->win_mean || out->win_p95;
+  const bool want_win = out->win_min || out->win_max || out->win_mean || out->win_p95 || out->win_packed;
+  if (out->win_packed && (out->win_min || out->win_max || out->win_mean || out->win_p95)) {
+    set_error("klm_collect: win_packed excludes the separate win_* arrays");
+    return KLM_EINVAL;
+  }
   if ((in->tick_values || want_win) && h->n_series <= 0) {
     set_error("klm_collect: no ring; call klm_ring_create first");
     return KLM_ESTATE;
@@ -789,7 +793,7 @@ int collect_impl(klm_handle* h, const klm_collect_in* in, const klm_collect_out*
     d_p95 = reinterpret_cast<float*>(o + 2 * c4);
     d_mean = reinterpret_cast<double*>(o + 3 * c4);
     KLM_TRY(klm_dev_window_stats(h->ring.as<float>(), h->seen.as<uint32_t>(), h->window, h->pitch, 0, S,
-                                 d_min, d_max, d_mean, out->win_p95 ? d_p95 : nullptr, st));
+                                 d_min, d_max, d_mean, (out->win_p95 || out->win_packed) ? d_p95 : nullptr, st));
   }
   // ---- snapshot branch: one upload of the columns serves the rates and the aggregate
   const size_t col8 = align256((size_t)n * 8), col4 = align256((size_t)n * 4), col1 = align256((size_t)n);
@@ -888,7 +892,9 @@ int collect_impl(klm_handle* h, const klm_collect_in* in, const klm_collect_out*
     }
   }
   // ---- ring branch, second half: the statistics go straight to the caller's arrays
-  if (want_win) {
+  if (out->win_packed) {  // the device block already has the packed layout
+    KLM_TRY(d2h(out->win_packed, d_min, (size_t)klm_collect_packed_bytes(S), st));
+  } else if (want_win) {
     if (out->win_min) KLM_TRY(d2h(out->win_min, d_min, (size_t)S * 4, st));
     if (out->win_max) KLM_TRY(d2h(out->win_max, d_max, (size_t)S * 4, st));
     if (out->win_mean) KLM_TRY(d2h(out->win_mean, d_mean, (size_t)S * 8, st));
@@ -911,6 +917,11 @@ int collect_impl(klm_handle* h, const klm_collect_in* in, const klm_collect_out*
 }
 
 }  // namespace
+
+extern "C" int64_t klm_collect_packed_bytes(int64_t n_series) {
+  if (n_series <= 0) return 0;
+  return (int64_t)(3 * align256((size_t)n_series * 4) + (size_t)n_series * 8);
+}
 
 extern "C" int klm_collect(klm_handle* h, const klm_collect_in* in, const klm_collect_out* out) {
   KLM_ENTER(h);

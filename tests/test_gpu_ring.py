@@ -246,3 +246,16 @@ def test_prepared_calls_match_wrappers(pkg):
             assert np.array_equal(res_i, wi) and np.array_equal(res_s, ws)
         with pytest.raises(ValueError):
             b.collect_prepared(snap, dict(out, min=np.empty(s, np.float64)))  # wrong dtype: refused
+        # the packed result block (one download): same numbers, as views into one array
+        pout = {k: v for k, v in out.items() if k not in ("min", "max", "mean", "p95")}
+        pcollect = b.collect_prepared(snap, pout, packed=True)
+        tick = (rng.random(s) * 100).astype(np.float32)
+        want = a.collect(tick, snap)
+        pcollect(tick)
+        for k in ("min", "max", "mean", "p95", "cpu_rate", "under_pressure"):
+            assert np.array_equal(pout[k], want[k]), k
+        import ctypes as C
+        bad = pkg.binding.CollectOut(None, *([None] * 5), pout["min"].ctypes.data, None, None, None,
+                                     pout["min"].ctypes.data)
+        cin = pkg.binding.CollectIn(None, None, 0, None, None, None, 0)
+        assert b._lib.klm_collect(b._h, C.byref(cin), C.byref(bad)) == pkg.binding.KLM_EINVAL
