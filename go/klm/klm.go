@@ -15,6 +15,7 @@ import "C"
 
 import (
 	"fmt"
+	"runtime"
 	"unsafe"
 )
 
@@ -131,23 +132,49 @@ type ClusterOut struct {
 
 // ClusterAggregate replaces Manager.calculateClusterMetrics (manager.go:493-565).
 func (k *Handle) ClusterAggregate(c *NodeCols, podRunning []uint8) (*ClusterOut, error) {
-	cc := C.klm_node_cols{
-		cpu_capacity: i64p(c.CPUCapacity), cpu_usage: i64p(c.CPUUsage),
-		memory_capacity: i64p(c.MemoryCapacity), memory_usage: i64p(c.MemoryUsage),
-		gpu_count: i32p(c.GPUCount), healthy: u8p(c.Healthy),
-		gpu_usage: f64p(c.GPUUsage), n_gpu_usage: C.int64_t(len(c.GPUUsage)),
-	}
+	var pin runtime.Pinner
+	defer pin.Unpin()
+	cc := c.toC(&pin)
 	var o C.klm_cluster_out
 	rc := C.klm_cluster_aggregate(k.h, &cc, C.int64_t(len(c.CPUCapacity)), u8p(podRunning),
 		C.int64_t(len(podRunning)), &o)
 	if rc != 0 {
 		return nil, lastErr("klm_cluster_aggregate")
 	}
-	return &ClusterOut{
+	out := clusterFromC(&o)
+	return &out, nil
+}
+
+// pinSlice pins the backing array of s for the duration of one call. A C struct that holds
+// Go pointers may be passed to C only if those pointers are pinned (cgo rules, Go >= 1.21).
+func pinSlice[T any](p *runtime.Pinner, s []T) {
+	if len(s) > 0 {
+		p.Pin(&s[0])
+	}
+}
+
+func (c *NodeCols) toC(p *runtime.Pinner) C.klm_node_cols {
+	pinSlice(p, c.CPUCapacity)
+	pinSlice(p, c.CPUUsage)
+	pinSlice(p, c.MemoryCapacity)
+	pinSlice(p, c.MemoryUsage)
+	pinSlice(p, c.GPUCount)
+	pinSlice(p, c.Healthy)
+	pinSlice(p, c.GPUUsage)
+	return C.klm_node_cols{
+		cpu_capacity: i64p(c.CPUCapacity), cpu_usage: i64p(c.CPUUsage),
+		memory_capacity: i64p(c.MemoryCapacity), memory_usage: i64p(c.MemoryUsage),
+		gpu_count: i32p(c.GPUCount), healthy: u8p(c.Healthy),
+		gpu_usage: f64p(c.GPUUsage), n_gpu_usage: C.int64_t(len(c.GPUUsage)),
+	}
+}
+
+func clusterFromC(o *C.klm_cluster_out) ClusterOut {
+	return ClusterOut{
 		int64(o.total_nodes), int64(o.healthy_nodes), int64(o.total_pods), int64(o.running_pods),
 		int64(o.total_cpu), int64(o.used_cpu), int64(o.total_memory), int64(o.used_memory),
 		int64(o.total_gpus), int64(o.available_gpus), float64(o.cpu_usage_rate),
-		float64(o.memory_usage_rate), int32(o.health_status), uint32(o.issues)}, nil
+		float64(o.memory_usage_rate), int32(o.health_status), uint32(o.issues)}
 }
 
 // FleetScan replaces GetHealthyUAVCount and GetLowBatteryUAVs
@@ -220,3 +247,66 @@ func HostFloat64s(n int) ([]float64, error) {
 
 // HostFree releases a slice obtained from a Host* allocator.
 func HostFree(p unsafe.Pointer) { C.klm_host_free(p) }
+
+// CollectResult is one Manager.Collect cycle: cluster metrics, per-node rates and the
+// window statistics of every series. Min / Max / P95 / Mean are views into one
+// page-locked block owned by the Collector (valid until the next Collect).
+type CollectResult struct {
+	Cluster       ClusterOut
+	CPURate       []float64
+	MemoryRate    []float64
+	Min, Max, P95 []float32
+	Mean          []float64
+}
+
+// Collector holds the page-locked result block for klm_collect's packed output.
+type Collector struct {
+	k       *Handle
+	nSeries int64
+	block   unsafe.Pointer
+}
+
+// NewCollector prepares the result block for a ring of nSeries series (RingCreate first).
+func (k *Handle) NewCollector(nSeries int64) (*Collector, error) {
+	var p unsafe.Pointer
+	if rc := C.klm_host_alloc(C.size_t(C.klm_collect_packed_bytes(C.int64_t(nSeries))), &p); rc != 0 {
+		return nil, lastErr("klm_host_alloc")
+	}
+	return &Collector{k: k, nSeries: nSeries, block: p}, nil
+}
+
+// Close releases the result block.
+func (c *Collector) Close() { C.klm_host_free(c.block); c.block = nil }
+
+// Collect replaces the tail of Manager.Collect (manager.go:195-319): appends `tick` (one
+// sample per series, or nil) to the ring and returns calculateClusterMetrics, the node
+// rates and the window statistics from one call and one synchronisation.
+func (c *Collector) Collect(tick []float32, cols *NodeCols, podRunning []uint8) (*CollectResult, error) {
+	n := len(cols.CPUCapacity)
+	res := &CollectResult{CPURate: make([]float64, n), MemoryRate: make([]float64, n)}
+	var pin runtime.Pinner
+	defer pin.Unpin()
+	nc := cols.toC(&pin)
+	var cl C.klm_cluster_out
+	pinSlice(&pin, tick)
+	pinSlice(&pin, podRunning)
+	pinSlice(&pin, res.CPURate)
+	pinSlice(&pin, res.MemoryRate)
+	pin.Pin(&nc)
+	pin.Pin(&cl)
+	in := C.klm_collect_in{tick_values: f32p(tick), nodes: &nc, n_nodes: C.int64_t(n),
+		pod_running: u8p(podRunning), n_pods: C.int64_t(len(podRunning))}
+	out := C.klm_collect_out{cluster: &cl, cpu_rate: f64p(res.CPURate), memory_rate: f64p(res.MemoryRate),
+		win_packed: c.block}
+	if rc := C.klm_collect(c.k.h, &in, &out); rc != 0 {
+		return nil, lastErr("klm_collect")
+	}
+	res.Cluster = clusterFromC(&cl)
+	s := int(c.nSeries)
+	c4 := uintptr((s*4 + 255) &^ 255)
+	res.Min = unsafe.Slice((*float32)(c.block), s)
+	res.Max = unsafe.Slice((*float32)(unsafe.Add(c.block, c4)), s)
+	res.P95 = unsafe.Slice((*float32)(unsafe.Add(c.block, 2*c4)), s)
+	res.Mean = unsafe.Slice((*float64)(unsafe.Add(c.block, 3*c4)), s)
+	return res, nil
+}
