@@ -112,6 +112,20 @@ func (k *Handle) ScheduleBatch(minBattery []float64, prefOff, prefIDs []int32) (
 	return idx, score, nil
 }
 
+// Reconcile is NodesSet + ScheduleBatch in one call (klm_reconcile): the whole of
+// controller.go:88-110 for one cycle, one lock and -- for a small reconcile -- one upload, one
+// download and one synchronisation.
+func (k *Handle) Reconcile(battery []float64, flags []uint8, minBattery []float64, prefOff, prefIDs []int32) ([]int32, []float64, error) {
+	r := len(minBattery)
+	idx, score := make([]int32, r), make([]float64, r)
+	rc := C.klm_reconcile(k.h, C.int64_t(len(battery)), f64p(battery), u8p(flags), C.int64_t(r),
+		f64p(minBattery), i32p(prefOff), i32p(prefIDs), i32p(idx), f64p(score), C.KLM_ALGO_DECOMPOSED)
+	if rc != 0 {
+		return nil, nil, lastErr("klm_reconcile")
+	}
+	return idx, score, nil
+}
+
 // NodeCols are the columns calculateClusterMetrics reads (manager.go:499-535).
 type NodeCols struct {
 	CPUCapacity, CPUUsage, MemoryCapacity, MemoryUsage []int64

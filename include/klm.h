@@ -144,6 +144,17 @@ int klm_schedule_batch(klm_handle* h, int64_t n_requests,
                        const int32_t* pref_ids, int32_t* out_idx,
                        double* out_score, int algo);
 
+/* One reconcile in one call (controller.go:88-110: one UAV snapshot, then every
+ * pending request): klm_nodes_set + klm_schedule_batch with the same arguments,
+ * results and errors, under one lock. A reconcile whose arrays fit the 256 KB
+ * staging block costs one upload, K1, K2 overlapping K1, one download and one
+ * synchronisation. The snapshot stays installed for later klm_schedule_batch calls. */
+int klm_reconcile(klm_handle* h, int64_t n_nodes, const double* battery,
+                  const uint8_t* flags, int64_t n_requests,
+                  const double* min_battery, const int32_t* pref_off,
+                  const int32_t* pref_ids, int32_t* out_idx, double* out_score,
+                  int algo);
+
 /* ----------------------------------------------------- cluster aggregate */
 
 /* Replaces Manager.calculateClusterMetrics (manager.go:493-565).

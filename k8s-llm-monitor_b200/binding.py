@@ -86,6 +86,7 @@ SIGNATURES = {
     "klm_host_free": (C.c_int, [_P]),
     "klm_nodes_set": (C.c_int, [_P, _I64, _P, _P]),
     "klm_schedule_batch": (C.c_int, [_P, _I64, _P, _P, _P, _P, _P, C.c_int]),
+    "klm_reconcile": (C.c_int, [_P, _I64, _P, _P, _I64, _P, _P, _P, _P, _P, C.c_int]),
     "klm_cluster_aggregate": (C.c_int, [_P, C.POINTER(NodeCols), _I64, _P, _I64, C.POINTER(ClusterOut)]),
     "klm_node_rates": (C.c_int, [_P, _I64] + [_P] * 11),
     "klm_pod_rates": (C.c_int, [_P, _I64] + [_P] * 13),
@@ -218,6 +219,21 @@ class Handle:
             ids = np.zeros(1, np.int32)
         check(self._lib.klm_schedule_batch(self._h, r, _ptr(mb), _ptr(off), _ptr(ids),
                                            _ptr(out_idx), _ptr(out_score), algo))
+        return out_idx, out_score
+
+    def reconcile(self, battery, flags, min_battery, pref_off, pref_ids, algo: int = ALGO_DECOMPOSED
+                  ) -> Tuple[np.ndarray, np.ndarray]:
+        """klm_reconcile: snapshot + batch in one call (== nodes_set then schedule_batch)."""
+        b, f = _np(battery, np.float64), _np(flags, np.uint8)
+        mb, off, ids = _np(min_battery, np.float64), _np(pref_off, np.int32), _np(pref_ids, np.int32)
+        r = mb.size
+        if b.shape != f.shape or b.ndim != 1 or off.size != r + 1:
+            raise ValueError("reconcile: array lengths disagree")
+        out_idx, out_score = np.empty(r, np.int32), np.empty(r, np.float64)
+        if ids.size == 0:
+            ids = np.zeros(1, np.int32)
+        check(self._lib.klm_reconcile(self._h, b.size, _ptr(b), _ptr(f), r, _ptr(mb), _ptr(off), _ptr(ids),
+                                      _ptr(out_idx), _ptr(out_score), algo))
         return out_idx, out_score
 
     # -- aggregation (manager.go:493-565)
@@ -383,8 +399,8 @@ class Handle:
 
     def reconcile_prepared(self, battery, flags, min_battery, pref_off, pref_ids, out_idx, out_score,
                            algo: int = ALGO_DECOMPOSED):
-        """Returns call(): klm_nodes_set + klm_schedule_batch on the given arrays, results in
-        out_idx / out_score (one reconcile: snapshot, then every pending request)."""
+        """Returns call(): klm_reconcile on the given arrays, results in out_idx / out_score
+        (one reconcile: snapshot, then every pending request)."""
         ex = self._exact
         n, r = battery.size, min_battery.size
         if flags.size != n or pref_off.size != r + 1 or out_idx.size != r or out_score.size != r:
@@ -393,12 +409,10 @@ class Handle:
              ex(min_battery, np.float64, "min_battery"), ex(pref_off, np.int32, "pref_off"),
              ex(pref_ids, np.int32, "pref_ids"), ex(out_idx, np.int32, "out_idx"),
              ex(out_score, np.float64, "out_score")]
-        set_fn, batch_fn, h = self._lib.klm_nodes_set, self._lib.klm_schedule_batch, self._h
+        fn, h = self._lib.klm_reconcile, self._h
 
         def call():
-            rc = set_fn(h, n, a[0], a[1])
-            if rc == KLM_OK:
-                rc = batch_fn(h, r, a[2], a[3], a[4], a[5], a[6], algo)
+            rc = fn(h, n, a[0], a[1], r, a[2], a[3], a[4], a[5], a[6], algo)
             if rc != KLM_OK:
                 raise KlmError(rc, last_error())
         call.keep = (battery, flags, min_battery, pref_off, pref_ids, out_idx, out_score)

@@ -118,6 +118,7 @@ struct klm_handle {
   double* d_battery = nullptr;
   uint8_t* d_flags = nullptr;
   DevBuf req_blk, res_blk;  // small batches: min | off | ids and score | idx as single blocks
+  DevBuf rec_blk;           // klm_reconcile, small case: node table | min | off | ids
   DevBuf best, best_scratch;
   DevBuf req_min, req_off, req_ids, res_idx, res_score;
   DevBuf snap_out;  // klm_collect, small snapshots: cluster_out | the five rate columns
@@ -178,7 +179,7 @@ size_t align256(size_t b) { return (b + 255) & ~size_t(255); }
 }  // namespace
 
 extern "C" const char* klm_last_error(void) { return g_err; }
-extern "C" int klm_abi_version(void) { return 1002; }
+extern "C" int klm_abi_version(void) { return 1003; }
 
 extern "C" int klm_host_alloc(size_t bytes, void** out) {
   if (!out || bytes == 0) {
@@ -267,7 +268,7 @@ extern "C" void klm_destroy(klm_handle* h) {
   cudaSetDevice(h->device);
   if (h->stream) cudaStreamSynchronize(h->stream);
   if (h->stream2) cudaStreamSynchronize(h->stream2);
-  DevBuf* bufs[] = {&h->node_tab, &h->req_blk,  &h->res_blk,    &h->snap_out,
+  DevBuf* bufs[] = {&h->node_tab, &h->req_blk,  &h->res_blk,    &h->snap_out,   &h->rec_blk,
                     &h->best,     &h->best_scratch, &h->req_min,
                     &h->req_off,  &h->req_ids,  &h->res_idx,    &h->res_score,    &h->agg_cols,
                     &h->agg_pods, &h->agg_gpu,  &h->agg_out,    &h->agg_scratch,  &h->rate_in,
@@ -287,9 +288,7 @@ extern "C" void klm_destroy(klm_handle* h) {
 
 // ------------------------------------------------------------ scheduling
 
-extern "C" int klm_nodes_set(klm_handle* h, int64_t n, const double* battery,
-                             const uint8_t* flags) {
-  KLM_ENTER(h);
+static int nodes_set_impl(klm_handle* h, int64_t n, const double* battery, const uint8_t* flags) {
   if (n < 0 || n > 0x7fffffff || (n > 0 && (!battery || !flags))) {
     set_error("klm_nodes_set: bad argument (0 <= n_nodes < 2^31, arrays non-null)");
     return KLM_EINVAL;
@@ -325,10 +324,15 @@ extern "C" int klm_nodes_set(klm_handle* h, int64_t n, const double* battery,
   return KLM_OK;
 }
 
-extern "C" int klm_schedule_batch(klm_handle* h, int64_t R, const double* min_battery,
-                                  const int32_t* pref_off, const int32_t* pref_ids,
-                                  int32_t* out_idx, double* out_score, int algo) {
+extern "C" int klm_nodes_set(klm_handle* h, int64_t n, const double* battery,
+                             const uint8_t* flags) {
   KLM_ENTER(h);
+  return nodes_set_impl(h, n, battery, flags);
+}
+
+static int schedule_batch_impl(klm_handle* h, int64_t R, const double* min_battery,
+                               const int32_t* pref_off, const int32_t* pref_ids, int32_t* out_idx,
+                               double* out_score, int algo) {
   if (h->n_nodes < 0) {
     set_error("klm_schedule_batch: no node snapshot; call klm_nodes_set first");
     return KLM_ESTATE;
@@ -454,6 +458,77 @@ extern "C" int klm_schedule_batch(klm_handle* h, int64_t R, const double* min_ba
   KLM_TRY(d2h(out_idx, d_idx, idx_bytes, h->stream));
   KLM_TRY(d2h(out_score, d_score, min_bytes, h->stream));
   return sync(h->stream);
+}
+
+extern "C" int klm_schedule_batch(klm_handle* h, int64_t R, const double* min_battery,
+                                  const int32_t* pref_off, const int32_t* pref_ids,
+                                  int32_t* out_idx, double* out_score, int algo) {
+  KLM_ENTER(h);
+  return schedule_batch_impl(h, R, min_battery, pref_off, pref_ids, out_idx, out_score, algo);
+}
+
+// One reconcile (controller.go:88-110): install the snapshot and decide every pending request.
+// Small reconciles (everything within the staging block) are one upload, K1, K2 launched
+// programmatically dependent on K1, one download and one synchronisation; anything larger
+// is klm_nodes_set followed by klm_schedule_batch under one lock.
+extern "C" int klm_reconcile(klm_handle* h, int64_t n, const double* battery, const uint8_t* flags,
+                             int64_t R, const double* min_battery, const int32_t* pref_off,
+                             const int32_t* pref_ids, int32_t* out_idx, double* out_score, int algo) {
+  KLM_ENTER(h);
+  const bool args_ok = n >= 0 && n <= 0x7fffffff && (n == 0 || (battery && flags)) && R >= 0 &&
+                       (algo == KLM_ALGO_DECOMPOSED || algo == KLM_ALGO_BRUTEFORCE) &&
+                       (R == 0 || (min_battery && pref_off && out_idx && out_score));
+  const int64_t n_ids = (args_ok && R > 0) ? pref_off[R] : 0;
+  const size_t bat_bytes = (size_t)(n > 0 ? n : 0) * sizeof(double), flag_off = align256(bat_bytes);
+  const size_t tab_bytes = align256(flag_off + (size_t)(n > 0 ? n : 0));
+  const size_t min_bytes = (size_t)R * sizeof(double), off_bytes = (size_t)(R + 1) * sizeof(int32_t);
+  const size_t ids_bytes = (size_t)(n_ids > 0 ? n_ids : 0) * sizeof(int32_t), idx_bytes = (size_t)R * sizeof(int32_t);
+  const size_t q_off = tab_bytes + align256(min_bytes), q_ids = q_off + align256(off_bytes);
+  const size_t in_bytes = q_ids + align256(ids_bytes), out_idx_at = align256(min_bytes);
+  const size_t out_bytes = out_idx_at + idx_bytes;
+  if (!args_ok || R == 0 || n_ids < 0 || pref_off[0] != 0 || (n_ids > 0 && !pref_ids) ||
+      in_bytes + out_bytes > kStageMax) {
+    // let the two calls validate and handle it (same error texts as calling them separately)
+    KLM_TRY(nodes_set_impl(h, n, battery, flags));
+    return schedule_batch_impl(h, R, min_battery, pref_off, pref_ids, out_idx, out_score, algo);
+  }
+  h->n_nodes = -1;
+  KLM_TRY(h->rec_blk.ensure(in_bytes + 256));
+  KLM_TRY(h->res_blk.ensure(out_bytes + 256));
+  KLM_TRY(h->sched_pin.ensure(kStageMax));
+  KLM_CUDA(cudaEventSynchronize(h->sched_read));
+  char* blk = h->rec_blk.as<char>();
+  h->d_battery = reinterpret_cast<double*>(blk);
+  h->d_flags = reinterpret_cast<uint8_t*>(blk + flag_off);
+  double* d_min = reinterpret_cast<double*>(blk + tab_bytes);
+  int32_t* d_off = reinterpret_cast<int32_t*>(blk + q_off);
+  int32_t* d_ids = reinterpret_cast<int32_t*>(blk + q_ids);
+  double* d_score = h->res_blk.as<double>();
+  int32_t* d_idx = reinterpret_cast<int32_t*>(h->res_blk.as<char>() + out_idx_at);
+  if (n > 0) {
+    std::memcpy(h->sched_pin.at(0), battery, bat_bytes);
+    std::memcpy(h->sched_pin.at(flag_off), flags, (size_t)n);
+  }
+  std::memcpy(h->sched_pin.at(tab_bytes), min_battery, min_bytes);
+  std::memcpy(h->sched_pin.at(q_off), pref_off, off_bytes);
+  if (ids_bytes) std::memcpy(h->sched_pin.at(q_ids), pref_ids, ids_bytes);
+  KLM_TRY(h2d(blk, h->sched_pin.p, in_bytes, h->stream));
+  KLM_TRY(klm_dev_node_best(h->d_battery, h->d_flags, n, 0, h->best.as<int64_t>(), h->best_scratch.p,
+                            h->stream));
+  h->n_nodes = n;
+  if (algo == KLM_ALGO_DECOMPOSED) {
+    // K1 (just enqueued) writes nothing K2 reads except `best`: the contract of the dependent launch
+    KLM_TRY(klm_dev_schedule_after_best(h->d_battery, h->d_flags, n, 0, h->best.as<int64_t>(), R, d_min, d_off,
+                                        d_ids, d_idx, d_score, h->stream));
+  } else {
+    KLM_TRY(klm_dev_schedule_bruteforce(h->d_battery, h->d_flags, n, 0, R, d_min, d_off, d_ids, d_idx, d_score,
+                                        h->stream));
+  }
+  KLM_TRY(d2h(h->sched_pin.p, d_score, out_bytes, h->stream));
+  KLM_TRY(sync(h->stream));
+  std::memcpy(out_score, h->sched_pin.at(0), min_bytes);
+  std::memcpy(out_idx, h->sched_pin.at(out_idx_at), idx_bytes);
+  return KLM_OK;
 }
 
 // ----------------------------------------------------- cluster aggregate

@@ -126,6 +126,23 @@ def test_host_alloc_arrays(pkg):
         _eq((res_i, res_s), want, "after a failed allocation")
 
 
+@pytest.mark.parametrize("n,r", [(1, 1), (300, 40), (300, 30_000), (60_000, 40), (5000, 0)])
+def test_reconcile_equals_two_calls(handle, pkg, n, r):
+    """klm_reconcile == klm_nodes_set + klm_schedule_batch (both algorithms), in its fused small
+    form and in its two-call form; the snapshot it installs serves later klm_schedule_batch calls."""
+    rng = np.random.default_rng(n + 3 * r)
+    bat, flags, mb, off, ids = helpers.random_problem(rng, n, r, kmax=3, grid=0.5)
+    want = ob.schedule_scan(bat, flags, mb, off, ids, threads=8)
+    other = helpers.random_problem(rng, n, 1, kmax=1, grid=1.0)
+    for algo in (pkg.binding.ALGO_DECOMPOSED, pkg.binding.ALGO_BRUTEFORCE):
+        handle.nodes_set(other[0], other[1])            # a different snapshot first
+        _eq(handle.reconcile(bat, flags, mb, off, ids, algo=algo), want, f"reconcile algo {algo}")
+        if r:
+            _eq(handle.schedule_batch(mb, off, ids), want, "batch on the snapshot reconcile installed")
+    with pytest.raises(pkg.KlmError):
+        handle.reconcile(bat, flags, mb, off, ids, algo=9)
+
+
 def test_edge_shapes(handle, pkg):
     # no nodes at all
     e = np.zeros(0)
