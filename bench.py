@@ -370,7 +370,7 @@ def run_ours(args):
         "clocks": clocks,
         "e2e": {"value": e2e_value, "unit": METRIC[wl][1], "h2d_bytes_per_step": e2e["h2d"],
                 "d2h_bytes_per_step": e2e["d2h"], "timing": "host wall clock around synchronous klm_* calls",
-                "calls_per_step": "klm_collect + klm_nodes_set + klm_schedule_batch" if weak else "klm_nodes_set + klm_schedule_batch"},
+                "calls_per_step": "klm_collect_begin + klm_collect_end (two cycles in flight, one handle) + klm_reconcile (scheduler handle)" if weak else "klm_nodes_set + klm_schedule_batch"},
         "gpu_launches": n_launch,
         "roofline": {"bound": "hbm", "kernel": "window_stats" if weak else "node_best+schedule",
                      "achieved": achieved, "peak": pk["hbm_gbs"], "unit": "GB/s",
@@ -397,6 +397,7 @@ def run_e2e(pkg, wl, cid, shp, rank, world, args, env):
     syn = pkg.synth
     pin = lambda a: torch.from_numpy(np.ascontiguousarray(a)).pin_memory().numpy()
     steps = max(3, min(args.steps, 50))
+    finish, sink = None, [0.0]
     with pkg.Handle(torch.cuda.current_device()) as h:
         if wl in ("c2", "c3"):
             S, T, N = shp["series"], shp["window"], shp["nodes"]
@@ -427,15 +428,35 @@ def run_e2e(pkg, wl, cid, shp, rank, world, args, env):
             # argument structs built once: the timed region is the C ABI calls themselves, as a
             # compiled (cgo) caller issues them, not the Python wrapper's array coercions
             res_i, res_s = pin(np.empty(mb.size, np.int32)), pin(np.empty(mb.size))
-            collect = h.collect_prepared(snap_h, outs, packed=True)   # one download for the four statistics
-            reconcile = h.reconcile_prepared(bat, flags, mb, off, ids, res_i, res_s)
+            # The metrics manager and the scheduler are separate components (separate goroutines
+            # in the reference): each owns a handle. The collector keeps two cycles in flight
+            # (klm_collect_begin / klm_collect_end): the tick upload and the result download of one
+            # cycle overlap the window statistics of the next; every cycle's results are read.
+            snap_x = {k: np.ascontiguousarray(v) for k, v in snap_h.items()}
+            begin, end = h.collect_pipeline(snap_x)
+            h_sched = pkg.Handle(torch.cuda.current_device())
+            reconcile = h_sched.reconcile_prepared(bat, flags, mb, off, ids, res_i, res_s)
+            in_flight = [0]
+
+            def next_tick():
+                t = ticks_h[e2e_tick[0] % ticks_h.shape[0]]
+                e2e_tick[0] += 1
+                return t
 
             def step():
-                # the metrics manager's cycle (Manager.Collect): one call, one synchronisation
-                collect(ticks_h[e2e_tick[0] % ticks_h.shape[0]])
-                e2e_tick[0] += 1
-                # the scheduler's reconcile: snapshot + batch
-                reconcile()
+                if not in_flight[0]:          # prime the pipeline (inside the timed region)
+                    begin(next_tick())
+                    in_flight[0] = 1
+                begin(next_tick())            # cycle i + 1 goes in ...
+                res = end()                   # ... cycle i comes out: statistics, rates, cluster metrics
+                sink[0] = float(res["p95"][0]) + res["cluster"]["total_nodes"]
+                reconcile()                   # the scheduler's reconcile: snapshot + batch, one call
+
+            def finish():                     # drain: the last cycle begun is completed and read
+                while in_flight[0]:
+                    end()
+                    in_flight[0] = 0
+                h_sched.close()
         else:
             n0, n1 = env["n0"], env["n1"]
             bat, flags = pin(env["bat"][n0:n1]), pin(env["flags"][n0:n1])
@@ -495,6 +516,8 @@ def run_e2e(pkg, wl, cid, shp, rank, world, args, env):
         t0 = time.perf_counter()
         for _ in range(steps):
             step()
+        if finish is not None:
+            finish()
         torch.cuda.synchronize()
         dt = time.perf_counter() - t0
     return {"ms_per_step": dt / steps * 1e3, "h2d": int(h2d), "d2h": int(d2h)}

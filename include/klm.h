@@ -261,6 +261,24 @@ int klm_collect(klm_handle* h, const klm_collect_in* in, const klm_collect_out* 
 /* size of the win_packed block for n_series series (0 if n_series <= 0) */
 int64_t klm_collect_packed_bytes(int64_t n_series);
 
+/* The same cycle, asynchronously, with up to TWO cycles in flight (no reference
+ * counterpart): klm_collect_begin enqueues one cycle and returns; klm_collect_end
+ * completes the OLDEST cycle begun. The tick upload and the result download of one
+ * cycle then overlap the window statistics of the next (three streams, everything
+ * two cycles could both touch exists once per cycle), so a collector loop
+ *     begin(0); for (i = 0; ; ++i) { begin(i + 1); end(); use results of cycle i; }
+ * runs at the pace of the kernels instead of kernels + copies.
+ * - `in` arrays are consumed by klm_collect_begin (staged in page-locked memory).
+ * - `out` arrays must stay valid until the matching klm_collect_end; their contents
+ *   are defined only after it returns. Window statistics come through win_packed
+ *   only (win_min/max/mean/p95 must be NULL).
+ * - The node snapshot must fit a 1 MB staging block (about 20 000 nodes plus
+ *   their pods), else KLM_ELIMIT: use klm_collect.
+ * - While cycles are in flight the synchronous ring / collect / aggregate calls on
+ *   this handle return KLM_ESTATE. A third klm_collect_begin returns KLM_ESTATE. */
+int klm_collect_begin(klm_handle* h, const klm_collect_in* in, const klm_collect_out* out);
+int klm_collect_end(klm_handle* h);
+
 /* ================================================= device-pointer layer */
 /* All pointers below are DEVICE pointers; nothing is allocated or freed;
  * work is enqueued on `stream` and the call returns without synchronising.

@@ -82,6 +82,8 @@ SIGNATURES = {
     "klm_last_error": (C.c_char_p, []),
     "klm_abi_version": (C.c_int, []),
     "klm_collect_packed_bytes": (_I64, [_I64]),
+    "klm_collect_begin": (C.c_int, [_P, C.POINTER(CollectIn), C.POINTER(CollectOut)]),
+    "klm_collect_end": (C.c_int, [_P]),
     "klm_host_alloc": (C.c_int, [C.c_size_t, C.POINTER(_P)]),
     "klm_host_free": (C.c_int, [_P]),
     "klm_nodes_set": (C.c_int, [_P, _I64, _P, _P]),
@@ -396,6 +398,63 @@ class Handle:
             return cl
         call.keep = keep
         return call
+
+    def collect_pipeline(self, snap: dict):
+        """klm_collect_begin / klm_collect_end with two cycles in flight. Returns
+        (begin(tick), end()): end() completes the oldest cycle begun and returns its result dict
+        (keys as collect(): cluster, cpu_rate, ..., min, max, mean, p95 -- views into that cycle's
+        page-locked block, valid until the cycle after next is begun). `snap` arrays are staged
+        by begin, so they may change between cycles; they must be exact-dtype C-contiguous."""
+        ex = self._exact
+        s = self._ring_shape[0]
+        n, p = snap["cpu_capacity"].size, snap["pod_running"].size
+        gu = snap.get("gpu_usage")
+        n_gu = 0 if gu is None else gu.size
+        cols = [ex(snap[k], dt, k) for k, dt in (("cpu_capacity", np.int64), ("cpu_usage", np.int64),
+                                                 ("memory_capacity", np.int64), ("memory_usage", np.int64),
+                                                 ("gpu_count", np.int32), ("healthy", np.uint8))]
+        nc = NodeCols(*cols, ex(gu, np.float64, "gpu_usage") if n_gu else None, n_gu)
+        cin = CollectIn(None, C.pointer(nc), n, ex(snap["disk_capacity"], np.int64, "disk_capacity"),
+                        ex(snap["disk_allocatable"], np.int64, "disk_allocatable"),
+                        ex(snap["pod_running"], np.uint8, "pod_running"), p)
+        nbytes = self._lib.klm_collect_packed_bytes(s)
+        c4 = (s * 4 + 255) & ~255
+        sets = []
+        for _ in range(2):
+            block = host_array(nbytes, np.uint8)
+            o = {"cpu_rate": np.empty(n), "memory_rate": np.empty(n), "disk_usage": np.empty(n, np.int64),
+                 "disk_rate": np.empty(n), "under_pressure": np.empty(n, np.uint8),
+                 "min": block[0:s * 4].view(np.float32), "max": block[c4:c4 + s * 4].view(np.float32),
+                 "p95": block[2 * c4:2 * c4 + s * 4].view(np.float32),
+                 "mean": block[3 * c4:3 * c4 + s * 8].view(np.float64)}
+            cl = ClusterOut()
+            cout = CollectOut(C.pointer(cl), *[o[k].ctypes.data if o[k].size else None
+                                               for k in ("cpu_rate", "memory_rate", "disk_usage", "disk_rate",
+                                                         "under_pressure")],
+                              None, None, None, None, block.ctypes.data)
+            sets.append((o, cl, cout, block))
+        b_fn, e_fn, h, pin_ = self._lib.klm_collect_begin, self._lib.klm_collect_end, self._h, C.byref(cin)
+        seq = {"begun": 0, "ended": 0}
+
+        def begin(tick):
+            if tick is not None and (tick.dtype != np.float32 or tick.size != s or not tick.flags["C_CONTIGUOUS"]):
+                raise ValueError("tick: need float32[n_series], C-contiguous")
+            cin.tick_values = None if tick is None else tick.ctypes.data
+            rc = b_fn(h, pin_, C.byref(sets[seq["begun"] & 1][2]))
+            if rc != KLM_OK:
+                raise KlmError(rc, last_error())
+            seq["begun"] += 1
+
+        def end():
+            rc = e_fn(h)
+            if rc != KLM_OK:
+                raise KlmError(rc, last_error())
+            o, cl, _, _ = sets[seq["ended"] & 1]
+            seq["ended"] += 1
+            o["cluster"] = cl.as_dict()
+            return o
+        begin.keep = (nc, cin, sets, snap)
+        return begin, end
 
     def reconcile_prepared(self, battery, flags, min_battery, pref_off, pref_ids, out_idx, out_score,
                            algo: int = ALGO_DECOMPOSED):

@@ -90,6 +90,8 @@ struct PinBuf {
 // Arrays up to this many bytes in total go through the staging block; above it the
 // memcpy would cost more than the extra copy submissions and the arrays are sent directly.
 constexpr size_t kStageMax = 256 << 10;
+// klm_collect_begin stages every snapshot (it must return without waiting): its own limit
+constexpr size_t kAsyncSnapMax = 1 << 20;
 
 // klm_schedule_batch pipelines batches of at least 2 * kChunkRequests requests over two
 // streams, in at most kMaxChunks chunks of at least kChunkRequests requests.
@@ -132,6 +134,21 @@ struct klm_handle {
   DevBuf ring, seen, ing_ids, ing_vals, stats_out;
   int64_t n_series = 0;
   int32_t window = 0, pitch = 0;
+
+  // klm_collect_begin / klm_collect_end: two cycles in flight. Uploads and the snapshot branch
+  // run on stream2, K6 + K7 on stream, the result download on stream3; what two overlapping
+  // cycles could both touch exists once per slot.
+  struct CollectSlot {
+    DevBuf tick_dev, stats;   // this cycle's samples; K7's packed results
+    PinBuf pin;               // tick | snapshot columns | small results
+    cudaEvent_t up = nullptr, k7 = nullptr, snap = nullptr, win = nullptr;
+    klm_collect_out out{};    // where klm_collect_end delivers the small results
+    int64_t n = 0;
+    size_t col8 = 0, out_at = 0;
+    bool rates = false, snapshot = false;
+  } slot[2];
+  cudaStream_t stream3 = nullptr, stream_bulk = nullptr;  // downloads; K6 + K7 of the async cycles
+  uint64_t begun = 0, ended = 0;
 };
 
 namespace {
@@ -176,10 +193,20 @@ int sync(cudaStream_t st) {
 
 size_t align256(size_t b) { return (b + 255) & ~size_t(255); }
 
+// the synchronous ring / collect / aggregate calls share buffers and streams with the cycles
+// klm_collect_begin has in flight
+int collect_idle(klm_handle* h, const char* who) {
+  if (h->begun != h->ended) {
+    set_error("%s: klm_collect_begin cycles are in flight; finish them with klm_collect_end first", who);
+    return KLM_ESTATE;
+  }
+  return KLM_OK;
+}
+
 }  // namespace
 
 extern "C" const char* klm_last_error(void) { return g_err; }
-extern "C" int klm_abi_version(void) { return 1003; }
+extern "C" int klm_abi_version(void) { return 1004; }
 
 extern "C" int klm_host_alloc(size_t bytes, void** out) {
   if (!out || bytes == 0) {
@@ -234,7 +261,12 @@ extern "C" int klm_create(const int* device_ids, int n_dev, klm_handle** out) {
     return KLM_EINVAL;
   }
   h->device = dev;
-  e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);
+  // The main stream carries the short synchronous calls (a reconcile is two tiny kernels): it
+  // gets the highest priority so that its CTAs are placed ahead of another handle's pending
+  // bulk work (the window statistics of klm_collect_begin run on a default-priority stream).
+  int prio_least = 0, prio_greatest = 0;
+  e = cudaDeviceGetStreamPriorityRange(&prio_least, &prio_greatest);
+  if (e == cudaSuccess) e = cudaStreamCreateWithPriority(&h->stream, cudaStreamNonBlocking, prio_greatest);
   if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->stream2, cudaStreamNonBlocking);
   if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->sched_read, cudaEventDisableTiming);
   if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming);
@@ -275,6 +307,17 @@ extern "C" void klm_destroy(klm_handle* h) {
                     &h->rate_out, &h->pod_tot, &h->fleet_in, &h->fleet_out,  &h->fleet_scratch, &h->ring,
                     &h->seen,     &h->ing_ids,  &h->ing_vals,   &h->stats_out};
   for (DevBuf* b : bufs) b->release();
+  if (h->stream_bulk) cudaStreamSynchronize(h->stream_bulk);
+  if (h->stream3) cudaStreamSynchronize(h->stream3);
+  for (auto& sl : h->slot) {
+    sl.tick_dev.release();
+    sl.stats.release();
+    sl.pin.release();
+    for (cudaEvent_t ev : {sl.up, sl.k7, sl.snap, sl.win})
+      if (ev) cudaEventDestroy(ev);
+  }
+  if (h->stream3) cudaStreamDestroy(h->stream3);
+  if (h->stream_bulk) cudaStreamDestroy(h->stream_bulk);
   h->sched_pin.release();
   h->snap_pin.release();
   if (h->sched_read) cudaEventDestroy(h->sched_read);
@@ -537,6 +580,7 @@ extern "C" int klm_cluster_aggregate(klm_handle* h, const klm_node_cols* c, int6
                                      const uint8_t* pod_running, int64_t n_pods,
                                      klm_cluster_out* out) {
   KLM_ENTER(h);
+  KLM_TRY(collect_idle(h, "klm_cluster_aggregate"));
   if (!c || !out || n < 0 || n_pods < 0 || c->n_gpu_usage < 0 ||
       (n > 0 && (!c->cpu_capacity || !c->cpu_usage || !c->memory_capacity || !c->memory_usage ||
                  !c->gpu_count || !c->healthy)) ||
@@ -701,6 +745,7 @@ extern "C" int klm_fleet_scan(klm_handle* h, int64_t n, const uint8_t* status_ok
 
 extern "C" int klm_ring_create(klm_handle* h, int64_t n_series, int32_t window) {
   KLM_ENTER(h);
+  KLM_TRY(collect_idle(h, "klm_ring_create"));
   if (n_series < 1 || window < 1) {
     set_error("klm_ring_create: n_series and window must be positive");
     return KLM_EINVAL;
@@ -730,6 +775,7 @@ extern "C" int klm_ring_ingest(klm_handle* h, int64_t n, const int64_t* series_i
                                const float* values) {
   KLM_ENTER(h);
   KLM_TRY(ring_ready(h, "klm_ring_ingest"));
+  KLM_TRY(collect_idle(h, "klm_ring_ingest"));
   if (n < 0 || (n > 0 && (!series_ids || !values))) {
     set_error("klm_ring_ingest: bad argument");
     return KLM_EINVAL;
@@ -748,6 +794,7 @@ extern "C" int klm_ring_ingest(klm_handle* h, int64_t n, const int64_t* series_i
 extern "C" int klm_ring_ingest_tick(klm_handle* h, const float* values) {
   KLM_ENTER(h);
   KLM_TRY(ring_ready(h, "klm_ring_ingest_tick"));
+  KLM_TRY(collect_idle(h, "klm_ring_ingest_tick"));
   if (!values) {
     set_error("klm_ring_ingest_tick: values is null");
     return KLM_EINVAL;
@@ -764,6 +811,7 @@ extern "C" int klm_ring_load(klm_handle* h, int64_t s0, int64_t s1, int32_t coun
                              const float* data) {
   KLM_ENTER(h);
   KLM_TRY(ring_ready(h, "klm_ring_load"));
+  KLM_TRY(collect_idle(h, "klm_ring_load"));
   if (s0 < 0 || s1 < s0 || s1 > h->n_series || count < 0 || count > h->window ||
       (s1 > s0 && count > 0 && !data)) {
     set_error("klm_ring_load: bad argument");
@@ -794,6 +842,7 @@ extern "C" int klm_ring_stats(klm_handle* h, int64_t s0, int64_t s1, float* out_
                               float* out_max, double* out_mean, float* out_p95) {
   KLM_ENTER(h);
   KLM_TRY(ring_ready(h, "klm_ring_stats"));
+  KLM_TRY(collect_idle(h, "klm_ring_stats"));
   if (s0 < 0 || s1 < s0 || s1 > h->n_series) {
     set_error("klm_ring_stats: series range out of bounds");
     return KLM_EINVAL;
@@ -993,6 +1042,180 @@ int collect_impl(klm_handle* h, const klm_collect_in* in, const klm_collect_out*
 
 }  // namespace
 
+// ---------------------------------------------- collect cycle, two in flight
+
+namespace {
+
+int collect_begin_impl(klm_handle* h, const klm_collect_in* in, const klm_collect_out* out) {
+  if (!in || !out || in->n_nodes < 0 || in->n_pods < 0 || (in->n_nodes > 0 && !in->nodes) ||
+      (in->n_pods > 0 && !in->pod_running)) {
+    set_error("klm_collect_begin: bad argument");
+    return KLM_EINVAL;
+  }
+  if (out->win_min || out->win_max || out->win_mean || out->win_p95) {
+    set_error("klm_collect_begin: window statistics are delivered through win_packed only");
+    return KLM_EINVAL;
+  }
+  if (h->begun - h->ended >= 2) {
+    set_error("klm_collect_begin: two cycles are already in flight");
+    return KLM_ESTATE;
+  }
+  const bool want_win = out->win_packed != nullptr;
+  if ((in->tick_values || want_win) && h->n_series <= 0) {
+    set_error("klm_collect_begin: no ring; call klm_ring_create first");
+    return KLM_ESTATE;
+  }
+  const int64_t n = in->n_nodes, np = in->n_pods, S = h->n_series;
+  const klm_node_cols* c = in->nodes;
+  const int64_t ng = (n > 0 && c) ? c->n_gpu_usage : 0;
+  if (n > 0 && (!c->cpu_capacity || !c->cpu_usage || !c->memory_capacity || !c->memory_usage ||
+                !c->gpu_count || !c->healthy || ng < 0 || (ng > 0 && !c->gpu_usage))) {
+    set_error("klm_collect_begin: null node column");
+    return KLM_EINVAL;
+  }
+  const size_t col8 = align256((size_t)n * 8), col4 = align256((size_t)n * 4), col1 = align256((size_t)n);
+  const size_t o_gc = 6 * col8, o_hl = o_gc + col4, o_pod = o_hl + col1;
+  const size_t o_gu = o_pod + align256((size_t)np), in_bytes = o_gu + align256((size_t)ng * 8);
+  const size_t out_bytes = 256 + 5 * col8;
+  if (in_bytes > kAsyncSnapMax || out_bytes > kAsyncSnapMax) {
+    set_error("klm_collect_begin: the node snapshot exceeds the %zu-byte staging block; use klm_collect",
+              kAsyncSnapMax);
+    return KLM_ELIMIT;
+  }
+  if (!h->stream3) KLM_CUDA(cudaStreamCreateWithFlags(&h->stream3, cudaStreamNonBlocking));
+  if (!h->stream_bulk) KLM_CUDA(cudaStreamCreateWithFlags(&h->stream_bulk, cudaStreamNonBlocking));
+  klm_handle::CollectSlot& sl = h->slot[h->begun & 1];
+  for (cudaEvent_t* ev : {&sl.up, &sl.k7, &sl.snap, &sl.win})
+    if (!*ev) KLM_CUDA(cudaEventCreateWithFlags(ev, cudaEventDisableTiming));
+  cudaStream_t st = h->stream_bulk, st2 = h->stream2, st3 = h->stream3;
+  const size_t tick_al = align256((size_t)(S > 0 ? S : 0) * 4);
+  KLM_TRY(sl.pin.ensure(tick_al + 2 * kAsyncSnapMax));
+  const bool snapshot = n > 0 || np > 0 || out->cluster;
+  // ---- uploads + snapshot branch on stream2
+  if (in->tick_values) {
+    KLM_TRY(sl.tick_dev.ensure((size_t)S * 4));
+    std::memcpy(sl.pin.at(0), in->tick_values, (size_t)S * 4);
+    KLM_TRY(h2d(sl.tick_dev.p, sl.pin.at(0), (size_t)S * 4, st2));
+  }
+  KLM_CUDA(cudaEventRecord(sl.up, st2));
+  const bool want_rates = (out->cpu_rate || out->memory_rate || out->disk_usage || out->disk_rate ||
+                           out->under_pressure) && n > 0;
+  if (snapshot) {
+    KLM_TRY(h->agg_cols.ensure(in_bytes + 256));
+    KLM_TRY(h->snap_out.ensure(out_bytes));
+    char* base = h->agg_cols.as<char>();
+    char* hin = sl.pin.at(tick_al);
+    klm_node_cols d{};
+    d.cpu_capacity = reinterpret_cast<int64_t*>(base);
+    d.cpu_usage = reinterpret_cast<int64_t*>(base + col8);
+    d.memory_capacity = reinterpret_cast<int64_t*>(base + 2 * col8);
+    d.memory_usage = reinterpret_cast<int64_t*>(base + 3 * col8);
+    int64_t* d_dcap = reinterpret_cast<int64_t*>(base + 4 * col8);
+    int64_t* d_dalloc = reinterpret_cast<int64_t*>(base + 5 * col8);
+    d.gpu_count = reinterpret_cast<int32_t*>(base + o_gc);
+    d.healthy = reinterpret_cast<uint8_t*>(base + o_hl);
+    uint8_t* d_pods = reinterpret_cast<uint8_t*>(base + o_pod);
+    d.gpu_usage = reinterpret_cast<double*>(base + o_gu);
+    d.n_gpu_usage = ng;
+    auto put = [&](size_t off, const void* src, size_t bytes) {
+      if (bytes && src) std::memcpy(hin + off, src, bytes);
+    };
+    if (n > 0) {
+      put(0, c->cpu_capacity, (size_t)n * 8);
+      put(col8, c->cpu_usage, (size_t)n * 8);
+      put(2 * col8, c->memory_capacity, (size_t)n * 8);
+      put(3 * col8, c->memory_usage, (size_t)n * 8);
+      put(4 * col8, in->disk_capacity, (size_t)n * 8);
+      put(5 * col8, in->disk_allocatable, (size_t)n * 8);
+      put(o_gc, c->gpu_count, (size_t)n * 4);
+      put(o_hl, c->healthy, (size_t)n);
+      put(o_gu, c->gpu_usage, (size_t)ng * 8);
+    }
+    put(o_pod, in->pod_running, (size_t)np);
+    KLM_TRY(h2d(base, hin, in_bytes, st2));
+    char* rout = h->snap_out.as<char>() + 256;
+    if (want_rates)
+      KLM_TRY(klm_dev_node_rates(n, d.cpu_capacity, d.cpu_usage, d.memory_capacity, d.memory_usage,
+                                 in->disk_capacity ? d_dcap : nullptr,
+                                 in->disk_allocatable ? d_dalloc : nullptr,
+                                 reinterpret_cast<double*>(rout), reinterpret_cast<double*>(rout + col8),
+                                 reinterpret_cast<int64_t*>(rout + 2 * col8),
+                                 reinterpret_cast<double*>(rout + 3 * col8),
+                                 reinterpret_cast<uint8_t*>(rout + 4 * col8), st2));
+    if (out->cluster)
+      KLM_TRY(klm_dev_cluster_aggregate(&d, n, d_pods, np, h->snap_out.as<klm_cluster_out>(),
+                                        h->agg_scratch.p, st2));
+    KLM_TRY(d2h(sl.pin.at(tick_al + kAsyncSnapMax), h->snap_out.p, want_rates ? out_bytes : 256, st2));
+  }
+  KLM_CUDA(cudaEventRecord(sl.snap, st2));
+  // ---- K6 + K7 on the main stream, as soon as the tick is on the device
+  KLM_CUDA(cudaStreamWaitEvent(st, sl.up, 0));
+  if (in->tick_values)
+    KLM_TRY(klm_dev_ring_ingest(h->ring.as<float>(), h->seen.as<uint32_t>(), S, h->window, h->pitch, S,
+                                nullptr, sl.tick_dev.as<float>(), st));
+  if (want_win) {
+    const size_t c4 = align256((size_t)S * 4);
+    KLM_TRY(sl.stats.ensure((size_t)klm_collect_packed_bytes(S) + 256));
+    char* o = sl.stats.as<char>();
+    KLM_TRY(klm_dev_window_stats(h->ring.as<float>(), h->seen.as<uint32_t>(), h->window, h->pitch, 0, S,
+                                 reinterpret_cast<float*>(o), reinterpret_cast<float*>(o + c4),
+                                 reinterpret_cast<double*>(o + 3 * c4), reinterpret_cast<float*>(o + 2 * c4), st));
+  }
+  KLM_CUDA(cudaEventRecord(sl.k7, st));
+  // ---- the one result download, behind K7, on its own stream
+  KLM_CUDA(cudaStreamWaitEvent(st3, sl.k7, 0));
+  if (want_win) KLM_TRY(d2h(out->win_packed, sl.stats.p, (size_t)klm_collect_packed_bytes(S), st3));
+  KLM_CUDA(cudaEventRecord(sl.win, st3));
+  sl.out = *out;
+  sl.n = n;
+  sl.col8 = col8;
+  sl.out_at = tick_al + kAsyncSnapMax;
+  sl.rates = want_rates;
+  sl.snapshot = snapshot;
+  ++h->begun;
+  return KLM_OK;
+}
+
+}  // namespace
+
+extern "C" int klm_collect_begin(klm_handle* h, const klm_collect_in* in, const klm_collect_out* out) {
+  KLM_ENTER(h);
+  const int rc = collect_begin_impl(h, in, out);
+  if (rc != KLM_OK && h->stream3) {  // nothing half-enqueued may outlive the failed call
+    if (h->stream_bulk) cudaStreamSynchronize(h->stream_bulk);
+    cudaStreamSynchronize(h->stream2);
+    cudaStreamSynchronize(h->stream3);
+  }
+  return rc;
+}
+
+extern "C" int klm_collect_end(klm_handle* h) {
+  KLM_ENTER(h);
+  if (h->begun == h->ended) {
+    set_error("klm_collect_end: no cycle in flight");
+    return KLM_ESTATE;
+  }
+  klm_handle::CollectSlot& sl = h->slot[h->ended & 1];
+  ++h->ended;  // the slot is free again whatever happens below
+  KLM_CUDA(cudaEventSynchronize(sl.snap));
+  if (sl.snapshot) {
+    const char* hout = sl.pin.at(sl.out_at);
+    const klm_collect_out& o = sl.out;
+    const size_t n = (size_t)sl.n, col8 = sl.col8;
+    if (o.cluster) std::memcpy(o.cluster, hout, sizeof(klm_cluster_out));
+    if (sl.rates) {
+      const char* r = hout + 256;
+      if (o.cpu_rate) std::memcpy(o.cpu_rate, r, n * 8);
+      if (o.memory_rate) std::memcpy(o.memory_rate, r + col8, n * 8);
+      if (o.disk_usage) std::memcpy(o.disk_usage, r + 2 * col8, n * 8);
+      if (o.disk_rate) std::memcpy(o.disk_rate, r + 3 * col8, n * 8);
+      if (o.under_pressure) std::memcpy(o.under_pressure, r + 4 * col8, n);
+    }
+  }
+  KLM_CUDA(cudaEventSynchronize(sl.win));
+  return KLM_OK;
+}
+
 extern "C" int64_t klm_collect_packed_bytes(int64_t n_series) {
   if (n_series <= 0) return 0;
   return (int64_t)(3 * align256((size_t)n_series * 4) + (size_t)n_series * 8);
@@ -1000,6 +1223,7 @@ extern "C" int64_t klm_collect_packed_bytes(int64_t n_series) {
 
 extern "C" int klm_collect(klm_handle* h, const klm_collect_in* in, const klm_collect_out* out) {
   KLM_ENTER(h);
+  KLM_TRY(collect_idle(h, "klm_collect"));
   const int rc = collect_impl(h, in, out);
   if (rc != KLM_OK) {  // leave nothing in flight that still reads or writes the staging blocks
     cudaStreamSynchronize(h->stream);

@@ -259,3 +259,50 @@ def test_prepared_calls_match_wrappers(pkg):
                                      pout["min"].ctypes.data)
         cin = pkg.binding.CollectIn(None, None, 0, None, None, None, 0)
         assert b._lib.klm_collect(b._h, C.byref(cin), C.byref(bad)) == pkg.binding.KLM_EINVAL
+
+
+def test_collect_pipeline_two_in_flight(pkg):
+    """klm_collect_begin / klm_collect_end: with two cycles in flight every cycle still gives
+    exactly what the synchronous klm_collect gives for the same tick and snapshot (the snapshot
+    changes between cycles: begin stages it), and the state rules hold: a third begin, the
+    synchronous ring calls while cycles are in flight, and an end with nothing in flight are
+    refused with KLM_ESTATE."""
+    rng = np.random.default_rng(21)
+    s, t, n, p = 900, 3600, 150, 700
+    rows = distributions(rng, s, t)
+    with pkg.Handle(0) as a, pkg.Handle(0) as b:
+        for h in (a, b):
+            h.ring_create(s, t)
+            h.ring_load(0, rows[:, : t - 1])
+        snap = {k: np.ascontiguousarray(v) for k, v in pkg.synth.cluster_snapshot(2, n, p, gpus_per_node=1).items()}
+        begin, end = b.collect_pipeline(snap)
+        ticks = [(rng.random(s) * 100).astype(np.float32) for _ in range(7)]
+        wants = []
+
+        def sync_cycle(i):
+            snap["cpu_usage"][:] = (snap["cpu_capacity"] * rng.random(n)).astype(np.int64)  # changes per cycle
+            w = a.collect(ticks[i], snap)
+            wants.append({k: (v.copy() if isinstance(v, np.ndarray) else v) for k, v in w.items()})
+
+        def check(i, got):
+            w = wants[i]
+            assert got["cluster"] == w["cluster"], i
+            for k in ("min", "max", "p95", "mean", "cpu_rate", "memory_rate", "disk_usage", "disk_rate",
+                      "under_pressure"):
+                assert np.array_equal(got[k], w[k]), (i, k)
+
+        sync_cycle(0); begin(ticks[0])
+        for i in range(1, 7):
+            sync_cycle(i); begin(ticks[i])          # two in flight
+            if i == 3:
+                with pytest.raises(pkg.KlmError) as ei:
+                    begin(ticks[i])                  # a third is refused ...
+                assert ei.value.code == pkg.binding.KLM_ESTATE
+                with pytest.raises(pkg.KlmError):
+                    b.ring_stats()                   # ... and so is a synchronous ring call
+            check(i - 1, end())
+        check(6, end())
+        with pytest.raises(pkg.KlmError):
+            end()                                    # nothing in flight
+        again = b.collect(None, snap)                # idle again: the synchronous call works
+        assert np.array_equal(again["p95"], wants[6]["p95"])
