@@ -369,7 +369,7 @@ def run_ours(args):
                    **extra},
         "clocks": clocks,
         "e2e": {"value": e2e_value, "unit": METRIC[wl][1], "h2d_bytes_per_step": e2e["h2d"],
-                "d2h_bytes_per_step": e2e["d2h"], "timing": "host wall clock around synchronous klm_* calls",
+                "d2h_bytes_per_step": e2e["d2h"], "timing": "host wall clock around the klm_* calls of K steps, priming and draining included",
                 "calls_per_step": "klm_collect_begin + klm_collect_end (two cycles in flight, one handle) + klm_reconcile (scheduler handle)" if weak else "klm_nodes_set + klm_schedule_batch"},
         "gpu_launches": n_launch,
         "roofline": {"bound": "hbm", "kernel": "window_stats" if weak else "node_best+schedule",
