@@ -419,6 +419,12 @@ int klm_dev_window_stats(const float* ring, const uint32_t* seen,
                          int32_t window, int32_t pitch, int64_t s0, int64_t s1,
                          float* out_min, float* out_max, double* out_mean,
                          float* out_p95, void* stream);
+/* The streaming variant of K7: one warp per series, the window is not kept on chip (rows pass
+ * through two small register buffers), so 24 warps fit an SM; any window size; same results. */
+int klm_dev_window_stats_stream(const float* ring, const uint32_t* seen,
+                                int32_t window, int32_t pitch, int64_t s0,
+                                int64_t s1, float* out_min, float* out_max,
+                                double* out_mean, float* out_p95, void* stream);
 /* The pipelined variant of K7: one persistent CTA per SM, a producer warp streams rows
  * into a ring of shared-memory slots with cp.async.bulk + mbarriers, 15 consumer warps
  * work on them in place. Windows up to 4096 (KLM_ELIMIT beyond); same results. Slower

@@ -118,6 +118,7 @@ SIGNATURES = {
     "klm_dev_fleet_scan": (C.c_int, [_I64, _P, _P, _F64, _P, _P, _P, _P]),
     "klm_dev_ring_ingest": (C.c_int, [_P, _P, _I64, _I32, _I32, _I64, _P, _P, _P]),
     "klm_dev_window_stats": (C.c_int, [_P, _P, _I32, _I32, _I64, _I64, _P, _P, _P, _P, _P]),
+    "klm_dev_window_stats_stream": (C.c_int, [_P, _P, _I32, _I32, _I64, _I64, _P, _P, _P, _P, _P]),
     "klm_dev_window_stats_pipe": (C.c_int, [_P, _P, _I32, _I32, _I64, _I64, _P, _P, _P, _P, _P]),
     "klm_dev_window_stats_warp": (C.c_int, [_P, _P, _I32, _I32, _I64, _I64, _P, _P, _P, _P, _P]),
     "klm_dev_window_stats_block": (C.c_int, [_P, _P, _I32, _I32, _I64, _I64, _P, _P, _P, _P, _P]),
@@ -655,6 +656,7 @@ class Dev:
         if block_variant:
             variant = "block"
         fn = {None: self.lib.klm_dev_window_stats, "pipe": self.lib.klm_dev_window_stats_pipe,
-              "warp": self.lib.klm_dev_window_stats_warp, "block": self.lib.klm_dev_window_stats_block}[variant]
+              "warp": self.lib.klm_dev_window_stats_warp, "stream": self.lib.klm_dev_window_stats_stream,
+              "block": self.lib.klm_dev_window_stats_block}[variant]
         check(fn(_dp(ring), _dp(seen), window, pitch, s0, s1, _dp(out_min), _dp(out_max), _dp(out_mean),
                  _dp(out_p95), _stream_ptr(stream)))

@@ -32,6 +32,19 @@ static inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t
 
 static inline int64_t ceil_div(int64_t a, int64_t b) { return (a + b - 1) / b; }
 
+// "Done once per device" flags for cudaFuncSetAttribute and the like: one bit per device
+// ordinal, set and tested atomically (handles of several threads share the launchers).
+// Devices beyond 63 simply repeat the (idempotent) set-up on every call.
+struct PerDeviceOnce {
+  unsigned long long mask = 0ull;
+  bool done(int dev) const {
+    return dev >= 0 && dev < 64 && ((__atomic_load_n(&mask, __ATOMIC_ACQUIRE) >> dev) & 1ull);
+  }
+  void set(int dev) {
+    if (dev >= 0 && dev < 64) __atomic_fetch_or(&mask, 1ull << dev, __ATOMIC_RELEASE);
+  }
+};
+
 #ifdef __CUDACC__
 
 // Streaming 128-bit load: read-only path, do not allocate in L1 (each byte of

@@ -217,13 +217,13 @@ int launch_window_stats_block(const float* ring, const uint32_t* seen, int32_t w
               window);
     return KLM_ELIMIT;
   }
-  static bool attr_set[64] = {};
+  static PerDeviceOnce attr_set;
   int dev = 0;
   KLM_CUDA(cudaGetDevice(&dev));
-  if (smem > 48 * 1024 && !(dev < 64 && attr_set[dev])) {
+  if (smem > 48 * 1024 && !attr_set.done(dev)) {
     KLM_CUDA(cudaFuncSetAttribute(window_stats_block_kernel,
                                   cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-    if (dev < 64) attr_set[dev] = true;
+    attr_set.set(dev);
   }
   // one CTA per series; grid.x is limited to 2^31 - 1, far above any ring here
   const int64_t rows = s1 - s0;
@@ -247,6 +247,9 @@ int launch_window_stats_warp(const float* ring, const uint32_t* seen, int32_t wi
 int launch_window_stats_pipe(const float* ring, const uint32_t* seen, int32_t window,
                              int32_t pitch, int64_t s0, int64_t s1, float* out_min,
                              float* out_max, double* out_mean, float* out_p95, cudaStream_t st);
+int launch_window_stats_stream(const float* ring, const uint32_t* seen, int32_t window,
+                               int32_t pitch, int64_t s0, int64_t s1, float* out_min,
+                               float* out_max, double* out_mean, float* out_p95, cudaStream_t st);
 }
 
 static int window_stats_args_ok(const float* ring, const uint32_t* seen, int32_t window,
@@ -266,6 +269,11 @@ extern "C" int klm_dev_window_stats(const float* ring, const uint32_t* seen, int
                                     void* stream) {
   const int rc = window_stats_args_ok(ring, seen, window, pitch, s0, s1);
   if (rc != KLM_OK || s1 == s0) return rc;
+#ifdef KLM_K7_STREAM_DEFAULT
+  if (window <= 8192)
+    return launch_window_stats_stream(ring, seen, window, pitch, s0, s1, out_min, out_max, out_mean,
+                                      out_p95, as_stream(stream));
+#endif
   // windows <= 4096: the register-resident warp kernel (fastest measured);
   // larger windows fall through to the shared-memory block kernel
   const int w = launch_window_stats_warp(ring, seen, window, pitch, s0, s1, out_min, out_max,
@@ -288,6 +296,16 @@ extern "C" int klm_dev_window_stats_warp(const float* ring, const uint32_t* seen
     return KLM_ELIMIT;
   }
   return w;
+}
+
+extern "C" int klm_dev_window_stats_stream(const float* ring, const uint32_t* seen, int32_t window,
+                                           int32_t pitch, int64_t s0, int64_t s1, float* out_min,
+                                           float* out_max, double* out_mean, float* out_p95,
+                                           void* stream) {
+  const int rc = window_stats_args_ok(ring, seen, window, pitch, s0, s1);
+  if (rc != KLM_OK || s1 == s0) return rc;
+  return launch_window_stats_stream(ring, seen, window, pitch, s0, s1, out_min, out_max, out_mean,
+                                    out_p95, as_stream(stream));
 }
 
 extern "C" int klm_dev_window_stats_pipe(const float* ring, const uint32_t* seen, int32_t window,

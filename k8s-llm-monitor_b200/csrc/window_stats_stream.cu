@@ -1,0 +1,466 @@
+// K7 window_stats, streaming variant: one warp per series, the window is NOT kept on chip.
+//
+// No reference code exists for this (the reference keeps only the latest snapshot,
+// internal/metrics/manager.go:29, :289-290); definition in window_stats.cuh / DESIGN.md,
+// "parity unpinned".
+//
+// The register-resident warp kernel (window_stats_warp.cu) holds a whole 14.4 KB window per
+// warp, which caps an SM at 16-20 warps; it then runs at the pace its few warps can hide
+// latency, not at the pace of HBM ("K7 in detail"). This kernel keeps only what the
+// statistics need:
+//   1. 128 samples (4 rows spread over the window, one element per lane and row) are fetched
+//      first, together with the first rows of the pass; the pivot is the smallest "second
+//      largest" of the four groups of 32, exactly as in the warp kernel.
+//   2. ONE pass streams the rows through two register buffers of four rows (the loads of one
+//      buffer are in flight while the other is consumed): min / max / exact f64 sum, and every
+//      element > the pivot is appended to the lane's list in shared memory.
+//   3. select_from_lists (window_stats.cuh) finds the k-th largest among the listed elements.
+//   The rare paths that need the window again (heavy ties at the pivot, a pivot that listed
+//   fewer than k elements, list overflow) re-read the row -- it is still in L2 -- in small
+//   rolled loops kept out of line.
+// 64-80 registers per thread instead of 128, no window-size template (any window, one
+// instantiation), and 24-32 warps per SM. Exact: every exit is an input element whose rank has
+// been counted, so the result is bit-identical to sorting.
+#include "common.cuh"
+#include "window_stats.cuh"
+
+namespace klm {
+
+constexpr int kWssWarps = 4;  // warps (series) per CTA
+constexpr int kWssThreads = kWssWarps * 32;
+constexpr int kWssAux = 256;  // per warp: the 64 candidates of the final sort
+constexpr int kWssSampledMinRows = 7;  // below 7 full rows (896 samples) list everything
+
+template <int CAP>
+struct WssCfg {
+  static constexpr int kListBytes = CAP * 128;  // [entry][lane] f32
+  static constexpr int kClamp = CAP - 4;        // a lane is held at this count (four appends may follow)
+  static constexpr size_t kSmem = (size_t)kWssWarps * (kListBytes + kWssAux);
+  static_assert(CAP >= kListPrefill + 8, "the prefilled part must fit");
+};
+
+// if (x > lox) { list[c / 128] = x; c += 128; }  c = byte offset of the lane's next slot; the
+// slot address lives in a temporary so that the store never holds up the counter.
+__device__ __forceinline__ void wss_append(uint32_t& c, uint32_t lb, float x, float lox) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t.reg .b32 t;\n\t"
+      "setp.gt.f32 p, %2, %3;\n\t"
+      "add.u32 t, %0, %1;\n\t"
+      "@p st.shared.f32 [t], %2;\n\t"
+      "@p add.u32 %0, %0, 128;\n\t}"
+      : "+r"(c)
+      : "r"(lb), "f"(x), "f"(lox));
+}
+
+struct WssAcc {
+  float mn0, mn1, mx0, mx1;
+  double sum0, sum1;
+};
+
+// four valid elements of one lane: min / max / f64 sum into the accumulators of parity `odd`,
+// append(x > lox)
+template <int CLAMP>
+__device__ __forceinline__ void wss_row(WssAcc& a, uint32_t& c, uint32_t lb, float lox, float4 t,
+                                        bool odd) {
+  if (odd) {
+    a.mn1 = fminf(fminf(a.mn1, t.x), fminf(t.y, fminf(t.z, t.w)));
+    a.mx1 = fmaxf(fmaxf(a.mx1, t.x), fmaxf(t.y, fmaxf(t.z, t.w)));
+    a.sum1 += ((double)t.x + (double)t.y) + ((double)t.z + (double)t.w);
+  } else {
+    a.mn0 = fminf(fminf(a.mn0, t.x), fminf(t.y, fminf(t.z, t.w)));
+    a.mx0 = fmaxf(fmaxf(a.mx0, t.x), fmaxf(t.y, fmaxf(t.z, t.w)));
+    a.sum0 += ((double)t.x + (double)t.y) + ((double)t.z + (double)t.w);
+  }
+  c = min(c, (uint32_t)(CLAMP * 128));
+  wss_append(c, lb, t.x, lox);
+  wss_append(c, lb, t.y, lox);
+  wss_append(c, lb, t.z, lox);
+  wss_append(c, lb, t.w, lox);
+}
+
+// ---- out-of-line helpers of the rare paths: they re-read the row (L2) in rolled loops
+
+// visits every valid sample of the row: f(x). Four 128-bit loads per lane are in flight per
+// trip (the row is in L2: a trip costs one round trip, not four).
+template <typename F>
+__device__ __forceinline__ void wss_for_each(const float* __restrict__ row, int lane, int n, F&& f) {
+  const int nfull = n >> 2;
+#pragma unroll 1
+  for (int g0 = lane; g0 < nfull; g0 += 128) {
+    float4 t[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+      if (g0 + 32 * u < nfull) t[u] = *reinterpret_cast<const float4*>(row + 4 * (g0 + 32 * u));
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+      if (g0 + 32 * u < nfull) { f(t[u].x); f(t[u].y); f(t[u].z); f(t[u].w); }
+  }
+  if (lane < (n & 3)) f(row[4 * nfull + lane]);
+}
+
+// counts of valid samples >= p1 and >= p2 (warp totals)
+__device__ __noinline__ int2 wss_count2(const float* __restrict__ row, int lane, int n, float p1, float p2) {
+  int c1 = 0, c2 = 0;
+  wss_for_each(row, lane, n, [&](float x) {
+    inc_if_ge(c1, x, p1);
+    inc_if_ge(c2, x, p2);
+  });
+  return make_int2(warp_sum_i32(c1), warp_sum_i32(c2));
+}
+
+// append(x > lox) over the whole window; returns the lane's slot offset
+template <int CLAMP>
+__device__ __noinline__ uint32_t wss_append_pass(const float* __restrict__ row, int lane, int n,
+                                                 float lox, uint32_t lb) {
+  uint32_t c = 0;
+  wss_for_each(row, lane, n, [&](float x) {
+    c = min(c, (uint32_t)(CLAMP * 128));
+    wss_append(c, lb, x, lox);
+  });
+  return c;
+}
+
+// Fallback when the sampled pivots listed fewer than k elements, or a lane's list overflowed:
+// narrow a bracket [a, b) with count_ge(a) = ca >= k > cb = count_ge(b) by counting passes over
+// the row (two pivots per pass, interpolated on the counts; thirds of the key space when that
+// stalls) until ca - cb elements fit the lists comfortably; the caller then lists the bracket
+// and selects from it. Returns a and ca; if every element of the bracket equals a (adjacent
+// keys), ca = -1 and a is the answer itself.
+struct WssBracket {
+  float a;
+  int ca;  // -1: a is the answer
+};
+__device__ __noinline__ WssBracket wss_narrow(const float* __restrict__ row, int lane, int n, int k, float mn,
+                                              float mx, int fit) {
+  float a = mn, b = POS_INF;
+  int ca = n, cb = 0;
+  int it = 0;
+  while (ca - cb > fit) {
+    const uint32_t ka = f32_key(a), kb = (cb == 0) ? f32_key(mx) + 1u : f32_key(b);
+    if (kb - ka <= 1u) return WssBracket{a, -1};
+    float p1, p2;
+    const float hi = (cb == 0) ? mx : b;
+    const int span = ca - cb;
+    const int dl = fit / 4;
+    const float inv = 1.0f / (float)span;
+    p1 = a + (hi - a) * ((float)max(ca - k - dl, 0) + 0.5f) * inv;
+    p2 = a + (hi - a) * ((float)min(ca - k + dl, span) - 0.5f) * inv;
+    uint32_t k1 = f32_key(p1), k2 = f32_key(p2);
+    if (!(p1 == p1) || !(p2 == p2) || (it & 1) || k1 <= ka || k2 >= kb || k1 > k2) {
+      // every other pass (and whenever the interpolation leaves the bracket): thirds of the key
+      // space, which bounds the number of passes whatever the distribution
+      k1 = ka + max((kb - ka) / 3u, 1u);
+      k2 = max(kb - max((kb - ka) / 3u, 1u), k1);
+    }
+    p1 = key_f32(k1); p2 = key_f32(k2);
+    const int2 cc = wss_count2(row, lane, n, p1, p2);
+    if (cc.y >= k) { a = p2; ca = cc.y; }
+    else if (cc.x >= k) { a = p1; ca = cc.x; b = p2; cb = cc.y; }
+    else { b = p1; cb = cc.x; }
+    ++it;
+  }
+  return WssBracket{a, ca};
+}
+
+// select_from_lists for the fallback path, out of line (one inlined copy serves the hot path)
+__device__ __noinline__ float wss_select_cold(float* lst, float* fin, int lane, int cnt, int total, int maxcnt,
+                                              int k, float a, float mx) {
+  return select_from_lists(lst, fin, lane, cnt, total, maxcnt, k, a, mx, false, 0.f, 0.f, kListPrefill);
+}
+
+template <int CAP, int MINB, int NBUF>
+__global__ void __launch_bounds__(kWssThreads, MINB)
+window_stats_stream_kernel(const float* __restrict__ ring, const uint32_t* __restrict__ seen,
+                           int32_t window, int32_t pitch, int64_t s0, int64_t n_series,
+                           float* __restrict__ out_min, float* __restrict__ out_max,
+                           double* __restrict__ out_mean, float* __restrict__ out_p95) {
+  using Cfg = WssCfg<CAP>;
+  extern __shared__ __align__(16) unsigned char s_raw[];
+
+  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  const int64_t o = (int64_t)blockIdx.x * kWssWarps + wib;  // output slot
+  if (o >= n_series) return;                                  // no block-wide barrier below
+  const int64_t s = s0 + o;
+  const float* __restrict__ row = ring + s * (int64_t)pitch;
+  const uint32_t sn = seen[s];  // consumed only after the first row loads are in flight
+
+  unsigned char* list_g = s_raw + wib * Cfg::kListBytes;
+  float* lst = reinterpret_cast<float*>(list_g) + lane;  // entry e: lst[e * 32]
+  float4* const lst4 = reinterpret_cast<float4*>(list_g) + lane;
+  const uint32_t lb = (uint32_t)__cvta_generic_to_shared(list_g) + ((uint32_t)lane << 2);
+  float* fin = reinterpret_cast<float*>(s_raw + kWssWarps * Cfg::kListBytes + wib * kWssAux);
+
+  // ---- 1. first loads: the sample rows and the first NBUF - 1 chunks of four rows, at
+  // addresses that depend only on the kernel arguments (a full window is the steady state; a
+  // ring that is still filling takes the generic sample below). All lie inside the row pitch.
+  const float* p = row + 4 * lane;
+  const int wjr = (window >> 2) >> 5;  // full rows of a full window
+  const bool want_p95 = out_p95 != nullptr;
+  float sm[4] = {NEG_INF, NEG_INF, NEG_INF, NEG_INF};
+  if (want_p95 && wjr >= kWssSampledMinRows) {
+#pragma unroll
+    for (int q = 0; q < 4; ++q) sm[q] = __ldg(p + 128 * (((2 * q + 1) * wjr) >> 3) + q);
+  }
+  float4 buf[NBUF][4];
+  auto load_chunk = [&](float4 (&dst)[4], int c) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) dst[i] = ld_stream_f4(p + 128 * (4 * c + i));
+  };
+#pragma unroll
+  for (int b = 0; b < NBUF - 1; ++b)
+    if (4 * b + 4 <= wjr) load_chunk(buf[b], b);
+  // While the loads are in flight: fill the first kListPrefill entries of this lane's list with
+  // -inf (128-bit stores across the warp), so the counting passes need no padding later.
+  auto prefill = [&]() {
+#pragma unroll
+    for (int e = 0; e < kListPrefill / 4; ++e)
+      lst4[e * 32] = make_float4(NEG_INF, NEG_INF, NEG_INF, NEG_INF);
+    __syncwarp();  // lanes append into slots another lane has just filled
+  };
+  prefill();
+  const int n = sn < (uint32_t)window ? (int)sn : window;
+  if (n == 0) {
+    if (lane == 0) {
+      if (out_min) out_min[o] = 0.f;
+      if (out_max) out_max[o] = 0.f;
+      if (out_mean) out_mean[o] = 0.0;
+      if (out_p95) out_p95[o] = 0.f;
+    }
+    return;
+  }
+#ifndef KLM_WSS_PF
+#define KLM_WSS_PF 1
+#endif
+  // Ask L2 for the row that a warp will want about one residency later: one bulk-prefetch
+  // instruction covers the whole row.
+  if (KLM_WSS_PF != 0 && lane == 0) {
+    const int64_t later = o + (int64_t)kNumSMs * MINB * kWssWarps;
+    if (later < n_series) {
+      const uint32_t bytes = ((uint32_t)n * 4u + 15u) & ~15u;
+      asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;"
+                   :: "l"(ring + (s0 + later) * (int64_t)pitch), "r"(bytes) : "memory");
+    }
+  }
+  const int nfull = n >> 2;   // complete float4 groups
+  const int jr = nfull >> 5;  // rows valid in every lane
+  const int k = n - p95_rank(n);
+  const bool sampled = want_p95 && jr >= kWssSampledMinRows;
+  if (sampled && n != window) {  // partly filled ring: sample the rows that hold data
+#pragma unroll
+    for (int q = 0; q < 4; ++q) sm[q] = __ldg(p + 128 * (((2 * q + 1) * jr) >> 3) + q);
+  }
+
+  bool narrow = false;             // settle by counting passes over the row (wss_narrow)
+  float lox = POS_INF;             // list predicate: x > lox (+inf: list nothing)
+  float hint_lo = 0.f, hint_hi = 0.f;  // first pair of pivots (sample order statistics)
+  float lox_retry = POS_INF;       // lower pivot for one retry of the append (+inf: none)
+  bool tie_mode = false, retried = false;
+  bool tie_hit = false;            // the heavy-tie test already found the answer
+  float tie_val = 0.f;
+
+  // ---- 2. sample pivot: four groups of 32 (one sample row each), top three of each
+  if (sampled) {
+    uint32_t h[4];
+#pragma unroll
+    for (int g = 0; g < 4; ++g) h[g] = f32_key(sm[g]);
+    const uint32_t lane_bit = 1u << lane;
+    uint32_t t1 = 0xffffffffu, t2 = 0xffffffffu, t3 = 0xffffffffu;  // min over groups of rank 1/2/3
+#pragma unroll
+    for (int r = 1; r <= 3; ++r) {
+      uint32_t m[4];
+#pragma unroll
+      for (int g = 0; g < 4; ++g) m[g] = warp_max_u32(h[g]);
+#pragma unroll
+      for (int g = 0; g < 4; ++g) {
+        const unsigned who = __ballot_sync(0xffffffffu, h[g] == m[g]);
+        if ((who & (0u - who)) == lane_bit) h[g] = 0u;  // retire one copy
+      }
+      const uint32_t mm = min(min(m[0], m[1]), min(m[2], m[3]));
+      if (r == 1) t1 = mm; else if (r == 2) t2 = mm; else t3 = mm;
+    }
+    // pivot: the smallest "second largest" (about 10 % of the window above it; fewer than k
+    // with probability ~5 %, in which case the append is redone from the "third largest")
+    const float V = key_f32(t2);
+    hint_lo = key_f32(t2);
+    hint_hi = key_f32(t1);
+    if (t3 < t2) lox_retry = next_down(key_f32(t3));
+    if (t1 == t2 || t2 == t3) {
+      tie_mode = true;
+      // heavy tie at V: place k against the block of copies of V (one pass over the row)
+      const int2 cc = wss_count2(row, lane, n, V, next_up(V));
+      if (cc.y >= k) {
+        lox = V;                       // the answer is above V: list the elements > V
+      } else if (cc.x >= k) {
+        tie_hit = true; tie_val = V;   // the answer is V itself
+      } else if (t3 < t2) {
+        lox = lox_retry;               // below V: list from the next sample statistic down
+        lox_retry = POS_INF;
+      } else {
+        narrow = true;                 // the answer is below V
+      }
+    } else {
+      lox = next_down(V);  // x > lox  <=>  x >= V
+    }
+  } else if (want_p95) {
+    lox = NEG_INF;  // short window: list every sample
+  }
+
+  // ---- 3. the pass: min / max / f64 sum + append(x > lox). Chunks of four rows rotate through
+  // NBUF register buffers: the loads of NBUF - 1 chunks are in flight while one is consumed.
+  WssAcc acc{POS_INF, POS_INF, NEG_INF, NEG_INF, 0.0, 0.0};
+  uint32_t c128 = 0;
+  const int nch = jr >> 2;
+  if (nch > 0) {
+#pragma unroll
+    for (int b = 0; b < NBUF - 1; ++b)  // chunks the early loads did not cover (cannot happen for
+      if (4 * b + 4 > wjr && b < nch) load_chunk(buf[b], b);  // n <= window; keeps buf defined)
+#pragma unroll 1
+    for (int c0 = 0; c0 < nch; c0 += NBUF) {
+#pragma unroll
+      for (int b = 0; b < NBUF; ++b) {
+        const int c = c0 + b;
+        if (c < nch) {
+          if (c + NBUF - 1 < nch) load_chunk(buf[(b + NBUF - 1) % NBUF], c + NBUF - 1);
+#pragma unroll
+          for (int i = 0; i < 4; ++i) wss_row<Cfg::kClamp>(acc, c128, lb, lox, buf[b][i], i & 1);
+        }
+      }
+    }
+  }
+  // the rows left over (at most three full ones), then the row that only some lanes hold
+#pragma unroll 1
+  for (int j = 4 * nch; j < jr; ++j)
+    wss_row<Cfg::kClamp>(acc, c128, lb, lox, ld_stream_f4(p + 128 * j), false);
+  if (lane + 32 * jr < nfull) wss_row<Cfg::kClamp>(acc, c128, lb, lox, ld_stream_f4(p + 128 * jr), false);
+  if (lane < (n & 3)) {
+    const float x = row[4 * nfull + lane];
+    acc.mn0 = fminf(acc.mn0, x);
+    acc.mx0 = fmaxf(acc.mx0, x);
+    acc.sum0 += (double)x;
+    c128 = min(c128, (uint32_t)(Cfg::kClamp * 128));
+    wss_append(c128, lb, x, lox);
+  }
+  __syncwarp();
+  asm volatile("" ::: "memory");  // the appends above are plain shared-memory stores
+  float mn = fminf(acc.mn0, acc.mn1), mx = fmaxf(acc.mx0, acc.mx1);
+  double sum = acc.sum0 + acc.sum1;
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) {
+    mn = fminf(mn, __shfl_xor_sync(0xffffffffu, mn, off));
+    mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, off));
+    sum += __shfl_xor_sync(0xffffffffu, sum, off);
+  }
+  if (lane == 0) {
+    if (out_min) out_min[o] = mn + 0.f;  // -0.0 -> +0.0: one canonical zero in the outputs
+    if (out_max) out_max[o] = mx + 0.f;
+    if (out_mean) out_mean[o] = sum / (double)n;
+  }
+  if (!want_p95) return;
+
+  // ---- 4. p95 = k-th largest
+  float result = 0.f;
+  do {  // single-trip block: `break` = result (or the request to narrow) is final
+    if (narrow) break;
+    if (tie_hit) { result = tie_val; break; }
+    if (mn == mx) { result = mx; break; }  // constant series
+    int cnt = (int)(c128 >> 7);
+    int total = warp_sum_i32(cnt);
+    int maxcnt = warp_max_i32(cnt);
+    if (total < k && !sampled) { result = NEG_INF; break; }  // lox = -inf: only -inf samples are unlisted
+    if (total < k && !tie_mode && lox_retry != POS_INF) {
+      // the pivot was too high: redo the append (only) from the next sample statistic down
+      __syncwarp();
+      prefill();
+      lox = lox_retry;
+      c128 = wss_append_pass<Cfg::kClamp>(row, lane, n, lox, lb);
+      __syncwarp();
+      asm volatile("" ::: "memory");
+      cnt = (int)(c128 >> 7);
+      total = warp_sum_i32(cnt);
+      maxcnt = warp_max_i32(cnt);
+      retried = true;
+    }
+    if (total < k || maxcnt >= Cfg::kClamp) {  // unlucky pivots, or a lane's list overflowed
+      narrow = true;
+      break;
+    }
+    result = select_from_lists(lst, fin, lane, cnt, total, maxcnt, k, sampled ? next_up(lox) : mn, mx,
+                               retried, hint_lo, hint_hi, kListPrefill);
+  } while (false);
+  if (narrow) {
+    if (mn == mx) {
+      result = mx;
+    } else {
+      // first try: a bracket of at most kFit elements on top of the < k above it, listed and
+      // selected from; if a single lane's share still overflows, settle by counting alone
+#pragma unroll 1
+      for (int attempt = 0; attempt < 2; ++attempt) {
+        const WssBracket br = wss_narrow(row, lane, n, k, mn, mx, attempt == 0 ? 16 * 32 : 0);
+        const float a = br.a;
+        if (br.ca < 0) { result = a; break; }
+        __syncwarp();
+        prefill();
+        lox = a == NEG_INF ? NEG_INF : next_down(a);
+        c128 = wss_append_pass<Cfg::kClamp>(row, lane, n, lox, lb);
+        __syncwarp();
+        asm volatile("" ::: "memory");
+        const int cnt = (int)(c128 >> 7);
+        const int total = warp_sum_i32(cnt);
+        const int maxcnt = warp_max_i32(cnt);
+        if (maxcnt >= Cfg::kClamp) continue;
+        if (total < k) { result = NEG_INF; break; }  // a = -inf: only -inf samples are unlisted
+        result = wss_select_cold(lst, fin, lane, cnt, total, maxcnt, k, a, mx);
+        break;
+      }
+    }
+  }
+  if (lane == 0) out_p95[o] = result + 0.f;
+}
+
+template <int CAP, int MINB, int NBUF>
+static int launch_stream(const float* ring, const uint32_t* seen, int32_t window, int32_t pitch,
+                         int64_t s0, int64_t n_series, float* out_min, float* out_max,
+                         double* out_mean, float* out_p95, cudaStream_t st) {
+  using Cfg = WssCfg<CAP>;
+  static_assert(MINB * (Cfg::kSmem + 1024) <= 227 * 1024, "the CTAs per SM must fit");
+  const int64_t blocks = ceil_div(n_series, kWssWarps);
+  if (blocks > 0x7fffffff) {
+    set_error("klm_dev_window_stats: too many series for one launch");
+    return KLM_ELIMIT;
+  }
+  static PerDeviceOnce attr_set;
+  int dev = 0;
+  KLM_CUDA(cudaGetDevice(&dev));
+  if (!attr_set.done(dev)) {
+    // opt in above 48 KB and ask for the largest shared-memory carve-out
+    KLM_CUDA(cudaFuncSetAttribute(window_stats_stream_kernel<CAP, MINB, NBUF>,
+                                  cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::kSmem));
+    KLM_CUDA(cudaFuncSetAttribute(window_stats_stream_kernel<CAP, MINB, NBUF>,
+                                  cudaFuncAttributePreferredSharedMemoryCarveout,
+                                  (int)cudaSharedmemCarveoutMaxShared));
+    attr_set.set(dev);
+  }
+  window_stats_stream_kernel<CAP, MINB, NBUF><<<(unsigned)blocks, kWssThreads, Cfg::kSmem, st>>>(
+      ring, seen, window, pitch, s0, n_series, out_min, out_max, out_mean, out_p95);
+  KLM_LAUNCH_CHECK("window_stats_stream_kernel");
+  return KLM_OK;
+}
+
+#ifndef KLM_WSS_CAP
+#define KLM_WSS_CAP 64
+#endif
+#ifndef KLM_WSS_MINB
+#define KLM_WSS_MINB 6
+#endif
+#ifndef KLM_WSS_NBUF
+#define KLM_WSS_NBUF 2
+#endif
+
+int launch_window_stats_stream(const float* ring, const uint32_t* seen, int32_t window, int32_t pitch,
+                               int64_t s0, int64_t s1, float* out_min, float* out_max,
+                               double* out_mean, float* out_p95, cudaStream_t st) {
+  return launch_stream<KLM_WSS_CAP, KLM_WSS_MINB, KLM_WSS_NBUF>(ring, seen, window, pitch, s0, s1 - s0, out_min, out_max,
+                                                  out_mean, out_p95, st);
+}
+
+}  // namespace klm

@@ -551,10 +551,10 @@ static int launch_warp(const float* ring, const uint32_t* seen, int32_t window, 
     set_error("klm_dev_window_stats: too many series for one launch");
     return KLM_ELIMIT;
   }
-  static bool attr_set[64] = {};
+  static PerDeviceOnce attr_set;
   int dev = 0;
   KLM_CUDA(cudaGetDevice(&dev));
-  if (!(dev < 64 && attr_set[dev])) {
+  if (!attr_set.done(dev)) {
     // opt in above 48 KB and ask for the largest shared-memory carve-out
     KLM_CUDA(cudaFuncSetAttribute(window_stats_warp_kernel<NV, NR, MINB, OVL>,
                                   cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -562,7 +562,7 @@ static int launch_warp(const float* ring, const uint32_t* seen, int32_t window, 
     KLM_CUDA(cudaFuncSetAttribute(window_stats_warp_kernel<NV, NR, MINB, OVL>,
                                   cudaFuncAttributePreferredSharedMemoryCarveout,
                                   (int)cudaSharedmemCarveoutMaxShared));
-    if (dev < 64) attr_set[dev] = true;
+    attr_set.set(dev);
   }
   window_stats_warp_kernel<NV, NR, MINB, OVL>
       <<<(unsigned)blocks, kWswThreads, wsw_smem_bytes<NV, NR, OVL>(), st>>>(

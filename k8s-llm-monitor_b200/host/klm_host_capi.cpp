@@ -112,6 +112,9 @@ int klmh_status_json(void* sv, int i, const char* last_updated, char* dst, int c
   return s->statuses[i].Updated ? 1 : 0;
 }
 
+// a float64 in Go's encoding/json form (what EncodeStatus writes for `score`)
+void klmh_format_float(double v, char* dst, int cap) { put(dst, cap, FormatJSONFloat(v)); }
+
 int klmh_reconcile(void* sv) {
   Session* s = static_cast<Session*>(sv);
   if (!s->h) { s->error = "no GPU handle in this session"; return -1; }

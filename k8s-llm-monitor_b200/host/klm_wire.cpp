@@ -248,18 +248,49 @@ static std::string quote(const std::string& s) {
   return o + "\"";
 }
 
-std::string EncodeStatus(const SchedulingRequestStatus& st, const std::string& last_updated) {
-  // Go's encoding/json prints float64 with strconv 'g'-like shortest form; integral scores
-  // print without a fraction (90 -> 90), others with the shortest round-trip digits.
-  char score[40];
-  if (st.Score == std::floor(st.Score) && std::fabs(st.Score) < 1e15) std::snprintf(score, sizeof(score), "%.0f", st.Score);
-  else std::snprintf(score, sizeof(score), "%.17g", st.Score);
-  double back = std::strtod(score, nullptr);
-  for (int p = 1; p < 17 && back == st.Score && score[0]; ++p) {  // shortest digits that round-trip
-    char t[40];
-    std::snprintf(t, sizeof(t), "%.*g", p, st.Score);
-    if (std::strtod(t, nullptr) == st.Score) { std::snprintf(score, sizeof(score), "%s", t); break; }
+// Go's encoding/json float64 encoder (encode.go floatEncoder): the shortest digits that
+// round-trip (strconv 'g' precision -1), written in plain decimal ('f') unless the exponent is
+// below -6 or at least 21, where it uses 'e' and trims "e-0X" to "e-X". 90 -> "90", 85.5 -> "85.5",
+// 1e21 -> "1e+21", 1e-7 -> "1e-7". (Non-finite values are an encoder error in Go; they print as 0.)
+std::string FormatJSONFloat(double v) {
+  if (!(v == v) || v == HUGE_VAL || v == -HUGE_VAL) return "0";
+  if (v == 0.0) return std::signbit(v) ? "-0" : "0";
+  char e[40];
+  int prec = 0;
+  for (; prec < 17; ++prec) {  // shortest digits that round-trip
+    std::snprintf(e, sizeof(e), "%.*e", prec, v);
+    if (std::strtod(e, nullptr) == v) break;
   }
+  // e = [-]d[.ddd]e[+-]XX: digits and decimal exponent
+  std::string digits;
+  const char* p = e;
+  const bool neg = *p == '-';
+  if (neg) ++p;
+  for (; *p && *p != 'e'; ++p)
+    if (*p != '.') digits += *p;
+  const int x = std::atoi(p + 1);
+  while (digits.size() > 1 && digits.back() == '0') digits.pop_back();
+  std::string out = neg ? "-" : "";
+  if (x < -6 || x >= 21) {
+    out += digits[0];
+    if (digits.size() > 1) out += "." + digits.substr(1);
+    char t[16];
+    if (x < 0 && x > -10) std::snprintf(t, sizeof(t), "e-%d", -x);  // json trims e-07 to e-7
+    else std::snprintf(t, sizeof(t), "e%c%02d", x < 0 ? '-' : '+', x < 0 ? -x : x);
+    return out + t;
+  }
+  if (x < 0) {
+    out += "0." + std::string(static_cast<size_t>(-x - 1), '0') + digits;
+  } else if (static_cast<size_t>(x) + 1 >= digits.size()) {
+    out += digits + std::string(static_cast<size_t>(x) + 1 - digits.size(), '0');
+  } else {
+    out += digits.substr(0, static_cast<size_t>(x) + 1) + "." + digits.substr(static_cast<size_t>(x) + 1);
+  }
+  return out;
+}
+
+std::string EncodeStatus(const SchedulingRequestStatus& st, const std::string& last_updated) {
+  const std::string score = FormatJSONFloat(st.Score);
   const std::string phase = st.Phase.empty() ? "Pending" : st.Phase;  // controller.go:238-240
   return "{\"phase\":" + quote(phase) + ",\"assignedNode\":" + quote(st.AssignedNode) +
          ",\"assignedUAV\":" + quote(st.AssignedUAV) + ",\"score\":" + score + ",\"message\":" +

@@ -28,5 +28,7 @@ std::vector<SchedulingRequest> DecodeSchedulingRequestList(const std::string& js
 // The status map of controller.go:229-236 as JSON; empty phase becomes "Pending" (:238-240);
 // last_updated is the RFC3339 UTC string the caller took from its clock.
 std::string EncodeStatus(const SchedulingRequestStatus& st, const std::string& last_updated);
+// a float64 as Go's encoding/json writes it (shortest round-trip digits, 'f' form for exponents in [-6, 21))
+std::string FormatJSONFloat(double v);
 
 }  // namespace klmhost

@@ -29,7 +29,7 @@ def load() -> C.CDLL:
                      "klmh_status", "klmh_add_node", "klmh_add_pod", "klmh_calculate_cluster_metrics",
                      "klmh_issue", "klmh_add_fleet_uav", "klmh_healthy_uav_count", "klmh_low_battery_uavs",
                      "klmh_name", "klmh_load_uavs_json", "klmh_load_requests_json", "klmh_request_info",
-                     "klmh_uav_info", "klmh_status_json"):
+                     "klmh_uav_info", "klmh_status_json", "klmh_format_float"):
             getattr(lib, name)
         _lib = lib
     return _lib
@@ -37,6 +37,13 @@ def load() -> C.CDLL:
 
 def _b(s: Optional[str]):
     return None if s is None else s.encode("utf-8")
+
+
+def format_json_float(v: float) -> str:
+    """A float64 as Go's encoding/json writes it (host/klm_wire.h FormatJSONFloat)."""
+    buf = C.create_string_buffer(64)
+    load().klmh_format_float(C.c_double(v), buf, 64)
+    return buf.value.decode()
 
 
 class HostSession:

@@ -161,7 +161,7 @@ def test_full_c2_properties(dev, pkg):
     check_stats(got, want, "full C2 sample")
 
 
-@pytest.mark.parametrize("t", [100, 1000, 3600, 4096])
+@pytest.mark.parametrize("t", [100, 1000, 3600, 4096, 8192])
 def test_k7_variants_agree(dev, t):
     """The pipelined kernel (default for windows <= 4096), the register-resident warp kernel
     and the shared-memory block kernel must all match the oracle."""
@@ -176,7 +176,9 @@ def test_k7_variants_agree(dev, t):
     seen_np[:3] = [0, 1, t]
     seen = torch.from_numpy(seen_np.astype(np.int32)).cuda()
     want = ob.window_stats(ring.cpu().numpy(), seen_np.astype(np.uint32), t, pitch)
-    for variant in ("pipe", "warp", "block"):
+    for variant in ("stream", "pipe", "warp", "block"):
+        if t > 4096 and variant in ("pipe", "warp"):
+            continue
         o = {k: torch.full((s,), -123.0, dtype=torch.float64 if k == "mean" else torch.float32, device="cuda")
              for k in ("min", "max", "mean", "p95")}
         dev.window_stats(ring, seen, t, o["min"], o["max"], o["mean"], o["p95"], variant=variant)

@@ -59,3 +59,22 @@ def test_bad_json_is_an_error(pkg):
         else:
             raise AssertionError(f"accepted {bad!r}")
     s.close()
+
+
+def test_json_float_matches_go_encoding(pkg):
+    """`score` in the status map is written like Go's encoding/json does (controller.go:233 puts a
+    float64 into the unstructured map): shortest round-trip digits, plain decimal for exponents in
+    [-6, 21), exponent form outside with e-0X trimmed to e-X. Expected strings are Go's output."""
+    go = {90.0: "90", 100.0: "100", 110.0: "110", 85.5: "85.5", 0.0: "0", 0.1: "0.1", 95.2: "95.2",
+          1e20: "100000000000000000000", 1e21: "1e+21", 1e-6: "0.000001", 1e-7: "1e-7", 1.5e-10: "1.5e-10",
+          123456789.125: "123456789.125", -3.25: "-3.25", 1.2345678901234567e19: "12345678901234567000",
+          5e-324: "5e-324", 1.7976931348623157e308: "1.7976931348623157e+308", 100.10000000000001: "100.10000000000001"}
+    for v, want in go.items():
+        assert pkg.hostbinding.format_json_float(v) == want, v
+    # and it always parses back to the same double
+    import random
+    rnd = random.Random(5)
+    for _ in range(2000):
+        v = rnd.choice([rnd.uniform(0, 110), rnd.uniform(-1e6, 1e6), rnd.random() * 10 ** rnd.randint(-30, 30),
+                        round(rnd.uniform(0, 110), 1)])
+        assert float(pkg.hostbinding.format_json_float(v)) == v
