@@ -48,9 +48,16 @@ extern "C" {
 #define KLM_NODE_STATUS_OK 0x2u /* lower(status.collection_status) in {"", "active"} */
 #define KLM_NODE_ELIGIBLE 0x3u
 
-/* klm_schedule_batch algorithms; both give identical results. */
+/* klm_schedule_batch / klm_reconcile `mode` = one algorithm | one sharding mode.
+ * Algorithms; both give identical results. */
 #define KLM_ALGO_DECOMPOSED 0 /* node_best_reduce + O(K) probe per request */
 #define KLM_ALGO_BRUTEFORCE 1 /* every request scans every node (verifier) */
+/* Sharding over the devices of the handle; identical results; on a
+ * one-device handle both are the same thing. The requests are split over the devices
+ * in both; the modes differ in where the node table lives. */
+#define KLM_SHARD_REQUESTS 0x000 /* every device holds the whole node table */
+#define KLM_SHARD_NODES 0x100    /* device g holds nodes [g L, (g+1) L), L = ceil(N / G) rounded up
+                                  * to 16; the others read them through peer pointers (NVLink) */
 
 /* cluster health (manager.go:558-564) */
 #define KLM_HEALTH_HEALTHY 0
@@ -97,8 +104,13 @@ typedef struct klm_cluster_out {
 
 /* ---------------------------------------------------------------- handle */
 
-/* One handle drives one GPU. device_ids/n_dev: round 1 accepts n_dev == 1
- * (multi-GPU runs are one process/handle per GPU).
+/* A handle drives the n_dev (1..16) devices listed in device_ids (NULL, 0: device 0).
+ * With more than one device -- one process driving the whole box, which is what the
+ * reference's scheduler is (cmd/scheduler/main.go:55-62 constructs one controller) --
+ * klm_nodes_set / klm_schedule_batch / klm_reconcile spread the batch over all of them
+ * (see KLM_SHARD_*); peer access between the devices is required and enabled here. Every
+ * other call of such a handle runs on device_ids[0] (metric rings shard by series with no
+ * exchange: use one handle per GPU for those).
  * Thread-safe: every call takes the handle's mutex and makes its device
  * current, so cgo may enter on any OS thread. */
 int klm_create(const int* device_ids, int n_dev, klm_handle** out);
@@ -142,7 +154,7 @@ int klm_nodes_set(klm_handle* h, int64_t n_nodes, const double* battery,
 int klm_schedule_batch(klm_handle* h, int64_t n_requests,
                        const double* min_battery, const int32_t* pref_off,
                        const int32_t* pref_ids, int32_t* out_idx,
-                       double* out_score, int algo);
+                       double* out_score, int mode);
 
 /* One reconcile in one call (controller.go:88-110: one UAV snapshot, then every
  * pending request): klm_nodes_set + klm_schedule_batch with the same arguments,
@@ -153,7 +165,7 @@ int klm_reconcile(klm_handle* h, int64_t n_nodes, const double* battery,
                   const uint8_t* flags, int64_t n_requests,
                   const double* min_battery, const int32_t* pref_off,
                   const int32_t* pref_ids, int32_t* out_idx, double* out_score,
-                  int algo);
+                  int mode);
 
 /* ----------------------------------------------------- cluster aggregate */
 
@@ -350,6 +362,45 @@ int klm_dev_schedule_bruteforce(const double* battery, const uint8_t* flags,
 int klm_dev_merge_partials(int n_parts, int64_t n_requests,
                            const int32_t* part_idx, const double* part_score,
                            int32_t* out_idx, double* out_score, void* stream);
+
+/* ---- node-range sharding without an all-gather (no reference counterpart).
+ * Rank g of G owns nodes [lo, hi) = klm_shard_range(N, G, g) and one array of exchange slots
+ * (klm_dev_shard_slots_bytes() bytes, zero-filled once) that every rank can WRITE: in one
+ * process after cudaDeviceEnablePeerAccess, across processes through CUDA IPC or symmetric
+ * memory. Per snapshot, with a fresh epoch >= 1 that all ranks agree on and that grows by one:
+ *   klm_dev_node_best_publish  K1 over the rank's shard; the 16-byte result goes into the
+ *                              rank's slot of EVERY rank's array (release store, system scope);
+ *   klm_dev_schedule_sharded   K2 over the rank's slice of the REQUESTS: waits (acquire) until
+ *                              its own slot array holds all G results of the epoch, folds them,
+ *                              and probes preferred nodes where they live -- battery_parts[q] /
+ *                              flags_parts[q] are rank q's shard as seen from this device (peer
+ *                              pointers; or slices of a local replica: request-shard mode).
+ * No host barrier, no gather of partial winners, no merge kernel: the exchange is 16 bytes per
+ * rank pair and per-rank work is N / G + R / G. Results equal klm_dev_schedule on the whole
+ * table (global indices, lowest index on ties: controller.go:160). Both kernels of a rank go
+ * on one stream, K1 first; every rank must launch its K1 (a K2 that waits 4 s for a missing
+ * peer gives up: klm_dev_shard_error then reports 1 and the affected results are void). Epochs
+ * alternate between two sets of slots, so a rank may publish epoch e + 1 while a slower rank
+ * still reads e; the node columns themselves must not be overwritten until every rank's K2 of
+ * the epoch has finished (double-buffer them, or synchronise once per snapshot). Never run
+ * ranks that wait for each other as separate launches on ONE GPU unless every K1 is enqueued
+ * before any K2 on the same stream. */
+int64_t klm_dev_shard_slots_bytes(void);
+void klm_shard_range(int64_t n_nodes, int n_parts, int part, int64_t* lo, int64_t* hi);
+int klm_dev_node_best_publish(const double* battery, const uint8_t* flags,
+                              int64_t n_nodes, int64_t node_base, int n_parts,
+                              int my_part, void* const* peer_slots /* host array */,
+                              uint64_t epoch, int64_t* best /* may be NULL */,
+                              void* scratch, void* stream);
+int klm_dev_schedule_sharded(int n_parts, int64_t n_nodes_total,
+                             const double* const* battery_parts /* host array */,
+                             const uint8_t* const* flags_parts /* host array */,
+                             void* my_slots, uint64_t epoch, int64_t n_requests,
+                             const double* min_battery, const int32_t* pref_off,
+                             const int32_t* pref_ids, int32_t* out_idx,
+                             double* out_score, void* stream);
+/* *out = 1 if a klm_dev_schedule_sharded on these slots gave up waiting; synchronises `stream`. */
+int klm_dev_shard_error(const void* my_slots, int* out, void* stream);
 
 /* K3 over peer memory: part_idx[g] / part_score[g] (HOST arrays of n_parts DEVICE
  * pointers, at most 16) are rank g's partial winners for ALL requests, readable from this

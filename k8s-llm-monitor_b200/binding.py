@@ -19,6 +19,7 @@ LIB_PATH = os.path.join(_HERE, os.environ.get("KLM_LIB_NAME", "libklm.so"))
 KLM_OK, KLM_EINVAL, KLM_ECUDA, KLM_ENODEV, KLM_ESTATE, KLM_ELIMIT = 0, -1, -2, -3, -4, -5
 NODE_HAS_NAME, NODE_STATUS_OK, NODE_ELIGIBLE = 1, 2, 3
 ALGO_DECOMPOSED, ALGO_BRUTEFORCE = 0, 1
+SHARD_REQUESTS, SHARD_NODES = 0x000, 0x100  # or-ed into the `algo` / mode argument
 HEALTH_NAMES = ("healthy", "warning", "critical")  # manager.go:558-564
 
 
@@ -107,6 +108,11 @@ SIGNATURES = {
     "klm_dev_schedule_after_best": (C.c_int, [_P, _P, _I64, _I64, _P, _I64, _P, _P, _P, _P, _P, _P]),
     "klm_dev_schedule_bruteforce": (C.c_int, [_P, _P, _I64, _I64, _I64, _P, _P, _P, _P, _P, _P]),
     "klm_dev_merge_partials": (C.c_int, [C.c_int, _I64, _P, _P, _P, _P, _P]),
+    "klm_dev_shard_slots_bytes": (_I64, []),
+    "klm_shard_range": (None, [_I64, C.c_int, C.c_int, C.POINTER(_I64), C.POINTER(_I64)]),
+    "klm_dev_node_best_publish": (C.c_int, [_P, _P, _I64, _I64, C.c_int, C.c_int, _P, C.c_uint64, _P, _P, _P]),
+    "klm_dev_schedule_sharded": (C.c_int, [C.c_int, _I64, _P, _P, _P, C.c_uint64, _I64, _P, _P, _P, _P, _P, _P]),
+    "klm_dev_shard_error": (C.c_int, [_P, C.POINTER(C.c_int), _P]),
     "klm_dev_merge_partials_peer": (C.c_int, [C.c_int, _P, _P, _I64, _I64, _P, _P, _P]),
     "klm_dev_cluster_scratch_bytes": (_I64, []),
     "klm_dev_cluster_aggregate": (C.c_int, [C.POINTER(NodeCols), _I64, _P, _I64, _P, _P, _P]),
@@ -177,14 +183,25 @@ def _ptr(a: Optional[np.ndarray]) -> Optional[int]:
     return None if a is None else a.ctypes.data
 
 
+def shard_range(n_nodes: int, n_parts: int, part: int) -> Tuple[int, int]:
+    """klm_shard_range: the node range [lo, hi) that rank `part` of `n_parts` owns."""
+    lo, hi = _I64(0), _I64(0)
+    load().klm_shard_range(n_nodes, n_parts, part, C.byref(lo), C.byref(hi))
+    return lo.value, hi.value
+
+
 class Handle:
     """Host-buffer API: numpy in, numpy out, everything computed on the GPU."""
 
-    def __init__(self, device: int = 0):
+    def __init__(self, device=0):
+        """device: one ordinal, or a sequence of ordinals (one handle over several GPUs: the
+        scheduling calls then spread every batch over all of them, see SHARD_*)."""
         self._lib = load()
         self._h = _P()
-        dev = (C.c_int * 1)(device)
-        check(self._lib.klm_create(dev, 1, C.byref(self._h)))
+        ids = [int(device)] if isinstance(device, (int, np.integer)) else [int(d) for d in device]
+        self.devices = ids
+        dev = (C.c_int * len(ids))(*ids)
+        check(self._lib.klm_create(dev, len(ids), C.byref(self._h)))
 
     def close(self) -> None:
         if getattr(self, "_h", None) is not None and self._h:
@@ -596,6 +613,43 @@ class Dev:
         n_parts, r = part_idx.shape
         check(self.lib.klm_dev_merge_partials(n_parts, r, _dp(part_idx), _dp(part_score), _dp(out_idx),
                                               _dp(out_score), _stream_ptr(stream)))
+
+    # -- node-range sharding without an all-gather (klm.h, "node-range sharding")
+    def shard_slots(self, device=None):
+        """A zero-filled exchange-slot array (uint8 tensor) for one rank."""
+        return self.torch.zeros(int(self.lib.klm_dev_shard_slots_bytes()), dtype=self.torch.uint8,
+                                device="cuda" if device is None else device)
+
+    def node_best_publish(self, battery, flags, node_base: int, n_parts: int, my_part: int, slot_ptrs, epoch,
+                          best=None, scratch=None, stream=None):
+        """slot_ptrs: device addresses (ints) of every rank's slot array, as seen from this device.
+        epoch: int, or a ctypes.c_uint64 whose value a prebound call re-reads at every issue."""
+        t = self.torch
+        _need(battery, t.float64, "battery"); _need(flags, t.uint8, "flags")
+        arr = (C.c_void_p * n_parts)(*[int(x) for x in slot_ptrs])
+        sc = self.best_scratch if scratch is None else scratch
+        check(self.lib.klm_dev_node_best_publish(_dp(battery), _dp(flags), battery.numel(), node_base, n_parts,
+                                                 my_part, arr, epoch, _dp(best) if best is not None else None,
+                                                 _dp(sc), _stream_ptr(stream)))
+
+    def schedule_sharded(self, n_total: int, bat_ptrs, flg_ptrs, my_slots, epoch, min_battery, pref_off, pref_ids,
+                         out_idx, out_score, stream=None):
+        """bat_ptrs / flg_ptrs: device addresses (ints) of every rank's shard columns."""
+        t = self.torch
+        _need(min_battery, t.float64, "min_battery"); _need(pref_off, t.int32, "pref_off")
+        _need(pref_ids, t.int32, "pref_ids"); _need(out_idx, t.int32, "out_idx")
+        _need(out_score, t.float64, "out_score")
+        n = len(bat_ptrs)
+        ab = (C.c_void_p * n)(*[int(x) for x in bat_ptrs])
+        af = (C.c_void_p * n)(*[int(x) for x in flg_ptrs])
+        check(self.lib.klm_dev_schedule_sharded(n, n_total, ab, af, _dp(my_slots), epoch, min_battery.numel(),
+                                                _dp(min_battery), _dp(pref_off), _dp(pref_ids), _dp(out_idx),
+                                                _dp(out_score), _stream_ptr(stream)))
+
+    def shard_error(self, my_slots, stream=None) -> int:
+        out = C.c_int(0)
+        check(self.lib.klm_dev_shard_error(_dp(my_slots), C.byref(out), _stream_ptr(stream)))
+        return out.value
 
     def merge_partials_peer(self, idx_ptrs, score_ptrs, r0: int, r1: int, out_idx, out_score, stream=None):
         """idx_ptrs / score_ptrs: device addresses (ints) of every rank's partial arrays."""

@@ -15,6 +15,7 @@
 #include <cstring>
 #include <mutex>
 #include <new>
+#include <vector>
 
 #include "common.cuh"
 
@@ -149,6 +150,26 @@ struct klm_handle {
   } slot[2];
   cudaStream_t stream3 = nullptr, stream_bulk = nullptr;  // downloads; K6 + K7 of the async cycles
   uint64_t begun = 0, ended = 0;
+
+  // ---- more than one device (klm_create with n_dev > 1): the scheduler's batch is split
+  // over the devices inside the library; `device` above is devs[0].device.
+  struct Dev {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    DevBuf tab;       // node columns this device holds: the whole table (request-shard mode)
+                      // or its own shard (node-shard mode); battery | flags
+    DevBuf slots, scratch;  // exchange slots peers write into; K1 scratch
+    DevBuf req_min, req_off, req_ids, res_idx, res_score;
+    double* d_battery = nullptr;  // base of the columns in `tab`
+    uint8_t* d_flags = nullptr;
+  };
+  std::vector<Dev> devs;
+  PinBuf md_tab;             // the snapshot of klm_nodes_set (page-locked copy: the layout is
+                             // only known when the batch arrives)
+  int64_t md_nodes = -1;     // -1: no snapshot
+  bool md_tab_valid = false; // md_tab holds the current snapshot (klm_nodes_set, not klm_reconcile)
+  int md_uploaded_mode = -1; // which layout the devices hold for this snapshot (-1: none)
+  uint64_t md_epoch = 0;     // exchange epoch of the last K1
 };
 
 namespace {
@@ -205,6 +226,212 @@ int collect_idle(klm_handle* h, const char* who) {
 
 }  // namespace
 
+
+// ------------------------------------------------- scheduling over several devices
+//
+// One process, one handle, G devices (what the Go scheduler is: cmd/scheduler/main.go:55-62
+// constructs one controller). Both modes split the REQUESTS over the devices; they differ in
+// where the node table lives:
+//   request-shard (KLM_SHARD_REQUESTS): every device holds the whole table and probes locally;
+//   node-shard (KLM_SHARD_NODES): device g holds nodes [g L, (g + 1) L), L = ceil(N / G) rounded
+//     up to 16, and the others read a preferred node that lives there through peer pointers.
+// In both, device g runs K1 over its N / G range only and publishes the 16-byte result into every
+// device's exchange slots; K2 folds the G results. No all-gather, no merge kernel, no host
+// barrier between K1 and K2 (schedule.cu, "node-range sharding").
+namespace {
+
+int multi_init(klm_handle* h, const int* ids, int n) {
+  h->devs.resize((size_t)n);
+  for (int i = 0; i < n; ++i) {
+    cudaDeviceProp prop;
+    KLM_CUDA(cudaGetDeviceProperties(&prop, ids[i]));
+    if (prop.major != 10) {
+      set_error("klm_create: device %d is sm_%d%d; libklm is built for sm_100a (B200) only", ids[i],
+                prop.major, prop.minor);
+      return KLM_ENODEV;
+    }
+    h->devs[(size_t)i].device = ids[i];
+  }
+  for (int i = 0; i < n; ++i) {
+    klm_handle::Dev& d = h->devs[(size_t)i];
+    KLM_CUDA(cudaSetDevice(d.device));
+    for (int j = 0; j < n; ++j) {
+      if (j == i) continue;
+      int can = 0;
+      KLM_CUDA(cudaDeviceCanAccessPeer(&can, d.device, ids[j]));
+      if (!can) {
+        set_error("klm_create: device %d cannot map device %d's memory (no peer access)", d.device, ids[j]);
+        return KLM_ENODEV;
+      }
+      const cudaError_t e = cudaDeviceEnablePeerAccess(ids[j], 0);
+      if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) return cuda_fail(e, "cudaDeviceEnablePeerAccess");
+      (void)cudaGetLastError();
+    }
+    int lo = 0, hi = 0;
+    KLM_CUDA(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+    KLM_CUDA(cudaStreamCreateWithPriority(&d.stream, cudaStreamNonBlocking, hi));
+    KLM_TRY(d.slots.ensure((size_t)klm_dev_shard_slots_bytes()));
+    KLM_TRY(d.scratch.ensure((size_t)klm_dev_node_best_scratch_bytes()));
+    KLM_CUDA(cudaMemsetAsync(d.slots.p, 0, d.slots.cap, d.stream));
+    KLM_CUDA(cudaMemsetAsync(d.scratch.p, 0, d.scratch.cap, d.stream));
+    KLM_CUDA(cudaStreamSynchronize(d.stream));
+  }
+  KLM_CUDA(cudaSetDevice(h->device));
+  return KLM_OK;
+}
+
+// make every device hold the snapshot in the layout of `node_shard`, then K1 + publication
+int multi_upload(klm_handle* h, bool node_shard, int64_t n, const double* battery, const uint8_t* flags) {
+  const int G = (int)h->devs.size();
+  ++h->md_epoch;
+  std::vector<void*> peer_slots((size_t)G);
+  for (int g = 0; g < G; ++g) peer_slots[(size_t)g] = h->devs[(size_t)g].slots.p;
+  for (int g = 0; g < G; ++g) {
+    klm_handle::Dev& d = h->devs[(size_t)g];
+    KLM_CUDA(cudaSetDevice(d.device));
+    int64_t lo = 0, hi = 0;
+    klm_shard_range(n, G, g, &lo, &hi);
+    const int64_t a = node_shard ? lo : 0, b = node_shard ? hi : n;  // what this device stores
+    const size_t bat_bytes = (size_t)(b - a) * sizeof(double), flag_off = align256(bat_bytes);
+    KLM_TRY(d.tab.ensure(flag_off + (size_t)(b - a) + 256));
+    d.d_battery = d.tab.as<double>();
+    d.d_flags = d.tab.as<uint8_t>() + flag_off;
+    KLM_TRY(h2d(d.d_battery, battery + a, bat_bytes, d.stream));
+    KLM_TRY(h2d(d.d_flags, flags + a, (size_t)(b - a), d.stream));
+    // K1 over this device's RANGE in either layout; global indices through node_base
+    KLM_TRY(klm_dev_node_best_publish(d.d_battery + (lo - a), d.d_flags + (lo - a), hi - lo, lo, G, g,
+                                      peer_slots.data(), h->md_epoch, nullptr, d.scratch.p, d.stream));
+  }
+  h->md_uploaded_mode = node_shard ? 1 : 0;
+  return KLM_OK;
+}
+
+int multi_sync(klm_handle* h) {
+  int rc = KLM_OK;
+  for (auto& d : h->devs) {
+    cudaSetDevice(d.device);
+    const cudaError_t e = cudaStreamSynchronize(d.stream);
+    if (e != cudaSuccess && rc == KLM_OK) rc = cuda_fail(e, "cudaStreamSynchronize");
+  }
+  cudaSetDevice(h->device);
+  return rc;
+}
+
+int multi_schedule(klm_handle* h, int64_t n, const double* battery, const uint8_t* flags, int64_t R,
+                   const double* min_battery, const int32_t* pref_off, const int32_t* pref_ids,
+                   int32_t* out_idx, double* out_score, int algo, bool node_shard) {
+  const int G = (int)h->devs.size();
+  if (algo == KLM_ALGO_BRUTEFORCE && node_shard) {
+    set_error("klm_schedule_batch: the brute-force verifier scans whole tables; use it with KLM_SHARD_REQUESTS");
+    return KLM_EINVAL;
+  }
+  if (R < 0 || (algo != KLM_ALGO_DECOMPOSED && algo != KLM_ALGO_BRUTEFORCE)) {
+    set_error("klm_schedule_batch: bad argument");
+    return KLM_EINVAL;
+  }
+  if (R > 0 && (!min_battery || !pref_off || !out_idx || !out_score)) {
+    set_error("klm_schedule_batch: null array");
+    return KLM_EINVAL;
+  }
+  const int64_t n_ids = R > 0 ? pref_off[R] : 0;
+  if (R > 0 && (pref_off[0] != 0 || n_ids < 0 || (n_ids > 0 && !pref_ids))) {
+    set_error("klm_schedule_batch: pref_off must start at 0 and pref_ids be non-null");
+    return KLM_EINVAL;
+  }
+  for (int g = 1; g <= G && R > 0; ++g) {  // slice boundaries, before anything is in flight
+    const int64_t r = R * g / G, rp = R * (g - 1) / G;
+    if (pref_off[r] < pref_off[rp] || pref_off[r] > n_ids) {
+      set_error("klm_schedule_batch: pref_off is not non-decreasing within [0, pref_off[R]]");
+      return KLM_EINVAL;
+    }
+  }
+  if (h->md_uploaded_mode != (node_shard ? 1 : 0)) KLM_TRY(multi_upload(h, node_shard, n, battery, flags));
+  if (R == 0) return multi_sync(h);
+  std::vector<const double*> bat_parts((size_t)G);
+  std::vector<const uint8_t*> flg_parts((size_t)G);
+  for (int g = 0; g < G; ++g) {
+    klm_handle::Dev& d = h->devs[(size_t)g];
+    KLM_CUDA(cudaSetDevice(d.device));
+    const int64_t r0 = R * g / G, r1 = R * (g + 1) / G, rl = r1 - r0;
+    if (rl == 0) continue;
+    const int64_t i0 = pref_off[r0], i1 = pref_off[r1];
+    KLM_TRY(d.req_min.ensure((size_t)rl * 8));
+    KLM_TRY(d.req_off.ensure((size_t)(rl + 1) * 4));
+    KLM_TRY(d.req_ids.ensure((size_t)(i1 - i0 > 0 ? i1 - i0 : 1) * 4));
+    KLM_TRY(d.res_idx.ensure((size_t)rl * 4));
+    KLM_TRY(d.res_score.ensure((size_t)rl * 8));
+    KLM_TRY(h2d(d.req_min.p, min_battery + r0, (size_t)rl * 8, d.stream));
+    KLM_TRY(h2d(d.req_off.p, pref_off + r0, (size_t)(rl + 1) * 4, d.stream));
+    KLM_TRY(h2d(d.req_ids.p, pref_ids + i0, (size_t)(i1 - i0) * 4, d.stream));
+    // the offsets stay absolute: hand the kernel the ids pointer moved back by i0 entries
+    const int32_t* ids_abs = d.req_ids.as<int32_t>() - i0;
+    if (algo == KLM_ALGO_BRUTEFORCE) {
+      KLM_TRY(klm_dev_schedule_bruteforce(d.d_battery, d.d_flags, n, 0, rl, d.req_min.as<double>(),
+                                          d.req_off.as<int32_t>(), ids_abs, d.res_idx.as<int32_t>(),
+                                          d.res_score.as<double>(), d.stream));
+    } else {
+      // the table as this device sees it: its own columns, or the peers' shards
+      for (int q = 0; q < G; ++q) {
+        int64_t lo = 0, hi = 0;
+        klm_shard_range(n, G, q, &lo, &hi);
+        const klm_handle::Dev& owner = h->devs[(size_t)(node_shard ? q : g)];
+        bat_parts[(size_t)q] = owner.d_battery + (node_shard ? 0 : lo);
+        flg_parts[(size_t)q] = owner.d_flags + (node_shard ? 0 : lo);
+      }
+      KLM_TRY(klm_dev_schedule_sharded(G, n, bat_parts.data(), flg_parts.data(), d.slots.p, h->md_epoch, rl,
+                                       d.req_min.as<double>(), d.req_off.as<int32_t>(), ids_abs,
+                                       d.res_idx.as<int32_t>(), d.res_score.as<double>(), d.stream));
+    }
+    KLM_TRY(d2h(out_idx + r0, d.res_idx.p, (size_t)rl * 4, d.stream));
+    KLM_TRY(d2h(out_score + r0, d.res_score.p, (size_t)rl * 8, d.stream));
+  }
+  KLM_TRY(multi_sync(h));
+  for (auto& d : h->devs) {  // a K2 that waited in vain for a peer's K1 says so
+    int err = 0;
+    KLM_CUDA(cudaSetDevice(d.device));
+    KLM_TRY(klm_dev_shard_error(d.slots.p, &err, d.stream));
+    if (err) {
+      KLM_CUDA(cudaMemsetAsync(static_cast<char*>(d.slots.p) + klm_dev_shard_slots_bytes() - 64, 0, 4, d.stream));
+      cudaSetDevice(h->device);
+      set_error("klm_schedule_batch: device %d timed out waiting for a peer's node_best result", d.device);
+      return KLM_ESTATE;
+    }
+  }
+  KLM_CUDA(cudaSetDevice(h->device));
+  return KLM_OK;
+}
+
+// `mode` = KLM_ALGO_* | KLM_SHARD_*; anything else is rejected
+bool split_mode(int mode, int* algo, bool* node_shard) {
+  *algo = mode & 0xff;
+  *node_shard = (mode & KLM_SHARD_NODES) != 0;
+  return (mode & ~(0xff | KLM_SHARD_NODES)) == 0;
+}
+
+// several devices: keep a page-locked copy; the devices are loaded when the first batch says
+// in which layout (the caller's arrays may be gone by then)
+int multi_nodes_set(klm_handle* h, int64_t n, const double* battery, const uint8_t* flags) {
+  if (n < 0 || n > 0x7fffffff || (n > 0 && (!battery || !flags))) {
+    set_error("klm_nodes_set: bad argument (0 <= n_nodes < 2^31, arrays non-null)");
+    return KLM_EINVAL;
+  }
+  h->md_nodes = -1;
+  h->md_uploaded_mode = -1;
+  h->md_tab_valid = false;
+  KLM_TRY(multi_sync(h));  // nothing may still read the previous copy
+  const size_t bat_bytes = (size_t)n * sizeof(double);
+  KLM_TRY(h->md_tab.ensure(align256(bat_bytes) + (size_t)n + 256));
+  if (n > 0) {
+    std::memcpy(h->md_tab.at(0), battery, bat_bytes);
+    std::memcpy(h->md_tab.at(align256(bat_bytes)), flags, (size_t)n);
+  }
+  h->md_nodes = n;
+  h->md_tab_valid = true;
+  return KLM_OK;
+}
+
+}  // namespace
+
 extern "C" const char* klm_last_error(void) { return g_err; }
 extern "C" int klm_abi_version(void) { return 1004; }
 
@@ -231,9 +458,9 @@ extern "C" int klm_create(const int* device_ids, int n_dev, klm_handle** out) {
     return KLM_EINVAL;
   }
   *out = nullptr;
-  if (n_dev != 1 && !(n_dev == 0 && !device_ids)) {
-    set_error("klm_create: one device per handle (n_dev == 1); run one handle per GPU");
-    return KLM_EINVAL;
+  if (n_dev < 0 || n_dev > 16 || (n_dev == 0 && device_ids) || (n_dev > 0 && !device_ids)) {
+    set_error("klm_create: n_dev must be 0 (device 0) or 1..16 with device_ids");
+    return n_dev > 16 ? KLM_ELIMIT : KLM_EINVAL;
   }
   int count = 0;
   cudaError_t e = cudaGetDeviceCount(&count);
@@ -246,6 +473,17 @@ extern "C" int klm_create(const int* device_ids, int n_dev, klm_handle** out) {
   if (dev < 0 || dev >= count) {
     set_error("klm_create: device %d out of range [0, %d)", dev, count);
     return KLM_EINVAL;
+  }
+  for (int i = 0; i < n_dev; ++i) {
+    if (device_ids[i] < 0 || device_ids[i] >= count) {
+      set_error("klm_create: device %d out of range [0, %d)", device_ids[i], count);
+      return KLM_EINVAL;
+    }
+    for (int j = 0; j < i; ++j)
+      if (device_ids[j] == device_ids[i]) {
+        set_error("klm_create: device %d listed twice", device_ids[i]);
+        return KLM_EINVAL;
+      }
   }
   KLM_CUDA(cudaSetDevice(dev));
   cudaDeviceProp prop;
@@ -291,12 +529,27 @@ extern "C" int klm_create(const int* device_ids, int n_dev, klm_handle** out) {
     klm_destroy(h);
     return rc;
   }
+  if (n_dev > 1) {
+    rc = multi_init(h, device_ids, n_dev);
+    if (rc != KLM_OK) {
+      klm_destroy(h);
+      return rc;
+    }
+  }
   *out = h;
   return KLM_OK;
 }
 
 extern "C" void klm_destroy(klm_handle* h) {
   if (!h) return;
+  for (auto& d : h->devs) {
+    cudaSetDevice(d.device);
+    if (d.stream) cudaStreamSynchronize(d.stream);
+    for (DevBuf* b : {&d.tab, &d.slots, &d.scratch, &d.req_min, &d.req_off, &d.req_ids, &d.res_idx, &d.res_score})
+      b->release();
+    if (d.stream) cudaStreamDestroy(d.stream);
+  }
+  h->md_tab.release();
   cudaSetDevice(h->device);
   if (h->stream) cudaStreamSynchronize(h->stream);
   if (h->stream2) cudaStreamSynchronize(h->stream2);
@@ -370,6 +623,7 @@ static int nodes_set_impl(klm_handle* h, int64_t n, const double* battery, const
 extern "C" int klm_nodes_set(klm_handle* h, int64_t n, const double* battery,
                              const uint8_t* flags) {
   KLM_ENTER(h);
+  if (!h->devs.empty()) return multi_nodes_set(h, n, battery, flags);
   return nodes_set_impl(h, n, battery, flags);
 }
 
@@ -505,9 +759,32 @@ static int schedule_batch_impl(klm_handle* h, int64_t R, const double* min_batte
 
 extern "C" int klm_schedule_batch(klm_handle* h, int64_t R, const double* min_battery,
                                   const int32_t* pref_off, const int32_t* pref_ids,
-                                  int32_t* out_idx, double* out_score, int algo) {
+                                  int32_t* out_idx, double* out_score, int mode) {
   KLM_ENTER(h);
-  return schedule_batch_impl(h, R, min_battery, pref_off, pref_ids, out_idx, out_score, algo);
+  int algo = 0;
+  bool node_shard = false;
+  if (!split_mode(mode, &algo, &node_shard)) {
+    set_error("klm_schedule_batch: bad mode %d", mode);
+    return KLM_EINVAL;
+  }
+  if (h->devs.empty())  // one device: the two sharding modes are the same thing
+    return schedule_batch_impl(h, R, min_battery, pref_off, pref_ids, out_idx, out_score, algo);
+  if (h->md_nodes < 0) {
+    set_error("klm_schedule_batch: no node snapshot; call klm_nodes_set first");
+    return KLM_ESTATE;
+  }
+  const int64_t n = h->md_nodes;
+  if (h->md_uploaded_mode != (node_shard ? 1 : 0) && !h->md_tab_valid) {
+    set_error("klm_schedule_batch: the snapshot installed by klm_reconcile is held in the other sharding "
+              "layout; install it with klm_nodes_set to use both");
+    return KLM_ESTATE;
+  }
+  const double* hb = h->md_tab_valid ? reinterpret_cast<const double*>(h->md_tab.p) : nullptr;
+  const uint8_t* hf = h->md_tab_valid ? reinterpret_cast<const uint8_t*>(h->md_tab.at(align256((size_t)n * 8))) : nullptr;
+  const int rc = multi_schedule(h, n, hb, hf, R, min_battery, pref_off, pref_ids, out_idx, out_score, algo,
+                                node_shard);
+  if (rc != KLM_OK) multi_sync(h);  // nothing may still write the caller's arrays
+  return rc;
 }
 
 // One reconcile (controller.go:88-110): install the snapshot and decide every pending request.
@@ -516,8 +793,33 @@ extern "C" int klm_schedule_batch(klm_handle* h, int64_t R, const double* min_ba
 // is klm_nodes_set followed by klm_schedule_batch under one lock.
 extern "C" int klm_reconcile(klm_handle* h, int64_t n, const double* battery, const uint8_t* flags,
                              int64_t R, const double* min_battery, const int32_t* pref_off,
-                             const int32_t* pref_ids, int32_t* out_idx, double* out_score, int algo) {
+                             const int32_t* pref_ids, int32_t* out_idx, double* out_score, int mode) {
   KLM_ENTER(h);
+  int algo = 0;
+  bool node_shard = false;
+  if (!split_mode(mode, &algo, &node_shard)) {
+    set_error("klm_reconcile: bad mode %d", mode);
+    return KLM_EINVAL;
+  }
+  if (!h->devs.empty()) {
+    // straight from the caller's arrays (they are valid for the whole call): no host copy
+    if (n < 0 || n > 0x7fffffff || (n > 0 && (!battery || !flags))) {
+      set_error("klm_nodes_set: bad argument (0 <= n_nodes < 2^31, arrays non-null)");
+      return KLM_EINVAL;
+    }
+    h->md_nodes = -1;
+    h->md_uploaded_mode = -1;
+    h->md_tab_valid = false;
+    const int rc = multi_schedule(h, n, battery, flags, R, min_battery, pref_off, pref_ids, out_idx, out_score,
+                                  algo, node_shard);
+    if (rc != KLM_OK) {
+      multi_sync(h);
+      h->md_uploaded_mode = -1;
+      return rc;
+    }
+    h->md_nodes = n;
+    return KLM_OK;
+  }
   const bool args_ok = n >= 0 && n <= 0x7fffffff && (n == 0 || (battery && flags)) && R >= 0 &&
                        (algo == KLM_ALGO_DECOMPOSED || algo == KLM_ALGO_BRUTEFORCE) &&
                        (R == 0 || (min_battery && pref_off && out_idx && out_score));

@@ -67,11 +67,34 @@ __device__ __forceinline__ Best block_best(Best v) {
 // One pass over the node table: 9 B/node (f64 battery + u8 flags), 128-bit
 // loads when both columns are 16-byte aligned. Block partials go to scratch;
 // the last block to finish (ticket) folds them, so one launch suffices.
+// Node-range sharding: every rank owns one shard of the node table and an array
+// of exchange slots, [2 epoch parities][kMaxShardParts] of 32 bytes, that its peers write into
+// over NVLink (peer pointers: cudaDeviceEnablePeerAccess in one process, CUDA IPC / symmetric
+// memory across processes). Rank r publishes its shard's K1 result into slot [epoch & 1][r] of
+// EVERY rank -- payload first, then the epoch with release semantics at system scope -- and the
+// sharded K2 of each rank waits (acquire) until all slots of its own array carry the epoch.
+// Alternating parities let step e + 1 publish while a slower rank still reads step e; a rank
+// cannot be two steps ahead, because its own K2 of step e + 1 needs every rank's K1 of e + 1.
+constexpr int kMaxShardParts = 16;
+struct alignas(32) ShardSlot {
+  int64_t idx;                // global index of the shard's best node, -1: none eligible
+  int64_t bat_bits;           // its battery (f64 bits)
+  unsigned long long epoch;   // written last
+  unsigned long long pad;
+};
+constexpr int64_t kShardSlotsBytes = 2 * kMaxShardParts * (int64_t)sizeof(ShardSlot) + 64;  // + error word
+struct ShardPublish {
+  ShardSlot* slots[kMaxShardParts];  // slot array of every rank, as seen from this device
+  int n_parts, my_part;
+  unsigned long long epoch;
+};
+
+template <bool PUBLISH>
 __global__ void __launch_bounds__(kBestThreads)
 node_best_kernel(const double* __restrict__ battery, const uint8_t* __restrict__ flags,
                  int64_t n, int64_t node_base, int vec_ok, int64_t* __restrict__ best,
                  unsigned int* __restrict__ ticket, double* __restrict__ part_bat,
-                 int64_t* __restrict__ part_idx) {
+                 int64_t* __restrict__ part_idx, ShardPublish pub) {
   // A kernel launched behind this one with programmatic stream serialisation
   // (klm_dev_schedule_after_best) may start now: K1 occupies a fraction of the SMs and its
   // result is needed only at the end of K2. Without such a dependent this is a no-op.
@@ -129,11 +152,21 @@ node_best_kernel(const double* __restrict__ battery, const uint8_t* __restrict__
     p.idx = __ldcg(part_idx + b);
     acc = better(acc, p);
   }
-  acc = block_best(acc);
+  acc = block_best(acc);  // warp 0 holds the result in every lane
+  const int64_t g_idx = acc.idx < 0 ? -1 : acc.idx + node_base;
+  const int64_t g_bits = __double_as_longlong(acc.idx < 0 ? 0.0 : acc.bat);
   if (threadIdx.x == 0) {
-    best[0] = acc.idx < 0 ? -1 : acc.idx + node_base;
-    best[1] = __double_as_longlong(acc.idx < 0 ? 0.0 : acc.bat);
+    if (best) {
+      best[0] = g_idx;
+      best[1] = g_bits;
+    }
     *ticket = 0;  // ready for the next launch on this scratch
+  }
+  if (PUBLISH && (int)threadIdx.x < pub.n_parts) {
+    // lane g writes rank g's copy of this rank's slot (n_parts <= 16: all in warp 0)
+    ShardSlot* sl = pub.slots[threadIdx.x] + (pub.epoch & 1ull) * kMaxShardParts + pub.my_part;
+    asm volatile("st.relaxed.sys.global.v2.s64 [%0], {%1, %2};" :: "l"(sl), "l"(g_idx), "l"(g_bits) : "memory");
+    asm volatile("st.release.sys.global.u64 [%0], %1;" :: "l"(&sl->epoch), "l"(pub.epoch) : "memory");
   }
 }
 
@@ -232,6 +265,152 @@ schedule_kernel(const double* __restrict__ battery, const uint8_t* __restrict__ 
           const double s = bk + 10;
           if (s > bs || (s == bs && pk < bi)) {
             bs = s;
+            bi = pk;
+          }
+        }
+      }
+      out_idx[r] = (int32_t)bi;
+      out_score[r] = bs;
+    }
+  }
+}
+
+// ---------------------------------------------------------------- K2, node table in shards
+
+// The node table as G contiguous shards of `shard_len` nodes (the last ones shorter or empty),
+// each readable from this device: its own memory, or a peer's mapped over NVLink / NVSwitch.
+// Node i lives in shard i / shard_len at offset i % shard_len.
+struct ShardView {
+  const double* bat[kMaxShardParts];
+  const uint8_t* flg[kMaxShardParts];
+  int64_t n_total;
+  int32_t shard_len;
+  float inv_len;  // 1 / shard_len, for the owner estimate
+  int n_parts;
+};
+
+__device__ __forceinline__ bool shard_lookup(const ShardView& v, int32_t id, uint8_t& f, double& b) {
+  if (id < 0 || (int64_t)id >= v.n_total) return false;
+  int g = __float2int_rz(__int2float_rz(id) * v.inv_len);  // within one of id / shard_len
+  g = min(g, v.n_parts - 1);
+  int32_t off = id - g * v.shard_len;
+  if (off < 0) { --g; off += v.shard_len; }
+  else if (off >= v.shard_len) { ++g; off -= v.shard_len; }
+  f = v.flg[g][off];
+  b = v.bat[g][off];
+  return true;
+}
+
+// Sharded form of schedule_kernel: this rank decides ITS slice of the requests. The global best
+// node is the fold of the G shard winners the ranks published into `my_slots` (waited for with
+// acquire loads: no host barrier, no K3); preferred nodes are probed where they live, through
+// the pointers of the view -- a 9-byte read over NVLink for a node another rank owns.
+// Results are identical to schedule_kernel on the whole table (global indices; lowest index on
+// ties, controller.go:160).
+__global__ void __launch_bounds__(kSchedThreads)
+schedule_sharded_kernel(ShardView v, const ShardSlot* __restrict__ my_slots, unsigned long long epoch,
+                        int* __restrict__ err, int64_t n_requests,
+                        const double* __restrict__ min_battery, const int32_t* __restrict__ pref_off,
+                        const int32_t* __restrict__ pref_ids, int32_t* __restrict__ out_idx,
+                        double* __restrict__ out_score) {
+  __shared__ int64_t s_g;
+  __shared__ double s_gb;
+  int64_t g = -1;
+  double gb = 0.0;
+  bool have_best = false;
+  const int64_t tile = (int64_t)blockDim.x * kSchedUnroll;
+  for (int64_t base = (int64_t)blockIdx.x * tile; base < n_requests; base += (int64_t)gridDim.x * tile) {
+    double mb[kSchedUnroll];
+    int32_t k0[kSchedUnroll], k1[kSchedUnroll];
+#pragma unroll
+    for (int j = 0; j < kSchedUnroll; ++j) {
+      const int64_t r = base + (int64_t)j * blockDim.x + threadIdx.x;
+      const bool live = r < n_requests;
+      mb[j] = live ? min_battery[r] : 0.0;
+      k0[j] = live ? pref_off[r] : 0;
+      k1[j] = live ? pref_off[r + 1] : 0;
+    }
+    int32_t p[kSchedUnroll][kSchedSlots];
+#pragma unroll
+    for (int j = 0; j < kSchedUnroll; ++j)
+#pragma unroll
+      for (int q = 0; q < kSchedSlots; ++q) p[j][q] = k0[j] + q < k1[j] ? pref_ids[k0[j] + q] : -1;
+    uint8_t f[kSchedUnroll][kSchedSlots];
+    double b[kSchedUnroll][kSchedSlots];
+#pragma unroll
+    for (int j = 0; j < kSchedUnroll; ++j)
+#pragma unroll
+      for (int q = 0; q < kSchedSlots; ++q) {
+        f[j][q] = 0;  // 0 fails the name/status test below
+        b[j][q] = 0.0;
+        shard_lookup(v, p[j][q], f[j][q], b[j][q]);
+      }
+    if (!have_best) {  // first tile only: every load of this tile is in flight by now
+      asm volatile("griddepcontrol.wait;" ::: "memory");
+      if (threadIdx.x < 32) {
+        Best w{0.0, -1};
+        if ((int)threadIdx.x < v.n_parts) {
+          const ShardSlot* sl = my_slots + (epoch & 1ull) * kMaxShardParts + threadIdx.x;
+          unsigned long long e = 0, t0 = 0, now = 0;
+          asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+          bool ok = true;
+          while (true) {
+            asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(e) : "l"(&sl->epoch) : "memory");
+            if (e == epoch) break;
+            __nanosleep(40);
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+            if (now - t0 > 4000000000ull) { ok = false; break; }  // 4 s: a peer never published
+          }
+          if (ok) {
+            int64_t pi, pb;
+            asm volatile("ld.relaxed.sys.global.v2.s64 {%0, %1}, [%2];" : "=l"(pi), "=l"(pb) : "l"(sl) : "memory");
+            w.idx = pi;
+            w.bat = __longlong_as_double(pb);
+          } else if (err) {
+            *err = 1;
+          }
+        }
+        w = warp_best(w);
+        if (threadIdx.x == 0) {
+          s_g = w.idx;
+          s_gb = w.bat;
+        }
+      }
+      __syncthreads();
+      g = s_g;
+      gb = s_gb;
+      have_best = true;
+    }
+#pragma unroll
+    for (int j = 0; j < kSchedUnroll; ++j) {
+      const int64_t r = base + (int64_t)j * blockDim.x + threadIdx.x;
+      if (r >= n_requests) continue;
+      const bool gate = mb[j] > 0;  // controller.go:194
+      int64_t bi = -1;
+      double bs = 0.0;
+      if (g >= 0 && !(gate && gb < mb[j])) {
+        bi = g;
+        bs = gb;
+#pragma unroll
+        for (int q = 0; q < kSchedSlots; ++q) {
+          if ((f[j][q] & 3u) != 3u) continue;     // :190, :198
+          if (gate && b[j][q] < mb[j]) continue;  // :194
+          const double sc = b[j][q] + 10;         // :205-208
+          if (sc > bs || (sc == bs && p[j][q] < bi)) {
+            bs = sc;
+            bi = p[j][q];
+          }
+        }
+        for (int32_t k = k0[j] + kSchedSlots; k < k1[j]; ++k) {  // longer preferred lists
+          const int32_t pk = pref_ids[k];
+          uint8_t fk = 0;
+          double bk = 0.0;
+          if (!shard_lookup(v, pk, fk, bk)) continue;
+          if ((fk & 3u) != 3u) continue;
+          if (gate && bk < mb[j]) continue;
+          const double sc = bk + 10;
+          if (sc > bs || (sc == bs && pk < bi)) {
+            bs = sc;
             bi = pk;
           }
         }
@@ -417,8 +596,8 @@ extern "C" int klm_dev_node_best(const double* battery, const uint8_t* flags, in
   if (blocks > kBestMaxBlocks) blocks = kBestMaxBlocks;
   if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
   const int vec_ok = aligned16(battery) && aligned16(flags);
-  node_best_kernel<<<(int)blocks, kBestThreads, 0, as_stream(stream)>>>(
-      battery, flags, n_nodes, node_base, vec_ok, best, ticket, part_bat, part_idx);
+  node_best_kernel<false><<<(int)blocks, kBestThreads, 0, as_stream(stream)>>>(
+      battery, flags, n_nodes, node_base, vec_ok, best, ticket, part_bat, part_idx, ShardPublish{});
   KLM_LAUNCH_CHECK("node_best_kernel");
   return KLM_OK;
 }
@@ -540,5 +719,119 @@ extern "C" int klm_dev_merge_partials_peer(int n_parts, const int32_t* const* pa
   merge_partials_peer_kernel<<<grid_for(r1 - r0, 256, 16), 256, 0, as_stream(stream)>>>(
       p, n_parts, r0, r1, out_idx, out_score);
   KLM_LAUNCH_CHECK("merge_partials_peer_kernel");
+  return KLM_OK;
+}
+
+// ---------------------------------------------------------------- node-range sharding
+
+extern "C" int64_t klm_dev_shard_slots_bytes(void) { return kShardSlotsBytes; }
+
+extern "C" void klm_shard_range(int64_t n_nodes, int n_parts, int part, int64_t* lo, int64_t* hi) {
+  // shards are multiples of 16 nodes, so that every shard's columns keep the 16-byte alignment
+  // of the table's (K1 reads them with 128-bit loads)
+  const int64_t len = n_parts > 0 ? (ceil_div(n_nodes > 0 ? n_nodes : 0, n_parts) + 15) / 16 * 16 : 0;
+  int64_t a = (int64_t)part * len, b = a + len;
+  if (a > n_nodes) a = n_nodes;
+  if (b > n_nodes) b = n_nodes;
+  if (a < 0) a = 0;
+  if (b < a) b = a;
+  if (lo) *lo = a;
+  if (hi) *hi = b;
+}
+
+extern "C" int klm_dev_node_best_publish(const double* battery, const uint8_t* flags, int64_t n_nodes,
+                                         int64_t node_base, int n_parts, int my_part,
+                                         void* const* peer_slots, uint64_t epoch, int64_t* best,
+                                         void* scratch, void* stream) {
+  if (n_nodes < 0 || !scratch || (n_nodes > 0 && (!battery || !flags)) || n_parts < 1 ||
+      n_parts > kMaxShardParts || my_part < 0 || my_part >= n_parts || !peer_slots || epoch == 0) {
+    set_error("klm_dev_node_best_publish: bad argument (1 <= n_parts <= %d, epoch >= 1)", kMaxShardParts);
+    return n_parts > kMaxShardParts ? KLM_ELIMIT : KLM_EINVAL;
+  }
+  ShardPublish pub{};
+  for (int g = 0; g < n_parts; ++g) {
+    if (!peer_slots[g]) {
+      set_error("klm_dev_node_best_publish: null slot array for part %d", g);
+      return KLM_EINVAL;
+    }
+    pub.slots[g] = static_cast<ShardSlot*>(peer_slots[g]);
+  }
+  pub.n_parts = n_parts;
+  pub.my_part = my_part;
+  pub.epoch = epoch;
+  char* s = static_cast<char*>(scratch);
+  unsigned int* ticket = reinterpret_cast<unsigned int*>(s);
+  double* part_bat = reinterpret_cast<double*>(s + 256);
+  int64_t* part_idx = reinterpret_cast<int64_t*>(s + 256 + (int64_t)kBestMaxBlocks * 8);
+  int64_t blocks = ceil_div(n_nodes, (int64_t)kBestThreads * kBestNodesPerThread);
+  if (blocks < 1) blocks = 1;
+  if (blocks > kBestMaxBlocks) blocks = kBestMaxBlocks;
+  if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
+  const int vec_ok = aligned16(battery) && aligned16(flags);
+  node_best_kernel<true><<<(int)blocks, kBestThreads, 0, as_stream(stream)>>>(
+      battery, flags, n_nodes, node_base, vec_ok, best, ticket, part_bat, part_idx, pub);
+  KLM_LAUNCH_CHECK("node_best_kernel<publish>");
+  return KLM_OK;
+}
+
+extern "C" int klm_dev_schedule_sharded(int n_parts, int64_t n_nodes_total,
+                                        const double* const* battery_parts,
+                                        const uint8_t* const* flags_parts, void* my_slots,
+                                        uint64_t epoch, int64_t n_requests, const double* min_battery,
+                                        const int32_t* pref_off, const int32_t* pref_ids,
+                                        int32_t* out_idx, double* out_score, void* stream) {
+  if (n_parts < 1 || n_parts > kMaxShardParts || n_nodes_total < 0 || n_nodes_total > 0x7fffffff ||
+      !battery_parts || !flags_parts || !my_slots || epoch == 0 || n_requests < 0) {
+    set_error("klm_dev_schedule_sharded: bad argument (1 <= n_parts <= %d, epoch >= 1)", kMaxShardParts);
+    return n_parts > kMaxShardParts ? KLM_ELIMIT : KLM_EINVAL;
+  }
+  if (n_requests == 0) return KLM_OK;
+  if (!min_battery || !pref_off || !out_idx || !out_score) {
+    set_error("klm_dev_schedule_sharded: null request array");
+    return KLM_EINVAL;
+  }
+  ShardView v{};
+  int64_t lo = 0, hi = 0;
+  klm_shard_range(n_nodes_total, n_parts, 0, &lo, &hi);
+  v.shard_len = (int32_t)(hi - lo > 0 ? hi - lo : 1);
+  v.inv_len = 1.0f / (float)v.shard_len;
+  v.n_total = n_nodes_total;
+  v.n_parts = n_parts;
+  for (int g = 0; g < n_parts; ++g) {
+    klm_shard_range(n_nodes_total, n_parts, g, &lo, &hi);
+    if (hi > lo && (!battery_parts[g] || !flags_parts[g])) {
+      set_error("klm_dev_schedule_sharded: null node columns for part %d", g);
+      return KLM_EINVAL;
+    }
+    v.bat[g] = battery_parts[g];
+    v.flg[g] = flags_parts[g];
+  }
+  ShardSlot* slots = static_cast<ShardSlot*>(my_slots);
+  int* err = reinterpret_cast<int*>(slots + 2 * kMaxShardParts);
+  const int grid = grid_for(ceil_div(n_requests, (int64_t)kSchedUnroll), kSchedThreads, 8);
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)grid);
+  cfg.blockDim = dim3(kSchedThreads);
+  cfg.stream = as_stream(stream);
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  KLM_CUDA(cudaLaunchKernelEx(&cfg, schedule_sharded_kernel, v, (const ShardSlot*)slots,
+                              (unsigned long long)epoch, err, n_requests, min_battery, pref_off, pref_ids,
+                              out_idx, out_score));
+  KLM_LAUNCH_CHECK("schedule_sharded_kernel");
+  return KLM_OK;
+}
+
+extern "C" int klm_dev_shard_error(const void* my_slots, int* out, void* stream) {
+  if (!my_slots || !out) {
+    set_error("klm_dev_shard_error: bad argument");
+    return KLM_EINVAL;
+  }
+  const ShardSlot* slots = static_cast<const ShardSlot*>(my_slots);
+  KLM_CUDA(cudaMemcpyAsync(out, slots + 2 * kMaxShardParts, sizeof(int), cudaMemcpyDeviceToHost, as_stream(stream)));
+  KLM_CUDA(cudaStreamSynchronize(as_stream(stream)));
   return KLM_OK;
 }

@@ -61,3 +61,18 @@ def test_host_layer_loads(pkg):
     for name in ("klmh_open", "klmh_reconcile", "klmh_status", "klmh_calculate_cluster_metrics",
                  "klmh_low_battery_uavs"):
         assert hasattr(lib, name)
+
+
+def test_shard_range_partitions_the_nodes(pkg):
+    """klm_shard_range (host arithmetic, no GPU): contiguous, ordered, covering, shards of a
+    multiple of 16 nodes so that every shard's columns keep 16-byte alignment."""
+    sr = pkg.binding.shard_range
+    for n in (0, 1, 3, 16, 17, 1000, 99_999, 100_000, 1_000_000, 2**31 - 1):
+        for g in (1, 2, 3, 4, 8, 16):
+            prev = 0
+            for k in range(g):
+                lo, hi = sr(n, g, k)
+                assert lo == prev and lo <= hi <= n
+                assert lo % 16 == 0 or lo == n
+                prev = hi
+            assert prev == n
