@@ -237,12 +237,17 @@ def run_series_workload(ctx, wl):
             ring[a * 64:a * 64 + rows.shape[0]] = torch.from_numpy(rows).cuda()
     assert ring.shape[1] % 4 == 0
     seen = torch.full((S,), T, dtype=torch.int32, device="cuda")
-    # fresh samples for every tick (a pool of 64 vectors, cycled): re-ingesting one
-    # vector would pile up identical values in every window and distort the p95 work
-    n_ticks = 64
+    # fresh samples for every tick: a pool of vectors larger than the number of steps a run
+    # takes (re-ingesting the same vectors would pile up identical values in every window and
+    # turn the p95 work into tie handling)
+    n_ticks = 2048 if wl == "c2" else 256
     if wl == "c2":
-        u = syn.uniform_torch(syn.seed_for(cid, 31), n_ticks * S, s_base * n_ticks).reshape(n_ticks, S)
-        ticks = (u * torch.as_tensor(scales, dtype=torch.float64, device="cuda")[None, :]).to(torch.float32)
+        sc_all = torch.as_tensor(scales, dtype=torch.float64, device="cuda")[None, :]
+        ticks = torch.empty((n_ticks, S), dtype=torch.float32, device="cuda")
+        for a in range(0, n_ticks, 256):
+            u = syn.uniform_torch(syn.seed_for(cid, 31), 256 * S, (s_base * n_ticks) + a * S).reshape(256, S)
+            ticks[a:a + 256] = (u * sc_all).to(torch.float32)
+        del u
     else:
         ticks = ring[:, torch.arange(0, T, T // n_ticks, device="cuda")[:n_ticks]].t().contiguous()
     o_min = torch.empty(S, dtype=torch.float32, device="cuda")

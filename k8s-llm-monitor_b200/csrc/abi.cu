@@ -214,6 +214,15 @@ int sync(cudaStream_t st) {
 
 size_t align256(size_t b) { return (b + 255) & ~size_t(255); }
 
+// CSR offsets off[0..n] must not decrease (with off[0] >= 0 and off[n] <= total checked by the
+// caller, every inner offset is then in range too): a kernel indexes pref_ids / container
+// columns with them. One pass over memory the call is about to copy anyway.
+bool csr_non_decreasing(const int32_t* off, int64_t n) {
+  int bad = 0;
+  for (int64_t i = 0; i < n; ++i) bad |= off[i + 1] < off[i];
+  return !bad;
+}
+
 // the synchronous ring / collect / aggregate calls share buffers and streams with the cycles
 // klm_collect_begin has in flight
 int collect_idle(klm_handle* h, const char* who) {
@@ -355,6 +364,10 @@ int multi_schedule(klm_handle* h, int64_t n, const double* battery, const uint8_
     const int64_t r0 = R * g / G, r1 = R * (g + 1) / G, rl = r1 - r0;
     if (rl == 0) continue;
     const int64_t i0 = pref_off[r0], i1 = pref_off[r1];
+    if (!csr_non_decreasing(pref_off + r0, rl)) {
+      set_error("klm_schedule_batch: pref_off is not non-decreasing");
+      return KLM_EINVAL;
+    }
     KLM_TRY(d.req_min.ensure((size_t)rl * 8));
     KLM_TRY(d.req_off.ensure((size_t)(rl + 1) * 4));
     KLM_TRY(d.req_ids.ensure((size_t)(i1 - i0 > 0 ? i1 - i0 : 1) * 4));
@@ -670,6 +683,10 @@ static int schedule_batch_impl(klm_handle* h, int64_t R, const double* min_batte
     d_ids = reinterpret_cast<int32_t*>(blk + in_ids);
     d_score = h->res_blk.as<double>();
     d_idx = reinterpret_cast<int32_t*>(h->res_blk.as<char>() + out_idx_at);
+    if (!csr_non_decreasing(pref_off, R)) {
+      set_error("klm_schedule_batch: pref_off is not non-decreasing");
+      return KLM_EINVAL;
+    }
     std::memcpy(h->sched_pin.at(0), min_battery, min_bytes);
     std::memcpy(h->sched_pin.at(in_off), pref_off, off_bytes);
     if (ids_bytes) std::memcpy(h->sched_pin.at(in_ids), pref_ids, ids_bytes);
@@ -709,6 +726,11 @@ static int schedule_batch_impl(klm_handle* h, int64_t R, const double* min_batte
           const int64_t r0 = R * c / n_chunks, r1 = R * (c + 1) / n_chunks;
           const int64_t i0 = pref_off[r0], i1 = pref_off[r1];
           cudaStream_t st = ss[c & 1];
+          // (checked chunk by chunk: the previous chunk's transfers are in flight meanwhile)
+          if (!csr_non_decreasing(pref_off + r0, r1 - r0)) {
+            set_error("klm_schedule_batch: pref_off is not non-decreasing");
+            return KLM_EINVAL;
+          }
           // offsets (r0, r1]: entry r0 came with the previous chunk (entry 0 with the first)
           const int64_t o0 = c == 0 ? 0 : r0 + 1;
           KLM_TRY(h2d(d_min + r0, min_battery + r0, (size_t)(r1 - r0) * sizeof(double), st));
@@ -731,6 +753,10 @@ static int schedule_batch_impl(klm_handle* h, int64_t R, const double* min_batte
         cudaStreamSynchronize(h->stream2);
       }
       return rc;
+    }
+    if (!csr_non_decreasing(pref_off, R)) {
+      set_error("klm_schedule_batch: pref_off is not non-decreasing");
+      return KLM_EINVAL;
     }
     KLM_TRY(h2d(d_min, min_battery, min_bytes, h->stream));
     KLM_TRY(h2d(d_off, pref_off, off_bytes, h->stream));
@@ -832,7 +858,7 @@ extern "C" int klm_reconcile(klm_handle* h, int64_t n, const double* battery, co
   const size_t in_bytes = q_ids + align256(ids_bytes), out_idx_at = align256(min_bytes);
   const size_t out_bytes = out_idx_at + idx_bytes;
   if (!args_ok || R == 0 || n_ids < 0 || pref_off[0] != 0 || (n_ids > 0 && !pref_ids) ||
-      in_bytes + out_bytes > kStageMax) {
+      in_bytes + out_bytes > kStageMax || !csr_non_decreasing(pref_off, R)) {
     // let the two calls validate and handle it (same error texts as calling them separately)
     KLM_TRY(nodes_set_impl(h, n, battery, flags));
     return schedule_batch_impl(h, R, min_battery, pref_off, pref_ids, out_idx, out_score, algo);
@@ -976,6 +1002,10 @@ extern "C" int klm_pod_rates(klm_handle* h, int64_t n_pods, const int32_t* ctr_o
       (n_ctr > 0 && (!c_cpu_use || !c_mem_use || !c_cpu_req || !c_cpu_lim || !c_mem_req ||
                      !c_mem_lim))) {
     set_error("klm_pod_rates: ctr_off must start at 0 and container columns be non-null");
+    return KLM_EINVAL;
+  }
+  if (!csr_non_decreasing(ctr_off, n_pods)) {
+    set_error("klm_pod_rates: ctr_off is not non-decreasing");
     return KLM_EINVAL;
   }
   const size_t ccol = align256((size_t)n_ctr * 8), off_b = align256((size_t)(n_pods + 1) * 4);

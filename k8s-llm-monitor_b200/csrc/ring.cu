@@ -132,8 +132,8 @@ window_stats_block_kernel(const float* __restrict__ ring, const uint32_t* __rest
       b = fmaxf(b, s_mx[w]);
       t += s_sum[w];
     }
-    if (out_min) out_min[o] = a;
-    if (out_max) out_max[o] = b;
+    if (out_min) out_min[o] = a + 0.f;
+    if (out_max) out_max[o] = b + 0.f;
     if (out_mean) out_mean[o] = t / (double)n;
   }
   if (!out_p95) return;
@@ -173,7 +173,7 @@ window_stats_block_kernel(const float* __restrict__ ring, const uint32_t* __rest
     }
     __syncthreads();
   }
-  if (threadIdx.x == 0) out_p95[o] = key_f32(s_prefix);
+  if (threadIdx.x == 0) out_p95[o] = key_f32(s_prefix) + 0.f;
 }
 
 }  // namespace klm

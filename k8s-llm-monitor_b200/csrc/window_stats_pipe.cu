@@ -408,8 +408,8 @@ window_stats_pipe_kernel(const float* __restrict__ ring, const uint32_t* __restr
       sum += __shfl_xor_sync(0xffffffffu, sum, off);
     }
     if (lane == 0) {
-      if (out_min) out_min[o] = mn;
-      if (out_max) out_max[o] = mx;
+      if (out_min) out_min[o] = mn + 0.f;  // -0.0 -> +0.0
+      if (out_max) out_max[o] = mx + 0.f;
       if (out_mean) out_mean[o] = sum / (double)n;
     }
     if (!want_p95) continue;
@@ -429,7 +429,7 @@ window_stats_pipe_kernel(const float* __restrict__ ring, const uint32_t* __restr
       result = pipe_bisect_global(ring + s * (int64_t)pitch, n, lane, f32_key(NEG_INF),
                                   bis_hi ? bis_hi : f32_key(mx) + 1u, k);
     }
-    if (lane == 0) out_p95[o] = result;
+    if (lane == 0) out_p95[o] = result + 0.f;
   }
 }
 

@@ -474,8 +474,8 @@ window_stats_warp_kernel(const float* __restrict__ ring, const uint32_t* __restr
     sum += __shfl_xor_sync(0xffffffffu, sum, off);
   }
   if (lane == 0) {
-    if (out_min) out_min[o] = mn;
-    if (out_max) out_max[o] = mx;
+    if (out_min) out_min[o] = mn + 0.f;  // -0.0 -> +0.0: one canonical zero in the outputs
+    if (out_max) out_max[o] = mx + 0.f;
     if (out_mean) out_mean[o] = sum / (double)n;
   }
   if (!want_p95) return;
@@ -525,7 +525,7 @@ window_stats_warp_kernel(const float* __restrict__ ring, const uint32_t* __restr
     if (OVL) reload_shared_rows();
     result = w.select_bisect(bis_lo, bis_hi, k, bis_first);
   }
-  if (lane == 0) out_p95[o] = result;
+  if (lane == 0) out_p95[o] = result + 0.f;
 }
 
 // dynamic shared memory of one CTA: NR == NV: lists (with alignment slack) then aux; else the

@@ -416,10 +416,12 @@ KLMO_API int klmo_window_stats(const float* ring, const uint32_t* seen,
       int64_t rank = (19 * n + 19) / 20 - 1;
       p95 = buf[rank];
     }
-    if (out_min) out_min[s - s0] = mn;
-    if (out_max) out_max[s - s0] = mx;
+    /* one canonical zero: -0.0 and +0.0 compare equal, so which of them a sort or a minimum
+     * returns is arbitrary; every implementation reports +0.0 (x + 0.0f in round-to-nearest) */
+    if (out_min) out_min[s - s0] = mn + 0.0f;
+    if (out_max) out_max[s - s0] = mx + 0.0f;
     if (out_mean) out_mean[s - s0] = mean;
-    if (out_p95) out_p95[s - s0] = p95;
+    if (out_p95) out_p95[s - s0] = p95 + 0.0f;
   }
   free(buf);
   return 0;
@@ -491,10 +493,10 @@ KLMO_API int klmo_window_stats_fast(const float* ring, const uint32_t* seen,
         mean = sum / (double)n;
         p95 = quickselect(buf, n, (19 * n + 19) / 20 - 1);
       }
-      if (out_min) out_min[s - s0] = mn;
-      if (out_max) out_max[s - s0] = mx;
+      if (out_min) out_min[s - s0] = mn + 0.0f;
+      if (out_max) out_max[s - s0] = mx + 0.0f;
       if (out_mean) out_mean[s - s0] = mean;
-      if (out_p95) out_p95[s - s0] = p95;
+      if (out_p95) out_p95[s - s0] = p95 + 0.0f;
     }
     free(buf);
   }

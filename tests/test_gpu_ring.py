@@ -12,7 +12,8 @@ RTOL = 1e-5
 
 def check_stats(got, want, what=""):
     for k in ("min", "max", "p95"):
-        bad = np.flatnonzero(got[k] != want[k])
+        # bit patterns, not values: a zero result is +0.0 in every implementation
+        bad = np.flatnonzero(got[k].view(np.uint32) != want[k].view(np.uint32))
         assert bad.size == 0, f"{what} {k}: {bad.size} mismatches, first at {bad[:5]}: {got[k][bad[:5]]} vs {want[k][bad[:5]]}"
     assert np.allclose(got["mean"], want["mean"], rtol=RTOL, atol=1e-300), f"{what} mean"
 
@@ -163,8 +164,8 @@ def test_full_c2_properties(dev, pkg):
 
 @pytest.mark.parametrize("t", [100, 1000, 3600, 4096, 8192])
 def test_k7_variants_agree(dev, t):
-    """The pipelined kernel (default for windows <= 4096), the register-resident warp kernel
-    and the shared-memory block kernel must all match the oracle."""
+    """Every K7 variant (streaming, pipelined, register-resident warp, shared-memory block)
+    must match the oracle bit for bit."""
     import torch
     rng = np.random.default_rng(1000 + t)
     s = 400

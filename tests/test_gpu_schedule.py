@@ -342,3 +342,27 @@ def test_handle_is_thread_safe(pkg):
         for t in threads:
             t.join()
     assert not errors, errors[:3]
+
+
+def test_offsets_that_decrease_are_refused(handle, pkg):
+    """pref_off / ctr_off index device arrays: offsets that decrease (or leave [0, off[R]]) would
+    make a kernel read out of bounds, so the host-buffer calls check them (small staged batch,
+    plain batch, chunked batch, klm_reconcile, klm_pod_rates)."""
+    b = pkg.binding
+    rng = np.random.default_rng(12)
+    for r in (50, 40_000, 300_000):
+        bat, flags, mb, off, ids = helpers.random_problem(rng, 500, r, kmax=2, grid=1.0)
+        ids = np.clip(ids, 0, 499).astype(np.int32)
+        handle.nodes_set(bat, flags)
+        bad = off.copy()
+        j = r // 2
+        bad[j] = bad[j + 1] + 3 if bad[j + 1] + 3 <= bad[-1] else bad[j - 1] - 1   # one inner offset out of order
+        assert not np.all(np.diff(bad) >= 0)
+        with pytest.raises(b.KlmError) as e:
+            handle.schedule_batch(mb, bad, ids)
+        assert e.value.code == b.KLM_EINVAL
+        with pytest.raises(b.KlmError):
+            handle.reconcile(bat, flags, mb, bad, ids)
+        got = handle.schedule_batch(mb, off, ids)                     # the handle is still usable
+        want = ob.schedule_decomposed(bat, flags, mb, off, ids)
+        assert np.array_equal(got[0], want[0])
