@@ -219,7 +219,11 @@ int klm_fleet_scan(klm_handle* h, int64_t n, const uint8_t* status_ok,
 int klm_ring_create(klm_handle* h, int64_t n_series, int32_t window);
 /* Append one sample to each listed series (UpdateUAVReport, manager.go:391-449,
  * and the end of Collect, :286, are the producers). series_ids must be
- * distinct within one call. */
+ * distinct within one call. While klm_collect_begin cycles are in flight the call
+ * does not fail: the samples are copied, queued in arrival order and applied by the
+ * next klm_collect_begin before its own tick (or by the next synchronous ring call
+ * once the pipeline has drained), which is the order manager.go:437-446 gets from
+ * its mutex. klm_ring_ingest_tick queues the same way. */
 int klm_ring_ingest(klm_handle* h, int64_t n, const int64_t* series_ids,
                     const float* values);
 /* Append one sample to EVERY series: values[n_series] (one collection tick). */
@@ -286,8 +290,10 @@ int64_t klm_collect_packed_bytes(int64_t n_series);
  *   only (win_min/max/mean/p95 must be NULL).
  * - The node snapshot must fit a 1 MB staging block (about 20 000 nodes plus
  *   their pods), else KLM_ELIMIT: use klm_collect.
- * - While cycles are in flight the synchronous ring / collect / aggregate calls on
- *   this handle return KLM_ESTATE. A third klm_collect_begin returns KLM_ESTATE. */
+ * - While cycles are in flight klm_ring_ingest / klm_ring_ingest_tick queue their
+ *   samples for the next klm_collect_begin (HTTP handlers push UAV reports at any
+ *   time, cmd/server/main.go:607); the other synchronous ring / collect / aggregate
+ *   calls on this handle return KLM_ESTATE. A third klm_collect_begin returns KLM_ESTATE. */
 int klm_collect_begin(klm_handle* h, const klm_collect_in* in, const klm_collect_out* out);
 int klm_collect_end(klm_handle* h);
 

@@ -150,6 +150,20 @@ struct klm_handle {
   } slot[2];
   cudaStream_t stream3 = nullptr, stream_bulk = nullptr;  // downloads; K6 + K7 of the async cycles
   uint64_t begun = 0, ended = 0;
+  // Samples pushed (klm_ring_ingest / klm_ring_ingest_tick) while cycles are in flight: kept in
+  // arrival order and applied by the next klm_collect_begin before its own tick, or by the next
+  // synchronous ring call once the pipeline is idle. One entry per call (ids of one call are
+  // distinct; calls may repeat a series, so every call is its own K6 launch, in order).
+  struct Pushed {
+    int64_t n;         // samples of the call
+    size_t ids_at;     // first id in q_ids, or SIZE_MAX for a whole tick (n == n_series)
+    size_t vals_at;    // first value in q_vals
+  };
+  std::vector<Pushed> q_calls;
+  std::vector<int64_t> q_ids;
+  std::vector<float> q_vals;
+  PinBuf q_pin[2];     // staging of the queue, one per cycle slot
+  DevBuf q_dev[2];
 
   // ---- more than one device (klm_create with n_dev > 1): the scheduler's batch is split
   // over the devices inside the library; `device` above is devs[0].device.
@@ -221,6 +235,29 @@ bool csr_non_decreasing(const int32_t* off, int64_t n) {
   int bad = 0;
   for (int64_t i = 0; i < n; ++i) bad |= off[i + 1] < off[i];
   return !bad;
+}
+
+// Apply the queued pushes in arrival order on `st` (staging block `which`). The host copy is
+// consumed before this returns; the device work is ordered by the stream.
+int flush_pushed(klm_handle* h, int which, cudaStream_t st) {
+  if (h->q_calls.empty()) return KLM_OK;
+  const size_t ids_bytes = align256(h->q_ids.size() * sizeof(int64_t)), vals_bytes = h->q_vals.size() * sizeof(float);
+  PinBuf& pin = h->q_pin[which];
+  DevBuf& dev = h->q_dev[which];
+  KLM_TRY(pin.ensure(ids_bytes + vals_bytes + 256));
+  KLM_TRY(dev.ensure(ids_bytes + vals_bytes + 256));
+  if (!h->q_ids.empty()) std::memcpy(pin.at(0), h->q_ids.data(), h->q_ids.size() * sizeof(int64_t));
+  std::memcpy(pin.at(ids_bytes), h->q_vals.data(), vals_bytes);
+  KLM_TRY(h2d(dev.p, pin.p, ids_bytes + vals_bytes, st));
+  const int64_t* d_ids = dev.as<int64_t>();
+  const float* d_vals = reinterpret_cast<const float*>(dev.as<char>() + ids_bytes);
+  for (const klm_handle::Pushed& c : h->q_calls)
+    KLM_TRY(klm_dev_ring_ingest(h->ring.as<float>(), h->seen.as<uint32_t>(), h->n_series, h->window, h->pitch,
+                                c.n, c.ids_at == SIZE_MAX ? nullptr : d_ids + c.ids_at, d_vals + c.vals_at, st));
+  h->q_calls.clear();
+  h->q_ids.clear();
+  h->q_vals.clear();
+  return KLM_OK;
 }
 
 // the synchronous ring / collect / aggregate calls share buffers and streams with the cycles
@@ -564,6 +601,10 @@ extern "C" void klm_destroy(klm_handle* h) {
   }
   h->md_tab.release();
   cudaSetDevice(h->device);
+  for (int i = 0; i < 2; ++i) {
+    h->q_pin[i].release();
+    h->q_dev[i].release();
+  }
   if (h->stream) cudaStreamSynchronize(h->stream);
   if (h->stream2) cudaStreamSynchronize(h->stream2);
   DevBuf* bufs[] = {&h->node_tab, &h->req_blk,  &h->res_blk,    &h->snap_out,   &h->rec_blk,
@@ -1092,6 +1133,9 @@ extern "C" int klm_ring_create(klm_handle* h, int64_t n_series, int32_t window) 
   h->n_series = n_series;
   h->window = window;
   h->pitch = pitch;
+  h->q_calls.clear();  // pushes queued for the previous ring
+  h->q_ids.clear();
+  h->q_vals.clear();
   return KLM_OK;
 }
 
@@ -1107,12 +1151,26 @@ extern "C" int klm_ring_ingest(klm_handle* h, int64_t n, const int64_t* series_i
                                const float* values) {
   KLM_ENTER(h);
   KLM_TRY(ring_ready(h, "klm_ring_ingest"));
-  KLM_TRY(collect_idle(h, "klm_ring_ingest"));
   if (n < 0 || (n > 0 && (!series_ids || !values))) {
     set_error("klm_ring_ingest: bad argument");
     return KLM_EINVAL;
   }
   if (n == 0) return KLM_OK;
+  if (h->begun != h->ended) {
+    // collect cycles are in flight (the pipelined collector always has one): the push is queued
+    // and applied, in arrival order, by the next klm_collect_begin before its own tick --
+    // UpdateUAVReport (manager.go:437-446) serialises with Collect under one mutex the same way
+    try {
+      h->q_calls.push_back({n, h->q_ids.size(), h->q_vals.size()});
+      h->q_ids.insert(h->q_ids.end(), series_ids, series_ids + n);
+      h->q_vals.insert(h->q_vals.end(), values, values + n);
+    } catch (const std::bad_alloc&) {
+      set_error("klm_ring_ingest: out of host memory");
+      return KLM_EINVAL;
+    }
+    return KLM_OK;
+  }
+  KLM_TRY(flush_pushed(h, 0, h->stream));  // (pushes queued behind a pipeline that has drained)
   KLM_TRY(h->ing_ids.ensure((size_t)n * 8));
   KLM_TRY(h->ing_vals.ensure((size_t)n * 4));
   KLM_TRY(h2d(h->ing_ids.p, series_ids, (size_t)n * 8, h->stream));
@@ -1126,11 +1184,21 @@ extern "C" int klm_ring_ingest(klm_handle* h, int64_t n, const int64_t* series_i
 extern "C" int klm_ring_ingest_tick(klm_handle* h, const float* values) {
   KLM_ENTER(h);
   KLM_TRY(ring_ready(h, "klm_ring_ingest_tick"));
-  KLM_TRY(collect_idle(h, "klm_ring_ingest_tick"));
   if (!values) {
     set_error("klm_ring_ingest_tick: values is null");
     return KLM_EINVAL;
   }
+  if (h->begun != h->ended) {  // queued like klm_ring_ingest, as one whole tick
+    try {
+      h->q_calls.push_back({h->n_series, SIZE_MAX, h->q_vals.size()});
+      h->q_vals.insert(h->q_vals.end(), values, values + h->n_series);
+    } catch (const std::bad_alloc&) {
+      set_error("klm_ring_ingest_tick: out of host memory");
+      return KLM_EINVAL;
+    }
+    return KLM_OK;
+  }
+  KLM_TRY(flush_pushed(h, 0, h->stream));
   KLM_TRY(h->ing_vals.ensure((size_t)h->n_series * 4));
   KLM_TRY(h2d(h->ing_vals.p, values, (size_t)h->n_series * 4, h->stream));
   KLM_TRY(klm_dev_ring_ingest(h->ring.as<float>(), h->seen.as<uint32_t>(), h->n_series,
@@ -1144,6 +1212,7 @@ extern "C" int klm_ring_load(klm_handle* h, int64_t s0, int64_t s1, int32_t coun
   KLM_ENTER(h);
   KLM_TRY(ring_ready(h, "klm_ring_load"));
   KLM_TRY(collect_idle(h, "klm_ring_load"));
+  KLM_TRY(flush_pushed(h, 0, h->stream));
   if (s0 < 0 || s1 < s0 || s1 > h->n_series || count < 0 || count > h->window ||
       (s1 > s0 && count > 0 && !data)) {
     set_error("klm_ring_load: bad argument");
@@ -1175,6 +1244,7 @@ extern "C" int klm_ring_stats(klm_handle* h, int64_t s0, int64_t s1, float* out_
   KLM_ENTER(h);
   KLM_TRY(ring_ready(h, "klm_ring_stats"));
   KLM_TRY(collect_idle(h, "klm_ring_stats"));
+  KLM_TRY(flush_pushed(h, 0, h->stream));
   if (s0 < 0 || s1 < s0 || s1 > h->n_series) {
     set_error("klm_ring_stats: series range out of bounds");
     return KLM_EINVAL;
@@ -1482,6 +1552,8 @@ int collect_begin_impl(klm_handle* h, const klm_collect_in* in, const klm_collec
   KLM_CUDA(cudaEventRecord(sl.snap, st2));
   // ---- K6 + K7 on the main stream, as soon as the tick is on the device
   KLM_CUDA(cudaStreamWaitEvent(st, sl.up, 0));
+  // pushes that arrived since the last cycle was begun go in first, in arrival order
+  if (h->n_series > 0) KLM_TRY(flush_pushed(h, (int)(h->begun & 1), st));
   if (in->tick_values)
     KLM_TRY(klm_dev_ring_ingest(h->ring.as<float>(), h->seen.as<uint32_t>(), S, h->window, h->pitch, S,
                                 nullptr, sl.tick_dev.as<float>(), st));
@@ -1556,6 +1628,7 @@ extern "C" int64_t klm_collect_packed_bytes(int64_t n_series) {
 extern "C" int klm_collect(klm_handle* h, const klm_collect_in* in, const klm_collect_out* out) {
   KLM_ENTER(h);
   KLM_TRY(collect_idle(h, "klm_collect"));
+  if (h->n_series > 0) KLM_TRY(flush_pushed(h, 0, h->stream));
   const int rc = collect_impl(h, in, out);
   if (rc != KLM_OK) {  // leave nothing in flight that still reads or writes the staging blocks
     cudaStreamSynchronize(h->stream);

@@ -309,3 +309,78 @@ def test_collect_pipeline_two_in_flight(pkg):
             end()                                    # nothing in flight
         again = b.collect(None, snap)                # idle again: the synchronous call works
         assert np.array_equal(again["p95"], wants[6]["p95"])
+
+
+def test_pushes_queue_behind_cycles_in_flight(pkg):
+    """UpdateUAVReport (manager.go:391-449) is called from HTTP handlers at any time, also while
+    the pipelined collector has cycles in flight: klm_ring_ingest / klm_ring_ingest_tick then queue
+    and the next klm_collect_begin applies the queue, in arrival order, before its own tick. A
+    test-side lock records the arrival order; a second handle replays it with synchronous calls
+    (itself checked against the oracle elsewhere) and every cycle's statistics must be identical."""
+    import threading
+    rng = np.random.default_rng(33)
+    s, t, cycles = 640, 1200, 12
+    rows = distributions(rng, s, t)
+    with pkg.Handle(0) as live, pkg.Handle(0) as replay:
+        for h in (live, replay):
+            h.ring_create(s, t)
+            h.ring_load(0, rows[:, : t - 7])
+        snap = {k: np.ascontiguousarray(v) for k, v in pkg.synth.cluster_snapshot(2, 10, 20).items()}
+        begin, end = live.collect_pipeline(snap)
+        order, lock, stop = [], threading.Lock(), threading.Event()
+        errors = []
+
+        def pusher(seed):
+            r = np.random.default_rng(seed)
+            try:
+                while not stop.is_set():
+                    if r.random() < 0.2:
+                        v = (r.random(s) * 50).astype(np.float32)
+                        with lock:
+                            live.ring_ingest_tick(v)
+                            order.append(("tick", v))
+                    else:
+                        ids = r.choice(s, size=int(r.integers(1, 40)), replace=False).astype(np.int64)
+                        v = (r.random(ids.size) * 50).astype(np.float32)
+                        with lock:
+                            live.ring_ingest(ids, v)
+                            order.append(("push", ids, v))
+            except Exception as e:  # noqa: BLE001
+                errors.append(repr(e))
+
+        threads = [threading.Thread(target=pusher, args=(k,)) for k in range(3)]
+        got = []
+        ticks = [(rng.random(s) * 100).astype(np.float32) for _ in range(cycles)]
+        with lock:
+            begin(ticks[0]); order.append(("cycle", 0))
+        for th in threads:
+            th.start()
+        for i in range(1, cycles):
+            with lock:
+                begin(ticks[i]); order.append(("cycle", i))
+            res = end()
+            got.append({k: res[k].copy() for k in ("min", "max", "mean", "p95")})
+        stop.set()
+        for th in threads:
+            th.join()
+        res = end()
+        got.append({k: res[k].copy() for k in ("min", "max", "mean", "p95")})
+        assert not errors, errors[:2]
+        assert sum(1 for o in order if o[0] != "cycle") > 20, "the pushers never ran"
+        final = live.ring_stats()            # idle again: applies what was pushed after the last begin
+        # replay the recorded order synchronously
+        want = []
+        for o in order:
+            if o[0] == "tick":
+                replay.ring_ingest_tick(o[1])
+            elif o[0] == "push":
+                replay.ring_ingest(o[1], o[2])
+            else:
+                replay.ring_ingest_tick(ticks[o[1]])
+                want.append(replay.ring_stats())
+        for i, (g, w) in enumerate(zip(got, want)):
+            for k in ("min", "max", "mean", "p95"):
+                assert np.array_equal(g[k], w[k]), (i, k)
+        want_final = replay.ring_stats()
+        for k in ("min", "max", "mean", "p95"):
+            assert np.array_equal(final[k], want_final[k]), k
