@@ -68,6 +68,24 @@ extern "C" {
 #define KLM_ISSUE_HIGH_CPU 0x2u
 #define KLM_ISSUE_HIGH_MEMORY 0x4u
 
+/* node condition types and statuses for klm_node_health (corev1.NodeConditionType /
+ * ConditionStatus as node_metrics.go:145-163 tests them) */
+#define KLM_COND_READY 0
+#define KLM_COND_MEMORY_PRESSURE 1
+#define KLM_COND_DISK_PRESSURE 2
+#define KLM_COND_PID_PRESSURE 3
+#define KLM_COND_NETWORK_UNAVAILABLE 4
+#define KLM_COND_OTHER 5
+#define KLM_COND_FALSE 0
+#define KLM_COND_TRUE 1
+#define KLM_COND_UNKNOWN 2
+/* NetworkMetrics.GetQuality (types.go:187-199) */
+#define KLM_QUALITY_DISCONNECTED 0
+#define KLM_QUALITY_EXCELLENT 1
+#define KLM_QUALITY_GOOD 2
+#define KLM_QUALITY_FAIR 3
+#define KLM_QUALITY_POOR 4
+
 typedef struct klm_handle klm_handle;
 
 /* Columns of the node snapshot that calculateClusterMetrics reads
@@ -200,6 +218,32 @@ int klm_pod_rates(klm_handle* h, int64_t n_pods, const int32_t* ctr_off,
                   const int64_t* ctr_memory_limit, int64_t* pod_totals,
                   double* cpu_rate, double* memory_rate, double* cpu_util,
                   double* memory_util, uint8_t* over_limit);
+
+/* NodeMetrics.GetAvailableResources (pkg/metrics/types.go:151-156): free CPU cores
+ * (millicores / 1000), memory and disk in GiB (/ 1024 / 1024 / 1024, left to right).
+ * disk_capacity / disk_usage may be NULL (0); any output may be NULL. */
+int klm_node_available(klm_handle* h, int64_t n_nodes, const int64_t* cpu_capacity,
+                       const int64_t* cpu_usage, const int64_t* memory_capacity,
+                       const int64_t* memory_usage, const int64_t* disk_capacity,
+                       const int64_t* disk_usage, double* cpu_cores, double* memory_gb,
+                       double* disk_gb);
+/* NetworkMetrics.GetQuality (pkg/metrics/types.go:187-199): KLM_QUALITY_* per probe
+ * from Connected and RTT (ms): < 10 excellent, < 50 good, < 100 fair, else poor. */
+int klm_network_quality(klm_handle* h, int64_t n, const uint8_t* connected,
+                        const double* rtt_ms, uint8_t* quality);
+/* Pod restart count (sources/pod_metrics.go:174-177): the sum of RestartCount over the
+ * pod's container statuses, rows st_off[p]..st_off[p+1] of restart_count; int32 that
+ * wraps as Go's does. */
+int klm_pod_restarts(klm_handle* h, int64_t n_pods, const int32_t* st_off,
+                     const int32_t* restart_count, int32_t* restarts);
+/* Node health from conditions (sources/node_metrics.go:142-164): node i's conditions are
+ * rows cond_off[i]..cond_off[i+1] of cond_type (KLM_COND_*) / cond_status. healthy[i] = 0
+ * if Ready is not True or a pressure / network-unavailable condition is True; failing[i]
+ * has bit t set for every condition type t that did it (the host formats the
+ * "NotReady: ..." strings from it). Either output may be NULL. */
+int klm_node_health(klm_handle* h, int64_t n_nodes, const int32_t* cond_off,
+                    const uint8_t* cond_type, const uint8_t* cond_status,
+                    uint8_t* healthy, uint8_t* failing);
 
 /* Fleet scans of sources/uav_metrics.go:197-233: number of UAVs whose
  * Health.SystemStatus == "OK" (status_ok[i] != 0), and the indices, in
@@ -453,6 +497,20 @@ int klm_dev_pod_rates(int64_t n_pods, const int32_t* ctr_off,
                       const int64_t* ctr_memory_limit, int64_t* pod_totals,
                       double* cpu_rate, double* memory_rate, double* cpu_util,
                       double* memory_util, uint8_t* over_limit, void* stream);
+/* Device-pointer forms of klm_node_available / klm_network_quality / klm_pod_restarts /
+ * klm_node_health; same arithmetic. */
+int klm_dev_node_available(int64_t n_nodes, const int64_t* cpu_capacity,
+                           const int64_t* cpu_usage, const int64_t* memory_capacity,
+                           const int64_t* memory_usage, const int64_t* disk_capacity,
+                           const int64_t* disk_usage, double* cpu_cores,
+                           double* memory_gb, double* disk_gb, void* stream);
+int klm_dev_network_quality(int64_t n, const uint8_t* connected, const double* rtt_ms,
+                            uint8_t* quality, void* stream);
+int klm_dev_pod_restarts(int64_t n_pods, const int32_t* st_off,
+                         const int32_t* restart_count, int32_t* restarts, void* stream);
+int klm_dev_node_health(int64_t n_nodes, const int32_t* cond_off, const uint8_t* cond_type,
+                        const uint8_t* cond_status, uint8_t* healthy, uint8_t* failing,
+                        void* stream);
 /* counters[0] = healthy count, counters[1] = n_low; both are overwritten by
  * the call. low_idx is written in ascending order. */
 int64_t klm_dev_fleet_scan_scratch_bytes(int64_t n);

@@ -94,6 +94,14 @@ SIGNATURES = {
     "klm_node_rates": (C.c_int, [_P, _I64] + [_P] * 11),
     "klm_pod_rates": (C.c_int, [_P, _I64] + [_P] * 13),
     "klm_fleet_scan": (C.c_int, [_P, _I64, _P, _P, _F64, C.POINTER(_I64), _P, C.POINTER(_I64)]),
+    "klm_node_available": (C.c_int, [_P, _I64] + [_P] * 9),
+    "klm_network_quality": (C.c_int, [_P, _I64, _P, _P, _P]),
+    "klm_pod_restarts": (C.c_int, [_P, _I64, _P, _P, _P]),
+    "klm_node_health": (C.c_int, [_P, _I64, _P, _P, _P, _P, _P]),
+    "klm_dev_node_available": (C.c_int, [_I64] + [_P] * 10),
+    "klm_dev_network_quality": (C.c_int, [_I64, _P, _P, _P, _P]),
+    "klm_dev_pod_restarts": (C.c_int, [_I64, _P, _P, _P, _P]),
+    "klm_dev_node_health": (C.c_int, [_I64, _P, _P, _P, _P, _P, _P]),
     "klm_ring_create": (C.c_int, [_P, _I64, _I32]),
     "klm_ring_ingest": (C.c_int, [_P, _I64, _P, _P]),
     "klm_ring_ingest_tick": (C.c_int, [_P, _P]),
@@ -255,6 +263,38 @@ class Handle:
         check(self._lib.klm_reconcile(self._h, b.size, _ptr(b), _ptr(f), r, _ptr(mb), _ptr(off), _ptr(ids),
                                       _ptr(out_idx), _ptr(out_score), algo))
         return out_idx, out_score
+
+    # -- element-wise leftovers (types.go:151-156, :187-199; pod_metrics.go:174-177; node_metrics.go:142-164)
+    def node_available(self, cpu_capacity, cpu_usage, memory_capacity, memory_usage, disk_capacity, disk_usage):
+        a = [_np(x, np.int64) for x in (cpu_capacity, cpu_usage, memory_capacity, memory_usage, disk_capacity,
+                                        disk_usage)]
+        n = a[0].size
+        out = [np.empty(n), np.empty(n), np.empty(n)]
+        check(self._lib.klm_node_available(self._h, n, *[_ptr(x) for x in a], *[_ptr(o) for o in out]))
+        return out
+
+    def network_quality(self, connected, rtt_ms) -> np.ndarray:
+        c, r = _np(connected, np.uint8), _np(rtt_ms, np.float64)
+        q = np.empty(c.size, np.uint8)
+        check(self._lib.klm_network_quality(self._h, c.size, _ptr(c), _ptr(r), _ptr(q)))
+        return q
+
+    def pod_restarts(self, st_off, restart_count) -> np.ndarray:
+        off, cnt = _np(st_off, np.int32), _np(restart_count, np.int32)
+        out = np.empty(off.size - 1, np.int32)
+        if cnt.size == 0:
+            cnt = np.zeros(1, np.int32)
+        check(self._lib.klm_pod_restarts(self._h, out.size, _ptr(off), _ptr(cnt), _ptr(out)))
+        return out
+
+    def node_health(self, cond_off, cond_type, cond_status):
+        off, t, s = _np(cond_off, np.int32), _np(cond_type, np.uint8), _np(cond_status, np.uint8)
+        n = off.size - 1
+        healthy, failing = np.empty(n, np.uint8), np.empty(n, np.uint8)
+        if t.size == 0:
+            t, s = np.zeros(1, np.uint8), np.zeros(1, np.uint8)
+        check(self._lib.klm_node_health(self._h, n, _ptr(off), _ptr(t), _ptr(s), _ptr(healthy), _ptr(failing)))
+        return healthy, failing
 
     # -- aggregation (manager.go:493-565)
     def cluster_aggregate(self, cpu_capacity, cpu_usage, memory_capacity, memory_usage, gpu_count,

@@ -1114,6 +1114,128 @@ extern "C" int klm_fleet_scan(klm_handle* h, int64_t n, const uint8_t* status_ok
   return KLM_OK;
 }
 
+
+// ------------------------------------------------ element-wise leftovers (A8 / A10)
+
+namespace {
+// upload `bytes` of src into blk at off (256-aligned parts); returns the device pointer or NULL
+template <typename T>
+const T* up(klm_handle* h, char* blk, size_t& off, const T* src, size_t count, int* rc) {
+  if (!src || count == 0 || *rc != KLM_OK) return nullptr;
+  char* d = blk + off;
+  off += align256(count * sizeof(T));
+  *rc = h2d(d, src, count * sizeof(T), h->stream);
+  return reinterpret_cast<const T*>(d);
+}
+}  // namespace
+
+extern "C" int klm_node_available(klm_handle* h, int64_t n, const int64_t* cpu_cap, const int64_t* cpu_use,
+                                  const int64_t* mem_cap, const int64_t* mem_use, const int64_t* disk_cap,
+                                  const int64_t* disk_use, double* cpu_cores, double* mem_gb, double* disk_gb) {
+  KLM_ENTER(h);
+  if (n < 0 || (n > 0 && ((cpu_cores && (!cpu_cap || !cpu_use)) || (mem_gb && (!mem_cap || !mem_use))))) {
+    set_error("klm_node_available: bad argument");
+    return KLM_EINVAL;
+  }
+  if (n == 0) return KLM_OK;
+  const size_t col = align256((size_t)n * 8);
+  KLM_TRY(h->rate_in.ensure(6 * col));
+  KLM_TRY(h->rate_out.ensure(3 * col));
+  size_t off = 0;
+  int rc = KLM_OK;
+  char* in = h->rate_in.as<char>();
+  const int64_t* d[6];
+  const int64_t* src[6] = {cpu_cap, cpu_use, mem_cap, mem_use, disk_cap, disk_use};
+  for (int k = 0; k < 6; ++k) d[k] = up(h, in, off, src[k], (size_t)n, &rc);
+  KLM_TRY(rc);
+  double* o = h->rate_out.as<double>();
+  double* o1 = reinterpret_cast<double*>(h->rate_out.as<char>() + col);
+  double* o2 = reinterpret_cast<double*>(h->rate_out.as<char>() + 2 * col);
+  KLM_TRY(klm_dev_node_available(n, d[0], d[1], d[2], d[3], d[4], d[5], cpu_cores ? o : nullptr,
+                                 mem_gb ? o1 : nullptr, disk_gb ? o2 : nullptr, h->stream));
+  if (cpu_cores) KLM_TRY(d2h(cpu_cores, o, (size_t)n * 8, h->stream));
+  if (mem_gb) KLM_TRY(d2h(mem_gb, o1, (size_t)n * 8, h->stream));
+  if (disk_gb) KLM_TRY(d2h(disk_gb, o2, (size_t)n * 8, h->stream));
+  return sync(h->stream);
+}
+
+extern "C" int klm_network_quality(klm_handle* h, int64_t n, const uint8_t* connected, const double* rtt,
+                                   uint8_t* quality) {
+  KLM_ENTER(h);
+  if (n < 0 || (n > 0 && (!connected || !rtt || !quality))) {
+    set_error("klm_network_quality: bad argument");
+    return KLM_EINVAL;
+  }
+  if (n == 0) return KLM_OK;
+  KLM_TRY(h->rate_in.ensure(align256((size_t)n * 8) + align256((size_t)n)));
+  KLM_TRY(h->rate_out.ensure((size_t)n));
+  size_t off = 0;
+  int rc = KLM_OK;
+  char* in = h->rate_in.as<char>();
+  const double* d_rtt = up(h, in, off, rtt, (size_t)n, &rc);
+  const uint8_t* d_con = up(h, in, off, connected, (size_t)n, &rc);
+  KLM_TRY(rc);
+  KLM_TRY(klm_dev_network_quality(n, d_con, d_rtt, h->rate_out.as<uint8_t>(), h->stream));
+  KLM_TRY(d2h(quality, h->rate_out.p, (size_t)n, h->stream));
+  return sync(h->stream);
+}
+
+extern "C" int klm_pod_restarts(klm_handle* h, int64_t n_pods, const int32_t* st_off,
+                                const int32_t* restart_count, int32_t* restarts) {
+  KLM_ENTER(h);
+  if (n_pods < 0 || (n_pods > 0 && (!st_off || !restarts))) {
+    set_error("klm_pod_restarts: bad argument");
+    return KLM_EINVAL;
+  }
+  if (n_pods == 0) return KLM_OK;
+  const int64_t n_st = st_off[n_pods];
+  if (st_off[0] != 0 || n_st < 0 || (n_st > 0 && !restart_count) || !csr_non_decreasing(st_off, n_pods)) {
+    set_error("klm_pod_restarts: st_off must start at 0 and not decrease; restart_count non-null");
+    return KLM_EINVAL;
+  }
+  KLM_TRY(h->rate_in.ensure(align256((size_t)(n_pods + 1) * 4) + align256((size_t)n_st * 4) + 256));
+  KLM_TRY(h->rate_out.ensure((size_t)n_pods * 4));
+  size_t off = 0;
+  int rc = KLM_OK;
+  char* in = h->rate_in.as<char>();
+  const int32_t* d_off = up(h, in, off, st_off, (size_t)n_pods + 1, &rc);
+  const int32_t* d_cnt = up(h, in, off, restart_count, (size_t)n_st, &rc);
+  KLM_TRY(rc);
+  KLM_TRY(klm_dev_pod_restarts(n_pods, d_off, d_cnt, h->rate_out.as<int32_t>(), h->stream));
+  KLM_TRY(d2h(restarts, h->rate_out.p, (size_t)n_pods * 4, h->stream));
+  return sync(h->stream);
+}
+
+extern "C" int klm_node_health(klm_handle* h, int64_t n, const int32_t* cond_off, const uint8_t* cond_type,
+                               const uint8_t* cond_status, uint8_t* healthy, uint8_t* failing) {
+  KLM_ENTER(h);
+  if (n < 0 || (n > 0 && !cond_off)) {
+    set_error("klm_node_health: bad argument");
+    return KLM_EINVAL;
+  }
+  if (n == 0) return KLM_OK;
+  const int64_t nc = cond_off[n];
+  if (cond_off[0] != 0 || nc < 0 || (nc > 0 && (!cond_type || !cond_status)) || !csr_non_decreasing(cond_off, n)) {
+    set_error("klm_node_health: cond_off must start at 0 and not decrease; condition columns non-null");
+    return KLM_EINVAL;
+  }
+  KLM_TRY(h->rate_in.ensure(align256((size_t)(n + 1) * 4) + 2 * align256((size_t)nc) + 256));
+  KLM_TRY(h->rate_out.ensure(2 * align256((size_t)n)));
+  size_t off = 0;
+  int rc = KLM_OK;
+  char* in = h->rate_in.as<char>();
+  const int32_t* d_off = up(h, in, off, cond_off, (size_t)n + 1, &rc);
+  const uint8_t* d_t = up(h, in, off, cond_type, (size_t)nc, &rc);
+  const uint8_t* d_s = up(h, in, off, cond_status, (size_t)nc, &rc);
+  KLM_TRY(rc);
+  uint8_t* o_h = h->rate_out.as<uint8_t>();
+  uint8_t* o_f = o_h + align256((size_t)n);
+  KLM_TRY(klm_dev_node_health(n, d_off, d_t, d_s, o_h, o_f, h->stream));
+  if (healthy) KLM_TRY(d2h(healthy, o_h, (size_t)n, h->stream));
+  if (failing) KLM_TRY(d2h(failing, o_f, (size_t)n, h->stream));
+  return sync(h->stream);
+}
+
 // ------------------------------------------------------------------ ring
 
 extern "C" int klm_ring_create(klm_handle* h, int64_t n_series, int32_t window) {

@@ -335,6 +335,40 @@ KLMO_API void klmo_pod_rates(int64_t n_pods, const int32_t* ctr_off,
   }
 }
 
+/* Pod restart count, internal/metrics/sources/pod_metrics.go:174-177:
+ *   var restarts int32; for each containerStatus: restarts += RestartCount
+ * (int32 that wraps). st_off is the CSR over a pod's container statuses. */
+KLMO_API void klmo_pod_restarts(int64_t n_pods, const int32_t* st_off,
+                                const int32_t* restart_count, int32_t* restarts) {
+  for (int64_t p = 0; p < n_pods; ++p) {
+    uint32_t acc = 0;
+    for (int32_t c = st_off[p]; c < st_off[p + 1]; ++c) acc += (uint32_t)restart_count[c];
+    restarts[p] = (int32_t)acc;
+  }
+}
+
+/* Node health from conditions, internal/metrics/sources/node_metrics.go:142-164.
+ * type: 0 Ready, 1 MemoryPressure, 2 DiskPressure, 3 PIDPressure, 4 NetworkUnavailable,
+ * 5 anything else; status: 0 False, 1 True, 2 Unknown. failing: bit per type that made the
+ * node unhealthy. */
+KLMO_API void klmo_node_health(int64_t n, const int32_t* cond_off, const uint8_t* cond_type,
+                               const uint8_t* cond_status, uint8_t* healthy, uint8_t* failing) {
+  for (int64_t i = 0; i < n; ++i) {
+    int ok = 1;                                               /* :143 healthy := true */
+    unsigned bad = 0;
+    for (int32_t c = cond_off[i]; c < cond_off[i + 1]; ++c) { /* :145 */
+      const unsigned t = cond_type[c], st = cond_status[c];
+      if (t == 0) {                                           /* :147 NodeReady */
+        if (st != 1) { ok = 0; bad |= 1u; }                   /* :148-151 */
+      } else if (st == 1) {                                   /* :154 */
+        if (t == 1 || t == 2 || t == 3 || t == 4) { ok = 0; bad |= 1u << t; }  /* :155-161 */
+      }
+    }
+    healthy[i] = (uint8_t)ok;
+    failing[i] = (uint8_t)bad;
+  }
+}
+
 /* NetworkMetrics.GetQuality, pkg/metrics/types.go:187-199:
  * 0 disconnected, 1 excellent, 2 good, 3 fair, 4 poor. */
 KLMO_API void klmo_network_quality(int64_t n, const uint8_t* connected,

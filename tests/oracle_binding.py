@@ -153,3 +153,41 @@ def window_stats(ring, seen, window, pitch=None, s0=0, s1=None, fast=False, thre
     f.restype = C.c_int
     assert f(*args) == 0
     return out
+
+
+def node_available(cpu_cap, cpu_use, mem_cap, mem_use, disk_cap, disk_use):
+    a = [_a(x, np.int64) for x in (cpu_cap, cpu_use, mem_cap, mem_use, disk_cap, disk_use)]
+    n = a[0].size
+    out = [np.empty(n), np.empty(n), np.empty(n)]
+    f = lib().klmo_node_available
+    f.restype = None
+    f(C.c_int64(n), *[_p(x) for x in a], *[_p(v) for v in out])
+    return out
+
+
+def network_quality(connected, rtt):
+    c, r = _a(connected, np.uint8), _a(rtt, np.float64)
+    q = np.empty(c.size, np.uint8)
+    f = lib().klmo_network_quality
+    f.restype = None
+    f(C.c_int64(c.size), _p(c), _p(r), _p(q))
+    return q
+
+
+def pod_restarts(st_off, restart_count):
+    off, cnt = _a(st_off, np.int32), _a(restart_count, np.int32)
+    out = np.empty(off.size - 1, np.int32)
+    f = lib().klmo_pod_restarts
+    f.restype = None
+    f(C.c_int64(out.size), _p(off), _p(cnt), _p(out))
+    return out
+
+
+def node_health(cond_off, cond_type, cond_status):
+    off, t, s = _a(cond_off, np.int32), _a(cond_type, np.uint8), _a(cond_status, np.uint8)
+    n = off.size - 1
+    healthy, failing = np.empty(n, np.uint8), np.empty(n, np.uint8)
+    f = lib().klmo_node_health
+    f.restype = None
+    f(C.c_int64(n), _p(off), _p(t), _p(s), _p(healthy), _p(failing))
+    return healthy, failing

@@ -92,3 +92,39 @@ def test_fleet_scan(handle, pkg, n):
         h, low = handle.fleet_scan(ok, pct, thr)
         wh, wlow = ob.fleet_scan(ok, pct, thr)
         assert h == wh and np.array_equal(low, wlow)
+
+
+@pytest.mark.parametrize("n", [1, 257, 100_003])
+def test_available_quality_restarts_health(handle, n):
+    """GetAvailableResources / GetQuality (types.go:151-156, :187-199), the pod restart sum
+    (pod_metrics.go:174-177) and node health from conditions (node_metrics.go:142-164): bit-exact
+    against the oracle, including the band edges, an int32 sum that wraps, and nodes without
+    conditions."""
+    rng = np.random.default_rng(n)
+    cap = rng.integers(1, 2**40, size=(3, n))
+    use = (cap * rng.random((3, n)) * 1.1).astype(np.int64)   # sometimes above capacity: negative free
+    got = handle.node_available(cap[0], use[0], cap[1], use[1], cap[2], use[2])
+    want = ob.node_available(cap[0], use[0], cap[1], use[1], cap[2], use[2])
+    for g, w in zip(got, want):
+        assert np.array_equal(g.view(np.uint64), w.view(np.uint64))
+    rtt = rng.choice([0.0, 9.999, 10.0, 49.99, 50.0, 99.9, 100.0, 1e6, -1.0], size=n) + rng.random(n) * 1e-9
+    rtt[: min(n, 7)] = [10.0, 50.0, 100.0, 9.0, 49.0, 99.0, 0.0][: min(n, 7)]
+    con = (rng.random(n) < 0.9).astype(np.uint8)
+    assert np.array_equal(handle.network_quality(con, rtt), ob.network_quality(con, rtt))
+    k = rng.integers(0, 5, size=n)
+    off = np.zeros(n + 1, np.int32)
+    off[1:] = np.cumsum(k)
+    cnt = rng.integers(0, 50, size=int(off[-1])).astype(np.int32)
+    if cnt.size >= 2:
+        cnt[:2] = 2**31 - 1                                   # wraps like Go's int32
+    assert np.array_equal(handle.pod_restarts(off, cnt), ob.pod_restarts(off, cnt))
+    kc = rng.integers(0, 7, size=n)
+    coff = np.zeros(n + 1, np.int32)
+    coff[1:] = np.cumsum(kc)
+    ctype = rng.integers(0, 6, size=int(coff[-1])).astype(np.uint8)
+    cstat = rng.choice([0, 1, 1, 1, 2], size=int(coff[-1])).astype(np.uint8)
+    cstat[ctype != 0] = rng.choice([0, 0, 0, 0, 1, 2], size=int((ctype != 0).sum())).astype(np.uint8)
+    gh, gf = handle.node_health(coff, ctype, cstat)
+    wh, wf = ob.node_health(coff, ctype, cstat)
+    assert np.array_equal(gh, wh) and np.array_equal(gf, wf)
+    assert 0 < gh.sum() < n or n < 10

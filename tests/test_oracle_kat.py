@@ -189,3 +189,20 @@ def test_ring_ingest_wraps():
     assert ring[0].tolist() == [4, 5, 2, 3] and seen.tolist() == [6, 6, 6]
     ob.ring_ingest(ring, seen, 4, np.array([99], np.float32), series_ids=[2])
     assert ring[2].tolist() == [24, 25, 99, 23] and seen.tolist() == [6, 6, 7]
+
+
+def test_predicate_leftovers_hand_derived():
+    """Known answers derived by hand from pkg/metrics/types.go:151-156 and :187-199,
+    sources/pod_metrics.go:174-177 and sources/node_metrics.go:142-164 (derived, not
+    reference-pinned: the reference has no tests)."""
+    import oracle_binding as ob
+    cores, mem, disk = ob.node_available([4000], [1500], [8 * 2**30], [2 * 2**30], [100 * 2**30], [25 * 2**30])
+    assert (cores[0], mem[0], disk[0]) == (2.5, 6.0, 75.0)
+    # disconnected, excellent (< 10), good (10 is not < 10), good, fair (50 is not < 50), poor
+    assert list(ob.network_quality([0, 1, 1, 1, 1, 1], [1, 9.9, 10, 49.9, 50, 100])) == [0, 1, 2, 2, 3, 4]
+    assert list(ob.pod_restarts([0, 2, 2, 3], [1, 2, 7])) == [3, 0, 7]
+    assert list(ob.pod_restarts([0, 2], [2**31 - 1, 1])) == [-2**31]            # int32 wraps
+    # node 0: Ready=True; node 1: Ready=True + MemoryPressure=True; node 2: no conditions;
+    # node 3: Ready=Unknown + an unrelated condition that is True
+    healthy, failing = ob.node_health([0, 1, 3, 3, 5], [0, 0, 1, 0, 5], [1, 1, 1, 2, 1])
+    assert list(healthy) == [1, 0, 1, 0] and list(failing) == [0, 2, 0, 1]
