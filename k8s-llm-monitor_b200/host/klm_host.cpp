@@ -1,4 +1,6 @@
 #include "klm_host.h"
+#include "klm_wire.h"
+#include <algorithm>
 
 #include <cstdio>
 #include <stdexcept>
@@ -139,6 +141,42 @@ ClusterMetrics Manager::CalculateClusterMetrics(const std::vector<NodeMetrics>& 
   static const char* kStatus[] = {"healthy", "warning", "critical"};                 // :558-564
   m.HealthStatus = kStatus[o.health_status];
   return m;
+}
+
+void Manager::EnableUAVRing(int64_t max_nodes, int32_t window) {
+  check(klm_ring_create(h_, max_nodes * kUAVChannels, window), "klm_ring_create");
+  ring_nodes_ = max_nodes;
+}
+
+int64_t Manager::UpdateUAVReport(UAVReport report, const std::string& now_rfc3339) {
+  if (!ApplyUAVReportDefaults(report, now_rfc3339)) return -1;  // manager.go:392-409
+  // m.uavSnapshot[report.NodeName] = entry (:437-442): one entry per node name
+  auto it = std::lower_bound(uav_index_.begin(), uav_index_.end(), report.NodeName,
+                             [](const std::pair<std::string, int64_t>& a, const std::string& k) { return a.first < k; });
+  int64_t idx;
+  if (it != uav_index_.end() && it->first == report.NodeName) {
+    idx = it->second;
+  } else {
+    idx = static_cast<int64_t>(uav_.size());
+    uav_index_.insert(it, {report.NodeName, idx});
+    uav_.emplace_back();
+  }
+  UAVEntry& e = uav_[static_cast<size_t>(idx)];
+  e.NodeName = report.NodeName; e.UAVID = report.UAVID; e.Status = report.Status; e.Source = report.Source;
+  e.Timestamp = report.Timestamp; e.LastHeartbeat = report.Timestamp;   // :417-418, :445
+  e.NodeIP = report.NodeIP;                                              // :420-422
+  e.HeartbeatIntervalSeconds = report.HeartbeatIntervalSeconds > 0 ? report.HeartbeatIntervalSeconds : 0;  // :424-426
+  e.HasState = report.HasState;                                          // :432-435
+  if (report.HasState) {
+    e.RemainingPercent = report.RemainingPercent;
+    e.SystemStatus = report.SystemStatus;
+    if (idx < ring_nodes_) {
+      int64_t ids[kUAVChannels];
+      for (int c = 0; c < kUAVChannels; ++c) ids[c] = idx * kUAVChannels + c;
+      check(klm_ring_ingest(h_, kUAVChannels, ids, report.Channels), "klm_ring_ingest");
+    }
+  }
+  return idx;
 }
 
 static void fleet_columns(const std::vector<UAVHealth>& fleet, std::vector<uint8_t>& ok,

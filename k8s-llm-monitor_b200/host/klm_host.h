@@ -12,6 +12,7 @@
 
 #include <cstdint>
 #include <string>
+#include <utility>
 #include <vector>
 
 #include "../../include/klm.h"
@@ -94,10 +95,29 @@ struct UAVHealth {
   double RemainingPercent = 0;
 };
 
+// What Manager.UpdateUAVReport keeps per node (the map entry of manager.go:411-435).
+struct UAVEntry {
+  std::string NodeName, UAVID, Status, Source, Timestamp, LastHeartbeat, NodeIP, SystemStatus;
+  int64_t HeartbeatIntervalSeconds = 0;
+  bool HasState = false;
+  double RemainingPercent = 0;  // state.battery.remaining_percent: the battery the scheduler scores
+};
+struct UAVReport;  // klm_wire.h
+
 // internal/metrics/manager.go Manager: the aggregation half.
 class Manager {
  public:
   explicit Manager(klm_handle* h) : h_(h) {}
+  // The 64-channel metric ring behind UpdateUAVReport: room for max_nodes UAV nodes (series
+  // node * 64 + channel), `window` samples each. No reference counterpart (F5: the reference keeps
+  // only the latest state).
+  void EnableUAVRing(int64_t max_nodes, int32_t window);
+  // manager.go:391-449: defaulting, latest entry per node, last heartbeat; and -- new -- the
+  // state's 64 channels appended to the node's ring rows (klm_ring_ingest; queued by the library
+  // while collect cycles are in flight). Returns the node's index (first-seen order), or -1 when
+  // the report is dropped (nil / empty node_name, :392-394).
+  int64_t UpdateUAVReport(UAVReport report, const std::string& now_rfc3339);
+  const std::vector<UAVEntry>& UAVSnapshot() const { return uav_; }
   // manager.go:493-565
   ClusterMetrics CalculateClusterMetrics(const std::vector<NodeMetrics>& nodes,
                                          const std::vector<PodMetrics>& pods);
@@ -108,6 +128,10 @@ class Manager {
 
  private:
   klm_handle* h_;
+  std::vector<UAVEntry> uav_;            // m.uavSnapshot, in first-seen order
+  std::vector<std::string> uav_names_;   // index -> node name (lookup is linear over a sorted copy below)
+  std::vector<std::pair<std::string, int64_t>> uav_index_;  // sorted by name
+  int64_t ring_nodes_ = 0;
 };
 
 }  // namespace klmhost

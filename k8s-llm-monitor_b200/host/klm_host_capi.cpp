@@ -11,7 +11,7 @@ using namespace klmhost;
 
 namespace {
 struct Session {
-  explicit Session(klm_handle* handle) : h(handle) {}
+  explicit Session(klm_handle* handle) : h(handle), uav_manager(handle) {}
   klm_handle* h;
   std::vector<UAVMetricItem> uavs;
   std::vector<SchedulingRequest> requests;
@@ -20,6 +20,7 @@ struct Session {
   std::vector<PodMetrics> pods;
   std::vector<UAVHealth> fleet;
   ClusterMetrics cluster;
+  Manager uav_manager{nullptr};   // the UAV ingestion half (UpdateUAVReport) keeps state between calls
   std::vector<std::string> names;
   std::string error;
 };
@@ -114,6 +115,46 @@ int klmh_status_json(void* sv, int i, const char* last_updated, char* dst, int c
 
 // a float64 in Go's encoding/json form (what EncodeStatus writes for `score`)
 void klmh_format_float(double v, char* dst, int cap) { put(dst, cap, FormatJSONFloat(v)); }
+
+// decode one UAVReport (models.go:182-192) and flatten its state: out64 gets the 64 channels.
+// Returns 1 with state, 0 without, -1 on a decode error (klmh_error).
+int klmh_report_decode(void* sv, const char* json, float* out64, char* node, char* status, char* source,
+                       double* remaining_percent, int cap) {
+  Session* s = static_cast<Session*>(sv);
+  try {
+    UAVReport r = DecodeUAVReport(json);
+    const bool kept = ApplyUAVReportDefaults(r, "now");
+    for (int c = 0; c < kUAVChannels; ++c) out64[c] = r.Channels[c];
+    put(node, cap, kept ? r.NodeName : "");
+    put(status, cap, r.Status);
+    put(source, cap, r.Source);
+    if (remaining_percent) *remaining_percent = r.RemainingPercent;
+    return r.HasState ? 1 : 0;
+  } catch (const std::exception& e) { s->error = e.what(); return -1; }
+}
+int klmh_enable_uav_ring(void* sv, int64_t max_nodes, int window) {
+  Session* s = static_cast<Session*>(sv);
+  try { s->uav_manager.EnableUAVRing(max_nodes, window); }
+  catch (const std::exception& e) { s->error = e.what(); return -1; }
+  return 0;
+}
+// Manager.UpdateUAVReport on a JSON report: node index, -1 dropped, -2 error
+int64_t klmh_update_uav_report(void* sv, const char* json, const char* now) {
+  Session* s = static_cast<Session*>(sv);
+  try { return s->uav_manager.UpdateUAVReport(DecodeUAVReport(json), now ? now : ""); }
+  catch (const std::exception& e) { s->error = e.what(); return -2; }
+}
+// entry i of the UAV snapshot: battery, status, last heartbeat
+int klmh_uav_entry(void* sv, int64_t i, double* remaining_percent, char* node, char* status, char* heartbeat, int cap) {
+  Session* s = static_cast<Session*>(sv);
+  const auto& snap = s->uav_manager.UAVSnapshot();
+  if (i < 0 || i >= static_cast<int64_t>(snap.size())) return -1;
+  if (remaining_percent) *remaining_percent = snap[i].RemainingPercent;
+  put(node, cap, snap[i].NodeName);
+  put(status, cap, snap[i].Status);
+  put(heartbeat, cap, snap[i].LastHeartbeat);
+  return snap[i].HasState ? 1 : 0;
+}
 
 int klmh_reconcile(void* sv) {
   Session* s = static_cast<Session*>(sv);

@@ -3,6 +3,7 @@
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
+#include <initializer_list>
 #include <map>
 #include <memory>
 #include <stdexcept>
@@ -229,6 +230,112 @@ std::vector<SchedulingRequest> DecodeSchedulingRequestList(const std::string& js
     out.push_back(q);
   }
   return out;
+}
+
+// ---------------------------------------------------------------- UAVReport (A11)
+
+namespace {
+[[noreturn]] void bad_type(const char* field, const char* want) {
+  throw std::runtime_error(std::string("JSON: cannot unmarshal field ") + field + " (want " + want + ")");
+}
+std::string str_field(const JValue* o, const char* k) {
+  const JValue* v = o ? o->get(k) : nullptr;
+  if (!v || v->kind == JValue::Null) return "";
+  if (v->kind != JValue::String) bad_type(k, "string");
+  return v->str;
+}
+double num_field(const JValue* o, const char* k) {  // float64 field: any JSON number
+  const JValue* v = o ? o->get(k) : nullptr;
+  if (!v || v->kind == JValue::Null) return 0.0;
+  if (v->kind != JValue::Int && v->kind != JValue::Float) bad_type(k, "number");
+  return v->num;
+}
+double int_field(const JValue* o, const char* k) {  // int field: Go rejects 3.5 and 1e2 alike
+  const JValue* v = o ? o->get(k) : nullptr;
+  if (!v || v->kind == JValue::Null) return 0.0;
+  if (v->kind != JValue::Int) bad_type(k, "integer");
+  return v->num;
+}
+double bool_field(const JValue* o, const char* k) {
+  const JValue* v = o ? o->get(k) : nullptr;
+  if (!v || v->kind == JValue::Null) return 0.0;
+  if (v->kind != JValue::Bool) bad_type(k, "bool");
+  return v->b ? 1.0 : 0.0;
+}
+const JValue* obj_field(const JValue* o, const char* k) {
+  const JValue* v = o ? o->get(k) : nullptr;
+  if (!v || v->kind == JValue::Null) return nullptr;
+  if (v->kind != JValue::Object) bad_type(k, "object");
+  return v;
+}
+double enum_code(const std::string& s, std::initializer_list<const char*> names) {
+  int i = 0;
+  for (const char* n : names) {
+    if (s == n) return i;
+    ++i;
+  }
+  return -1.0;
+}
+}  // namespace
+
+UAVReport DecodeUAVReport(const std::string& json) {
+  JPtr root = Parser(json).parse();
+  if (root->kind != JValue::Object) throw std::runtime_error("JSON: a UAVReport is an object");
+  const JValue* o = root.get();
+  UAVReport r;
+  r.NodeName = str_field(o, "node_name");     // models.go:183-187
+  r.NodeIP = str_field(o, "node_ip");
+  r.UAVID = str_field(o, "uav_id");
+  r.Source = str_field(o, "source");
+  r.Status = str_field(o, "status");
+  r.Timestamp = str_field(o, "timestamp");    // :188 (time.Time travels as RFC3339 text)
+  if (r.Timestamp == "0001-01-01T00:00:00Z") r.Timestamp.clear();  // Go's zero time
+  r.HeartbeatIntervalSeconds = static_cast<int64_t>(int_field(o, "heartbeat_interval_seconds"));  // :189
+  const JValue* st = obj_field(o, "state");   // :190 *uav.UAVState
+  if (!st) return r;
+  r.HasState = true;
+  float* c = r.Channels;
+  const JValue* gps = obj_field(st, "gps");   // mavlink_simulator.go:39-50
+  c[0] = (float)num_field(gps, "latitude"); c[1] = (float)num_field(gps, "longitude");
+  c[2] = (float)num_field(gps, "altitude"); c[3] = (float)num_field(gps, "relative_altitude");
+  c[4] = (float)num_field(gps, "hdop"); c[5] = (float)int_field(gps, "satellite_count");
+  c[6] = (float)int_field(gps, "fix_type"); c[7] = (float)num_field(gps, "ground_speed");
+  c[8] = (float)num_field(gps, "course_over_ground");
+  const JValue* at = obj_field(st, "attitude");  // :53-61
+  c[9] = (float)num_field(at, "roll"); c[10] = (float)num_field(at, "pitch"); c[11] = (float)num_field(at, "yaw");
+  c[12] = (float)num_field(at, "roll_rate"); c[13] = (float)num_field(at, "pitch_rate");
+  c[14] = (float)num_field(at, "yaw_rate");
+  const JValue* fl = obj_field(st, "flight");    // :64-72
+  c[15] = (float)num_field(fl, "airspeed"); c[16] = (float)num_field(fl, "ground_speed");
+  c[17] = (float)num_field(fl, "vertical_speed"); c[18] = (float)num_field(fl, "throttle_percent");
+  const JValue* bt = obj_field(st, "battery");   // :75-85
+  r.RemainingPercent = num_field(bt, "remaining_percent");
+  c[19] = (float)num_field(bt, "voltage"); c[20] = (float)num_field(bt, "current");
+  c[21] = (float)r.RemainingPercent; c[22] = (float)num_field(bt, "remaining_capacity");
+  c[23] = (float)num_field(bt, "total_capacity"); c[24] = (float)num_field(bt, "temperature");
+  c[25] = (float)int_field(bt, "cell_count"); c[26] = (float)int_field(bt, "time_remaining");
+  const JValue* ms = obj_field(st, "mission");   // :88-95
+  c[27] = (float)int_field(ms, "current_waypoint"); c[28] = (float)int_field(ms, "total_waypoints");
+  c[29] = (float)num_field(ms, "distance_to_wp"); c[30] = (float)int_field(ms, "eta_to_wp");
+  const JValue* he = obj_field(st, "health");    // :98-106
+  c[31] = (float)int_field(he, "error_count"); c[32] = (float)int_field(he, "warning_count");
+  c[33] = (float)bool_field(fl, "armed");
+  const JValue* sh = obj_field(he, "sensors_health");
+  static const char* kSensors[6] = {"accelerometer", "barometer", "battery", "compass", "gps", "gyroscope"};
+  for (int k = 0; k < 6; ++k) c[34 + k] = (float)bool_field(sh, kSensors[k]);
+  r.SystemStatus = str_field(he, "system_status");
+  c[40] = (float)enum_code(str_field(fl, "mode"), {"MANUAL", "STABILIZE", "LOITER", "AUTO", "RTL", "LAND"});
+  c[41] = (float)enum_code(str_field(ms, "mission_state"), {"IDLE", "ACTIVE", "PAUSED", "COMPLETED"});
+  c[42] = (float)enum_code(r.SystemStatus, {"OK", "WARNING", "CRITICAL", "ERROR"});
+  return r;
+}
+
+bool ApplyUAVReportDefaults(UAVReport& r, const std::string& now_rfc3339) {
+  if (r.NodeName.empty()) return false;                     // manager.go:392-394
+  if (r.Timestamp.empty()) r.Timestamp = now_rfc3339;       // :396-399
+  if (r.Status.empty()) r.Status = "active";                // :401-404
+  if (r.Source.empty()) r.Source = "agent";                 // :406-409
+  return true;
 }
 
 static std::string quote(const std::string& s) {

@@ -25,11 +25,13 @@ def load() -> C.CDLL:
         lib.klmh_error.restype = C.c_char_p
         lib.klmh_error.argtypes = [C.c_void_p]
         lib.klmh_healthy_uav_count.restype = C.c_int64
+        lib.klmh_update_uav_report.restype = C.c_int64
         for name in ("klmh_close", "klmh_clear", "klmh_add_uav", "klmh_add_request", "klmh_reconcile",
                      "klmh_status", "klmh_add_node", "klmh_add_pod", "klmh_calculate_cluster_metrics",
                      "klmh_issue", "klmh_add_fleet_uav", "klmh_healthy_uav_count", "klmh_low_battery_uavs",
                      "klmh_name", "klmh_load_uavs_json", "klmh_load_requests_json", "klmh_request_info",
-                     "klmh_uav_info", "klmh_status_json", "klmh_format_float"):
+                     "klmh_uav_info", "klmh_status_json", "klmh_format_float", "klmh_report_decode",
+                     "klmh_enable_uav_ring", "klmh_update_uav_report", "klmh_uav_entry"):
             getattr(lib, name)
         _lib = lib
     return _lib
@@ -105,6 +107,36 @@ class HostSession:
         buf = C.create_string_buffer(2048)
         self.lib.klmh_status_json(self.s, i, last_updated.encode(), buf, 2048)
         return buf.value.decode("utf-8")
+
+    # --- UAV push ingestion (manager.go:391-449; host/klm_wire.h UAVReport)
+    def report_decode(self, text: str) -> dict:
+        import numpy as np
+        ch = np.zeros(64, np.float32)
+        bufs = [C.create_string_buffer(_CAP) for _ in range(3)]
+        pct = C.c_double(0)
+        rc = self.lib.klmh_report_decode(self.s, text.encode("utf-8"), ch.ctypes.data_as(C.c_void_p), bufs[0], bufs[1],
+                                         bufs[2], C.byref(pct), _CAP)
+        if rc < 0:
+            self._err()
+        return {"has_state": rc == 1, "channels": ch, "node_name": bufs[0].value.decode(),
+                "status": bufs[1].value.decode(), "source": bufs[2].value.decode(), "remaining_percent": pct.value}
+
+    def enable_uav_ring(self, max_nodes: int, window: int):
+        if self.lib.klmh_enable_uav_ring(self.s, C.c_int64(max_nodes), C.c_int(window)) < 0:
+            self._err()
+
+    def update_uav_report(self, text: str, now: str = "2026-01-01T00:00:00Z") -> int:
+        rc = self.lib.klmh_update_uav_report(self.s, text.encode("utf-8"), now.encode())
+        if rc == -2:
+            self._err()
+        return rc
+
+    def uav_entry(self, i: int) -> dict:
+        pct = C.c_double(0)
+        bufs = [C.create_string_buffer(_CAP) for _ in range(3)]
+        rc = self.lib.klmh_uav_entry(self.s, C.c_int64(i), C.byref(pct), bufs[0], bufs[1], bufs[2], _CAP)
+        return {"has_state": rc == 1, "remaining_percent": pct.value, "node_name": bufs[0].value.decode(),
+                "status": bufs[1].value.decode(), "last_heartbeat": bufs[2].value.decode()}
 
     def reconcile(self):
         n = self.lib.klmh_reconcile(self.s)

@@ -164,3 +164,50 @@ def test_wire_path_at_scale(host):
             m = json.loads(host.status_json(q, stamp))
             assert m == {"phase": w.phase, "assignedNode": w.assigned_node, "assignedUAV": w.assigned_uav,
                          "score": w.score, "message": w.message, "lastUpdated": stamp}, (ints, q)
+
+
+def test_update_uav_report_feeds_the_ring(pkg):
+    """Manager.UpdateUAVReport (manager.go:391-449) through the host layer: reports decoded from
+    JSON, defaulted, and their 64 channels appended to the node's ring rows; the window statistics
+    over what was pushed equal the oracle's over the same samples, and channel 21's latest sample
+    is the battery the node table (and the scheduler) gets."""
+    import json
+    import oracle_binding as ob
+    from test_host_wire import _state_from_channels
+    nodes, t, window = 5, 48, 32
+    rows = pkg.synth.uav_channel_rows(3, 0, nodes, t).reshape(nodes, 64, t)
+    with pkg.Handle(0) as h:
+        s = pkg.hostbinding.HostSession(h)
+        s.enable_uav_ring(nodes, window)
+        order = [4, 0, 2, 1, 3]                       # first-seen order defines the node index
+        for k in range(t):
+            for node in order:
+                if node == 3 and k % 2:               # node 3 reports every other tick
+                    continue
+                rep = {"node_name": f"uav-node-{node}", "uav_id": f"uav-{node}", "source": "agent",
+                       "status": "active", "timestamp": "2026-01-01T00:00:%02dZ" % (k % 60),
+                       "state": _state_from_channels(rows[node, :, k])}
+                idx = s.update_uav_report(json.dumps(rep))
+                assert idx == order.index(node)
+        assert s.update_uav_report(json.dumps({"node_name": "", "uav_id": "x"})) == -1   # dropped
+        assert s.update_uav_report(json.dumps({"node_name": "late", "uav_id": "x"})) == nodes  # no state: entry only
+        got = h.ring_stats()
+        # the ring rows as pushed: node at index i, channel c, its samples in arrival order
+        ring = np.zeros((nodes * 64, window), np.float32)
+        seen = np.zeros(nodes * 64, np.uint32)
+        for i, node in enumerate(order):
+            ks = [k for k in range(t) if not (node == 3 and k % 2)]
+            for j, k in enumerate(ks):
+                ring[i * 64:(i + 1) * 64, j % window] = rows[node, :, k]
+            seen[i * 64:(i + 1) * 64] = len(ks)
+        want = ob.window_stats(ring, seen, window, window)
+        for key in ("min", "max", "p95"):
+            assert np.array_equal(got[key].view(np.uint32), want[key].view(np.uint32)), key
+        assert np.allclose(got["mean"], want["mean"], rtol=1e-5, atol=1e-300)
+        for i, node in enumerate(order):
+            e = s.uav_entry(i)
+            last = max(k for k in range(t) if not (node == 3 and k % 2))
+            assert e["node_name"] == f"uav-node-{node}" and e["status"] == "active" and e["has_state"]
+            assert np.float32(e["remaining_percent"]) == rows[node, 21, last]
+        assert not s.uav_entry(nodes)["has_state"]
+        s.close()

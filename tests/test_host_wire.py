@@ -3,6 +3,8 @@ oracle: the same items and specs the Go controller would see after decoding the 
 server's JSON, including apimachinery's int64-for-integral-numbers quirk."""
 import json
 
+import numpy as np
+
 import controller_oracle as co
 import helpers
 
@@ -78,3 +80,62 @@ def test_json_float_matches_go_encoding(pkg):
         v = rnd.choice([rnd.uniform(0, 110), rnd.uniform(-1e6, 1e6), rnd.random() * 10 ** rnd.randint(-30, 30),
                         round(rnd.uniform(0, 110), 1)])
         assert float(pkg.hostbinding.format_json_float(v)) == v
+
+
+def _state_from_channels(c):
+    """A UAVState JSON object (pkg/uav/mavlink_simulator.go:11-106) whose flattening is `c`."""
+    modes = ["MANUAL", "STABILIZE", "LOITER", "AUTO", "RTL", "LAND"]
+    missions = ["IDLE", "ACTIVE", "PAUSED", "COMPLETED"]
+    health = ["OK", "WARNING", "CRITICAL", "ERROR"]
+    f = lambda i: float(c[i])
+    return {
+        "uav_id": "uav-x", "node_name": "n", "system_time": "2026-01-01T00:00:00Z",
+        "gps": {"latitude": f(0), "longitude": f(1), "altitude": f(2), "relative_altitude": f(3), "hdop": f(4),
+                "satellite_count": int(c[5]), "fix_type": int(c[6]), "ground_speed": f(7),
+                "course_over_ground": f(8), "timestamp": "2026-01-01T00:00:00Z"},
+        "attitude": {"roll": f(9), "pitch": f(10), "yaw": f(11), "roll_rate": f(12), "pitch_rate": f(13),
+                     "yaw_rate": f(14)},
+        "flight": {"mode": modes[int(c[40])], "armed": bool(c[33]), "airspeed": f(15), "ground_speed": f(16),
+                   "vertical_speed": f(17), "throttle_percent": f(18)},
+        "battery": {"voltage": f(19), "current": f(20), "remaining_percent": f(21), "remaining_capacity": f(22),
+                    "total_capacity": f(23), "temperature": f(24), "cell_count": int(c[25]),
+                    "time_remaining": int(c[26])},
+        "mission": {"current_waypoint": int(c[27]), "total_waypoints": int(c[28]),
+                    "mission_state": missions[int(c[41])], "distance_to_wp": f(29), "eta_to_wp": int(c[30])},
+        "health": {"system_status": health[int(c[42])],
+                   "sensors_health": {k: bool(c[34 + i]) for i, k in enumerate(
+                       ["accelerometer", "barometer", "battery", "compass", "gps", "gyroscope"])},
+                   "error_count": int(c[31]), "warning_count": int(c[32]), "messages": []},
+    }
+
+
+def test_uav_report_decode_flatten_and_defaults(pkg):
+    """models.UAVReport (models.go:182-192) -> the 64 channels in the order of SURVEY.md 8a A11,
+    which is the order synth.uav_channel_rows generates; defaulting of manager.go:392-409."""
+    s = pkg.hostbinding.HostSession(None)
+    rows = pkg.synth.uav_channel_rows(3, 0, 3, 40).reshape(3, 64, 40)
+    for node in range(3):
+        for t in (0, 17, 39):
+            c = rows[node, :, t]
+            rep = {"node_name": f"node-{node}", "uav_id": f"uav-{node}", "source": "", "status": "",
+                   "timestamp": "0001-01-01T00:00:00Z", "state": _state_from_channels(c)}
+            d = s.report_decode(json.dumps(rep))
+            assert d["has_state"] and d["node_name"] == f"node-{node}"
+            assert d["status"] == "active" and d["source"] == "agent"           # manager.go:401-409
+            assert np.array_equal(d["channels"].view(np.uint32), c.view(np.uint32)), (node, t)
+            assert np.float32(d["remaining_percent"]) == c[21]                     # the scheduler's battery
+    d = s.report_decode(json.dumps({"node_name": "", "uav_id": "u"}))              # dropped, manager.go:392-394
+    assert d["node_name"] == "" and not d["has_state"]
+    d = s.report_decode(json.dumps({"node_name": "n", "status": "degraded", "source": "pull",
+                                    "state": {"flight": {"mode": "ACRO"}, "health": {"system_status": "??"}}}))
+    assert d["status"] == "degraded" and d["source"] == "pull" and d["has_state"]
+    assert d["channels"][40] == -1 and d["channels"][42] == -1 and d["channels"][41] == -1
+    for bad in ('{"node_name": 5}', '{"node_name": "n", "state": {"gps": {"satellite_count": 3.5}}}',
+                '{"node_name": "n", "state": []}', '[1]', '{"node_name": "n", "state": {"flight": {"armed": "yes"}}}'):
+        try:
+            s.report_decode(bad)
+        except RuntimeError as e:
+            assert "JSON" in str(e)
+        else:
+            raise AssertionError(f"accepted {bad!r}")
+    s.close()
