@@ -76,3 +76,19 @@ def test_shard_range_partitions_the_nodes(pkg):
                 assert lo % 16 == 0 or lo == n
                 prev = hi
             assert prev == n
+
+
+def test_go_shim_names_every_host_buffer_symbol():
+    """go/klm/klm.go (uncompiled here: no Go toolchain) must at least bind every klm_* host-buffer
+    entry point the header declares; a regex over the source is what can be checked without a
+    compiler. It must also fetch klm_last_error on a locked OS thread (the error text is
+    thread-local and goroutines migrate)."""
+    import re
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    hdr = open(os.path.join(root, "include", "klm.h")).read()
+    go = open(os.path.join(root, "go", "klm", "klm.go")).read()
+    names = sorted(set(re.findall(r"\b(klm_(?!dev_)\w+)\s*\(", hdr)))
+    assert len(names) > 25
+    missing = [n for n in names if f"C.{n}(" not in go]
+    assert not missing, missing
+    assert "runtime.LockOSThread()" in go and go.count("C.klm_last_error()") == 1
