@@ -164,7 +164,7 @@ class Ctx:
         return bool(t.item() > 0.5)
 
 
-def timed_rounds(ctx, step, steps, warmup, flush, events):
+def timed_rounds(ctx, step, steps, warmup, flush, events, pre_step=None):
     """W warm-up steps, then `rounds` x K timed steps between one pair of CUDA events (inputs
     larger than L2) or one pair per step around an L2 flush (inputs that fit L2). Returns
     (ms_per_step, rounds, clocks); max over ranks."""
@@ -200,6 +200,8 @@ def timed_rounds(ctx, step, steps, warmup, flush, events):
         total_ms = 0.0
         for _ in range(rounds * steps):
             flush.zero_()
+            if pre_step is not None:
+                pre_step()   # ranks line up on the device, so that no rank's region includes a peer's flush
             t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             t0.record()
             step(True)
@@ -461,10 +463,25 @@ def run_schedule_workload(ctx, wl):
         hs = symm_mem.rendezvous(slots, ctx.dist.group.WORLD)
         slot_ptrs = [int(x) for x in hs.buffer_ptrs]
         keep += [hs]
+        sync_slots = symm_mem.empty(int(dev.lib.klm_dev_shard_slots_bytes()), dtype=torch.uint8, device="cuda")
+        sync_slots.zero_()
+        hy = symm_mem.rendezvous(sync_slots, ctx.dist.group.WORLD)
+        sync_ptrs = [int(x) for x in hy.buffer_ptrs]
+        keep += [hy]
     else:
         slots = dev.shard_slots()
         slot_ptrs = [slots.data_ptr()]
     ctx.barrier()   # every rank's shard and zeroed slots are in place
+    pre_step = None
+    if world > 1:
+        sync_epoch = ctypes.c_uint64(0)
+        rdv = dev.prebind("shard_rendezvous", world, rank, sync_ptrs, sync_slots, sync_epoch)
+
+        def pre_step():
+            sync_epoch.value += 1
+            rdv()
+        extra["timing"] = ("per step: L2 flush, device-side rendezvous of the ranks, then CUDA events around "
+                           "K1 + exchange + K2; max over ranks")
     epoch = ctypes.c_uint64(0)
     k1 = dev.prebind("node_best_publish", my_bat, my_flags, lo, world, rank, slot_ptrs, epoch)       # K1 + exchange
     k2 = dev.prebind("schedule_sharded", N, bat_ptrs, flg_ptrs, slots, epoch, d_mb, d_off, d_ids, o_idx, o_score)  # K2
@@ -498,7 +515,7 @@ def run_schedule_workload(ctx, wl):
     del fb2, ff2, fi, fs
 
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
-    ms_per_step, rounds, clocks = timed_rounds(ctx, step, args.steps, max(args.warmup, 3), flush, events)
+    ms_per_step, rounds, clocks = timed_rounds(ctx, step, args.steps, max(args.warmup, 3), flush, events, pre_step)
     kern_ms = float(np.mean([a.elapsed_time(b) for a, b in events]))
     n_launch = 2 * rounds * args.steps
     value = R / (ms_per_step * 1e-3)

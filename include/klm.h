@@ -449,6 +449,14 @@ int klm_dev_schedule_sharded(int n_parts, int64_t n_nodes_total,
                              const double* min_battery, const int32_t* pref_off,
                              const int32_t* pref_ids, int32_t* out_idx,
                              double* out_score, void* stream);
+/* Line the ranks up on their streams (no reference counterpart): publishes `epoch` into this
+ * rank's slot of every rank's array and waits until its own array carries it from all
+ * n_parts ranks. Needs slot arrays of its own (not the ones K1 publishes into), zero-filled
+ * once, epochs growing by one. The data path needs no barrier; this is for a caller that wants
+ * its ranks to start a region together (bench.py does, in front of every timed step). Every
+ * rank must call it, each on its own GPU. */
+int klm_dev_shard_rendezvous(int n_parts, int my_part, void* const* peer_slots,
+                             void* my_slots, uint64_t epoch, void* stream);
 /* *out = 1 if a klm_dev_schedule_sharded on these slots gave up waiting; synchronises `stream`. */
 int klm_dev_shard_error(const void* my_slots, int* out, void* stream);
 

@@ -121,6 +121,7 @@ SIGNATURES = {
     "klm_dev_node_best_publish": (C.c_int, [_P, _P, _I64, _I64, C.c_int, C.c_int, _P, C.c_uint64, _P, _P, _P]),
     "klm_dev_schedule_sharded": (C.c_int, [C.c_int, _I64, _P, _P, _P, C.c_uint64, _I64, _P, _P, _P, _P, _P, _P]),
     "klm_dev_shard_error": (C.c_int, [_P, C.POINTER(C.c_int), _P]),
+    "klm_dev_shard_rendezvous": (C.c_int, [C.c_int, C.c_int, _P, _P, C.c_uint64, _P]),
     "klm_dev_merge_partials_peer": (C.c_int, [C.c_int, _P, _P, _I64, _I64, _P, _P, _P]),
     "klm_dev_cluster_scratch_bytes": (_I64, []),
     "klm_dev_cluster_aggregate": (C.c_int, [C.POINTER(NodeCols), _I64, _P, _I64, _P, _P, _P]),
@@ -685,6 +686,11 @@ class Dev:
         check(self.lib.klm_dev_schedule_sharded(n, n_total, ab, af, _dp(my_slots), epoch, min_battery.numel(),
                                                 _dp(min_battery), _dp(pref_off), _dp(pref_ids), _dp(out_idx),
                                                 _dp(out_score), _stream_ptr(stream)))
+
+    def shard_rendezvous(self, n_parts: int, my_part: int, slot_ptrs, my_slots, epoch, stream=None):
+        """Device-side rendezvous of the ranks (slot arrays of its own; epoch as in node_best_publish)."""
+        arr = (C.c_void_p * n_parts)(*[int(x) for x in slot_ptrs])
+        check(self.lib.klm_dev_shard_rendezvous(n_parts, my_part, arr, _dp(my_slots), epoch, _stream_ptr(stream)))
 
     def shard_error(self, my_slots, stream=None) -> int:
         out = C.c_int(0)

@@ -275,6 +275,31 @@ schedule_kernel(const double* __restrict__ battery, const uint8_t* __restrict__ 
   }
 }
 
+// Rendezvous of the ranks on their streams: publish `epoch` into this rank's slot of every rank's
+// array, then wait until this rank's own array carries it from everybody. One warp. Used to line
+// the ranks up in front of a timed region (bench.py) or a snapshot change; the data path itself
+// (K1 publish -> sharded K2) needs no barrier. `slots` arrays are separate from the K1 ones.
+__global__ void __launch_bounds__(32)
+shard_rendezvous_kernel(ShardPublish pub, const ShardSlot* __restrict__ my_slots, int* __restrict__ err) {
+  const int g = threadIdx.x;
+  if (g >= pub.n_parts) return;
+  ShardSlot* out = pub.slots[g] + (pub.epoch & 1ull) * kMaxShardParts + pub.my_part;
+  asm volatile("st.release.sys.global.u64 [%0], %1;" :: "l"(&out->epoch), "l"(pub.epoch) : "memory");
+  const ShardSlot* in = my_slots + (pub.epoch & 1ull) * kMaxShardParts + g;
+  unsigned long long e = 0, t0 = 0, now = 0;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+  while (true) {
+    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(e) : "l"(&in->epoch) : "memory");
+    if (e == pub.epoch) break;
+    __nanosleep(40);
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+    if (now - t0 > 4000000000ull) {  // 4 s: a peer never arrived
+      if (err) *err = 1;
+      break;
+    }
+  }
+}
+
 // ---------------------------------------------------------------- K2, node table in shards
 
 // The node table as G contiguous shards of `shard_len` nodes (the last ones shorter or empty),
@@ -822,6 +847,30 @@ extern "C" int klm_dev_schedule_sharded(int n_parts, int64_t n_nodes_total,
                               (unsigned long long)epoch, err, n_requests, min_battery, pref_off, pref_ids,
                               out_idx, out_score));
   KLM_LAUNCH_CHECK("schedule_sharded_kernel");
+  return KLM_OK;
+}
+
+extern "C" int klm_dev_shard_rendezvous(int n_parts, int my_part, void* const* peer_slots, void* my_slots,
+                                        uint64_t epoch, void* stream) {
+  if (n_parts < 1 || n_parts > kMaxShardParts || my_part < 0 || my_part >= n_parts || !peer_slots || !my_slots ||
+      epoch == 0) {
+    set_error("klm_dev_shard_rendezvous: bad argument (1 <= n_parts <= %d, epoch >= 1)", kMaxShardParts);
+    return n_parts > kMaxShardParts ? KLM_ELIMIT : KLM_EINVAL;
+  }
+  ShardPublish pub{};
+  for (int g = 0; g < n_parts; ++g) {
+    if (!peer_slots[g]) {
+      set_error("klm_dev_shard_rendezvous: null slot array for part %d", g);
+      return KLM_EINVAL;
+    }
+    pub.slots[g] = static_cast<ShardSlot*>(peer_slots[g]);
+  }
+  pub.n_parts = n_parts;
+  pub.my_part = my_part;
+  pub.epoch = epoch;
+  ShardSlot* slots = static_cast<ShardSlot*>(my_slots);
+  shard_rendezvous_kernel<<<1, 32, 0, as_stream(stream)>>>(pub, slots, reinterpret_cast<int*>(slots + 2 * kMaxShardParts));
+  KLM_LAUNCH_CHECK("shard_rendezvous_kernel");
   return KLM_OK;
 }
 

@@ -191,7 +191,7 @@ def test_update_uav_report_feeds_the_ring(pkg):
                 assert idx == order.index(node)
         assert s.update_uav_report(json.dumps({"node_name": "", "uav_id": "x"})) == -1   # dropped
         assert s.update_uav_report(json.dumps({"node_name": "late", "uav_id": "x"})) == nodes  # no state: entry only
-        got = h.ring_stats()
+        got = h.ring_stats(0, nodes * 64)   # (the ring was created by the host layer, not this wrapper)
         # the ring rows as pushed: node at index i, channel c, its samples in arrival order
         ring = np.zeros((nodes * 64, window), np.float32)
         seen = np.zeros(nodes * 64, np.uint32)
