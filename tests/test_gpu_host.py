@@ -2,6 +2,7 @@
 Controller and Manager around the C ABI, checked against the string-level oracle: same
 phase, node, UAV id, score and status message as internal/scheduler/controller.go would
 write, same ClusterMetrics issues and health strings as internal/metrics/manager.go."""
+import numpy as np
 import pytest
 
 import controller_oracle as co
