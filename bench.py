@@ -435,13 +435,14 @@ def run_schedule_workload(ctx, wl):
     o_idx = torch.empty(rl, dtype=torch.int32, device="cuda")
     o_score = torch.empty(rl, dtype=torch.float64, device="cuda")
     keep = []
+    spread_ptrs = None
     if wl == "c4" or world == 1:
         fb, ff = cu(bat), cu(flags)
         keep += [fb, ff]
         my_bat, my_flags = fb[lo:hi], ff[lo:hi]
         bat_ptrs = [fb[a:b].data_ptr() if b > a else 0 for a, b in ranges]
         flg_ptrs = [ff[a:b].data_ptr() if b > a else 0 for a, b in ranges]
-    else:
+    elif args.c5_probe:
         import torch.distributed._symmetric_memory as symm_mem
         L = ranges[0][1] - ranges[0][0]
         sb = symm_mem.empty(max(L, 1), dtype=torch.float64, device="cuda")
@@ -455,7 +456,26 @@ def run_schedule_workload(ctx, wl):
         bat_ptrs = [int(x) for x in hb.buffer_ptrs]
         flg_ptrs = [int(x) for x in hf.buffer_ptrs]
         extra["exchange"] = ("16 B per rank pair into symmetric-memory slots + preferred-node probes through peer "
-                             "pointers (plain loads; no multicast)")
+                             "pointers (plain loads)")
+    else:
+        # every rank holds a replica in symmetric memory but fills in only its own shard; K1 pushes
+        # the shard into the peers' replicas while it scans it, K2 probes the local replica
+        import torch.distributed._symmetric_memory as symm_mem
+        sb = symm_mem.empty(N, dtype=torch.float64, device="cuda")
+        sf = symm_mem.empty(N, dtype=torch.uint8, device="cuda")
+        hb = symm_mem.rendezvous(sb, ctx.dist.group.WORLD)
+        hf = symm_mem.rendezvous(sf, ctx.dist.group.WORLD)
+        sb.fill_(-1.0)
+        sf.zero_()
+        sb[lo:hi].copy_(cu(bat[lo:hi]))
+        sf[lo:hi].copy_(cu(flags[lo:hi]))
+        keep += [sb, sf, hb, hf]
+        my_bat, my_flags = sb[lo:hi], sf[lo:hi]
+        bat_ptrs = [sb[a:].data_ptr() if b > a else 0 for a, b in ranges]
+        flg_ptrs = [sf[a:].data_ptr() if b > a else 0 for a, b in ranges]
+        spread_ptrs = ([int(x) for x in hb.buffer_ptrs], [int(x) for x in hf.buffer_ptrs])
+        extra["exchange"] = ("K1 pushes its shard (9 B/node) into every peer's replica over NVLink while scanning it "
+                             "(plain stores through peer pointers) + 16 B per rank pair into the slots; K2 probes locally")
     if world > 1:
         import torch.distributed._symmetric_memory as symm_mem
         slots = symm_mem.empty(int(dev.lib.klm_dev_shard_slots_bytes()), dtype=torch.uint8, device="cuda")
@@ -483,7 +503,11 @@ def run_schedule_workload(ctx, wl):
         extra["timing"] = ("per step: L2 flush, device-side rendezvous of the ranks, then CUDA events around "
                            "K1 + exchange + K2; max over ranks")
     epoch = ctypes.c_uint64(0)
-    k1 = dev.prebind("node_best_publish", my_bat, my_flags, lo, world, rank, slot_ptrs, epoch)       # K1 + exchange
+    if spread_ptrs is not None:
+        k1 = dev.prebind("node_best_spread", my_bat, my_flags, lo, world, rank, slot_ptrs, spread_ptrs[0],
+                         spread_ptrs[1], epoch)                                                      # K1 + all-gather
+    else:
+        k1 = dev.prebind("node_best_publish", my_bat, my_flags, lo, world, rank, slot_ptrs, epoch)   # K1 + exchange
     k2 = dev.prebind("schedule_sharded", N, bat_ptrs, flg_ptrs, slots, epoch, d_mb, d_off, d_ids, o_idx, o_score)  # K2
     events = []
 
@@ -723,6 +747,8 @@ def main():
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--only", action="store_true", help="run only --workload (no `workloads` sub-records)")
+    ap.add_argument("--c5-probe", action="store_true",
+                    help="c5, N > 1: probe the peers' shards in place instead of replicating them in K1")
     args = ap.parse_args()
     if args.impl == "reference":
         args.steps = args.steps or 5

@@ -442,6 +442,21 @@ int klm_dev_node_best_publish(const double* battery, const uint8_t* flags,
                               int my_part, void* const* peer_slots /* host array */,
                               uint64_t epoch, int64_t* best /* may be NULL */,
                               void* scratch, void* stream);
+/* klm_dev_node_best_publish that also pushes the shard into every peer's REPLICA of the node
+ * table while it scans it (an all-gather fused into K1: plain stores through peer pointers, the
+ * shard crosses NVLink once per peer, in full lines). peer_battery[q] / peer_flags[q] are the
+ * BASES of rank q's replica as seen from this device (entry my_part is not used: the rank's own
+ * shard already is that part of its replica); the shard lands at offset node_base. A
+ * klm_dev_schedule_sharded whose parts are slices of the local replica then probes locally: the
+ * right trade once a batch probes more than about 0.08 G N preferred nodes -- a remote probe
+ * costs two 32-byte NVLink packets, about 11 G/s per GPU measured, against a bulk copy at several
+ * hundred GB/s; for a handful of requests klm_dev_node_best_publish + peer probes moves less.
+ * The replicas must not be rewritten before every rank's K2 of the epoch has finished. */
+int klm_dev_node_best_spread(const double* battery, const uint8_t* flags,
+                             int64_t n_nodes, int64_t node_base, int n_parts,
+                             int my_part, void* const* peer_slots,
+                             double* const* peer_battery, uint8_t* const* peer_flags,
+                             uint64_t epoch, int64_t* best, void* scratch, void* stream);
 int klm_dev_schedule_sharded(int n_parts, int64_t n_nodes_total,
                              const double* const* battery_parts /* host array */,
                              const uint8_t* const* flags_parts /* host array */,

@@ -121,6 +121,7 @@ SIGNATURES = {
     "klm_dev_node_best_publish": (C.c_int, [_P, _P, _I64, _I64, C.c_int, C.c_int, _P, C.c_uint64, _P, _P, _P]),
     "klm_dev_schedule_sharded": (C.c_int, [C.c_int, _I64, _P, _P, _P, C.c_uint64, _I64, _P, _P, _P, _P, _P, _P]),
     "klm_dev_shard_error": (C.c_int, [_P, C.POINTER(C.c_int), _P]),
+    "klm_dev_node_best_spread": (C.c_int, [_P, _P, _I64, _I64, C.c_int, C.c_int, _P, _P, _P, C.c_uint64, _P, _P, _P]),
     "klm_dev_shard_rendezvous": (C.c_int, [C.c_int, C.c_int, _P, _P, C.c_uint64, _P]),
     "klm_dev_merge_partials_peer": (C.c_int, [C.c_int, _P, _P, _I64, _I64, _P, _P, _P]),
     "klm_dev_cluster_scratch_bytes": (_I64, []),
@@ -672,6 +673,20 @@ class Dev:
         check(self.lib.klm_dev_node_best_publish(_dp(battery), _dp(flags), battery.numel(), node_base, n_parts,
                                                  my_part, arr, epoch, _dp(best) if best is not None else None,
                                                  _dp(sc), _stream_ptr(stream)))
+
+    def node_best_spread(self, battery, flags, node_base: int, n_parts: int, my_part: int, slot_ptrs, rep_bat_ptrs,
+                         rep_flg_ptrs, epoch, best=None, scratch=None, stream=None):
+        """node_best_publish that also pushes the shard into every peer's replica (rep_*_ptrs: device
+        addresses of the replica BASES of all ranks, as seen from this device)."""
+        t = self.torch
+        _need(battery, t.float64, "battery"); _need(flags, t.uint8, "flags")
+        arr = (C.c_void_p * n_parts)(*[int(x) for x in slot_ptrs])
+        ab = (C.c_void_p * n_parts)(*[int(x) for x in rep_bat_ptrs])
+        af = (C.c_void_p * n_parts)(*[int(x) for x in rep_flg_ptrs])
+        sc = self.best_scratch if scratch is None else scratch
+        check(self.lib.klm_dev_node_best_spread(_dp(battery), _dp(flags), battery.numel(), node_base, n_parts,
+                                                my_part, arr, ab, af, epoch, _dp(best) if best is not None else None,
+                                                _dp(sc), _stream_ptr(stream)))
 
     def schedule_sharded(self, n_total: int, bat_ptrs, flg_ptrs, my_slots, epoch, min_battery, pref_off, pref_ids,
                          out_idx, out_score, stream=None):

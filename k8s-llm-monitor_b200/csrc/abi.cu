@@ -169,7 +169,8 @@ struct klm_handle {
   // over the devices inside the library; `device` above is devs[0].device.
   struct Dev {
     int device = 0;
-    cudaStream_t stream = nullptr;
+    cudaStream_t stream = nullptr, stream2 = nullptr;  // the chunks of a large slice alternate between them
+    cudaEvent_t ev_k1 = nullptr, ev_chain[2] = {nullptr, nullptr};
     DevBuf tab;       // node columns this device holds: the whole table (request-shard mode)
                       // or its own shard (node-shard mode); battery | flags
     DevBuf slots, scratch;  // exchange slots peers write into; K1 scratch
@@ -183,6 +184,7 @@ struct klm_handle {
   int64_t md_nodes = -1;     // -1: no snapshot
   bool md_tab_valid = false; // md_tab holds the current snapshot (klm_nodes_set, not klm_reconcile)
   int md_uploaded_mode = -1; // which layout the devices hold for this snapshot (-1: none)
+  bool md_spread = false;    // node-shard layout with replicas filled over NVLink by K1 (else: peer probes)
   uint64_t md_epoch = 0;     // exchange epoch of the last K1
 };
 
@@ -316,6 +318,10 @@ int multi_init(klm_handle* h, const int* ids, int n) {
     int lo = 0, hi = 0;
     KLM_CUDA(cudaDeviceGetStreamPriorityRange(&lo, &hi));
     KLM_CUDA(cudaStreamCreateWithPriority(&d.stream, cudaStreamNonBlocking, hi));
+    KLM_CUDA(cudaStreamCreateWithPriority(&d.stream2, cudaStreamNonBlocking, hi));
+    KLM_CUDA(cudaEventCreateWithFlags(&d.ev_k1, cudaEventDisableTiming));
+    KLM_CUDA(cudaEventCreateWithFlags(&d.ev_chain[0], cudaEventDisableTiming));
+    KLM_CUDA(cudaEventCreateWithFlags(&d.ev_chain[1], cudaEventDisableTiming));
     KLM_TRY(d.slots.ensure((size_t)klm_dev_shard_slots_bytes()));
     KLM_TRY(d.scratch.ensure((size_t)klm_dev_node_best_scratch_bytes()));
     KLM_CUDA(cudaMemsetAsync(d.slots.p, 0, d.slots.cap, d.stream));
@@ -326,29 +332,57 @@ int multi_init(klm_handle* h, const int* ids, int n) {
   return KLM_OK;
 }
 
-// make every device hold the snapshot in the layout of `node_shard`, then K1 + publication
-int multi_upload(klm_handle* h, bool node_shard, int64_t n, const double* battery, const uint8_t* flags) {
+// Make every device hold the snapshot, then K1 + publication. Layouts:
+//   request-shard: the whole table goes to every device over its own PCIe link;
+//   node-shard:    device g receives only its shard from the host. With `spread` K1 then pushes
+//                  the shard into every peer's replica over NVLink while it scans it, and K2 probes
+//                  locally; without, K2 probes the peers' shards in place (fewer bytes when the
+//                  batch is small).
+int multi_upload(klm_handle* h, bool node_shard, bool spread, int64_t n, const double* battery,
+                 const uint8_t* flags) {
   const int G = (int)h->devs.size();
   ++h->md_epoch;
+  const bool whole = !node_shard || spread;  // every device has room for the whole table
   std::vector<void*> peer_slots((size_t)G);
-  for (int g = 0; g < G; ++g) peer_slots[(size_t)g] = h->devs[(size_t)g].slots.p;
+  std::vector<double*> rep_bat((size_t)G);
+  std::vector<uint8_t*> rep_flg((size_t)G);
   for (int g = 0; g < G; ++g) {
     klm_handle::Dev& d = h->devs[(size_t)g];
     KLM_CUDA(cudaSetDevice(d.device));
     int64_t lo = 0, hi = 0;
     klm_shard_range(n, G, g, &lo, &hi);
-    const int64_t a = node_shard ? lo : 0, b = node_shard ? hi : n;  // what this device stores
-    const size_t bat_bytes = (size_t)(b - a) * sizeof(double), flag_off = align256(bat_bytes);
-    KLM_TRY(d.tab.ensure(flag_off + (size_t)(b - a) + 256));
+    const int64_t cnt = whole ? n : hi - lo;
+    const size_t flag_off = align256((size_t)cnt * sizeof(double));
+    KLM_TRY(d.tab.ensure(flag_off + (size_t)cnt + 256));
     d.d_battery = d.tab.as<double>();
     d.d_flags = d.tab.as<uint8_t>() + flag_off;
-    KLM_TRY(h2d(d.d_battery, battery + a, bat_bytes, d.stream));
-    KLM_TRY(h2d(d.d_flags, flags + a, (size_t)(b - a), d.stream));
-    // K1 over this device's RANGE in either layout; global indices through node_base
-    KLM_TRY(klm_dev_node_best_publish(d.d_battery + (lo - a), d.d_flags + (lo - a), hi - lo, lo, G, g,
-                                      peer_slots.data(), h->md_epoch, nullptr, d.scratch.p, d.stream));
+    peer_slots[(size_t)g] = d.slots.p;
+    rep_bat[(size_t)g] = d.d_battery;
+    rep_flg[(size_t)g] = d.d_flags;
+  }
+  for (int g = 0; g < G; ++g) {
+    klm_handle::Dev& d = h->devs[(size_t)g];
+    KLM_CUDA(cudaSetDevice(d.device));
+    int64_t lo = 0, hi = 0;
+    klm_shard_range(n, G, g, &lo, &hi);
+    const int64_t a = node_shard ? lo : 0, b = node_shard ? hi : n;  // what the host sends here
+    const int64_t at = whole ? a : 0;                               // where it lands in `tab`
+    KLM_TRY(h2d(d.d_battery + at, battery + a, (size_t)(b - a) * sizeof(double), d.stream));
+    KLM_TRY(h2d(d.d_flags + at, flags + a, (size_t)(b - a), d.stream));
+    // K1 over this device's RANGE in every layout; global indices through node_base
+    const int64_t k1_at = whole ? lo : 0;
+    if (node_shard && spread) {
+      KLM_TRY(klm_dev_node_best_spread(d.d_battery + k1_at, d.d_flags + k1_at, hi - lo, lo, G, g, peer_slots.data(),
+                                       rep_bat.data(), rep_flg.data(), h->md_epoch, nullptr, d.scratch.p, d.stream));
+    } else {
+      KLM_TRY(klm_dev_node_best_publish(d.d_battery + k1_at, d.d_flags + k1_at, hi - lo, lo, G, g,
+                                        peer_slots.data(), h->md_epoch, nullptr, d.scratch.p, d.stream));
+    }
+    KLM_CUDA(cudaEventRecord(d.ev_k1, d.stream));
+    KLM_CUDA(cudaStreamWaitEvent(d.stream2, d.ev_k1, 0));  // K2 chunks on stream2 start behind this K1
   }
   h->md_uploaded_mode = node_shard ? 1 : 0;
+  h->md_spread = node_shard && spread;
   return KLM_OK;
 }
 
@@ -356,8 +390,10 @@ int multi_sync(klm_handle* h) {
   int rc = KLM_OK;
   for (auto& d : h->devs) {
     cudaSetDevice(d.device);
-    const cudaError_t e = cudaStreamSynchronize(d.stream);
-    if (e != cudaSuccess && rc == KLM_OK) rc = cuda_fail(e, "cudaStreamSynchronize");
+    for (cudaStream_t st : {d.stream, d.stream2}) {
+      const cudaError_t e = cudaStreamSynchronize(st);
+      if (e != cudaSuccess && rc == KLM_OK) rc = cuda_fail(e, "cudaStreamSynchronize");
+    }
   }
   cudaSetDevice(h->device);
   return rc;
@@ -391,49 +427,81 @@ int multi_schedule(klm_handle* h, int64_t n, const double* battery, const uint8_
       return KLM_EINVAL;
     }
   }
-  if (h->md_uploaded_mode != (node_shard ? 1 : 0)) KLM_TRY(multi_upload(h, node_shard, n, battery, flags));
+  if (h->md_uploaded_mode != (node_shard ? 1 : 0)) {
+    // node-shard: replicate over NVLink (K1 spreads its shard) once the batch probes more preferred
+    // nodes than about 0.08 G N -- a remote probe is two 32-byte packets at ~11 G/s, a bulk
+    // copy runs at several hundred GB/s (measured); a small batch probes in place
+    const bool spread = node_shard && n_ids * 12 > n * (int64_t)G;
+    KLM_TRY(multi_upload(h, node_shard, spread, n, battery, flags));
+  }
   if (R == 0) return multi_sync(h);
+  const bool local_table = !node_shard || h->md_spread;  // K2 probes this device's own memory
   std::vector<const double*> bat_parts((size_t)G);
   std::vector<const uint8_t*> flg_parts((size_t)G);
+  // Every device's slice is cut into chunks that alternate between its two streams, so that the
+  // download of one chunk overlaps the upload of the next (PCIe is full duplex and is what bounds
+  // a large batch); the chunk loop is the outer one, so all devices' copy engines fill together.
+  int64_t n_chunks = (R / G) / kChunkRequests;
+  if (n_chunks > kMaxChunks) n_chunks = kMaxChunks;
+  if (n_chunks < 1 || algo == KLM_ALGO_BRUTEFORCE) n_chunks = 1;
   for (int g = 0; g < G; ++g) {
     klm_handle::Dev& d = h->devs[(size_t)g];
     KLM_CUDA(cudaSetDevice(d.device));
     const int64_t r0 = R * g / G, r1 = R * (g + 1) / G, rl = r1 - r0;
     if (rl == 0) continue;
     const int64_t i0 = pref_off[r0], i1 = pref_off[r1];
-    if (!csr_non_decreasing(pref_off + r0, rl)) {
-      set_error("klm_schedule_batch: pref_off is not non-decreasing");
-      return KLM_EINVAL;
-    }
     KLM_TRY(d.req_min.ensure((size_t)rl * 8));
     KLM_TRY(d.req_off.ensure((size_t)(rl + 1) * 4));
     KLM_TRY(d.req_ids.ensure((size_t)(i1 - i0 > 0 ? i1 - i0 : 1) * 4));
     KLM_TRY(d.res_idx.ensure((size_t)rl * 4));
     KLM_TRY(d.res_score.ensure((size_t)rl * 8));
-    KLM_TRY(h2d(d.req_min.p, min_battery + r0, (size_t)rl * 8, d.stream));
-    KLM_TRY(h2d(d.req_off.p, pref_off + r0, (size_t)(rl + 1) * 4, d.stream));
-    KLM_TRY(h2d(d.req_ids.p, pref_ids + i0, (size_t)(i1 - i0) * 4, d.stream));
-    // the offsets stay absolute: hand the kernel the ids pointer moved back by i0 entries
-    const int32_t* ids_abs = d.req_ids.as<int32_t>() - i0;
-    if (algo == KLM_ALGO_BRUTEFORCE) {
-      KLM_TRY(klm_dev_schedule_bruteforce(d.d_battery, d.d_flags, n, 0, rl, d.req_min.as<double>(),
-                                          d.req_off.as<int32_t>(), ids_abs, d.res_idx.as<int32_t>(),
-                                          d.res_score.as<double>(), d.stream));
-    } else {
-      // the table as this device sees it: its own columns, or the peers' shards
-      for (int q = 0; q < G; ++q) {
-        int64_t lo = 0, hi = 0;
-        klm_shard_range(n, G, q, &lo, &hi);
-        const klm_handle::Dev& owner = h->devs[(size_t)(node_shard ? q : g)];
-        bat_parts[(size_t)q] = owner.d_battery + (node_shard ? 0 : lo);
-        flg_parts[(size_t)q] = owner.d_flags + (node_shard ? 0 : lo);
+  }
+  for (int64_t c = 0; c < n_chunks; ++c) {
+    for (int g = 0; g < G; ++g) {
+      klm_handle::Dev& d = h->devs[(size_t)g];
+      const int64_t r0 = R * g / G, r1 = R * (g + 1) / G, rl = r1 - r0;
+      if (rl == 0) continue;
+      KLM_CUDA(cudaSetDevice(d.device));
+      const int64_t q0 = r0 + rl * c / n_chunks, q1 = r0 + rl * (c + 1) / n_chunks;  // this chunk's requests
+      if (q1 == q0) continue;
+      if (!csr_non_decreasing(pref_off + q0, q1 - q0)) {
+        set_error("klm_schedule_batch: pref_off is not non-decreasing");
+        return KLM_EINVAL;
       }
-      KLM_TRY(klm_dev_schedule_sharded(G, n, bat_parts.data(), flg_parts.data(), d.slots.p, h->md_epoch, rl,
-                                       d.req_min.as<double>(), d.req_off.as<int32_t>(), ids_abs,
-                                       d.res_idx.as<int32_t>(), d.res_score.as<double>(), d.stream));
+      const int64_t i0 = pref_off[r0], j0 = pref_off[q0], j1 = pref_off[q1];
+      cudaStream_t st = (c & 1) ? d.stream2 : d.stream;
+      // offsets (q0, q1]: entry q0 came with the previous chunk (the slice's first with chunk 0)
+      const int64_t o0 = c == 0 ? q0 : q0 + 1;
+      KLM_TRY(h2d(d.req_min.as<double>() + (q0 - r0), min_battery + q0, (size_t)(q1 - q0) * 8, st));
+      KLM_TRY(h2d(d.req_off.as<int32_t>() + (o0 - r0), pref_off + o0, (size_t)(q1 + 1 - o0) * 4, st));
+      KLM_TRY(h2d(d.req_ids.as<int32_t>() + (j0 - i0), pref_ids + j0, (size_t)(j1 - j0) * 4, st));
+      KLM_CUDA(cudaEventRecord(d.ev_chain[c & 1], st));
+      // ... which is why this chunk's kernel waits for the previous chunk's upload
+      if (c > 0) KLM_CUDA(cudaStreamWaitEvent(st, d.ev_chain[(c - 1) & 1], 0));
+      // the offsets stay absolute: hand the kernel the ids pointer moved back by i0 entries
+      const int32_t* ids_abs = d.req_ids.as<int32_t>() - i0;
+      const double* c_min = d.req_min.as<double>() + (q0 - r0);
+      const int32_t* c_off = d.req_off.as<int32_t>() + (q0 - r0);
+      int32_t* c_idx = d.res_idx.as<int32_t>() + (q0 - r0);
+      double* c_score = d.res_score.as<double>() + (q0 - r0);
+      if (algo == KLM_ALGO_BRUTEFORCE) {
+        KLM_TRY(klm_dev_schedule_bruteforce(d.d_battery, d.d_flags, n, 0, q1 - q0, c_min, c_off, ids_abs, c_idx,
+                                            c_score, st));
+      } else {
+        // the table as this device sees it: its own columns, or the peers' shards
+        for (int q = 0; q < G; ++q) {
+          int64_t lo = 0, hi = 0;
+          klm_shard_range(n, G, q, &lo, &hi);
+          const klm_handle::Dev& owner = h->devs[(size_t)(local_table ? g : q)];
+          bat_parts[(size_t)q] = owner.d_battery + (local_table ? lo : 0);
+          flg_parts[(size_t)q] = owner.d_flags + (local_table ? lo : 0);
+        }
+        KLM_TRY(klm_dev_schedule_sharded(G, n, bat_parts.data(), flg_parts.data(), d.slots.p, h->md_epoch, q1 - q0,
+                                         c_min, c_off, ids_abs, c_idx, c_score, st));
+      }
+      KLM_TRY(d2h(out_idx + q0, c_idx, (size_t)(q1 - q0) * 4, st));
+      KLM_TRY(d2h(out_score + q0, c_score, (size_t)(q1 - q0) * 8, st));
     }
-    KLM_TRY(d2h(out_idx + r0, d.res_idx.p, (size_t)rl * 4, d.stream));
-    KLM_TRY(d2h(out_score + r0, d.res_score.p, (size_t)rl * 8, d.stream));
   }
   KLM_TRY(multi_sync(h));
   for (auto& d : h->devs) {  // a K2 that waited in vain for a peer's K1 says so
@@ -595,6 +663,10 @@ extern "C" void klm_destroy(klm_handle* h) {
   for (auto& d : h->devs) {
     cudaSetDevice(d.device);
     if (d.stream) cudaStreamSynchronize(d.stream);
+    if (d.stream2) cudaStreamSynchronize(d.stream2);
+    for (cudaEvent_t ev : {d.ev_k1, d.ev_chain[0], d.ev_chain[1]})
+      if (ev) cudaEventDestroy(ev);
+    if (d.stream2) cudaStreamDestroy(d.stream2);
     for (DevBuf* b : {&d.tab, &d.slots, &d.scratch, &d.req_min, &d.req_off, &d.req_ids, &d.res_idx, &d.res_score})
       b->release();
     if (d.stream) cudaStreamDestroy(d.stream);

@@ -88,13 +88,22 @@ struct ShardPublish {
   int n_parts, my_part;
   unsigned long long epoch;
 };
+// K1 with SPREAD also pushes the shard it is reading into every peer's replica of the node table
+// (plain stores through peer pointers: an all-gather fused into the scan, the shard crosses NVLink
+// once per peer in full lines while K1 would be reading it anyway). rep_* are the replica BASES;
+// the shard goes to offset node_base. The rank's own replica is skipped (the shard already is
+// that part of it).
+struct ShardSpread {
+  double* rep_bat[kMaxShardParts];
+  uint8_t* rep_flg[kMaxShardParts];
+};
 
-template <bool PUBLISH>
+template <bool PUBLISH, bool SPREAD = false>
 __global__ void __launch_bounds__(kBestThreads)
 node_best_kernel(const double* __restrict__ battery, const uint8_t* __restrict__ flags,
                  int64_t n, int64_t node_base, int vec_ok, int64_t* __restrict__ best,
                  unsigned int* __restrict__ ticket, double* __restrict__ part_bat,
-                 int64_t* __restrict__ part_idx, ShardPublish pub) {
+                 int64_t* __restrict__ part_idx, ShardPublish pub, ShardSpread spr) {
   // A kernel launched behind this one with programmatic stream serialisation
   // (klm_dev_schedule_after_best) may start now: K1 occupies a fraction of the SMs and its
   // result is needed only at the end of K2. Without such a dependent this is a no-op.
@@ -111,6 +120,15 @@ node_best_kernel(const double* __restrict__ battery, const uint8_t* __restrict__
       double2 b[kBestNodesPerThread / 2];
 #pragma unroll
       for (int k = 0; k < kBestNodesPerThread / 2; ++k) b[k] = ld_stream_d2(battery + i0 + 2 * k);
+      if (SPREAD) {
+        for (int g = 0; g < pub.n_parts; ++g) {
+          if (g == pub.my_part) continue;
+          double2* db = reinterpret_cast<double2*>(spr.rep_bat[g] + node_base + i0);
+#pragma unroll
+          for (int k = 0; k < kBestNodesPerThread / 2; ++k) db[k] = b[k];
+          *reinterpret_cast<int4*>(spr.rep_flg[g] + node_base + i0) = fw;
+        }
+      }
       const unsigned int f[4] = {(unsigned)fw.x, (unsigned)fw.y, (unsigned)fw.z, (unsigned)fw.w};
 #pragma unroll
       for (int k = 0; k < kBestNodesPerThread; ++k) {
@@ -127,6 +145,14 @@ node_best_kernel(const double* __restrict__ battery, const uint8_t* __restrict__
   }
   for (int64_t i = done + tid; i < n; i += nthreads) {
     const double v = battery[i];
+    if (SPREAD) {
+      const uint8_t fl = flags[i];
+      for (int g = 0; g < pub.n_parts; ++g) {
+        if (g == pub.my_part) continue;
+        spr.rep_bat[g][node_base + i] = v;
+        spr.rep_flg[g][node_base + i] = fl;
+      }
+    }
     if ((flags[i] & 3u) == 3u && (me.idx < 0 || v > me.bat)) {
       me.bat = v;
       me.idx = i;
@@ -138,7 +164,9 @@ node_best_kernel(const double* __restrict__ battery, const uint8_t* __restrict__
   if (threadIdx.x == 0) {
     part_bat[blockIdx.x] = me.bat;
     part_idx[blockIdx.x] = me.idx;
-    __threadfence();
+    // SPREAD: the block's stores into the peers' replicas (made visible to this thread by the
+    // barrier inside block_best) must be performed system-wide before the ticket says "done"
+    if (SPREAD) __threadfence_system(); else __threadfence();
     const unsigned int t = atomicAdd(ticket, 1u);
     s_last = (t == gridDim.x - 1);
   }
@@ -622,7 +650,7 @@ extern "C" int klm_dev_node_best(const double* battery, const uint8_t* flags, in
   if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
   const int vec_ok = aligned16(battery) && aligned16(flags);
   node_best_kernel<false><<<(int)blocks, kBestThreads, 0, as_stream(stream)>>>(
-      battery, flags, n_nodes, node_base, vec_ok, best, ticket, part_bat, part_idx, ShardPublish{});
+      battery, flags, n_nodes, node_base, vec_ok, best, ticket, part_bat, part_idx, ShardPublish{}, ShardSpread{});
   KLM_LAUNCH_CHECK("node_best_kernel");
   return KLM_OK;
 }
@@ -764,22 +792,28 @@ extern "C" void klm_shard_range(int64_t n_nodes, int n_parts, int part, int64_t*
   if (hi) *hi = b;
 }
 
-extern "C" int klm_dev_node_best_publish(const double* battery, const uint8_t* flags, int64_t n_nodes,
-                                         int64_t node_base, int n_parts, int my_part,
-                                         void* const* peer_slots, uint64_t epoch, int64_t* best,
-                                         void* scratch, void* stream) {
+static int launch_publish(const char* who, const double* battery, const uint8_t* flags, int64_t n_nodes,
+                          int64_t node_base, int n_parts, int my_part, void* const* peer_slots,
+                          double* const* peer_bat, uint8_t* const* peer_flg, uint64_t epoch, int64_t* best,
+                          void* scratch, void* stream) {
   if (n_nodes < 0 || !scratch || (n_nodes > 0 && (!battery || !flags)) || n_parts < 1 ||
       n_parts > kMaxShardParts || my_part < 0 || my_part >= n_parts || !peer_slots || epoch == 0) {
-    set_error("klm_dev_node_best_publish: bad argument (1 <= n_parts <= %d, epoch >= 1)", kMaxShardParts);
+    set_error("%s: bad argument (1 <= n_parts <= %d, epoch >= 1)", who, kMaxShardParts);
     return n_parts > kMaxShardParts ? KLM_ELIMIT : KLM_EINVAL;
   }
   ShardPublish pub{};
+  ShardSpread spr{};
+  const bool spread = peer_bat != nullptr;
   for (int g = 0; g < n_parts; ++g) {
-    if (!peer_slots[g]) {
-      set_error("klm_dev_node_best_publish: null slot array for part %d", g);
+    if (!peer_slots[g] || (spread && g != my_part && n_nodes > 0 && (!peer_bat[g] || !peer_flg || !peer_flg[g]))) {
+      set_error("%s: null slot array or replica for part %d", who, g);
       return KLM_EINVAL;
     }
     pub.slots[g] = static_cast<ShardSlot*>(peer_slots[g]);
+    if (spread) {
+      spr.rep_bat[g] = peer_bat[g];
+      spr.rep_flg[g] = peer_flg[g];
+    }
   }
   pub.n_parts = n_parts;
   pub.my_part = my_part;
@@ -792,11 +826,42 @@ extern "C" int klm_dev_node_best_publish(const double* battery, const uint8_t* f
   if (blocks < 1) blocks = 1;
   if (blocks > kBestMaxBlocks) blocks = kBestMaxBlocks;
   if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
-  const int vec_ok = aligned16(battery) && aligned16(flags);
-  node_best_kernel<true><<<(int)blocks, kBestThreads, 0, as_stream(stream)>>>(
-      battery, flags, n_nodes, node_base, vec_ok, best, ticket, part_bat, part_idx, pub);
+  int vec_ok = aligned16(battery) && aligned16(flags);
+  if (spread) {
+    // the 128-bit stores land at replica + node_base: every replica base and node_base must keep
+    // the alignment too (klm_shard_range hands out multiples of 16 nodes)
+    vec_ok = vec_ok && (node_base % 16 == 0);
+    for (int g = 0; g < n_parts && vec_ok; ++g)
+      if (g != my_part) vec_ok = aligned16(spr.rep_bat[g]) && aligned16(spr.rep_flg[g]);
+    node_best_kernel<true, true><<<(int)blocks, kBestThreads, 0, as_stream(stream)>>>(
+        battery, flags, n_nodes, node_base, vec_ok, best, ticket, part_bat, part_idx, pub, spr);
+  } else {
+    node_best_kernel<true, false><<<(int)blocks, kBestThreads, 0, as_stream(stream)>>>(
+        battery, flags, n_nodes, node_base, vec_ok, best, ticket, part_bat, part_idx, pub, spr);
+  }
   KLM_LAUNCH_CHECK("node_best_kernel<publish>");
   return KLM_OK;
+}
+
+extern "C" int klm_dev_node_best_publish(const double* battery, const uint8_t* flags, int64_t n_nodes,
+                                         int64_t node_base, int n_parts, int my_part,
+                                         void* const* peer_slots, uint64_t epoch, int64_t* best,
+                                         void* scratch, void* stream) {
+  return launch_publish("klm_dev_node_best_publish", battery, flags, n_nodes, node_base, n_parts, my_part,
+                        peer_slots, nullptr, nullptr, epoch, best, scratch, stream);
+}
+
+extern "C" int klm_dev_node_best_spread(const double* battery, const uint8_t* flags, int64_t n_nodes,
+                                        int64_t node_base, int n_parts, int my_part,
+                                        void* const* peer_slots, double* const* peer_battery,
+                                        uint8_t* const* peer_flags, uint64_t epoch, int64_t* best,
+                                        void* scratch, void* stream) {
+  if (!peer_battery || !peer_flags) {
+    set_error("klm_dev_node_best_spread: null replica arrays");
+    return KLM_EINVAL;
+  }
+  return launch_publish("klm_dev_node_best_spread", battery, flags, n_nodes, node_base, n_parts, my_part,
+                        peer_slots, peer_battery, peer_flags, epoch, best, scratch, stream);
 }
 
 extern "C" int klm_dev_schedule_sharded(int n_parts, int64_t n_nodes_total,

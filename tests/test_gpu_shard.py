@@ -25,7 +25,15 @@ def _run_emulated(dev, pkg, bat, flags, mb, off, ids, g, replicated, epochs=(1,)
     d_mb, d_off = t(mb), t(off)
     d_ids = t(ids if ids.size else np.zeros(1, np.int32))
     ranges = [pkg.binding.shard_range(n, g, k) for k in range(g)]
-    if replicated:   # request-shard layout: one table, the parts are slices of it
+    spread = replicated == "spread"
+    if spread:       # every rank has a replica; only its own shard is filled in, K1 pushes it to the others
+        reps = [(torch.full((max(n, 1),), -1.0, dtype=torch.float64, device="cuda"),
+                 torch.zeros(max(n, 1), dtype=torch.uint8, device="cuda")) for _ in range(g)]
+        for k, (lo, hi) in enumerate(ranges):
+            reps[k][0][lo:hi] = t(bat[lo:hi])
+            reps[k][1][lo:hi] = t(flags[lo:hi])
+        parts = [(reps[k][0][lo:hi], reps[k][1][lo:hi]) for k, (lo, hi) in enumerate(ranges)]
+    elif replicated:   # request-shard layout: one table, the parts are slices of it
         fb, ff = t(bat), t(flags)
         parts = [(fb[lo:hi], ff[lo:hi]) for lo, hi in ranges]
     else:            # node-shard layout: every rank's shard is its own allocation
@@ -41,11 +49,18 @@ def _run_emulated(dev, pkg, bat, flags, mb, off, ids, g, replicated, epochs=(1,)
     out_score = torch.full((r,), -7.0, dtype=torch.float64, device="cuda")
     for e in epochs:
         for k, (lo, hi) in enumerate(ranges):      # every rank's K1 first ...
-            dev.node_best_publish(parts[k][0], parts[k][1], lo, g, k, slot_ptrs, e, scratch=scratch[k])
+            if spread:
+                dev.node_best_spread(parts[k][0], parts[k][1], lo, g, k, slot_ptrs, [x[0].data_ptr() for x in reps],
+                                     [x[1].data_ptr() for x in reps], e, scratch=scratch[k])
+            else:
+                dev.node_best_publish(parts[k][0], parts[k][1], lo, g, k, slot_ptrs, e, scratch=scratch[k])
         for k in range(g):                         # ... then every rank's K2 on its request slice
             r0, r1 = r * k // g, r * (k + 1) // g
             if r1 == r0:
                 continue
+            if spread:   # rank k probes its own replica, which the peers have completed
+                bp = [reps[k][0][lo:].data_ptr() if hi > lo else 0 for lo, hi in ranges]
+                fp = [reps[k][1][lo:].data_ptr() if hi > lo else 0 for lo, hi in ranges]
             # offsets stay absolute: the slice of pref_off indexes the whole pref_ids array
             dev.schedule_sharded(n, bp, fp, slots[k], e, d_mb[r0:r1], d_off[r0:r1 + 1], d_ids,
                                  out_idx[r0:r1], out_score[r0:r1])
@@ -56,7 +71,7 @@ def _run_emulated(dev, pkg, bat, flags, mb, off, ids, g, replicated, epochs=(1,)
 
 
 @pytest.mark.parametrize("g", [1, 2, 3, 8, 16])
-@pytest.mark.parametrize("replicated", [False, True])
+@pytest.mark.parametrize("replicated", [False, True, "spread"])
 def test_sharded_equals_oracle_tie_heavy(dev, pkg, g, replicated):
     rng = np.random.default_rng(100 + g)
     for n, r, kmax in ((1, 5, 2), (17, 40, 3), (1000, 3000, 3), (40_003, 20_001, 6)):
@@ -92,6 +107,8 @@ def test_c5_full_size_sharded(dev, pkg, g):
     mb, off, ids = pkg.synth.requests(5, r, n)
     want = ob.schedule_decomposed(bat, flags, mb, off, ids)
     got = _run_emulated(dev, pkg, bat, flags, mb, off, ids, g, False)
+    assert np.array_equal(got[0], want[0]) and np.array_equal(got[1], want[1])
+    got = _run_emulated(dev, pkg, bat, flags, mb, off, ids, g, "spread")   # K1 fused with the all-gather
     assert np.array_equal(got[0], want[0]) and np.array_equal(got[1], want[1])
 
 
