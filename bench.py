@@ -508,7 +508,8 @@ def run_schedule_workload(ctx, wl):
                          spread_ptrs[1], epoch)                                                      # K1 + all-gather
     else:
         k1 = dev.prebind("node_best_publish", my_bat, my_flags, lo, world, rank, slot_ptrs, epoch)   # K1 + exchange
-    k2 = dev.prebind("schedule_sharded", N, bat_ptrs, flg_ptrs, slots, epoch, d_mb, d_off, d_ids, o_idx, o_score)  # K2
+    k2 = dev.prebind("schedule_sharded", N, bat_ptrs, flg_ptrs, slots, epoch, d_mb, d_off, d_ids, o_idx, o_score,
+                     table_from_k1=spread_ptrs is not None)                                          # K2
     events = []
 
     def step(timed):

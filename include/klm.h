@@ -425,6 +425,10 @@ int klm_dev_merge_partials(int n_parts, int64_t n_requests,
  *                              and probes preferred nodes where they live -- battery_parts[q] /
  *                              flags_parts[q] are rank q's shard as seen from this device (peer
  *                              pointers; or slices of a local replica: request-shard mode).
+ *                              table_from_k1 != 0: the columns are filled by this epoch's K1s
+ *                              (klm_dev_node_best_spread), so they are read only after the
+ *                              wait; 0: they were complete before K1 started and the first
+ *                              probes are issued ahead of the wait.
  * No host barrier, no gather of partial winners, no merge kernel: the exchange is 16 bytes per
  * rank pair and per-rank work is N / G + R / G. Results equal klm_dev_schedule on the whole
  * table (global indices, lowest index on ties: controller.go:160). Both kernels of a rank go
@@ -463,7 +467,7 @@ int klm_dev_schedule_sharded(int n_parts, int64_t n_nodes_total,
                              void* my_slots, uint64_t epoch, int64_t n_requests,
                              const double* min_battery, const int32_t* pref_off,
                              const int32_t* pref_ids, int32_t* out_idx,
-                             double* out_score, void* stream);
+                             double* out_score, int table_from_k1, void* stream);
 /* Line the ranks up on their streams (no reference counterpart): publishes `epoch` into this
  * rank's slot of every rank's array and waits until its own array carries it from all
  * n_parts ranks. Needs slot arrays of its own (not the ones K1 publishes into), zero-filled

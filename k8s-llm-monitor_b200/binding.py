@@ -119,7 +119,7 @@ SIGNATURES = {
     "klm_dev_shard_slots_bytes": (_I64, []),
     "klm_shard_range": (None, [_I64, C.c_int, C.c_int, C.POINTER(_I64), C.POINTER(_I64)]),
     "klm_dev_node_best_publish": (C.c_int, [_P, _P, _I64, _I64, C.c_int, C.c_int, _P, C.c_uint64, _P, _P, _P]),
-    "klm_dev_schedule_sharded": (C.c_int, [C.c_int, _I64, _P, _P, _P, C.c_uint64, _I64, _P, _P, _P, _P, _P, _P]),
+    "klm_dev_schedule_sharded": (C.c_int, [C.c_int, _I64, _P, _P, _P, C.c_uint64, _I64, _P, _P, _P, _P, _P, C.c_int, _P]),
     "klm_dev_shard_error": (C.c_int, [_P, C.POINTER(C.c_int), _P]),
     "klm_dev_node_best_spread": (C.c_int, [_P, _P, _I64, _I64, C.c_int, C.c_int, _P, _P, _P, C.c_uint64, _P, _P, _P]),
     "klm_dev_shard_rendezvous": (C.c_int, [C.c_int, C.c_int, _P, _P, C.c_uint64, _P]),
@@ -689,8 +689,9 @@ class Dev:
                                                 _dp(sc), _stream_ptr(stream)))
 
     def schedule_sharded(self, n_total: int, bat_ptrs, flg_ptrs, my_slots, epoch, min_battery, pref_off, pref_ids,
-                         out_idx, out_score, stream=None):
-        """bat_ptrs / flg_ptrs: device addresses (ints) of every rank's shard columns."""
+                         out_idx, out_score, stream=None, table_from_k1: bool = False):
+        """bat_ptrs / flg_ptrs: device addresses (ints) of every rank's shard columns.
+        table_from_k1: the columns are filled by this epoch's node_best_spread calls."""
         t = self.torch
         _need(min_battery, t.float64, "min_battery"); _need(pref_off, t.int32, "pref_off")
         _need(pref_ids, t.int32, "pref_ids"); _need(out_idx, t.int32, "out_idx")
@@ -700,7 +701,7 @@ class Dev:
         af = (C.c_void_p * n)(*[int(x) for x in flg_ptrs])
         check(self.lib.klm_dev_schedule_sharded(n, n_total, ab, af, _dp(my_slots), epoch, min_battery.numel(),
                                                 _dp(min_battery), _dp(pref_off), _dp(pref_ids), _dp(out_idx),
-                                                _dp(out_score), _stream_ptr(stream)))
+                                                _dp(out_score), int(table_from_k1), _stream_ptr(stream)))
 
     def shard_rendezvous(self, n_parts: int, my_part: int, slot_ptrs, my_slots, epoch, stream=None):
         """Device-side rendezvous of the ranks (slot arrays of its own; epoch as in node_best_publish)."""

@@ -497,7 +497,7 @@ int multi_schedule(klm_handle* h, int64_t n, const double* battery, const uint8_
           flg_parts[(size_t)q] = owner.d_flags + (local_table ? lo : 0);
         }
         KLM_TRY(klm_dev_schedule_sharded(G, n, bat_parts.data(), flg_parts.data(), d.slots.p, h->md_epoch, q1 - q0,
-                                         c_min, c_off, ids_abs, c_idx, c_score, st));
+                                         c_min, c_off, ids_abs, c_idx, c_score, h->md_spread ? 1 : 0, st));
       }
       KLM_TRY(d2h(out_idx + q0, c_idx, (size_t)(q1 - q0) * 4, st));
       KLM_TRY(d2h(out_score + q0, c_score, (size_t)(q1 - q0) * 8, st));

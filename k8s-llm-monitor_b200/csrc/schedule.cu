@@ -354,20 +354,65 @@ __device__ __forceinline__ bool shard_lookup(const ShardView& v, int32_t id, uin
   return true;
 }
 
+// Wait until this rank's slot array holds every rank's K1 result of `epoch`, fold them into the
+// global best (largest battery, lowest global index). Block-wide.
+__device__ __forceinline__ void shard_wait_best(const ShardView& v, const ShardSlot* __restrict__ my_slots,
+                                                unsigned long long epoch, int* __restrict__ err, int64_t& g,
+                                                double& gb) {
+  __shared__ int64_t s_g;
+  __shared__ double s_gb;
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+  if (threadIdx.x < 32) {
+    Best w{0.0, -1};
+    if ((int)threadIdx.x < v.n_parts) {
+      const ShardSlot* sl = my_slots + (epoch & 1ull) * kMaxShardParts + threadIdx.x;
+      unsigned long long e = 0, t0 = 0, now = 0;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+      bool ok = true;
+      while (true) {
+        asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(e) : "l"(&sl->epoch) : "memory");
+        if (e == epoch) break;
+        __nanosleep(40);
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+        if (now - t0 > 4000000000ull) { ok = false; break; }  // 4 s: a peer never published
+      }
+      if (ok) {
+        int64_t pi, pb;
+        asm volatile("ld.relaxed.sys.global.v2.s64 {%0, %1}, [%2];" : "=l"(pi), "=l"(pb) : "l"(sl) : "memory");
+        w.idx = pi;
+        w.bat = __longlong_as_double(pb);
+      } else if (err) {
+        *err = 1;
+      }
+    }
+    w = warp_best(w);
+    if (threadIdx.x == 0) {
+      s_g = w.idx;
+      s_gb = w.bat;
+    }
+  }
+  __syncthreads();
+  g = s_g;
+  gb = s_gb;
+}
+
 // Sharded form of schedule_kernel: this rank decides ITS slice of the requests. The global best
 // node is the fold of the G shard winners the ranks published into `my_slots` (waited for with
 // acquire loads: no host barrier, no K3); preferred nodes are probed where they live, through
 // the pointers of the view -- a 9-byte read over NVLink for a node another rank owns.
 // Results are identical to schedule_kernel on the whole table (global indices; lowest index on
 // ties, controller.go:160).
+// WAIT_FIRST: the node columns themselves are written by this epoch's K1s (klm_dev_node_best_spread
+// fills the replicas), so nothing of them may be read before the slots say that every rank is
+// done; otherwise the columns were complete before K1 started and the first tile's probes are
+// issued ahead of the wait.
+template <bool WAIT_FIRST>
 __global__ void __launch_bounds__(kSchedThreads)
 schedule_sharded_kernel(ShardView v, const ShardSlot* __restrict__ my_slots, unsigned long long epoch,
                         int* __restrict__ err, int64_t n_requests,
                         const double* __restrict__ min_battery, const int32_t* __restrict__ pref_off,
                         const int32_t* __restrict__ pref_ids, int32_t* __restrict__ out_idx,
                         double* __restrict__ out_score) {
-  __shared__ int64_t s_g;
-  __shared__ double s_gb;
   int64_t g = -1;
   double gb = 0.0;
   bool have_best = false;
@@ -388,6 +433,10 @@ schedule_sharded_kernel(ShardView v, const ShardSlot* __restrict__ my_slots, uns
     for (int j = 0; j < kSchedUnroll; ++j)
 #pragma unroll
       for (int q = 0; q < kSchedSlots; ++q) p[j][q] = k0[j] + q < k1[j] ? pref_ids[k0[j] + q] : -1;
+    if (WAIT_FIRST && !have_best) {  // the request loads above are in flight; the node columns come after
+      shard_wait_best(v, my_slots, epoch, err, g, gb);
+      have_best = true;
+    }
     uint8_t f[kSchedUnroll][kSchedSlots];
     double b[kSchedUnroll][kSchedSlots];
 #pragma unroll
@@ -398,40 +447,8 @@ schedule_sharded_kernel(ShardView v, const ShardSlot* __restrict__ my_slots, uns
         b[j][q] = 0.0;
         shard_lookup(v, p[j][q], f[j][q], b[j][q]);
       }
-    if (!have_best) {  // first tile only: every load of this tile is in flight by now
-      asm volatile("griddepcontrol.wait;" ::: "memory");
-      if (threadIdx.x < 32) {
-        Best w{0.0, -1};
-        if ((int)threadIdx.x < v.n_parts) {
-          const ShardSlot* sl = my_slots + (epoch & 1ull) * kMaxShardParts + threadIdx.x;
-          unsigned long long e = 0, t0 = 0, now = 0;
-          asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
-          bool ok = true;
-          while (true) {
-            asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(e) : "l"(&sl->epoch) : "memory");
-            if (e == epoch) break;
-            __nanosleep(40);
-            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
-            if (now - t0 > 4000000000ull) { ok = false; break; }  // 4 s: a peer never published
-          }
-          if (ok) {
-            int64_t pi, pb;
-            asm volatile("ld.relaxed.sys.global.v2.s64 {%0, %1}, [%2];" : "=l"(pi), "=l"(pb) : "l"(sl) : "memory");
-            w.idx = pi;
-            w.bat = __longlong_as_double(pb);
-          } else if (err) {
-            *err = 1;
-          }
-        }
-        w = warp_best(w);
-        if (threadIdx.x == 0) {
-          s_g = w.idx;
-          s_gb = w.bat;
-        }
-      }
-      __syncthreads();
-      g = s_g;
-      gb = s_gb;
+    if (!WAIT_FIRST && !have_best) {  // first tile only: every load of this tile is in flight by now
+      shard_wait_best(v, my_slots, epoch, err, g, gb);
       have_best = true;
     }
 #pragma unroll
@@ -869,7 +886,7 @@ extern "C" int klm_dev_schedule_sharded(int n_parts, int64_t n_nodes_total,
                                         const uint8_t* const* flags_parts, void* my_slots,
                                         uint64_t epoch, int64_t n_requests, const double* min_battery,
                                         const int32_t* pref_off, const int32_t* pref_ids,
-                                        int32_t* out_idx, double* out_score, void* stream) {
+                                        int32_t* out_idx, double* out_score, int table_from_k1, void* stream) {
   if (n_parts < 1 || n_parts > kMaxShardParts || n_nodes_total < 0 || n_nodes_total > 0x7fffffff ||
       !battery_parts || !flags_parts || !my_slots || epoch == 0 || n_requests < 0) {
     set_error("klm_dev_schedule_sharded: bad argument (1 <= n_parts <= %d, epoch >= 1)", kMaxShardParts);
@@ -908,9 +925,15 @@ extern "C" int klm_dev_schedule_sharded(int n_parts, int64_t n_nodes_total,
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  KLM_CUDA(cudaLaunchKernelEx(&cfg, schedule_sharded_kernel, v, (const ShardSlot*)slots,
-                              (unsigned long long)epoch, err, n_requests, min_battery, pref_off, pref_ids,
-                              out_idx, out_score));
+  if (table_from_k1) {
+    KLM_CUDA(cudaLaunchKernelEx(&cfg, schedule_sharded_kernel<true>, v, (const ShardSlot*)slots,
+                                (unsigned long long)epoch, err, n_requests, min_battery, pref_off, pref_ids,
+                                out_idx, out_score));
+  } else {
+    KLM_CUDA(cudaLaunchKernelEx(&cfg, schedule_sharded_kernel<false>, v, (const ShardSlot*)slots,
+                                (unsigned long long)epoch, err, n_requests, min_battery, pref_off, pref_ids,
+                                out_idx, out_score));
+  }
   KLM_LAUNCH_CHECK("schedule_sharded_kernel");
   return KLM_OK;
 }

@@ -63,7 +63,7 @@ def _run_emulated(dev, pkg, bat, flags, mb, off, ids, g, replicated, epochs=(1,)
                 fp = [reps[k][1][lo:].data_ptr() if hi > lo else 0 for lo, hi in ranges]
             # offsets stay absolute: the slice of pref_off indexes the whole pref_ids array
             dev.schedule_sharded(n, bp, fp, slots[k], e, d_mb[r0:r1], d_off[r0:r1 + 1], d_ids,
-                                 out_idx[r0:r1], out_score[r0:r1])
+                                 out_idx[r0:r1], out_score[r0:r1], table_from_k1=spread)
     torch.cuda.synchronize()
     for s in slots:
         assert dev.shard_error(s) == 0
