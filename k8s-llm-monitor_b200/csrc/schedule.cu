@@ -113,35 +113,56 @@ node_best_kernel(const double* __restrict__ battery, const uint8_t* __restrict__
   const int64_t nthreads = (int64_t)gridDim.x * blockDim.x;
   int64_t done = 0;
   if (vec_ok) {
-    const int64_t nchunks = n / kBestNodesPerThread;
-    for (int64_t c = tid; c < nchunks; c += nthreads) {
-      const int64_t i0 = c * kBestNodesPerThread;
-      const int4 fw = ld_stream_v4(flags + i0);
-      double2 b[kBestNodesPerThread / 2];
+    // Tiles of 256 x 8 node pairs: in every load and store the lanes of a warp touch consecutive
+    // 16 bytes (battery pairs) / 2 bytes (flag pairs), i.e. whole 512-byte and 64-byte runs --
+    // which is what lets the pushes into the peers' replicas (SPREAD) cross NVLink as full lines.
+    constexpr int kPairs = kBestNodesPerThread / 2;  // node pairs per thread per tile
+    const int64_t npairs = n >> 1;
+    const int64_t tile_pairs = (int64_t)kBestThreads * kPairs;
+    for (int64_t p0 = (int64_t)blockIdx.x * tile_pairs; p0 < npairs; p0 += (int64_t)gridDim.x * tile_pairs) {
+      double2 b[kPairs];
+      unsigned short f[kPairs];
 #pragma unroll
-      for (int k = 0; k < kBestNodesPerThread / 2; ++k) b[k] = ld_stream_d2(battery + i0 + 2 * k);
+      for (int u = 0; u < kPairs; ++u) {
+        const int64_t p = p0 + (int64_t)u * kBestThreads + threadIdx.x;
+        b[u] = make_double2(0.0, 0.0);
+        f[u] = 0;
+        if (p < npairs) {
+          b[u] = ld_stream_d2(battery + 2 * p);
+          f[u] = __ldg(reinterpret_cast<const unsigned short*>(flags) + p);
+        }
+      }
       if (SPREAD) {
         for (int g = 0; g < pub.n_parts; ++g) {
           if (g == pub.my_part) continue;
-          double2* db = reinterpret_cast<double2*>(spr.rep_bat[g] + node_base + i0);
+          double2* db = reinterpret_cast<double2*>(spr.rep_bat[g] + node_base);
+          unsigned short* df = reinterpret_cast<unsigned short*>(spr.rep_flg[g] + node_base);
 #pragma unroll
-          for (int k = 0; k < kBestNodesPerThread / 2; ++k) db[k] = b[k];
-          *reinterpret_cast<int4*>(spr.rep_flg[g] + node_base + i0) = fw;
+          for (int u = 0; u < kPairs; ++u) {
+            const int64_t p = p0 + (int64_t)u * kBestThreads + threadIdx.x;
+            if (p < npairs) {
+              db[p] = b[u];
+              df[p] = f[u];
+            }
+          }
         }
       }
-      const unsigned int f[4] = {(unsigned)fw.x, (unsigned)fw.y, (unsigned)fw.z, (unsigned)fw.w};
 #pragma unroll
-      for (int k = 0; k < kBestNodesPerThread; ++k) {
-        const unsigned int fl = (f[k >> 2] >> (8 * (k & 3))) & 3u;
-        const double v = (k & 1) ? b[k >> 1].y : b[k >> 1].x;
-        // indices grow within a thread, so a strict > keeps the first maximum
-        if (fl == 3u && (me.idx < 0 || v > me.bat)) {
-          me.bat = v;
-          me.idx = i0 + k;
+      for (int u = 0; u < kPairs; ++u) {
+        const int64_t p = p0 + (int64_t)u * kBestThreads + threadIdx.x;
+        // indices grow within a thread (u, then the tile), so a strict > keeps the first maximum;
+        // a pair beyond the end carries flags 0 and is never eligible
+        if ((f[u] & 3u) == 3u && (me.idx < 0 || b[u].x > me.bat)) {
+          me.bat = b[u].x;
+          me.idx = 2 * p;
+        }
+        if (((f[u] >> 8) & 3u) == 3u && (me.idx < 0 || b[u].y > me.bat)) {
+          me.bat = b[u].y;
+          me.idx = 2 * p + 1;
         }
       }
     }
-    done = nchunks * kBestNodesPerThread;
+    done = npairs * 2;
   }
   for (int64_t i = done + tid; i < n; i += nthreads) {
     const double v = battery[i];
@@ -407,7 +428,7 @@ __device__ __forceinline__ void shard_wait_best(const ShardView& v, const ShardS
 // done; otherwise the columns were complete before K1 started and the first tile's probes are
 // issued ahead of the wait.
 template <bool WAIT_FIRST>
-__global__ void __launch_bounds__(kSchedThreads)
+__global__ void __launch_bounds__(kSchedThreads, 4)  // 64 registers: a rank's slice of C4 / C5 is one wave
 schedule_sharded_kernel(ShardView v, const ShardSlot* __restrict__ my_slots, unsigned long long epoch,
                         int* __restrict__ err, int64_t n_requests,
                         const double* __restrict__ min_battery, const int32_t* __restrict__ pref_off,
