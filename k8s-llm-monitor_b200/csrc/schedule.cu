@@ -8,6 +8,8 @@
 // list index (what a stable descending sort followed by [0] yields).
 // All score arithmetic is IEEE f64, as Go's float64; comparisons are on
 // values, never on bit patterns (so -0.0 == +0.0 like in Go).
+#include <cstdlib>
+
 #include "common.cuh"
 
 namespace klm {
@@ -98,16 +100,12 @@ struct ShardSpread {
   uint8_t* rep_flg[kMaxShardParts];
 };
 
-template <bool PUBLISH, bool SPREAD = false>
-__global__ void __launch_bounds__(kBestThreads)
-node_best_kernel(const double* __restrict__ battery, const uint8_t* __restrict__ flags,
-                 int64_t n, int64_t node_base, int vec_ok, int64_t* __restrict__ best,
-                 unsigned int* __restrict__ ticket, double* __restrict__ part_bat,
-                 int64_t* __restrict__ part_idx, ShardPublish pub, ShardSpread spr) {
-  // A kernel launched behind this one with programmatic stream serialisation
-  // (klm_dev_schedule_after_best) may start now: K1 occupies a fraction of the SMs and its
-  // result is needed only at the end of K2. Without such a dependent this is a no-op.
-  asm volatile("griddepcontrol.launch_dependents;");
+// The scan of K1: this CTA's share of the nodes (tiles strided by the grid), per-thread first
+// maximum; with SPREAD every tile is also pushed into the peers' replicas.
+template <bool SPREAD>
+__device__ __forceinline__ Best scan_nodes(const double* __restrict__ battery, const uint8_t* __restrict__ flags,
+                                           int64_t n, int64_t node_base, int vec_ok, const ShardPublish& pub,
+                                           const ShardSpread& spr) {
   Best me{0.0, -1};
   const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   const int64_t nthreads = (int64_t)gridDim.x * blockDim.x;
@@ -179,6 +177,29 @@ node_best_kernel(const double* __restrict__ battery, const uint8_t* __restrict__
       me.idx = i;
     }
   }
+  return me;
+}
+
+// The publication at the end of K1: lane g of warp 0 writes rank g's copy of this rank's slot.
+__device__ __forceinline__ void publish_best(const ShardPublish& pub, int64_t g_idx, int64_t g_bits) {
+  if ((int)threadIdx.x < pub.n_parts) {
+    ShardSlot* sl = pub.slots[threadIdx.x] + (pub.epoch & 1ull) * kMaxShardParts + pub.my_part;
+    asm volatile("st.relaxed.sys.global.v2.s64 [%0], {%1, %2};" :: "l"(sl), "l"(g_idx), "l"(g_bits) : "memory");
+    asm volatile("st.release.sys.global.u64 [%0], %1;" :: "l"(&sl->epoch), "l"(pub.epoch) : "memory");
+  }
+}
+
+template <bool PUBLISH, bool SPREAD = false>
+__global__ void __launch_bounds__(kBestThreads)
+node_best_kernel(const double* __restrict__ battery, const uint8_t* __restrict__ flags,
+                 int64_t n, int64_t node_base, int vec_ok, int64_t* __restrict__ best,
+                 unsigned int* __restrict__ ticket, double* __restrict__ part_bat,
+                 int64_t* __restrict__ part_idx, ShardPublish pub, ShardSpread spr) {
+  // A kernel launched behind this one with programmatic stream serialisation
+  // (klm_dev_schedule_after_best) may start now: K1 occupies a fraction of the SMs and its
+  // result is needed only at the end of K2. Without such a dependent this is a no-op.
+  asm volatile("griddepcontrol.launch_dependents;");
+  Best me = scan_nodes<SPREAD>(battery, flags, n, node_base, vec_ok, pub, spr);
   me = block_best(me);
 
   __shared__ bool s_last;
@@ -211,12 +232,55 @@ node_best_kernel(const double* __restrict__ battery, const uint8_t* __restrict__
     }
     *ticket = 0;  // ready for the next launch on this scratch
   }
-  if (PUBLISH && (int)threadIdx.x < pub.n_parts) {
-    // lane g writes rank g's copy of this rank's slot (n_parts <= 16: all in warp 0)
-    ShardSlot* sl = pub.slots[threadIdx.x] + (pub.epoch & 1ull) * kMaxShardParts + pub.my_part;
-    asm volatile("st.relaxed.sys.global.v2.s64 [%0], {%1, %2};" :: "l"(sl), "l"(g_idx), "l"(g_bits) : "memory");
-    asm volatile("st.release.sys.global.u64 [%0], %1;" :: "l"(&sl->epoch), "l"(pub.epoch) : "memory");
+  if (PUBLISH) publish_best(pub, g_idx, g_bits);  // (n_parts <= 16: all in warp 0, which holds the result)
+}
+
+// K1 as ONE thread-block cluster (tables up to a few million nodes): the CTAs' partial winners
+// meet in CTA 0's shared memory through distributed shared memory and a cluster barrier -- no
+// global partials, no __threadfence + ticket, no scratch. Same result as node_best_kernel.
+constexpr int kBestClusterMax = 16;
+template <bool PUBLISH, bool SPREAD>
+__global__ void __launch_bounds__(kBestThreads)
+node_best_cluster_kernel(const double* __restrict__ battery, const uint8_t* __restrict__ flags, int64_t n,
+                         int64_t node_base, int vec_ok, int64_t* __restrict__ best, ShardPublish pub,
+                         ShardSpread spr) {
+  __shared__ double c_bat[kBestClusterMax];
+  __shared__ int64_t c_idx[kBestClusterMax];
+  asm volatile("griddepcontrol.launch_dependents;");
+  Best me = scan_nodes<SPREAD>(battery, flags, n, node_base, vec_ok, pub, spr);
+  me = block_best(me);
+  unsigned int rank, n_cta;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(rank));
+  asm volatile("mov.u32 %0, %%cluster_nctarank;" : "=r"(n_cta));
+  if (threadIdx.x == 0) {
+    // slot `rank` of CTA 0's arrays
+    const uint32_t lb = (uint32_t)__cvta_generic_to_shared(&c_bat[rank]);
+    const uint32_t li = (uint32_t)__cvta_generic_to_shared(&c_idx[rank]);
+    uint32_t rb, ri;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, 0;" : "=r"(rb) : "r"(lb));
+    asm volatile("mapa.shared::cluster.u32 %0, %1, 0;" : "=r"(ri) : "r"(li));
+    asm volatile("st.shared::cluster.f64 [%0], %1;" :: "r"(rb), "d"(me.bat) : "memory");
+    asm volatile("st.shared::cluster.s64 [%0], %1;" :: "r"(ri), "l"(me.idx) : "memory");
   }
+  // SPREAD: this CTA's pushes into the peers' replicas must be performed system-wide before CTA 0
+  // may publish; the cluster barrier orders them only at cluster scope
+  if (SPREAD) __threadfence_system();
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+  if (rank != 0 || threadIdx.x >= 32) return;
+  Best w{0.0, -1};
+  if (threadIdx.x < n_cta) {
+    w.bat = c_bat[threadIdx.x];
+    w.idx = c_idx[threadIdx.x];
+  }
+  w = warp_best(w);
+  const int64_t g_idx = w.idx < 0 ? -1 : w.idx + node_base;
+  const int64_t g_bits = __double_as_longlong(w.idx < 0 ? 0.0 : w.bat);
+  if (threadIdx.x == 0 && best) {
+    best[0] = g_idx;
+    best[1] = g_bits;
+  }
+  if (PUBLISH) publish_best(pub, g_idx, g_bits);
 }
 
 // ---------------------------------------------------------------- K2
@@ -670,6 +734,56 @@ static int grid_for(int64_t work_items, int threads, int max_waves = 8) {
 
 using namespace klm;
 
+// Tables (shards) up to this many nodes take the one-cluster form of K1: a CTA works through its
+// tiles one memory round trip at a time, so 16 CTAs win only while each has two or three tiles
+// (100 k nodes: 12.3 us against 14.3 us for the ticket chain, cold; 500 k: 22.5 against 14.3 --
+// profiles/r02_c5_phases_n2_cluster_ab.jsonl).
+constexpr int64_t kBestClusterNodes = 160 * 1024;
+
+// Launches K1 as one cluster of 1..16 CTAs. Returns KLM_OK, or 1 if the cluster launch is not
+// possible here (the caller then takes the multi-block kernel), or an error.
+template <bool PUBLISH, bool SPREAD>
+static int launch_best_cluster(const double* battery, const uint8_t* flags, int64_t n, int64_t node_base,
+                               int vec_ok, int64_t* best, const ShardPublish& pub, const ShardSpread& spr,
+                               cudaStream_t st) {
+  static PerDeviceOnce attr_set, unusable;
+  static const bool disabled = std::getenv("KLM_K1_NO_CLUSTER") != nullptr;  // A/B measurements
+  int dev = 0;
+  KLM_CUDA(cudaGetDevice(&dev));
+  if (disabled || unusable.done(dev)) return 1;
+  auto kern = node_best_cluster_kernel<PUBLISH, SPREAD>;
+  if (!attr_set.done(dev)) {
+    if (cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) != cudaSuccess) {
+      (void)cudaGetLastError();
+      unusable.set(dev);
+      return 1;
+    }
+    attr_set.set(dev);
+  }
+  int csize = 1;
+  while (csize < kBestClusterMax && (int64_t)csize * kBestThreads * kBestNodesPerThread < n) csize *= 2;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)csize);
+  cfg.blockDim = dim3(kBestThreads);
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = (unsigned)csize;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  const cudaError_t e = cudaLaunchKernelEx(&cfg, kern, battery, flags, n, node_base, vec_ok, best, pub, spr);
+  if (e == cudaErrorInvalidValue || e == cudaErrorInvalidConfiguration || e == cudaErrorLaunchOutOfResources ||
+      e == cudaErrorNotSupported) {
+    (void)cudaGetLastError();  // a 16-CTA cluster cannot be placed on this device / partition
+    unusable.set(dev);
+    return 1;
+  }
+  if (e != cudaSuccess) return cuda_fail(e, "node_best_cluster_kernel");
+  return KLM_OK;
+}
+
 extern "C" int64_t klm_dev_node_best_scratch_bytes(void) { return kBestScratchBytes; }
 
 extern "C" int klm_dev_node_best(const double* battery, const uint8_t* flags, int64_t n_nodes,
@@ -687,6 +801,11 @@ extern "C" int klm_dev_node_best(const double* battery, const uint8_t* flags, in
   if (blocks > kBestMaxBlocks) blocks = kBestMaxBlocks;
   if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
   const int vec_ok = aligned16(battery) && aligned16(flags);
+  if (n_nodes <= kBestClusterNodes) {
+    const int rc = launch_best_cluster<false, false>(battery, flags, n_nodes, node_base, vec_ok, best, ShardPublish{},
+                                                     ShardSpread{}, as_stream(stream));
+    if (rc != 1) return rc;
+  }
   node_best_kernel<false><<<(int)blocks, kBestThreads, 0, as_stream(stream)>>>(
       battery, flags, n_nodes, node_base, vec_ok, best, ticket, part_bat, part_idx, ShardPublish{}, ShardSpread{});
   KLM_LAUNCH_CHECK("node_best_kernel");
@@ -871,9 +990,19 @@ static int launch_publish(const char* who, const double* battery, const uint8_t*
     vec_ok = vec_ok && (node_base % 16 == 0);
     for (int g = 0; g < n_parts && vec_ok; ++g)
       if (g != my_part) vec_ok = aligned16(spr.rep_bat[g]) && aligned16(spr.rep_flg[g]);
+    if (n_nodes <= kBestClusterNodes) {
+      const int rc = launch_best_cluster<true, true>(battery, flags, n_nodes, node_base, vec_ok, best, pub, spr,
+                                                     as_stream(stream));
+      if (rc != 1) return rc;
+    }
     node_best_kernel<true, true><<<(int)blocks, kBestThreads, 0, as_stream(stream)>>>(
         battery, flags, n_nodes, node_base, vec_ok, best, ticket, part_bat, part_idx, pub, spr);
   } else {
+    if (n_nodes <= kBestClusterNodes) {
+      const int rc = launch_best_cluster<true, false>(battery, flags, n_nodes, node_base, vec_ok, best, pub, spr,
+                                                      as_stream(stream));
+      if (rc != 1) return rc;
+    }
     node_best_kernel<true, false><<<(int)blocks, kBestThreads, 0, as_stream(stream)>>>(
         battery, flags, n_nodes, node_base, vec_ok, best, ticket, part_bat, part_idx, pub, spr);
   }
