@@ -567,6 +567,20 @@ int klm_dev_window_stats_stream(const float* ring, const uint32_t* seen,
                                 int32_t window, int32_t pitch, int64_t s0,
                                 int64_t s1, float* out_min, float* out_max,
                                 double* out_mean, float* out_p95, void* stream);
+/* K7 for streaming windows (no reference counterpart): the streaming kernel with a per-series
+ * bracket around the p95 carried from call to call in `state` (2 floats per series, indexed from
+ * s0 like the outputs; fill it with 0xFF bytes -- NaN -- before the first call). Between two
+ * collection ticks one sample enters a window and one leaves, so the previous bracket still
+ * holds the answer: the kernel skips the pivot sampling, lists about k + 12 samples instead of
+ * 10 % of the window, and finishes with one counting pass and one sort. The bracket is only a
+ * pivot: results are exact and identical to klm_dev_window_stats whatever `state` contains
+ * (stale, another ring's, garbage); a useless bracket costs the time of the unhinted kernel.
+ * Windows up to 8192 (KLM_ELIMIT beyond). Calls on the same series must not overlap. */
+int klm_dev_window_stats_hinted(const float* ring, const uint32_t* seen,
+                                int32_t window, int32_t pitch, int64_t s0,
+                                int64_t s1, float* out_min, float* out_max,
+                                double* out_mean, float* out_p95, float* state,
+                                void* stream);
 /* The pipelined variant of K7: one persistent CTA per SM, a producer warp streams rows
  * into a ring of shared-memory slots with cp.async.bulk + mbarriers, 15 consumer warps
  * work on them in place. Windows up to 4096 (KLM_ELIMIT beyond); same results. Slower

@@ -249,8 +249,11 @@ int launch_window_stats_pipe(const float* ring, const uint32_t* seen, int32_t wi
                              float* out_max, double* out_mean, float* out_p95, cudaStream_t st);
 int launch_window_stats_stream(const float* ring, const uint32_t* seen, int32_t window,
                                int32_t pitch, int64_t s0, int64_t s1, float* out_min,
-                               float* out_max, double* out_mean, float* out_p95, cudaStream_t st);
+                               float* out_max, double* out_mean, float* out_p95, float* state,
+                               cudaStream_t st);
 }
+
+constexpr int kHintedMaxWindow = 8192;  // the streaming kernel's lists hold ~10 % of a window this large
 
 static int window_stats_args_ok(const float* ring, const uint32_t* seen, int32_t window,
                                 int32_t pitch, int64_t s0, int64_t s1) {
@@ -272,7 +275,7 @@ extern "C" int klm_dev_window_stats(const float* ring, const uint32_t* seen, int
 #ifdef KLM_K7_STREAM_DEFAULT
   if (window <= 8192)
     return launch_window_stats_stream(ring, seen, window, pitch, s0, s1, out_min, out_max, out_mean,
-                                      out_p95, as_stream(stream));
+                                      out_p95, nullptr, as_stream(stream));
 #endif
   // windows <= 4096: the register-resident warp kernel (fastest measured);
   // larger windows fall through to the shared-memory block kernel
@@ -305,7 +308,25 @@ extern "C" int klm_dev_window_stats_stream(const float* ring, const uint32_t* se
   const int rc = window_stats_args_ok(ring, seen, window, pitch, s0, s1);
   if (rc != KLM_OK || s1 == s0) return rc;
   return launch_window_stats_stream(ring, seen, window, pitch, s0, s1, out_min, out_max, out_mean,
-                                    out_p95, as_stream(stream));
+                                    out_p95, nullptr, as_stream(stream));
+}
+
+extern "C" int klm_dev_window_stats_hinted(const float* ring, const uint32_t* seen, int32_t window,
+                                           int32_t pitch, int64_t s0, int64_t s1, float* out_min,
+                                           float* out_max, double* out_mean, float* out_p95,
+                                           float* state, void* stream) {
+  const int rc = window_stats_args_ok(ring, seen, window, pitch, s0, s1);
+  if (rc != KLM_OK || s1 == s0) return rc;
+  if (!state || (reinterpret_cast<uintptr_t>(state) & 7u)) {
+    set_error("klm_dev_window_stats_hinted: state must be a non-null, 8-byte aligned array of 2 floats per series");
+    return KLM_EINVAL;
+  }
+  if (window > kHintedMaxWindow) {
+    set_error("klm_dev_window_stats_hinted: window %d exceeds %d (use klm_dev_window_stats)", window, kHintedMaxWindow);
+    return KLM_ELIMIT;
+  }
+  return launch_window_stats_stream(ring, seen, window, pitch, s0, s1, out_min, out_max, out_mean,
+                                    out_p95, state, as_stream(stream));
 }
 
 extern "C" int klm_dev_window_stats_pipe(const float* ring, const uint32_t* seen, int32_t window,

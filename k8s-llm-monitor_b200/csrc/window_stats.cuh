@@ -117,6 +117,20 @@ __device__ __forceinline__ void sort64_desc(uint32_t& k0, uint32_t& k1, int lane
 }
 
 constexpr int kMaxCand = 64;  // candidates sorted exactly at the end of select_from_lists
+constexpr int kHintMargin = 12;  // the hint brackets ranks k - 12 .. k + 12 of the window
+
+// The bracket handed to the next call on this series (one tick later at most one sample has
+// entered and one has left, so ranks move by at most one): from the sorted candidates (descending,
+// element e in lane e / 2, register e % 2; n_cand of them; the answer at 1-based position kk),
+// floor = the candidate kHintMargin places below the answer, ceil = the one kHintMargin places
+// above (or `above`, a value with fewer than k samples at or over it, when the candidates do not
+// reach that far). A hint is only ever a pivot: any value gives exact results.
+__device__ __forceinline__ float2 hint_from_sorted(uint32_t k0, uint32_t k1, int kk, int n_cand, float above) {
+  const int pl = min(kk - 1 + kHintMargin, n_cand - 1), ph = kk - 1 - kHintMargin;
+  const uint32_t lo = __shfl_sync(0xffffffffu, (pl & 1) ? k1 : k0, pl >> 1);
+  const uint32_t hi = __shfl_sync(0xffffffffu, (max(ph, 0) & 1) ? k1 : k0, max(ph, 0) >> 1);
+  return make_float2(key_f32(lo), ph >= 0 ? key_f32(hi) : above);
+}
 constexpr int kListPrefill = 24;  // list entries per lane the kernels pre-fill with -inf
 
 // The k-th largest of the elements held in the lane lists (lst = this lane's list, entry e at
@@ -131,7 +145,7 @@ constexpr int kListPrefill = 24;  // list entries per lane the kernels pre-fill 
 __device__ __forceinline__ float select_from_lists(float* lst, float* fin, int lane, int cnt,
                                                    int total, int maxcnt, int k, float a, float mx,
                                                    bool have_hints, float hint_lo, float hint_hi,
-                                                   int prefilled) {
+                                                   int prefilled, float2* next_hint = nullptr) {
   const int m8 = (maxcnt + 7) & ~7;
   // entries below `prefilled` beyond the lane's count already hold -inf (pre-filled by the
   // caller); pad the rest up to m8 here. prefilled == 0: the usual lengths as straight-line
@@ -221,8 +235,57 @@ __device__ __forceinline__ float select_from_lists(float* lst, float* fin, int l
   const float2 y = *reinterpret_cast<const float2*>(fin + 2 * lane);  // -inf beyond ca - cb
   uint32_t k0 = f32_key(y.x), k1 = f32_key(y.y);
   sort64_desc(k0, k1, lane);
+  if (next_hint) *next_hint = hint_from_sorted(k0, k1, kk, ca - cb, open ? POS_INF : b);
   const uint32_t pick = ((kk - 1) & 1) ? k1 : k0;
   return key_f32(__shfl_sync(0xffffffffu, pick, (kk - 1) >> 1));
+}
+
+// The hinted finish (streaming windows): `fl` < `ce` bracket the answer as left by the previous
+// call on this series -- every element >= fl is in the lists (total of them, total >= k). One
+// counting pass at `ce` leaves the candidates in [fl, ce); if they are at most 64 and the answer is
+// among them they are gathered and sorted at once. Returns false (nothing decided) when the
+// bracket no longer holds the answer or is too wide: the caller then runs select_from_lists on
+// the same lists. Exact like select_from_lists: the result is a listed element whose rank has
+// been counted.
+__device__ __forceinline__ bool select_hinted(float* lst, float* fin, int lane, int cnt, int total,
+                                              int maxcnt, int k, float fl, float ce, float* result,
+                                              float2* next_hint) {
+  const int m8 = (maxcnt + 7) & ~7;
+  for (int e = max(cnt, kListPrefill); e < m8; ++e) lst[e * 32] = NEG_INF;  // (entries < kListPrefill are pre-filled)
+  fin[lane] = NEG_INF;
+  fin[lane + 32] = NEG_INF;
+  __syncwarp();
+  int lane_cb, dummy;
+  const int cb = (int)(list_count2(lst, m8, ce, ce, lane_cb, dummy) & 0xffffu);
+  if (cb >= k || total - cb > kMaxCand) return false;
+  const int mine = cnt - lane_cb;
+  int incl = mine;
+#pragma unroll
+  for (int off = 1; off < 32; off <<= 1) {
+    const int u = __shfl_up_sync(0xffffffffu, incl, off);
+    if (lane >= off) incl += u;
+  }
+  float* dst = fin + (incl - mine);
+  if (mine > 0) {
+#pragma unroll 1
+    for (int e = 0; e < m8; e += 8) {
+      float x[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) x[u] = lst[(e + u) * 32];
+#pragma unroll
+      for (int u = 0; u < 8; ++u)
+        if (x[u] >= fl && x[u] < ce) *dst++ = x[u];
+    }
+  }
+  __syncwarp();
+  const int kk = k - cb;
+  const float2 y = *reinterpret_cast<const float2*>(fin + 2 * lane);
+  uint32_t k0 = f32_key(y.x), k1 = f32_key(y.y);
+  sort64_desc(k0, k1, lane);
+  *next_hint = hint_from_sorted(k0, k1, kk, total - cb, ce);
+  const uint32_t pick = ((kk - 1) & 1) ? k1 : k0;
+  *result = key_f32(__shfl_sync(0xffffffffu, pick, (kk - 1) >> 1));
+  return true;
 }
 
 #endif  // __CUDACC__

@@ -173,7 +173,8 @@ __global__ void __launch_bounds__(kWssThreads, MINB)
 window_stats_stream_kernel(const float* __restrict__ ring, const uint32_t* __restrict__ seen,
                            int32_t window, int32_t pitch, int64_t s0, int64_t n_series,
                            float* __restrict__ out_min, float* __restrict__ out_max,
-                           double* __restrict__ out_mean, float* __restrict__ out_p95) {
+                           double* __restrict__ out_mean, float* __restrict__ out_p95,
+                           float2* __restrict__ state) {
   using Cfg = WssCfg<CAP>;
   extern __shared__ __align__(16) unsigned char s_raw[];
 
@@ -196,8 +197,19 @@ window_stats_stream_kernel(const float* __restrict__ ring, const uint32_t* __res
   const float* p = row + 4 * lane;
   const int wjr = (window >> 2) >> 5;  // full rows of a full window
   const bool want_p95 = out_p95 != nullptr;
+  // Streaming windows: `state` holds, per series, the bracket (floor, ceil) around the p95 that
+  // the previous call left (window_stats.cuh, hint_from_sorted). A usable bracket replaces the
+  // sampling: the pass lists everything >= floor, about k + 12 elements, and the finish is one
+  // counting pass and one sort. The bracket is only a pivot: stale, wrong or garbage values cost
+  // time, never exactness.
+  float2 hint = make_float2(0.f, 0.f);
+  bool hinted = false;
+  if (state != nullptr && want_p95) {
+    hint = state[o];
+    hinted = wjr >= kWssSampledMinRows && hint.x < hint.y && hint.x > NEG_INF;  // (NaN fails every test)
+  }
   float sm[4] = {NEG_INF, NEG_INF, NEG_INF, NEG_INF};
-  if (want_p95 && wjr >= kWssSampledMinRows) {
+  if (!hinted && want_p95 && wjr >= kWssSampledMinRows) {
 #pragma unroll
     for (int q = 0; q < 4; ++q) sm[q] = __ldg(p + 128 * (((2 * q + 1) * wjr) >> 3) + q);
   }
@@ -244,11 +256,13 @@ window_stats_stream_kernel(const float* __restrict__ ring, const uint32_t* __res
   const int nfull = n >> 2;   // complete float4 groups
   const int jr = nfull >> 5;  // rows valid in every lane
   const int k = n - p95_rank(n);
-  const bool sampled = want_p95 && jr >= kWssSampledMinRows;
-  if (sampled && n != window) {  // partly filled ring: sample the rows that hold data
+  hinted = hinted && n == window;  // (a ring that is still filling changes too fast for a bracket)
+  const bool sampled = want_p95 && jr >= kWssSampledMinRows && !hinted;
+  if (sampled && n != window) {  // partly filled ring (or a bracket dropped for it): sample the rows that hold data
 #pragma unroll
     for (int q = 0; q < 4; ++q) sm[q] = __ldg(p + 128 * (((2 * q + 1) * jr) >> 3) + q);
   }
+  float2 next_hint = make_float2(__int_as_float(0x7fc00000), __int_as_float(0x7fc00000));  // NaN: no bracket
 
   bool narrow = false;             // settle by counting passes over the row (wss_narrow)
   float lox = POS_INF;             // list predicate: x > lox (+inf: list nothing)
@@ -301,6 +315,8 @@ window_stats_stream_kernel(const float* __restrict__ ring, const uint32_t* __res
     } else {
       lox = next_down(V);  // x > lox  <=>  x >= V
     }
+  } else if (hinted) {
+    lox = next_down(hint.x);  // x > lox  <=>  x >= floor
   } else if (want_p95) {
     lox = NEG_INF;  // short window: list every sample
   }
@@ -366,6 +382,15 @@ window_stats_stream_kernel(const float* __restrict__ ring, const uint32_t* __res
     int cnt = (int)(c128 >> 7);
     int total = warp_sum_i32(cnt);
     int maxcnt = warp_max_i32(cnt);
+    if (hinted) {
+      // the bracket's floor lists too few (it has drifted above the answer) or far too many
+      if (total < k || maxcnt >= Cfg::kClamp) { narrow = true; break; }
+      if (select_hinted(lst, fin, lane, cnt, total, maxcnt, k, hint.x, hint.y, &result, &next_hint)) break;
+      // the answer left the bracket, or the bracket is wide: the lists still hold everything >= floor
+      result = select_from_lists(lst, fin, lane, cnt, total, maxcnt, k, hint.x, mx, false, 0.f, 0.f, kListPrefill,
+                                 &next_hint);
+      break;
+    }
     if (total < k && !sampled) { result = NEG_INF; break; }  // lox = -inf: only -inf samples are unlisted
     if (total < k && !tie_mode && lox_retry != POS_INF) {
       // the pivot was too high: redo the append (only) from the next sample statistic down
@@ -385,7 +410,7 @@ window_stats_stream_kernel(const float* __restrict__ ring, const uint32_t* __res
       break;
     }
     result = select_from_lists(lst, fin, lane, cnt, total, maxcnt, k, sampled ? next_up(lox) : mn, mx,
-                               retried, hint_lo, hint_hi, kListPrefill);
+                               retried, hint_lo, hint_hi, kListPrefill, &next_hint);
   } while (false);
   if (narrow) {
     if (mn == mx) {
@@ -414,13 +439,16 @@ window_stats_stream_kernel(const float* __restrict__ ring, const uint32_t* __res
       }
     }
   }
-  if (lane == 0) out_p95[o] = result + 0.f;
+  if (lane == 0) {
+    out_p95[o] = result + 0.f;
+    if (state != nullptr) state[o] = next_hint;  // NaN pair when this path produced no bracket
+  }
 }
 
 template <int CAP, int MINB, int NBUF>
 static int launch_stream(const float* ring, const uint32_t* seen, int32_t window, int32_t pitch,
                          int64_t s0, int64_t n_series, float* out_min, float* out_max,
-                         double* out_mean, float* out_p95, cudaStream_t st) {
+                         double* out_mean, float* out_p95, float2* state, cudaStream_t st) {
   using Cfg = WssCfg<CAP>;
   static_assert(MINB * (Cfg::kSmem + 1024) <= 227 * 1024, "the CTAs per SM must fit");
   const int64_t blocks = ceil_div(n_series, kWssWarps);
@@ -441,7 +469,7 @@ static int launch_stream(const float* ring, const uint32_t* seen, int32_t window
     attr_set.set(dev);
   }
   window_stats_stream_kernel<CAP, MINB, NBUF><<<(unsigned)blocks, kWssThreads, Cfg::kSmem, st>>>(
-      ring, seen, window, pitch, s0, n_series, out_min, out_max, out_mean, out_p95);
+      ring, seen, window, pitch, s0, n_series, out_min, out_max, out_mean, out_p95, state);
   KLM_LAUNCH_CHECK("window_stats_stream_kernel");
   return KLM_OK;
 }
@@ -458,9 +486,9 @@ static int launch_stream(const float* ring, const uint32_t* seen, int32_t window
 
 int launch_window_stats_stream(const float* ring, const uint32_t* seen, int32_t window, int32_t pitch,
                                int64_t s0, int64_t s1, float* out_min, float* out_max,
-                               double* out_mean, float* out_p95, cudaStream_t st) {
+                               double* out_mean, float* out_p95, float* state, cudaStream_t st) {
   return launch_stream<KLM_WSS_CAP, KLM_WSS_MINB, KLM_WSS_NBUF>(ring, seen, window, pitch, s0, s1 - s0, out_min, out_max,
-                                                  out_mean, out_p95, st);
+                                                  out_mean, out_p95, reinterpret_cast<float2*>(state), st);
 }
 
 }  // namespace klm

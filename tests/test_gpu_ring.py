@@ -384,3 +384,43 @@ def test_pushes_queue_behind_cycles_in_flight(pkg):
         want_final = replay.ring_stats()
         for k in ("min", "max", "mean", "p95"):
             assert np.array_equal(final[k], want_final[k]), k
+
+
+@pytest.mark.parametrize("t", [900, 1000, 3600, 4096, 8192])
+def test_hinted_window_stats_exact_over_ticks(dev, t):
+    """klm_dev_window_stats_hinted: the bracket carried in `state` is only a pivot. Over a run of
+    ticks (each appends one sample per series, wrapping the ring) every call must equal the oracle
+    bit for bit -- from a NaN state, from the brackets the kernel left, and from garbage brackets
+    (reversed, infinite, far off, another series')."""
+    import torch
+    rng = np.random.default_rng(7000 + t)
+    s = 240
+    rows = distributions(rng, s, t)
+    pitch = (t + 3) & ~3
+    ring = torch.zeros((s, pitch), dtype=torch.float32, device="cuda")
+    ring[:, :t] = torch.from_numpy(rows).cuda()
+    seen_np = np.full(s, t, np.int64)
+    seen_np[:4] = [0, 1, t - 1, t // 2]                     # rings that are still filling
+    seen = torch.from_numpy(seen_np.astype(np.int32)).cuda()
+    state = torch.full((s, 2), float("nan"), dtype=torch.float32, device="cuda")
+    o = {k: torch.empty(s, dtype=torch.float64 if k == "mean" else torch.float32, device="cuda")
+         for k in ("min", "max", "mean", "p95")}
+    used = 0
+    for tick in range(12):
+        if tick:
+            vals = torch.from_numpy(distributions(rng, s, 1)[:, 0].copy()).cuda()
+            dev.ring_ingest(ring, seen, t, vals)
+            seen_np += 1
+        if tick == 5:    # garbage brackets
+            g = torch.from_numpy(rng.standard_normal((s, 2)).astype(np.float32) * 1e3).cuda()
+            g[::7, 0] = float("inf"); g[1::7, 1] = float("-inf"); g[2::7] = 0.0; g[3::7, 0] = -1e30; g[3::7, 1] = 1e30
+            state.copy_(g)
+        if tick == 8:    # another series' brackets
+            state.copy_(state.roll(17, 0))
+        dev.window_stats(ring, seen, t, o["min"], o["max"], o["mean"], o["p95"], state=state)
+        torch.cuda.synchronize()
+        want = ob.window_stats(ring.cpu().numpy(), seen_np.astype(np.uint32), t, pitch)
+        check_stats({k: v.cpu().numpy() for k, v in o.items()}, want, f"hinted t={t} tick={tick}")
+        st = state.cpu().numpy()
+        used += int(np.sum(st[:, 0] < st[:, 1]))
+    assert used > 0 or t < 896, "no series ever produced a bracket"

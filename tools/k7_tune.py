@@ -54,6 +54,28 @@ def worker():
             e1.synchronize()
             reps.append(e0.elapsed_time(e1) / 20 * 1e3)
         out[dist + "_us"] = round(float(np.median(reps)), 2)
+        if hasattr(dev.lib, "klm_dev_window_stats_hinted") and t <= 8192:
+            # streaming: one fresh sample per series between calls, the bracket carried in `state`
+            state = torch.full((s, 2), float("nan"), dtype=torch.float32, device="cuda")
+            ticks = torch.rand((64, s), device="cuda", generator=g) * 100
+            if dist == "quantised":
+                ticks = torch.round(ticks / 5) * 5
+            k6 = [dev.prebind("ring_ingest", ring, seen, t, ticks[i].contiguous()) for i in range(64)]
+            kh = dev.prebind("window_stats", ring, seen, t, o[0], o[1], om, o[2], state=state)
+            kc = dev.prebind("window_stats", ring, seen, t, o[0], o[1], om, o[2], variant="stream")
+            for name, fn in (("hinted", kh), ("stream_cold", kc)):
+                for i in range(6):
+                    k6[i](); fn()
+                evs = []
+                for i in range(40):
+                    k6[(6 + i) % 64]()
+                    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    e0.record(); fn(); e1.record()
+                    evs.append((e0, e1))
+                torch.cuda.synchronize()
+                out[f"{dist}_{name}_us"] = round(float(np.median([a.elapsed_time(b) for a, b in evs])) * 1e3, 2)
+            st = state.cpu().numpy()
+            out[dist + "_bracketed_frac"] = round(float(np.mean(st[:, 0] < st[:, 1])), 3)
         out[dist + "_min_us"] = round(float(min(reps)), 2)
         for x in (o[0], o[1], o[2]):
             digest.update(x.cpu().numpy().tobytes())
