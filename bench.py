@@ -278,7 +278,12 @@ def run_series_workload(ctx, wl):
     # arguments are validated once; a launch in the loop is then a single ctypes call
     k6s = [dev.prebind("ring_ingest", ring, seen, T, ticks[i]) for i in range(n_ticks)]   # K6
     tick_no = [0]
-    k7 = dev.prebind("window_stats", ring, seen, T, o_min, o_max, o_mean, o_p95)          # K7
+    k7_state = None
+    if args.k7 == "hinted":
+        # streaming form of K7: the bracket around every series' p95 is carried from step to step
+        # (exact whatever it holds); the steps ingest one fresh sample per series in between
+        k7_state = torch.full((S, 2), float("nan"), dtype=torch.float32, device="cuda")
+    k7 = dev.prebind("window_stats", ring, seen, T, o_min, o_max, o_mean, o_p95, state=k7_state)   # K7
     # the snapshot kernels do not touch the ring: they run on a second stream, beside K7
     side = torch.cuda.Stream()
     with torch.cuda.stream(side):
@@ -313,7 +318,7 @@ def run_series_workload(ctx, wl):
     kern_ms = float(np.mean([a.elapsed_time(b) for a, b in k7_events]))
     units = S * T
     value = units * world / (ms_per_step * 1e-3)
-    k7_bytes = S * (4 * T + 20)
+    k7_bytes = S * (4 * T + 20 + (16 if k7_state is not None else 0))
     e2e = e2e_series(ctx, wl, dict(ring=ring, ticks=ticks, bat=bat, flags=flags, mb=mb, off=off, ids=ids, snap=snap))
     e2e_ms = ctx.max_over_ranks(e2e["ms_per_step"])
     pk, pk_src = peaks()
@@ -330,7 +335,8 @@ def run_series_workload(ctx, wl):
                 "calls_per_step": "klm_collect_begin + klm_collect_end (two cycles in flight, one handle) + "
                                   "klm_reconcile (scheduler handle)"},
         "gpu_launches": n_launch,
-        "roofline": {"bound": "hbm", "kernel": "window_stats", "achieved": achieved, "peak": pk["hbm_gbs"],
+        "roofline": {"bound": "hbm", "kernel": "window_stats" + ("_hinted" if k7_state is not None else ""),
+                     "achieved": achieved, "peak": pk["hbm_gbs"],
                      "unit": "GB/s", "frac": achieved / pk["hbm_gbs"], "frac_of_nominal_8TBs": achieved / 8000.0,
                      "peak_source": pk_src, "algorithmic_bytes_per_launch": k7_bytes, "avg_launch_ms": kern_ms,
                      "launches_timed": len(k7_events), "traffic": K7_TRAFFIC_C2 if wl == "c2" else None},
@@ -748,6 +754,8 @@ def main():
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--only", action="store_true", help="run only --workload (no `workloads` sub-records)")
+    ap.add_argument("--k7", choices=["default", "hinted"], default="default",
+                    help="c2 / c3: klm_dev_window_stats (default) or its streaming form with carried brackets")
     ap.add_argument("--c5-probe", action="store_true",
                     help="c5, N > 1: probe the peers' shards in place instead of replicating them in K1")
     args = ap.parse_args()

@@ -184,6 +184,15 @@ window_stats_stream_kernel(const float* __restrict__ ring, const uint32_t* __res
   const int64_t s = s0 + o;
   const float* __restrict__ row = ring + s * (int64_t)pitch;
   const uint32_t sn = seen[s];  // consumed only after the first row loads are in flight
+#ifndef KLM_WSS_PF
+#define KLM_WSS_PF 0
+#endif
+  // KLM_WSS_PF == 2: one bulk-prefetch instruction asks L2 for this warp's whole row right away, so
+  // that the register buffers, which hold only a few rows, are refilled from L2 and not from DRAM
+  if (KLM_WSS_PF == 2 && lane == 0) {
+    const uint32_t bytes = ((uint32_t)window * 4u + 15u) & ~15u;
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" :: "l"(row), "r"(bytes) : "memory");
+  }
 
   unsigned char* list_g = s_raw + wib * Cfg::kListBytes;
   float* lst = reinterpret_cast<float*>(list_g) + lane;  // entry e: lst[e * 32]
@@ -240,12 +249,9 @@ window_stats_stream_kernel(const float* __restrict__ ring, const uint32_t* __res
     }
     return;
   }
-#ifndef KLM_WSS_PF
-#define KLM_WSS_PF 1
-#endif
-  // Ask L2 for the row that a warp will want about one residency later: one bulk-prefetch
-  // instruction covers the whole row.
-  if (KLM_WSS_PF != 0 && lane == 0) {
+  // (tuning builds, KLM_WSS_PF == 1: ask L2 for the row that a warp will want about one residency
+  // later; measured slower than no prefetch)
+  if (KLM_WSS_PF == 1 && lane == 0) {
     const int64_t later = o + (int64_t)kNumSMs * MINB * kWssWarps;
     if (later < n_series) {
       const uint32_t bytes = ((uint32_t)n * 4u + 15u) & ~15u;
