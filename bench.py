@@ -319,6 +319,15 @@ def run_series_workload(ctx, wl):
     units = S * T
     value = units * world / (ms_per_step * 1e-3)
     k7_bytes = S * (4 * T + 20 + (16 if k7_state is not None else 0))
+    # the stateless kernel on the same ring, for the record (every step above ran the form named in --k7)
+    k7_other = dev.prebind("window_stats", ring, seen, T, o_min, o_max, o_mean, o_p95)
+    oe = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(20)]
+    for a, b in oe:
+        k6s[tick_no[0] % n_ticks]()
+        tick_no[0] += 1
+        a.record(); k7_other(); b.record()
+    torch.cuda.synchronize()
+    stateless_ms = float(np.median([a.elapsed_time(b) for a, b in oe]))
     e2e = e2e_series(ctx, wl, dict(ring=ring, ticks=ticks, bat=bat, flags=flags, mb=mb, off=off, ids=ids, snap=snap))
     e2e_ms = ctx.max_over_ranks(e2e["ms_per_step"])
     pk, pk_src = peaks()
@@ -339,7 +348,11 @@ def run_series_workload(ctx, wl):
                      "achieved": achieved, "peak": pk["hbm_gbs"],
                      "unit": "GB/s", "frac": achieved / pk["hbm_gbs"], "frac_of_nominal_8TBs": achieved / 8000.0,
                      "peak_source": pk_src, "algorithmic_bytes_per_launch": k7_bytes, "avg_launch_ms": kern_ms,
-                     "launches_timed": len(k7_events), "traffic": K7_TRAFFIC_C2 if wl == "c2" else None},
+                     "launches_timed": len(k7_events), "traffic": K7_TRAFFIC_C2 if wl == "c2" else None,
+                     "stateless_kernel_launch_ms": stateless_ms,
+                     "note": "klm_dev_window_stats_hinted: the bracket around each series' p95 is carried from step "
+                             "to step (exact whatever it holds); stateless_kernel_launch_ms is klm_dev_window_stats "
+                             "alone on the same ring" if k7_state is not None else "klm_dev_window_stats"},
     }
     del ring, ticks
     torch.cuda.empty_cache()
@@ -754,8 +767,9 @@ def main():
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--only", action="store_true", help="run only --workload (no `workloads` sub-records)")
-    ap.add_argument("--k7", choices=["default", "hinted"], default="default",
-                    help="c2 / c3: klm_dev_window_stats (default) or its streaming form with carried brackets")
+    ap.add_argument("--k7", choices=["hinted", "stateless"], default="hinted",
+                    help="c2 / c3: K7 with the brackets carried from step to step (what klm_collect runs), or "
+                         "the stateless klm_dev_window_stats")
     ap.add_argument("--c5-probe", action="store_true",
                     help="c5, N > 1: probe the peers' shards in place instead of replicating them in K1")
     args = ap.parse_args()

@@ -133,6 +133,7 @@ struct klm_handle {
 
   // ring
   DevBuf ring, seen, ing_ids, ing_vals, stats_out;
+  DevBuf win_state;  // per series, the bracket K7 carries from one call to the next (2 floats; NaN: none)
   int64_t n_series = 0;
   int32_t window = 0, pitch = 0;
 
@@ -237,6 +238,20 @@ bool csr_non_decreasing(const int32_t* off, int64_t n) {
   int bad = 0;
   for (int64_t i = 0; i < n; ++i) bad |= off[i + 1] < off[i];
   return !bad;
+}
+
+// K7 over series [s0, s1) of the handle's ring. Rings whose windows the streaming kernel takes
+// (<= 8192 samples) run it with the per-series brackets of win_state: between two collection
+// ticks a window changes by one sample, so the previous bracket stands in for the pivot sampling
+// (klm.h, klm_dev_window_stats_hinted; exact whatever the bracket holds). p95 not wanted, or
+// longer windows: the stateless kernels.
+int ring_window_stats(klm_handle* h, int64_t s0, int64_t s1, float* d_min, float* d_max, double* d_mean,
+                      float* d_p95, cudaStream_t st) {
+  if (d_p95 != nullptr && h->window <= 8192 && h->win_state.p != nullptr)
+    return klm_dev_window_stats_hinted(h->ring.as<float>(), h->seen.as<uint32_t>(), h->window, h->pitch, s0, s1,
+                                       d_min, d_max, d_mean, d_p95, h->win_state.as<float>() + 2 * s0, st);
+  return klm_dev_window_stats(h->ring.as<float>(), h->seen.as<uint32_t>(), h->window, h->pitch, s0, s1, d_min,
+                              d_max, d_mean, d_p95, st);
 }
 
 // Apply the queued pushes in arrival order on `st` (staging block `which`). The host copy is
@@ -684,7 +699,7 @@ extern "C" void klm_destroy(klm_handle* h) {
                     &h->req_off,  &h->req_ids,  &h->res_idx,    &h->res_score,    &h->agg_cols,
                     &h->agg_pods, &h->agg_gpu,  &h->agg_out,    &h->agg_scratch,  &h->rate_in,
                     &h->rate_out, &h->pod_tot, &h->fleet_in, &h->fleet_out,  &h->fleet_scratch, &h->ring,
-                    &h->seen,     &h->ing_ids,  &h->ing_vals,   &h->stats_out};
+                    &h->seen,     &h->ing_ids,  &h->ing_vals,   &h->stats_out, &h->win_state};
   for (DevBuf* b : bufs) b->release();
   if (h->stream_bulk) cudaStreamSynchronize(h->stream_bulk);
   if (h->stream3) cudaStreamSynchronize(h->stream3);
@@ -1321,6 +1336,8 @@ extern "C" int klm_ring_create(klm_handle* h, int64_t n_series, int32_t window) 
   const size_t bytes = (size_t)n_series * pitch * sizeof(float);
   KLM_TRY(h->ring.ensure(bytes));
   KLM_TRY(h->seen.ensure((size_t)n_series * sizeof(uint32_t)));
+  KLM_TRY(h->win_state.ensure((size_t)n_series * 2 * sizeof(float)));
+  KLM_CUDA(cudaMemsetAsync(h->win_state.p, 0xFF, (size_t)n_series * 2 * sizeof(float), h->stream));  // NaN: no bracket
   KLM_CUDA(cudaMemsetAsync(h->ring.p, 0, bytes, h->stream));
   KLM_CUDA(cudaMemsetAsync(h->seen.p, 0, (size_t)n_series * sizeof(uint32_t), h->stream));
   KLM_TRY(sync(h->stream));
@@ -1415,6 +1432,8 @@ extern "C" int klm_ring_load(klm_handle* h, int64_t s0, int64_t s1, int32_t coun
   if (s1 == s0) return KLM_OK;
   const int64_t rows = s1 - s0;
   cudaStream_t st = h->stream;
+  // the rows change wholesale: their brackets would only cost time
+  KLM_CUDA(cudaMemsetAsync(h->win_state.as<float>() + 2 * s0, 0xFF, (size_t)rows * 2 * sizeof(float), st));
   // stage through device memory in chunks of <= 64 Mi samples (256 MiB)
   int64_t rows_per_chunk = rows;
   if (count > 0) {
@@ -1453,8 +1472,7 @@ extern "C" int klm_ring_stats(klm_handle* h, int64_t s0, int64_t s1, float* out_
   float* d_p95 = reinterpret_cast<float*>(o + 2 * c4);
   double* d_mean = reinterpret_cast<double*>(o + 3 * c4);
   cudaStream_t st = h->stream;
-  KLM_TRY(klm_dev_window_stats(h->ring.as<float>(), h->seen.as<uint32_t>(), h->window, h->pitch,
-                               s0, s1, d_min, d_max, d_mean, out_p95 ? d_p95 : nullptr, st));
+  KLM_TRY(ring_window_stats(h, s0, s1, d_min, d_max, d_mean, out_p95 ? d_p95 : nullptr, st));
   if (out_min) KLM_TRY(d2h(out_min, d_min, (size_t)rows * 4, st));
   if (out_max) KLM_TRY(d2h(out_max, d_max, (size_t)rows * 4, st));
   if (out_mean) KLM_TRY(d2h(out_mean, d_mean, (size_t)rows * 8, st));
@@ -1512,8 +1530,7 @@ int collect_impl(klm_handle* h, const klm_collect_in* in, const klm_collect_out*
     d_max = reinterpret_cast<float*>(o + c4);
     d_p95 = reinterpret_cast<float*>(o + 2 * c4);
     d_mean = reinterpret_cast<double*>(o + 3 * c4);
-    KLM_TRY(klm_dev_window_stats(h->ring.as<float>(), h->seen.as<uint32_t>(), h->window, h->pitch, 0, S,
-                                 d_min, d_max, d_mean, (out->win_p95 || out->win_packed) ? d_p95 : nullptr, st));
+    KLM_TRY(ring_window_stats(h, 0, S, d_min, d_max, d_mean, (out->win_p95 || out->win_packed) ? d_p95 : nullptr, st));
   }
   // ---- snapshot branch: one upload of the columns serves the rates and the aggregate
   const size_t col8 = align256((size_t)n * 8), col4 = align256((size_t)n * 4), col1 = align256((size_t)n);
@@ -1755,9 +1772,8 @@ int collect_begin_impl(klm_handle* h, const klm_collect_in* in, const klm_collec
     const size_t c4 = align256((size_t)S * 4);
     KLM_TRY(sl.stats.ensure((size_t)klm_collect_packed_bytes(S) + 256));
     char* o = sl.stats.as<char>();
-    KLM_TRY(klm_dev_window_stats(h->ring.as<float>(), h->seen.as<uint32_t>(), h->window, h->pitch, 0, S,
-                                 reinterpret_cast<float*>(o), reinterpret_cast<float*>(o + c4),
-                                 reinterpret_cast<double*>(o + 3 * c4), reinterpret_cast<float*>(o + 2 * c4), st));
+    KLM_TRY(ring_window_stats(h, 0, S, reinterpret_cast<float*>(o), reinterpret_cast<float*>(o + c4),
+                              reinterpret_cast<double*>(o + 3 * c4), reinterpret_cast<float*>(o + 2 * c4), st));
   }
   KLM_CUDA(cudaEventRecord(sl.k7, st));
   // ---- the one result download, behind K7, on its own stream
