@@ -59,8 +59,11 @@ struct WssAcc {
 
 // four valid elements of one lane: min / max / f64 sum into the accumulators of parity `odd`,
 // append(x > lox)
-template <int CLAMP>
-__device__ __forceinline__ void wss_row(WssAcc& a, uint32_t& c, uint32_t lb, float lox, float4 t,
+// COUNT: instead of the append, c += (x >= lox) and lb += (x > lox) -- the pass of a series whose
+// p95 sat on a block of equal samples last time (`lox` is that value): two counts settle whether
+// it still does, with no list and no select.
+template <int CLAMP, bool COUNT = false>
+__device__ __forceinline__ void wss_row(WssAcc& a, uint32_t& c, uint32_t& lb, float lox, float4 t,
                                         bool odd) {
   if (odd) {
     a.mn1 = fminf(fminf(a.mn1, t.x), fminf(t.y, fminf(t.z, t.w)));
@@ -70,6 +73,14 @@ __device__ __forceinline__ void wss_row(WssAcc& a, uint32_t& c, uint32_t lb, flo
     a.mn0 = fminf(fminf(a.mn0, t.x), fminf(t.y, fminf(t.z, t.w)));
     a.mx0 = fmaxf(fmaxf(a.mx0, t.x), fmaxf(t.y, fmaxf(t.z, t.w)));
     a.sum0 += ((double)t.x + (double)t.y) + ((double)t.z + (double)t.w);
+  }
+  if (COUNT) {
+    int ge = (int)c, gt = (int)lb;
+    inc_if_ge(ge, t.x, lox); inc_if_ge(ge, t.y, lox); inc_if_ge(ge, t.z, lox); inc_if_ge(ge, t.w, lox);
+    inc_if_gt(gt, t.x, lox); inc_if_gt(gt, t.y, lox); inc_if_gt(gt, t.z, lox); inc_if_gt(gt, t.w, lox);
+    c = (uint32_t)ge;
+    lb = (uint32_t)gt;
+    return;
   }
   c = min(c, (uint32_t)(CLAMP * 128));
   wss_append(c, lb, t.x, lox);
@@ -212,13 +223,16 @@ window_stats_stream_kernel(const float* __restrict__ ring, const uint32_t* __res
   // counting pass and one sort. The bracket is only a pivot: stale, wrong or garbage values cost
   // time, never exactness.
   float2 hint = make_float2(0.f, 0.f);
-  bool hinted = false;
+  bool hinted = false, tie_hinted = false;
   if (state != nullptr && want_p95) {
     hint = state[o];
     hinted = wjr >= kWssSampledMinRows && hint.x < hint.y && hint.x > NEG_INF;  // (NaN fails every test)
+    // floor == ceil: last time the p95 sat on a block of equal samples (quantised channels, flags,
+    // constants); the pass then only counts around that value
+    tie_hinted = hint.x == hint.y && hint.x > NEG_INF && hint.x < POS_INF;
   }
   float sm[4] = {NEG_INF, NEG_INF, NEG_INF, NEG_INF};
-  if (!hinted && want_p95 && wjr >= kWssSampledMinRows) {
+  if (!hinted && !tie_hinted && want_p95 && wjr >= kWssSampledMinRows) {
 #pragma unroll
     for (int q = 0; q < 4; ++q) sm[q] = __ldg(p + 128 * (((2 * q + 1) * wjr) >> 3) + q);
   }
@@ -263,8 +277,9 @@ window_stats_stream_kernel(const float* __restrict__ ring, const uint32_t* __res
   const int jr = nfull >> 5;  // rows valid in every lane
   const int k = n - p95_rank(n);
   hinted = hinted && n == window;  // (a ring that is still filling changes too fast for a bracket)
-  const bool sampled = want_p95 && jr >= kWssSampledMinRows && !hinted;
-  if (sampled && n != window) {  // partly filled ring (or a bracket dropped for it): sample the rows that hold data
+  tie_hinted = tie_hinted && n >= 1;
+  const bool sampled = want_p95 && jr >= kWssSampledMinRows && !hinted && !tie_hinted;
+  if (sampled && (n != window || hint.x < hint.y)) {  // partly filled ring, or a bracket dropped for it: sample the rows that hold data
 #pragma unroll
     for (int q = 0; q < 4; ++q) sm[q] = __ldg(p + 128 * (((2 * q + 1) * jr) >> 3) + q);
   }
@@ -323,6 +338,8 @@ window_stats_stream_kernel(const float* __restrict__ ring, const uint32_t* __res
     }
   } else if (hinted) {
     lox = next_down(hint.x);  // x > lox  <=>  x >= floor
+  } else if (tie_hinted) {
+    lox = POS_INF;            // (the tie pass lists nothing)
   } else if (want_p95) {
     lox = NEG_INF;  // short window: list every sample
   }
@@ -331,36 +348,52 @@ window_stats_stream_kernel(const float* __restrict__ ring, const uint32_t* __res
   // NBUF register buffers: the loads of NBUF - 1 chunks are in flight while one is consumed.
   WssAcc acc{POS_INF, POS_INF, NEG_INF, NEG_INF, 0.0, 0.0};
   uint32_t c128 = 0;
+  uint32_t tie_gt = 0;  // tie pass: samples > the tied value (c128 then counts those >= it)
   const int nch = jr >> 2;
-  if (nch > 0) {
+  auto pass = [&](auto row_fn, auto tail_fn) {
+    if (nch > 0) {
 #pragma unroll
-    for (int b = 0; b < NBUF - 1; ++b)  // chunks the early loads did not cover (cannot happen for
-      if (4 * b + 4 > wjr && b < nch) load_chunk(buf[b], b);  // n <= window; keeps buf defined)
+      for (int b = 0; b < NBUF - 1; ++b)  // chunks the early loads did not cover (cannot happen for
+        if (4 * b + 4 > wjr && b < nch) load_chunk(buf[b], b);  // n <= window; keeps buf defined)
 #pragma unroll 1
-    for (int c0 = 0; c0 < nch; c0 += NBUF) {
+      for (int c0 = 0; c0 < nch; c0 += NBUF) {
 #pragma unroll
-      for (int b = 0; b < NBUF; ++b) {
-        const int c = c0 + b;
-        if (c < nch) {
-          if (c + NBUF - 1 < nch) load_chunk(buf[(b + NBUF - 1) % NBUF], c + NBUF - 1);
+        for (int b = 0; b < NBUF; ++b) {
+          const int c = c0 + b;
+          if (c < nch) {
+            if (c + NBUF - 1 < nch) load_chunk(buf[(b + NBUF - 1) % NBUF], c + NBUF - 1);
 #pragma unroll
-          for (int i = 0; i < 4; ++i) wss_row<Cfg::kClamp>(acc, c128, lb, lox, buf[b][i], i & 1);
+            for (int i = 0; i < 4; ++i) row_fn(buf[b][i], i & 1);
+          }
         }
       }
     }
-  }
-  // the rows left over (at most three full ones), then the row that only some lanes hold
+    // the rows left over (at most three full ones), then the row that only some lanes hold
 #pragma unroll 1
-  for (int j = 4 * nch; j < jr; ++j)
-    wss_row<Cfg::kClamp>(acc, c128, lb, lox, ld_stream_f4(p + 128 * j), false);
-  if (lane + 32 * jr < nfull) wss_row<Cfg::kClamp>(acc, c128, lb, lox, ld_stream_f4(p + 128 * jr), false);
-  if (lane < (n & 3)) {
-    const float x = row[4 * nfull + lane];
-    acc.mn0 = fminf(acc.mn0, x);
-    acc.mx0 = fmaxf(acc.mx0, x);
-    acc.sum0 += (double)x;
-    c128 = min(c128, (uint32_t)(Cfg::kClamp * 128));
-    wss_append(c128, lb, x, lox);
+    for (int j = 4 * nch; j < jr; ++j) row_fn(ld_stream_f4(p + 128 * j), false);
+    if (lane + 32 * jr < nfull) row_fn(ld_stream_f4(p + 128 * jr), false);
+    if (lane < (n & 3)) {
+      const float x = row[4 * nfull + lane];
+      acc.mn0 = fminf(acc.mn0, x);
+      acc.mx0 = fmaxf(acc.mx0, x);
+      acc.sum0 += (double)x;
+      tail_fn(x);
+    }
+  };
+  if (tie_hinted) {
+    const float V = hint.x;
+    pass([&](float4 t, bool odd) { wss_row<Cfg::kClamp, true>(acc, c128, tie_gt, V, t, odd); },
+         [&](float x) {
+           c128 += x >= V;
+           tie_gt += x > V;
+         });
+  } else {
+    uint32_t lbv = lb;
+    pass([&](float4 t, bool odd) { wss_row<Cfg::kClamp, false>(acc, c128, lbv, lox, t, odd); },
+         [&](float x) {
+           c128 = min(c128, (uint32_t)(Cfg::kClamp * 128));
+           wss_append(c128, lb, x, lox);
+         });
   }
   __syncwarp();
   asm volatile("" ::: "memory");  // the appends above are plain shared-memory stores
@@ -382,9 +415,15 @@ window_stats_stream_kernel(const float* __restrict__ ring, const uint32_t* __res
   // ---- 4. p95 = k-th largest
   float result = 0.f;
   do {  // single-trip block: `break` = result (or the request to narrow) is final
+    if (tie_hinted) {
+      const int c_ge = warp_sum_i32((int)c128), c_gt = warp_sum_i32((int)tie_gt);
+      if (c_gt < k && k <= c_ge) { result = hint.x; next_hint = hint; break; }  // still on the same block
+      narrow = true;  // the p95 moved off that value: settle it from the row
+      break;
+    }
     if (narrow) break;
-    if (tie_hit) { result = tie_val; break; }
-    if (mn == mx) { result = mx; break; }  // constant series
+    if (tie_hit) { result = tie_val; next_hint = make_float2(tie_val, tie_val); break; }
+    if (mn == mx) { result = mx; next_hint = make_float2(mx, mx); break; }  // constant series
     int cnt = (int)(c128 >> 7);
     int total = warp_sum_i32(cnt);
     int maxcnt = warp_max_i32(cnt);
