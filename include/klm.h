@@ -524,6 +524,28 @@ int klm_dev_pod_rates(int64_t n_pods, const int32_t* ctr_off,
                       const int64_t* ctr_memory_limit, int64_t* pod_totals,
                       double* cpu_rate, double* memory_rate, double* cpu_util,
                       double* memory_util, uint8_t* over_limit, void* stream);
+/* Window-derived node features (NO reference semantics -- the reference
+ * parses last_update and drops it, controller.go:202-203, and scores the latest battery only;
+ * opt-in, parity unpinned). Turns the node table of a snapshot and the window statistics of
+ * the UAV ring (series node * 64 + channel; channel 21 remaining_percent, 24 battery
+ * temperature) into the table the scheduler then sees:
+ *   heartbeat_age[i] > max_age_s        -> status bit cleared (a stale node is no candidate)
+ *   p95(temperature) > temp_limit       -> status bit cleared
+ *   battery_out[i] = clamp(battery[i] - horizon_s * (max - min of remaining_percent) / span_s,
+ *                          0, battery[i])   (the charge projected horizon_s ahead at the window's drain)
+ * A parameter <= 0, or a NULL input array, switches its rule off. Feed battery_out / flags_out
+ * to klm_dev_node_best / klm_dev_schedule (or copy them out for klm_nodes_set). */
+typedef struct klm_feature_params {
+  double max_age_s;   /* staleness limit for heartbeat_age, seconds */
+  double temp_limit;  /* limit on the window's p95 battery temperature */
+  double horizon_s;   /* how far ahead the battery is projected */
+  double span_s;      /* time the window spans (window * sampling period) */
+} klm_feature_params;
+int klm_dev_node_features(int64_t n_nodes, const double* battery, const uint8_t* flags,
+                          const double* heartbeat_age, const float* win_min,
+                          const float* win_max, const float* win_p95,
+                          const klm_feature_params* params, double* battery_out,
+                          uint8_t* flags_out, void* stream);
 /* Device-pointer forms of klm_node_available / klm_network_quality / klm_pod_restarts /
  * klm_node_health; same arithmetic. */
 int klm_dev_node_available(int64_t n_nodes, const int64_t* cpu_capacity,

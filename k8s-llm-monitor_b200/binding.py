@@ -53,6 +53,11 @@ class ClusterOut(C.Structure):  # klm_cluster_out
         return {name: getattr(self, name) for name, _ in self._fields_}
 
 
+class FeatureParams(C.Structure):  # klm_feature_params
+    _fields_ = [("max_age_s", C.c_double), ("temp_limit", C.c_double), ("horizon_s", C.c_double),
+                ("span_s", C.c_double)]
+
+
 class CollectIn(C.Structure):  # klm_collect_in
     _fields_ = [("tick_values", C.c_void_p), ("nodes", C.POINTER(NodeCols)), ("n_nodes", C.c_int64),
                 ("disk_capacity", C.c_void_p), ("disk_allocatable", C.c_void_p),
@@ -102,6 +107,7 @@ SIGNATURES = {
     "klm_dev_network_quality": (C.c_int, [_I64, _P, _P, _P, _P]),
     "klm_dev_pod_restarts": (C.c_int, [_I64, _P, _P, _P, _P]),
     "klm_dev_node_health": (C.c_int, [_I64, _P, _P, _P, _P, _P, _P]),
+    "klm_dev_node_features": (C.c_int, [_I64, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
     "klm_ring_create": (C.c_int, [_P, _I64, _I32]),
     "klm_ring_ingest": (C.c_int, [_P, _I64, _P, _P]),
     "klm_ring_ingest_tick": (C.c_int, [_P, _P]),
@@ -703,6 +709,14 @@ class Dev:
         check(self.lib.klm_dev_schedule_sharded(n, n_total, ab, af, _dp(my_slots), epoch, min_battery.numel(),
                                                 _dp(min_battery), _dp(pref_off), _dp(pref_ids), _dp(out_idx),
                                                 _dp(out_score), int(table_from_k1), _stream_ptr(stream)))
+
+    def node_features(self, battery, flags, heartbeat_age, win_min, win_max, win_p95, params: dict, battery_out,
+                      flags_out, stream=None):
+        """klm_dev_node_features: window statistics + heartbeat age -> the node table the scheduler sees."""
+        prm = FeatureParams(**params)
+        check(self.lib.klm_dev_node_features(battery.numel(), _dp(battery), _dp(flags), _dp(heartbeat_age), _dp(win_min),
+                                             _dp(win_max), _dp(win_p95), C.byref(prm), _dp(battery_out),
+                                             _dp(flags_out), _stream_ptr(stream)))
 
     def shard_rendezvous(self, n_parts: int, my_part: int, slot_ptrs, my_slots, epoch, stream=None):
         """Device-side rendezvous of the ranks (slot arrays of its own; epoch as in node_best_publish)."""

@@ -144,3 +144,53 @@ extern "C" int klm_dev_node_health(int64_t n, const int32_t* cond_off, const uin
   KLM_LAUNCH_CHECK("node_health_kernel");
   return KLM_OK;
 }
+
+// ------------------------------------------------- window-derived node features
+//
+// NOT IN THE REFERENCE: controller.go:202-203 parses last_update and drops it, manager.go:296-313
+// records heartbeats nobody reads, and no score looks at history. This opt-in step connects the
+// window statistics (K7) to the scheduler's inputs (K1 / K2): per UAV node i, from the node's ring
+// rows (series i * 64 + channel, host/klm_wire.h channel map),
+//   stale      heartbeat_age[i] > max_age_s                     -> node ineligible (status bit cleared)
+//   too hot    p95 of battery temperature (channel 24) > temp_limit -> node ineligible
+//   projected  battery[i] - horizon_s * drain, drain = (max - min of remaining_percent, channel 21)
+//              / span_s, clamped to [0, battery[i]]             -> the battery the scheduler scores
+// Parity: unpinned by construction (no reference semantics); the oracle restates this definition.
+namespace klm {
+__global__ void __launch_bounds__(256)
+node_features_kernel(int64_t n, const double* __restrict__ battery, const uint8_t* __restrict__ flags,
+                     const double* __restrict__ heartbeat_age, const float* __restrict__ win_min,
+                     const float* __restrict__ win_max, const float* __restrict__ win_p95,
+                     klm_feature_params prm, double* __restrict__ battery_out, uint8_t* __restrict__ flags_out) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    uint8_t f = flags[i];
+    double b = battery[i];
+    if (heartbeat_age && prm.max_age_s > 0 && heartbeat_age[i] > prm.max_age_s) f &= (uint8_t)~KLM_NODE_STATUS_OK;
+    if (win_p95 && prm.temp_limit > 0 && (double)win_p95[i * 64 + 24] > prm.temp_limit) f &= (uint8_t)~KLM_NODE_STATUS_OK;
+    if (win_min && win_max && prm.horizon_s > 0 && prm.span_s > 0) {
+      const double drop = (double)win_max[i * 64 + 21] - (double)win_min[i * 64 + 21];  // exact in f64
+      double proj = b - __dmul_rn(__ddiv_rn(drop, prm.span_s), prm.horizon_s);
+      if (proj < 0) proj = 0;
+      if (proj < b) b = proj;
+    }
+    battery_out[i] = b;
+    flags_out[i] = f;
+  }
+}
+}  // namespace klm
+
+extern "C" int klm_dev_node_features(int64_t n, const double* battery, const uint8_t* flags,
+                                     const double* heartbeat_age, const float* win_min, const float* win_max,
+                                     const float* win_p95, const klm_feature_params* prm, double* battery_out,
+                                     uint8_t* flags_out, void* stream) {
+  if (n < 0 || !prm || (n > 0 && (!battery || !flags || !battery_out || !flags_out))) {
+    set_error("klm_dev_node_features: bad argument");
+    return KLM_EINVAL;
+  }
+  if (n == 0) return KLM_OK;
+  node_features_kernel<<<grid1d(n), 256, 0, as_stream(stream)>>>(n, battery, flags, heartbeat_age, win_min, win_max,
+                                                                 win_p95, *prm, battery_out, flags_out);
+  KLM_LAUNCH_CHECK("node_features_kernel");
+  return KLM_OK;
+}

@@ -369,6 +369,31 @@ KLMO_API void klmo_node_health(int64_t n, const int32_t* cond_off, const uint8_t
   }
 }
 
+/* Window-derived node features: NOT in the reference (controller.go:202-203
+ * drops last_update; no score reads history) -- the build's own definition, parity unpinned:
+ * stale heartbeat or a hot battery (p95 of channel 24) clears the status bit; the battery is
+ * projected horizon_s ahead at the window's drain of channel 21, clamped to [0, battery]. */
+KLMO_API void klmo_node_features(int64_t n, const double* battery, const uint8_t* flags,
+                                 const double* age, const float* wmin, const float* wmax,
+                                 const float* wp95, double max_age_s, double temp_limit,
+                                 double horizon_s, double span_s, double* battery_out,
+                                 uint8_t* flags_out) {
+  for (int64_t i = 0; i < n; ++i) {
+    uint8_t f = flags[i];
+    double b = battery[i];
+    if (age && max_age_s > 0 && age[i] > max_age_s) f &= (uint8_t)~2u;
+    if (wp95 && temp_limit > 0 && (double)wp95[i * 64 + 24] > temp_limit) f &= (uint8_t)~2u;
+    if (wmin && wmax && horizon_s > 0 && span_s > 0) {
+      const double drop = (double)wmax[i * 64 + 21] - (double)wmin[i * 64 + 21];
+      double proj = b - drop / span_s * horizon_s;
+      if (proj < 0) proj = 0;
+      if (proj < b) b = proj;
+    }
+    battery_out[i] = b;
+    flags_out[i] = f;
+  }
+}
+
 /* NetworkMetrics.GetQuality, pkg/metrics/types.go:187-199:
  * 0 disconnected, 1 excellent, 2 good, 3 fair, 4 poor. */
 KLMO_API void klmo_network_quality(int64_t n, const uint8_t* connected,

@@ -191,3 +191,15 @@ def node_health(cond_off, cond_type, cond_status):
     f.restype = None
     f(C.c_int64(n), _p(off), _p(t), _p(s), _p(healthy), _p(failing))
     return healthy, failing
+
+
+def node_features(battery, flags, age, wmin, wmax, wp95, max_age_s, temp_limit, horizon_s, span_s):
+    b, f = _a(battery, np.float64), _a(flags, np.uint8)
+    a = _a(age, np.float64)
+    mn, mx, p = _a(wmin, np.float32), _a(wmax, np.float32), _a(wp95, np.float32)
+    bo, fo = np.empty_like(b), np.empty_like(f)
+    fn = lib().klmo_node_features
+    fn.restype = None
+    fn(C.c_int64(b.size), _p(b), _p(f), _p(a), _p(mn), _p(mx), _p(p), C.c_double(max_age_s), C.c_double(temp_limit),
+       C.c_double(horizon_s), C.c_double(span_s), _p(bo), _p(fo))
+    return bo, fo
