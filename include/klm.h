@@ -174,6 +174,18 @@ int klm_schedule_batch(klm_handle* h, int64_t n_requests,
                        const int32_t* pref_ids, int32_t* out_idx,
                        double* out_score, int mode);
 
+/* The k best candidates of every request, in the order the reference's
+ * stable descending sort leaves them (controller.go:160: score desc, list index asc); the
+ * reference keeps only [0] (:161), so k = 1 gives exactly klm_schedule_batch and anything
+ * beyond has no reference semantics (examples/multi-pod-request.yaml asks for two GPUs nobody
+ * assigns). out_idx / out_score are [n_requests][k], padded with -1 / 0 when a request has fewer
+ * than k candidates. 1 <= k <= klm_topk_max() (8). One-device handles. */
+int klm_topk_max(void);
+int klm_schedule_batch_topk(klm_handle* h, int64_t n_requests,
+                            const double* min_battery, const int32_t* pref_off,
+                            const int32_t* pref_ids, int k, int32_t* out_idx,
+                            double* out_score);
+
 /* One reconcile in one call (controller.go:88-110: one UAV snapshot, then every
  * pending request): klm_nodes_set + klm_schedule_batch with the same arguments,
  * results and errors, under one lock. A reconcile whose arrays fit the 256 KB
@@ -384,6 +396,17 @@ int klm_dev_schedule(const double* battery, const uint8_t* flags,
                      int64_t n_requests, const double* min_battery,
                      const int32_t* pref_off, const int32_t* pref_ids,
                      int32_t* out_idx, double* out_score, void* stream);
+/* Top-k forms of K1 / K2 (klm_schedule_batch_topk): top = the k best eligible nodes of the
+ * table as k (index int64, battery bits) pairs; scratch as for klm_dev_node_best
+ * (klm_dev_node_topk_scratch_bytes() bytes, zero-filled once). */
+int64_t klm_dev_node_topk_scratch_bytes(void);
+int klm_dev_node_topk(const double* battery, const uint8_t* flags, int64_t n_nodes,
+                      int64_t node_base, int k, int64_t* top, void* scratch, void* stream);
+int klm_dev_schedule_topk(const double* battery, const uint8_t* flags, int64_t n_nodes,
+                          int64_t node_base, const int64_t* top, int k, int64_t n_requests,
+                          const double* min_battery, const int32_t* pref_off,
+                          const int32_t* pref_ids, int32_t* out_idx, double* out_score,
+                          void* stream);
 /* K2 launched to overlap the kernel before it on `stream` (no reference
  * counterpart; same result as klm_dev_schedule). Meant for the pair
  * klm_dev_node_best -> this call: K2 starts while K1 is still running, issues

@@ -94,6 +94,11 @@ SIGNATURES = {
     "klm_host_free": (C.c_int, [_P]),
     "klm_nodes_set": (C.c_int, [_P, _I64, _P, _P]),
     "klm_schedule_batch": (C.c_int, [_P, _I64, _P, _P, _P, _P, _P, C.c_int]),
+    "klm_topk_max": (C.c_int, []),
+    "klm_schedule_batch_topk": (C.c_int, [_P, _I64, _P, _P, _P, C.c_int, _P, _P]),
+    "klm_dev_node_topk_scratch_bytes": (_I64, []),
+    "klm_dev_node_topk": (C.c_int, [_P, _P, _I64, _I64, C.c_int, _P, _P, _P]),
+    "klm_dev_schedule_topk": (C.c_int, [_P, _P, _I64, _I64, _P, C.c_int, _I64, _P, _P, _P, _P, _P, _P]),
     "klm_reconcile": (C.c_int, [_P, _I64, _P, _P, _I64, _P, _P, _P, _P, _P, C.c_int]),
     "klm_cluster_aggregate": (C.c_int, [_P, C.POINTER(NodeCols), _I64, _P, _I64, C.POINTER(ClusterOut)]),
     "klm_node_rates": (C.c_int, [_P, _I64] + [_P] * 11),
@@ -256,6 +261,17 @@ class Handle:
             ids = np.zeros(1, np.int32)
         check(self._lib.klm_schedule_batch(self._h, r, _ptr(mb), _ptr(off), _ptr(ids),
                                            _ptr(out_idx), _ptr(out_score), algo))
+        return out_idx, out_score
+
+    def schedule_batch_topk(self, min_battery, pref_off, pref_ids, k: int) -> Tuple[np.ndarray, np.ndarray]:
+        """klm_schedule_batch_topk: ([R, k] indices, [R, k] scores), -1 / 0 padded."""
+        mb, off, ids = _np(min_battery, np.float64), _np(pref_off, np.int32), _np(pref_ids, np.int32)
+        r = mb.size
+        out_idx, out_score = np.empty((r, k), np.int32), np.empty((r, k), np.float64)
+        if ids.size == 0:
+            ids = np.zeros(1, np.int32)
+        check(self._lib.klm_schedule_batch_topk(self._h, r, _ptr(mb), _ptr(off), _ptr(ids), k, _ptr(out_idx),
+                                                _ptr(out_score)))
         return out_idx, out_score
 
     def reconcile(self, battery, flags, min_battery, pref_off, pref_ids, algo: int = ALGO_DECOMPOSED

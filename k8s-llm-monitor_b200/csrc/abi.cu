@@ -125,6 +125,7 @@ struct klm_handle {
   DevBuf best, best_scratch;
   DevBuf req_min, req_off, req_ids, res_idx, res_score;
   DevBuf snap_out;  // klm_collect, small snapshots: cluster_out | the five rate columns
+  DevBuf topk_top, topk_scratch;  // klm_schedule_batch_topk: the global top-k list; its scratch
 
   // aggregation
   DevBuf agg_cols, agg_pods, agg_gpu, agg_out, agg_scratch;
@@ -699,7 +700,8 @@ extern "C" void klm_destroy(klm_handle* h) {
                     &h->req_off,  &h->req_ids,  &h->res_idx,    &h->res_score,    &h->agg_cols,
                     &h->agg_pods, &h->agg_gpu,  &h->agg_out,    &h->agg_scratch,  &h->rate_in,
                     &h->rate_out, &h->pod_tot, &h->fleet_in, &h->fleet_out,  &h->fleet_scratch, &h->ring,
-                    &h->seen,     &h->ing_ids,  &h->ing_vals,   &h->stats_out, &h->win_state};
+                    &h->seen,     &h->ing_ids,  &h->ing_vals,   &h->stats_out, &h->win_state,
+                    &h->topk_top, &h->topk_scratch};
   for (DevBuf* b : bufs) b->release();
   if (h->stream_bulk) cudaStreamSynchronize(h->stream_bulk);
   if (h->stream3) cudaStreamSynchronize(h->stream3);
@@ -939,6 +941,59 @@ extern "C" int klm_schedule_batch(klm_handle* h, int64_t R, const double* min_ba
                                 node_shard);
   if (rc != KLM_OK) multi_sync(h);  // nothing may still write the caller's arrays
   return rc;
+}
+
+// The k best candidates of every request (the reference keeps only [0] of its
+// sorted list, controller.go:160-161).
+extern "C" int klm_schedule_batch_topk(klm_handle* h, int64_t R, const double* min_battery,
+                                       const int32_t* pref_off, const int32_t* pref_ids, int k,
+                                       int32_t* out_idx, double* out_score) {
+  KLM_ENTER(h);
+  if (!h->devs.empty()) {
+    set_error("klm_schedule_batch_topk: not available on a handle over several devices");
+    return KLM_EINVAL;
+  }
+  if (h->n_nodes < 0) {
+    set_error("klm_schedule_batch_topk: no node snapshot; call klm_nodes_set first");
+    return KLM_ESTATE;
+  }
+  if (R < 0 || k < 1 || k > klm_topk_max()) {
+    set_error("klm_schedule_batch_topk: bad argument (1 <= k <= %d)", klm_topk_max());
+    return k > klm_topk_max() ? KLM_ELIMIT : KLM_EINVAL;
+  }
+  if (R == 0) return KLM_OK;
+  if (!min_battery || !pref_off || !out_idx || !out_score) {
+    set_error("klm_schedule_batch_topk: null array");
+    return KLM_EINVAL;
+  }
+  const int64_t n_ids = pref_off[R];
+  if (pref_off[0] != 0 || n_ids < 0 || (n_ids > 0 && !pref_ids) || !csr_non_decreasing(pref_off, R)) {
+    set_error("klm_schedule_batch_topk: pref_off must start at 0 and not decrease; pref_ids non-null");
+    return KLM_EINVAL;
+  }
+  if (!h->topk_scratch.p) {
+    KLM_TRY(h->topk_scratch.ensure((size_t)klm_dev_node_topk_scratch_bytes()));
+    KLM_TRY(h->topk_top.ensure(2 * 8 * sizeof(int64_t)));
+    KLM_CUDA(cudaMemsetAsync(h->topk_scratch.p, 0, 256, h->stream));
+  }
+  const size_t min_bytes = (size_t)R * 8, off_bytes = (size_t)(R + 1) * 4, ids_bytes = (size_t)n_ids * 4;
+  KLM_TRY(h->req_min.ensure(min_bytes));
+  KLM_TRY(h->req_off.ensure(off_bytes));
+  KLM_TRY(h->req_ids.ensure(ids_bytes ? ids_bytes : 4));
+  KLM_TRY(h->res_idx.ensure((size_t)R * k * 4));
+  KLM_TRY(h->res_score.ensure((size_t)R * k * 8));
+  cudaStream_t st = h->stream;
+  KLM_TRY(h2d(h->req_min.p, min_battery, min_bytes, st));
+  KLM_TRY(h2d(h->req_off.p, pref_off, off_bytes, st));
+  KLM_TRY(h2d(h->req_ids.p, pref_ids, ids_bytes, st));
+  KLM_TRY(klm_dev_node_topk(h->d_battery, h->d_flags, h->n_nodes, 0, k, h->topk_top.as<int64_t>(),
+                            h->topk_scratch.p, st));
+  KLM_TRY(klm_dev_schedule_topk(h->d_battery, h->d_flags, h->n_nodes, 0, h->topk_top.as<int64_t>(), k, R,
+                                h->req_min.as<double>(), h->req_off.as<int32_t>(), h->req_ids.as<int32_t>(),
+                                h->res_idx.as<int32_t>(), h->res_score.as<double>(), st));
+  KLM_TRY(d2h(out_idx, h->res_idx.p, (size_t)R * k * 4, st));
+  KLM_TRY(d2h(out_score, h->res_score.p, (size_t)R * k * 8, st));
+  return sync(st);
 }
 
 // One reconcile (controller.go:88-110): install the snapshot and decide every pending request.

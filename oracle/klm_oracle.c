@@ -369,6 +369,45 @@ KLMO_API void klmo_node_health(int64_t n, const int32_t* cond_off, const uint8_t
   }
 }
 
+/* Top-k: the literal candidate list of controller.go:174-221 in list order,
+ * sorted by a STABLE descending sort on Score (controller.go:160), cut at k. The reference takes
+ * [0] only (:161); beyond that there are no reference semantics (parity unpinned).
+ * out_idx / out_score are [R][k], padded with -1 / 0. */
+KLMO_API int klmo_schedule_topk(int64_t n, const double* battery, const uint8_t* flags, int64_t r,
+                                const double* min_battery, const int32_t* pref_off,
+                                const int32_t* pref_ids, int k, int32_t* out_idx,
+                                double* out_score) {
+  double* cs = (double*)malloc((size_t)(n > 0 ? n : 1) * sizeof(double));
+  int32_t* ci = (int32_t*)malloc((size_t)(n > 0 ? n : 1) * sizeof(int32_t));
+  if (!cs || !ci) { free(cs); free(ci); return -1; }
+  for (int64_t q = 0; q < r; ++q) {
+    int64_t m = 0;
+    const double mb = min_battery[q];
+    for (int64_t i = 0; i < n; ++i) {                         /* :181 items in list order */
+      if (!(flags[i] & 1u)) continue;                         /* :190 */
+      if (mb > 0 && battery[i] < mb) continue;                /* :194 */
+      if (!(flags[i] & 2u)) continue;                         /* :198 */
+      double sc = battery[i];                                 /* :205 */
+      for (int32_t p = pref_off[q]; p < pref_off[q + 1]; ++p)
+        if (pref_ids[p] == i) { sc += 10; break; }            /* :206-208 */
+      cs[m] = sc; ci[m] = (int32_t)i; ++m;
+    }
+    /* stable descending insertion sort of the first k places (what SliceStable + [0:k] yields) */
+    for (int j = 0; j < k; ++j) {
+      int64_t best = -1;
+      for (int64_t c = 0; c < m; ++c) {
+        if (ci[c] < 0) continue;                              /* already taken */
+        if (best < 0 || cs[c] > cs[best]) best = c;           /* strict >: the earlier one stays on ties */
+      }
+      if (best < 0) { out_idx[q * k + j] = -1; out_score[q * k + j] = 0.0; continue; }
+      out_idx[q * k + j] = ci[best]; out_score[q * k + j] = cs[best];
+      ci[best] = -1;
+    }
+  }
+  free(cs); free(ci);
+  return 0;
+}
+
 /* Window-derived node features: NOT in the reference (controller.go:202-203
  * drops last_update; no score reads history) -- the build's own definition, parity unpinned:
  * stale heartbeat or a hot battery (p95 of channel 24) clears the status bit; the battery is

@@ -203,3 +203,16 @@ def node_features(battery, flags, age, wmin, wmax, wp95, max_age_s, temp_limit, 
     fn(C.c_int64(b.size), _p(b), _p(f), _p(a), _p(mn), _p(mx), _p(p), C.c_double(max_age_s), C.c_double(temp_limit),
        C.c_double(horizon_s), C.c_double(span_s), _p(bo), _p(fo))
     return bo, fo
+
+
+def schedule_topk(battery, flags, min_battery, pref_off, pref_ids, k):
+    b, f = _a(battery, np.float64), _a(flags, np.uint8)
+    mb, off, ids = _a(min_battery, np.float64), _a(pref_off, np.int32), _a(pref_ids, np.int32)
+    r = mb.size
+    oi, os_ = np.empty((r, k), np.int32), np.empty((r, k), np.float64)
+    fn = lib().klmo_schedule_topk
+    fn.restype = C.c_int
+    rc = fn(C.c_int64(b.size), _p(b), _p(f), C.c_int64(r), _p(mb), _p(off), _p(ids if ids.size else np.zeros(1, np.int32)),
+            C.c_int(k), _p(oi), _p(os_))
+    assert rc == 0
+    return oi, os_

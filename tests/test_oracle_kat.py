@@ -206,3 +206,15 @@ def test_predicate_leftovers_hand_derived():
     # node 3: Ready=Unknown + an unrelated condition that is True
     healthy, failing = ob.node_health([0, 1, 3, 3, 5], [0, 0, 1, 0, 5], [1, 1, 1, 2, 1])
     assert list(healthy) == [1, 0, 1, 0] and list(failing) == [0, 2, 0, 1]
+
+
+def test_topk_oracle_hand_derived():
+    """Top-k restatement pinned on the reference's own fixture (derived by hand from
+    controller.go:160, :174-221; the reference itself keeps only [0])."""
+    import oracle_binding as ob
+    idx, score = ob.schedule_topk([85.0, 75.0, 90.0], [3, 3, 3], [60.0], [0, 2], [1, 2], 3)
+    assert idx.tolist() == [[2, 0, 1]] and score.tolist() == [[100.0, 85.0, 85.0]]
+    idx, score = ob.schedule_topk([100.0, 100.0, 100.0], [3, 3, 3], [50.0], [0, 1], [0], 2)   # Fixture B
+    assert idx.tolist() == [[0, 1]] and score.tolist() == [[110.0, 100.0]]
+    idx, _ = ob.schedule_topk([10.0, 20.0], [3, 1], [0.0], [0, 0], [], 2)
+    assert idx.tolist() == [[0, -1]]
