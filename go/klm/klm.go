@@ -621,3 +621,38 @@ func ShardRange(nNodes int64, parts, part int) (lo, hi int64) {
 	C.klm_shard_range(C.int64_t(nNodes), C.int(parts), C.int(part), &a, &b)
 	return int64(a), int64(b)
 }
+
+// TopKMax is the largest k ScheduleBatchTopK accepts.
+func TopKMax() int { return int(C.klm_topk_max()) }
+
+// ScheduleBatchTopK returns, for every request, its k best candidates in the order
+// sort.SliceStable leaves them (controller.go:160); the reference keeps only [0] (:161).
+// idx and score are [len(minBattery)][k] flattened, padded with -1 / 0.
+func (k *Handle) ScheduleBatchTopK(minBattery []float64, prefOff, prefIDs []int32, topK int) ([]int32, []float64, error) {
+	r := len(minBattery)
+	if len(prefOff) != r+1 {
+		return nil, nil, fmt.Errorf("klm: prefOff must have len(minBattery)+1 entries")
+	}
+	if n := int(prefOff[r]); n < 0 || n > len(prefIDs) {
+		return nil, nil, fmt.Errorf("klm: prefOff[len] = %d but %d preferred ids", n, len(prefIDs))
+	}
+	if topK < 1 || topK > TopKMax() {
+		return nil, nil, fmt.Errorf("klm: k must be in [1, %d]", TopKMax())
+	}
+	idx, score := make([]int32, r*topK), make([]float64, r*topK)
+	if r == 0 {
+		return idx, score, nil
+	}
+	ids := prefIDs
+	if len(ids) == 0 {
+		ids = []int32{0}
+	}
+	err := call("klm_schedule_batch_topk", func() C.int {
+		return C.klm_schedule_batch_topk(k.h, C.int64_t(r), f64p(minBattery), i32p(prefOff), i32p(ids),
+			C.int(topK), i32p(idx), f64p(score))
+	})
+	if err != nil {
+		return nil, nil, err
+	}
+	return idx, score, nil
+}
