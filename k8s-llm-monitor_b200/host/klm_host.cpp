@@ -97,6 +97,116 @@ std::vector<SchedulingRequestStatus> Controller::Reconcile(
   return out;
 }
 
+// ---- multi-assignment with per-node capacity (NO reference semantics: the
+// reference assigns every request independently and ignores e.g. gpu-count). Requests are taken in
+// list order; a node can be chosen `capacity[i]` times in this reconcile and is no candidate once it
+// is full. One GPU call gives every request its k best candidates on the snapshot; walking them in
+// order, the first candidate that still has room is exactly what a sequential buildCandidates over
+// the remaining nodes would choose (every node ranked before it is in the list and full). Only when
+// a whole list of k is full are the remaining requests re-batched against the snapshot without
+// the full nodes.
+std::vector<SchedulingRequestStatus> Controller::ReconcileWithCapacity(
+    const std::vector<SchedulingRequest>& requests, const std::vector<UAVMetricItem>& uavs,
+    std::vector<int32_t> capacity) {
+  const int64_t n = static_cast<int64_t>(uavs.size());
+  if (static_cast<int64_t>(capacity.size()) != n) throw std::runtime_error("capacity: one entry per UAV item");
+  std::vector<double> battery(n);
+  std::vector<uint8_t> flags(n);
+  std::unordered_map<std::string, std::vector<int32_t>> by_name;
+  for (int64_t i = 0; i < n; ++i) {
+    const UAVMetricItem& u = uavs[i];
+    const std::string name = u.HasNodeName ? u.NodeName : std::string();
+    battery[i] = u.HasBattery ? u.Battery : 0.0;
+    const std::string st = u.HasStatus ? ToLower(u.CollectionStatus) : std::string();
+    uint8_t f = 0;
+    if (!name.empty()) f |= KLM_NODE_HAS_NAME;
+    if (st.empty() || st == "active") f |= KLM_NODE_STATUS_OK;
+    flags[i] = f;
+    if (!name.empty()) by_name[ToLower(name)].push_back(static_cast<int32_t>(i));
+  }
+  std::vector<SchedulingRequestStatus> out(requests.size());
+  std::vector<size_t> live;
+  std::vector<double> min_battery;
+  std::vector<int32_t> pref_off{0}, pref_ids;
+  for (size_t r = 0; r < requests.size(); ++r) {
+    const SchedulingRequest& q = requests[r];
+    if (q.HasPhase && !q.Phase.empty() && q.Phase != "Pending") continue;
+    out[r].Updated = true;
+    if (q.Spec.Workload.Name.empty() || q.Spec.Workload.Namespace.empty()) {
+      out[r].Phase = "Failed";
+      out[r].Message = "workload name/namespace 不能为空";
+      continue;
+    }
+    live.push_back(r);
+    min_battery.push_back(q.Spec.MinBatteryPercent);
+    std::unordered_map<std::string, bool> seen;
+    for (const std::string& p : q.Spec.PreferredNodes) {
+      const std::string lp = ToLower(p);
+      if (seen.emplace(lp, true).second) {
+        auto it = by_name.find(lp);
+        if (it != by_name.end()) pref_ids.insert(pref_ids.end(), it->second.begin(), it->second.end());
+      }
+    }
+    pref_off.push_back(static_cast<int32_t>(pref_ids.size()));
+  }
+  if (live.empty()) return out;
+  if (pref_ids.empty()) pref_ids.push_back(0);
+  const int k = klm_topk_max();
+  std::vector<int32_t> idx;
+  std::vector<double> score;
+  size_t batch_from = 0;  // the candidate lists in idx / score start at this live request
+  auto rebatch = [&](size_t from) {
+    // the snapshot without the nodes that are full; offsets re-based to the first remaining request
+    std::vector<uint8_t> f2(flags);
+    for (int64_t i = 0; i < n; ++i)
+      if (capacity[i] <= 0) f2[i] = static_cast<uint8_t>(f2[i] & ~KLM_NODE_STATUS_OK);
+    const size_t m = live.size() - from;
+    std::vector<int32_t> off2(m + 1);
+    for (size_t j = 0; j <= m; ++j) off2[j] = pref_off[from + j] - pref_off[from];
+    idx.assign(m * k, -1);
+    score.assign(m * k, 0.0);
+    check(klm_nodes_set(h_, n, battery.data(), f2.data()), "klm_nodes_set");
+    check(klm_schedule_batch_topk(h_, static_cast<int64_t>(m), min_battery.data() + from, off2.data(),
+                                  pref_ids.data() + pref_off[from], k, idx.data(), score.data()),
+          "klm_schedule_batch_topk");
+    batch_from = from;
+  };
+  rebatch(0);
+  for (size_t q = 0; q < live.size(); ++q) {
+    SchedulingRequestStatus& s = out[live[q]];
+    int32_t chosen = -1;
+    double chosen_score = 0;
+    for (int attempt = 0; attempt < 2 && chosen < 0; ++attempt) {
+      const int32_t* li = idx.data() + (q - batch_from) * k;
+      const double* ls = score.data() + (q - batch_from) * k;
+      int listed = 0;
+      for (int j = 0; j < k && li[j] >= 0; ++j) {
+        ++listed;
+        if (capacity[li[j]] > 0) {
+          chosen = li[j];
+          chosen_score = ls[j];
+          break;
+        }
+      }
+      if (chosen >= 0 || listed < k || attempt == 1) break;  // a short list names every candidate there is
+      rebatch(q);  // all k are full: look further down, for this request and the ones after it
+    }
+    if (chosen < 0) {
+      s.Phase = "Failed";
+      s.Message = "无满足要求的 UAV 节点";
+      continue;
+    }
+    --capacity[chosen];
+    const UAVMetricItem& c = uavs[chosen];
+    s.Phase = "Assigned";
+    s.AssignedNode = c.NodeName;
+    s.AssignedUAV = c.UAVID;
+    s.Score = chosen_score;
+    s.Message = sprintf1("选中节点 %s (电量 %.1f%%)", c.NodeName.c_str(), battery[chosen]);
+  }
+  return out;
+}
+
 ClusterMetrics Manager::CalculateClusterMetrics(const std::vector<NodeMetrics>& nodes,
                                                 const std::vector<PodMetrics>& pods) {
   const int64_t n = static_cast<int64_t>(nodes.size()), p = static_cast<int64_t>(pods.size());

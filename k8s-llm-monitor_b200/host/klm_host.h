@@ -65,6 +65,11 @@ class Controller {
   // retried next tick by the caller like controller.go:75-77).
   std::vector<SchedulingRequestStatus> Reconcile(const std::vector<SchedulingRequest>& requests,
                                                  const std::vector<UAVMetricItem>& uavs);
+  // Multi-assignment (opt-in, no reference semantics): requests in list order,
+  // node i can be assigned capacity[i] times in this reconcile. Built on klm_schedule_batch_topk.
+  std::vector<SchedulingRequestStatus> ReconcileWithCapacity(const std::vector<SchedulingRequest>& requests,
+                                                             const std::vector<UAVMetricItem>& uavs,
+                                                             std::vector<int32_t> capacity);
 
  private:
   klm_handle* h_;

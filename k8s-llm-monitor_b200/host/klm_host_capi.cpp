@@ -156,6 +156,19 @@ int klmh_uav_entry(void* sv, int64_t i, double* remaining_percent, char* node, c
   return snap[i].HasState ? 1 : 0;
 }
 
+int klmh_reconcile_capacity(void* sv, const int32_t* capacity, int n) {
+  Session* s = static_cast<Session*>(sv);
+  if (!s->h) { s->error = "no GPU handle in this session"; return -1; }
+  try {
+    s->statuses = Controller(s->h).ReconcileWithCapacity(s->requests, s->uavs,
+                                                         std::vector<int32_t>(capacity, capacity + n));
+  } catch (const std::exception& e) {
+    s->error = e.what();
+    return -1;
+  }
+  return static_cast<int>(s->statuses.size());
+}
+
 int klmh_reconcile(void* sv) {
   Session* s = static_cast<Session*>(sv);
   if (!s->h) { s->error = "no GPU handle in this session"; return -1; }

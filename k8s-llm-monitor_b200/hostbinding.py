@@ -26,7 +26,7 @@ def load() -> C.CDLL:
         lib.klmh_error.argtypes = [C.c_void_p]
         lib.klmh_healthy_uav_count.restype = C.c_int64
         lib.klmh_update_uav_report.restype = C.c_int64
-        for name in ("klmh_close", "klmh_clear", "klmh_add_uav", "klmh_add_request", "klmh_reconcile",
+        for name in ("klmh_close", "klmh_clear", "klmh_add_uav", "klmh_add_request", "klmh_reconcile", "klmh_reconcile_capacity",
                      "klmh_status", "klmh_add_node", "klmh_add_pod", "klmh_calculate_cluster_metrics",
                      "klmh_issue", "klmh_add_fleet_uav", "klmh_healthy_uav_count", "klmh_low_battery_uavs",
                      "klmh_name", "klmh_load_uavs_json", "klmh_load_requests_json", "klmh_request_info",
@@ -138,8 +138,17 @@ class HostSession:
         return {"has_state": rc == 1, "remaining_percent": pct.value, "node_name": bufs[0].value.decode(),
                 "status": bufs[1].value.decode(), "last_heartbeat": bufs[2].value.decode()}
 
+    def reconcile_capacity(self, capacity):
+        """Controller::ReconcileWithCapacity: requests in order, node i assignable capacity[i] times."""
+        cap = (C.c_int32 * max(len(capacity), 1))(*[int(c) for c in capacity])
+        n = self.lib.klmh_reconcile_capacity(self.s, cap, C.c_int(len(capacity)))
+        return self._statuses(n)
+
     def reconcile(self):
         n = self.lib.klmh_reconcile(self.s)
+        return self._statuses(n)
+
+    def _statuses(self, n):
         if n < 0:
             self._err()
         out = []

@@ -212,3 +212,39 @@ def test_update_uav_report_feeds_the_ring(pkg):
             assert np.float32(e["remaining_percent"]) == rows[node, 21, last]
         assert not s.uav_entry(nodes)["has_state"]
         s.close()
+
+
+def test_reconcile_with_capacity_is_sequential_consistent(host):
+    """Controller::ReconcileWithCapacity (SURVEY.md 8f row 3; no reference semantics): requests in
+    list order, every assignment uses up one unit of its node. Oracle: the reference's own
+    process_request run sequentially over the items that still have room. Small capacities force
+    the re-batch path (a request whose eight best are all full)."""
+    rng = np.random.default_rng(17)
+    n_nodes, n_req = 40, 120
+    items = []
+    for i in range(n_nodes):
+        items.append({"spec": {"node_name": f"Node-{i % 37}", "uav_id": f"uav-{i}",
+                               "battery": {"remaining_percent": float(rng.integers(40, 100))}},
+                      "status": {"collection_status": rng.choice(["active", "", "ACTIVE", "error"], p=[.5, .2, .2, .1])}})
+    capacity = rng.integers(0, 4, size=n_nodes)
+    host.clear()
+    _add_items(host, items)
+    specs = []
+    for r in range(n_req):
+        pref = [f"node-{int(x)}" for x in rng.integers(0, 37, size=int(rng.integers(0, 3)))]
+        specs.append(_add_request(host, {"workload": {"name": f"w{r}", "namespace": "d"},
+                                         "minBatteryPercent": float(rng.choice([0.0, 50.0, 70.0, 90.0])),
+                                         "preferredNodes": pref}))
+    got = host.reconcile_capacity(capacity.tolist())
+    left = capacity.copy()
+    n_failed = 0
+    for g, sp in zip(got, specs):
+        avail = [it if left[i] > 0 else {"spec": {}} for i, it in enumerate(items)]   # a full node is no candidate
+        w = co.process_request(sp, avail)
+        assert (g["phase"], g["node"], g["uav"], g["score"], g["message"]) == \
+            (w.phase, w.assigned_node, w.assigned_uav, w.score, w.message)
+        if w.phase == "Assigned":
+            left[co.chosen_index(sp, avail)] -= 1
+        else:
+            n_failed += 1
+    assert left.min() >= 0 and 0 < n_failed < n_req
