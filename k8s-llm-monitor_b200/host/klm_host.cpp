@@ -2,16 +2,77 @@
 #include "klm_wire.h"
 #include <algorithm>
 
+#include <atomic>
 #include <cstdio>
+#include <thread>
 #include <stdexcept>
 #include <unordered_map>
 
 namespace klmhost {
 
+// unicode.ToLower for the scripts a node name realistically uses: ASCII, Latin-1, Latin
+// Extended-A, Greek, Cyrillic (Go's tables cover every script; anything else passes through).
+static uint32_t lower_rune(uint32_t r) {
+  if (r < 0x80) return (r >= 'A' && r <= 'Z') ? r + 32 : r;
+  if (r >= 0xC0 && r <= 0xDE) return r == 0xD7 ? r : r + 32;
+  if (r >= 0x100 && r <= 0x17F) {
+    if (r == 0x130) return 'i';            // LATIN CAPITAL LETTER I WITH DOT ABOVE
+    if (r == 0x178) return 0xFF;           // Y WITH DIAERESIS
+    if (r <= 0x137 || (r >= 0x14A && r <= 0x177)) return (r & 1) ? r : r + 1;    // even capitals
+    if ((r >= 0x139 && r <= 0x148) || (r >= 0x179 && r <= 0x17E)) return (r & 1) ? r + 1 : r;  // odd capitals
+    return r;
+  }
+  if (r >= 0x391 && r <= 0x3A9) return r == 0x3A2 ? r : r + 32;  // Greek
+  if (r == 0x386) return 0x3AC;
+  if (r >= 0x388 && r <= 0x38A) return r + 37;
+  if (r == 0x38C) return 0x3CC;
+  if (r == 0x38E || r == 0x38F) return r + 63;
+  if (r >= 0x410 && r <= 0x42F) return r + 32;                   // Cyrillic
+  if (r >= 0x400 && r <= 0x40F) return r + 80;
+  return r;
+}
+
+static void put_rune(std::string& o, uint32_t r) {
+  if (r < 0x80) o += static_cast<char>(r);
+  else if (r < 0x800) { o += static_cast<char>(0xC0 | (r >> 6)); o += static_cast<char>(0x80 | (r & 0x3F)); }
+  else if (r < 0x10000) {
+    o += static_cast<char>(0xE0 | (r >> 12)); o += static_cast<char>(0x80 | ((r >> 6) & 0x3F));
+    o += static_cast<char>(0x80 | (r & 0x3F));
+  } else {
+    o += static_cast<char>(0xF0 | (r >> 18)); o += static_cast<char>(0x80 | ((r >> 12) & 0x3F));
+    o += static_cast<char>(0x80 | ((r >> 6) & 0x3F)); o += static_cast<char>(0x80 | (r & 0x3F));
+  }
+}
+
+// strings.ToLower (controller.go:177, :188, :206): rune by rune over UTF-8; like Go's strings.Map
+// an invalid byte becomes U+FFFD once the string is not pure ASCII.
 std::string ToLower(const std::string& s) {
-  std::string o = s;
-  for (char& c : o)
-    if (c >= 'A' && c <= 'Z') c = static_cast<char>(c - 'A' + 'a');
+  bool ascii = true;
+  for (unsigned char c : s) ascii = ascii && c < 0x80;
+  std::string o;
+  o.reserve(s.size());
+  if (ascii) {
+    for (char c : s) o += (c >= 'A' && c <= 'Z') ? static_cast<char>(c + 32) : c;
+    return o;
+  }
+  const size_t n = s.size();
+  for (size_t i = 0; i < n;) {
+    const unsigned char c = static_cast<unsigned char>(s[i]);
+    uint32_t r = 0xFFFD;
+    size_t len = 1;
+    auto cont = [&](size_t k) { return i + k < n && (static_cast<unsigned char>(s[i + k]) & 0xC0) == 0x80; };
+    if (c < 0x80) r = c;
+    else if (c >= 0xC2 && c <= 0xDF && cont(1)) { r = ((c & 0x1Fu) << 6) | (s[i + 1] & 0x3F); len = 2; }
+    else if (c >= 0xE0 && c <= 0xEF && cont(1) && cont(2)) {
+      const uint32_t v = ((c & 0x0Fu) << 12) | ((s[i + 1] & 0x3Fu) << 6) | (s[i + 2] & 0x3F);
+      if (v >= 0x800 && !(v >= 0xD800 && v <= 0xDFFF)) { r = v; len = 3; }
+    } else if (c >= 0xF0 && c <= 0xF4 && cont(1) && cont(2) && cont(3)) {
+      const uint32_t v = ((c & 0x07u) << 18) | ((s[i + 1] & 0x3Fu) << 12) | ((s[i + 2] & 0x3Fu) << 6) | (s[i + 3] & 0x3F);
+      if (v >= 0x10000 && v <= 0x10FFFF) { r = v; len = 4; }
+    }
+    put_rune(o, lower_rune(r));
+    i += len;
+  }
   return o;
 }
 
@@ -251,6 +312,35 @@ ClusterMetrics Manager::CalculateClusterMetrics(const std::vector<NodeMetrics>& 
   static const char* kStatus[] = {"healthy", "warning", "critical"};                 // :558-564
   m.HealthStatus = kStatus[o.health_status];
   return m;
+}
+
+// ---- status write-back (controller.go:223-250): one UpdateStatus per request in the reference,
+// issued one after the other from the reconcile goroutine; with scoring down to microseconds the
+// round trips are the whole reconcile, so they are issued from `workers` threads at once. The
+// status objects are independent API objects, so their order does not matter.
+std::vector<WriteResult> WriteStatuses(const std::vector<StatusUpdate>& updates, const std::string& now_rfc3339,
+                                       const UpdateStatusFn& update_status, int workers) {
+  std::vector<WriteResult> res(updates.size());
+  std::atomic<size_t> next{0};
+  auto run = [&]() {
+    for (size_t i = next.fetch_add(1); i < updates.size(); i = next.fetch_add(1)) {
+      const StatusUpdate& u = updates[i];
+      if (!u.Status.Updated) {  // skipped by the phase gate (:117-119): nothing to write
+        res[i].Ok = true;
+        continue;
+      }
+      std::string err;
+      res[i].Written = true;
+      res[i].Ok = update_status(u.Namespace, u.Name, EncodeStatus(u.Status, now_rfc3339), &err);  // :229-248
+      if (!res[i].Ok) res[i].Error = err;
+    }
+  };
+  const int w = workers < 1 ? 1 : (workers > 256 ? 256 : workers);
+  std::vector<std::thread> pool;
+  for (int t = 1; t < w && static_cast<size_t>(t) < updates.size(); ++t) pool.emplace_back(run);
+  run();
+  for (std::thread& t : pool) t.join();
+  return res;
 }
 
 void Manager::EnableUAVRing(int64_t max_nodes, int32_t window) {

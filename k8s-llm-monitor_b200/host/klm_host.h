@@ -11,6 +11,7 @@
 #pragma once
 
 #include <cstdint>
+#include <functional>
 #include <string>
 #include <utility>
 #include <vector>
@@ -51,8 +52,8 @@ struct SchedulingRequest {
   SchedulingRequestSpec Spec;
 };
 
-// Go's strings.ToLower for the byte ranges that can occur in Kubernetes object names
-// (ASCII). Non-ASCII bytes pass through unchanged (documented limitation).
+// Go's strings.ToLower over UTF-8 for ASCII, Latin-1, Latin Extended-A, Greek and Cyrillic
+// (other scripts pass through unchanged); invalid bytes of a non-ASCII string become U+FFFD as in Go.
 std::string ToLower(const std::string& s);
 
 // internal/scheduler/controller.go Controller: reconcile over one snapshot.
@@ -74,6 +75,25 @@ class Controller {
  private:
   klm_handle* h_;
 };
+
+// ---- status write-back (controller.go:223-250)
+struct StatusUpdate {
+  std::string Namespace, Name;  // req.GetNamespace() / req.GetName()
+  SchedulingRequestStatus Status;
+};
+struct WriteResult {
+  bool Ok = false;       // the update succeeded, or there was nothing to write
+  bool Written = false;  // update_status was called
+  std::string Error;
+};
+// The apiserver call itself (dynamic.Resource(...).Namespace(ns).UpdateStatus, :246-248) belongs to
+// the host; it is injected: returns false and fills *err on failure.
+using UpdateStatusFn = std::function<bool(const std::string& ns, const std::string& name,
+                                          const std::string& status_json, std::string* err)>;
+// Encodes every updated status (EncodeStatus: the map of :229-236, "Pending" for an empty phase,
+// lastUpdated = now_rfc3339) and issues the updates from `workers` threads at once.
+std::vector<WriteResult> WriteStatuses(const std::vector<StatusUpdate>& updates, const std::string& now_rfc3339,
+                                       const UpdateStatusFn& update_status, int workers);
 
 // ---- pkg/metrics/types.go (fields calculateClusterMetrics reads)
 struct NodeMetrics {

@@ -156,6 +156,45 @@ int klmh_uav_entry(void* sv, int64_t i, double* remaining_percent, char* node, c
   return snap[i].HasState ? 1 : 0;
 }
 
+// strings.ToLower as the host layer applies it to node names and statuses
+void klmh_to_lower(const char* in, char* dst, int cap) { put(dst, cap, ToLower(in ? in : "")); }
+
+// status write-back: the statuses of the last reconcile go to `cb` (ns, name, status JSON; nonzero
+// = failure) from `workers` threads; names are "req-<i>" in namespace "default" unless set with
+// klmh_name_request. Returns how many calls failed, -1 on error.
+typedef int (*klmh_update_cb)(const char* ns, const char* name, const char* status_json);
+int klmh_write_statuses(void* sv, const char* now, int workers, klmh_update_cb cb) {
+  Session* s = static_cast<Session*>(sv);
+  try {
+    std::vector<StatusUpdate> ups(s->statuses.size());
+    for (size_t i = 0; i < ups.size(); ++i) {
+      ups[i].Namespace = "default";
+      ups[i].Name = "req-" + std::to_string(i);
+      ups[i].Status = s->statuses[i];
+    }
+    const auto res = WriteStatuses(ups, now ? now : "", [&](const std::string& ns, const std::string& name,
+                                                            const std::string& js, std::string* err) {
+      if (cb(ns.c_str(), name.c_str(), js.c_str()) != 0) { *err = "update refused"; return false; }
+      return true;
+    }, workers);
+    int failed = 0;
+    for (const auto& r : res) failed += r.Ok ? 0 : 1;
+    return failed;
+  } catch (const std::exception& e) { s->error = e.what(); return -1; }
+}
+// a status without a reconcile (tests of the write-back path alone)
+void klmh_add_status(void* sv, int updated, const char* phase, const char* node, const char* uav, double score,
+                     const char* message) {
+  SchedulingRequestStatus st;
+  st.Updated = updated != 0;
+  st.Phase = phase ? phase : "";
+  st.AssignedNode = node ? node : "";
+  st.AssignedUAV = uav ? uav : "";
+  st.Score = score;
+  st.Message = message ? message : "";
+  static_cast<Session*>(sv)->statuses.push_back(st);
+}
+
 int klmh_reconcile_capacity(void* sv, const int32_t* capacity, int n) {
   Session* s = static_cast<Session*>(sv);
   if (!s->h) { s->error = "no GPU handle in this session"; return -1; }

@@ -26,7 +26,7 @@ def load() -> C.CDLL:
         lib.klmh_error.argtypes = [C.c_void_p]
         lib.klmh_healthy_uav_count.restype = C.c_int64
         lib.klmh_update_uav_report.restype = C.c_int64
-        for name in ("klmh_close", "klmh_clear", "klmh_add_uav", "klmh_add_request", "klmh_reconcile", "klmh_reconcile_capacity",
+        for name in ("klmh_close", "klmh_clear", "klmh_add_uav", "klmh_add_request", "klmh_reconcile", "klmh_reconcile_capacity", "klmh_to_lower", "klmh_write_statuses", "klmh_add_status",
                      "klmh_status", "klmh_add_node", "klmh_add_pod", "klmh_calculate_cluster_metrics",
                      "klmh_issue", "klmh_add_fleet_uav", "klmh_healthy_uav_count", "klmh_low_battery_uavs",
                      "klmh_name", "klmh_load_uavs_json", "klmh_load_requests_json", "klmh_request_info",
@@ -46,6 +46,17 @@ def format_json_float(v: float) -> str:
     buf = C.create_string_buffer(64)
     load().klmh_format_float(C.c_double(v), buf, 64)
     return buf.value.decode()
+
+
+def to_lower(text: str) -> str:
+    """strings.ToLower as the host layer applies it (host/klm_host.h ToLower)."""
+    raw = text.encode("utf-8", "surrogateescape") if isinstance(text, str) else text
+    buf = C.create_string_buffer(4 * len(raw) + 8)
+    load().klmh_to_lower(raw, buf, len(buf))
+    return buf.value.decode("utf-8", "replace")
+
+
+UPDATE_CB = C.CFUNCTYPE(C.c_int, C.c_char_p, C.c_char_p, C.c_char_p)
 
 
 class HostSession:
@@ -137,6 +148,19 @@ class HostSession:
         rc = self.lib.klmh_uav_entry(self.s, C.c_int64(i), C.byref(pct), bufs[0], bufs[1], bufs[2], _CAP)
         return {"has_state": rc == 1, "remaining_percent": pct.value, "node_name": bufs[0].value.decode(),
                 "status": bufs[1].value.decode(), "last_heartbeat": bufs[2].value.decode()}
+
+    def add_status(self, updated: bool, phase: str, node: str, uav: str, score: float, message: str):
+        self.lib.klmh_add_status(self.s, C.c_int(int(updated)), _b(phase), _b(node), _b(uav), C.c_double(score),
+                                 _b(message))
+
+    def write_statuses(self, now: str, workers: int, callback) -> int:
+        """WriteStatuses over the session's statuses: callback(ns, name, status_json) -> bool (True = ok),
+        called from `workers` threads. Returns the number of failed updates."""
+        cb = UPDATE_CB(lambda ns, name, js: 0 if callback(ns.decode(), name.decode(), js.decode("utf-8")) else 1)
+        n = self.lib.klmh_write_statuses(self.s, now.encode(), C.c_int(workers), cb)
+        if n < 0:
+            self._err()
+        return n
 
     def reconcile_capacity(self, capacity):
         """Controller::ReconcileWithCapacity: requests in order, node i assignable capacity[i] times."""

@@ -139,3 +139,46 @@ def test_uav_report_decode_flatten_and_defaults(pkg):
         else:
             raise AssertionError(f"accepted {bad!r}")
     s.close()
+
+
+def test_to_lower_matches_go_for_common_scripts(pkg):
+    """strings.ToLower (controller.go:177, :188, :206) is Unicode-aware: a preferred node written
+    'ÉDGE-1' or 'УЗЕЛ-2' must still match. Python's str.lower agrees with Go's unicode.ToLower on
+    these ranges except U+0130, which Go maps to plain 'i'."""
+    tl = pkg.hostbinding.to_lower
+    for s in ("Node-1", "ÉDGE-Ünïté", "ÀÁÂÃÄÅÆÇÈÉÊËÌÍÎÏÐÑÒÓÔÕÖ×ØÙÚÛÜÝÞß", "ĀĂĄĆĈĊČĎĐĒĔĖĘĚĜĞĠĢĤĦĨĪĬĮĲĴĶĹĻĽĿŁŃŅŇŊŌŎŐŒŔŖŘŚŜŞŠŢŤŦŨŪŬŮŰŲŴŶŸŹŻŽ",
+              "ΑΒΓΔΕΖΗΘΙΚΛΜΝΞΟΠΡΣΤΥΦΧΨΩΆΈΉΊΌΎΏ", "УЗЕЛ-2 ЁЂЃЄЅІЇЈЉЊЋЌЍЎЏ АБВГДЕЖЗИЙКЛМНОПРСТУФХЦЧШЩЪЫЬЭЮЯ", "日本語-Node", "mixed-ß-ſ"):
+        assert tl(s) == s.lower(), s
+    assert tl("İstanbul") == "istanbul"                       # Go: U+0130 -> 'i'
+    assert tl(b"N\xffode-\xc9") == "n�ode-�"         # invalid bytes in a non-ASCII string: U+FFFD, like strings.Map
+    assert tl(b"ASCII\x7f") == "ascii\x7f"
+
+
+def test_status_write_back_is_concurrent_and_complete(pkg):
+    """WriteStatuses (controller.go:223-250 batched): every updated status is encoded and handed to
+    the injected UpdateStatus exactly once, from several threads; skipped requests are not written;
+    failures are reported per request."""
+    import threading
+    s = pkg.hostbinding.HostSession(None)
+    n = 200
+    for i in range(n):
+        s.add_status(i % 7 != 0, "Assigned" if i % 3 else "", f"node-{i}", f"uav-{i}", 90.0 + (i % 5) * 2.5,
+                     "选中节点 node-%d (电量 %.1f%%)" % (i, 80.0))
+    seen, threads, lock = {}, set(), threading.Lock()
+
+    def update(ns, name, js):
+        with lock:
+            assert name not in seen
+            seen[name] = json.loads(js)
+            threads.add(threading.get_ident())
+        return int(name.split("-")[1]) % 50 != 49            # a few refused updates
+    failed = s.write_statuses("2026-01-01T00:00:00Z", 8, update)
+    want = [i for i in range(n) if i % 7 != 0]
+    assert sorted(int(k.split("-")[1]) for k in seen) == want
+    assert failed == sum(1 for i in want if i % 50 == 49)
+    for i in want:
+        st = seen[f"req-{i}"]
+        assert st["phase"] == ("Assigned" if i % 3 else "Pending")          # controller.go:238-240
+        assert st["assignedNode"] == f"node-{i}" and st["score"] == 90.0 + (i % 5) * 2.5
+        assert st["lastUpdated"] == "2026-01-01T00:00:00Z" and st["message"].startswith("选中节点")
+    s.close()
