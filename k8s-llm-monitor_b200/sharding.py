@@ -55,6 +55,74 @@ class NodeShardedScheduler:
         return self.merge_fn(g_idx.view(self.world, r), g_score.view(self.world, r))
 
 
+class FusedShardedScheduler:
+    """The round-2 form of node-range sharding (klm.h, "node-range sharding without an all-gather"):
+    every rank owns one shard of the node table AND one slice of the requests.
+
+      1. best_fn(local_battery, local_flags, node_base) -> (battery, global index) of the shard's
+         best eligible node (K1). On GPUs the 16-byte result is stored into every rank's exchange
+         slots over NVLink by the kernel itself; here an all_gather of one (f64, i64) record per
+         rank stands in for those stores.
+      2. The G records are folded: largest battery, lowest global index on ties
+         (controller.go:160 across shards).
+      3. decide_fn(table_view, g_idx, g_bat, request slice) -> the slice's decisions (sharded K2).
+         table_view(ids) returns (flags, battery) of arbitrary global node ids: on GPUs a peer
+         pointer read, or a read of the local replica that klm_dev_node_best_spread filled; here
+         the shards are all-gathered once per snapshot to play that role.
+    Results are disjoint request slices; no rank ever holds partial winners of other ranks'
+    requests, and nothing is merged afterwards."""
+
+    def __init__(self, n_nodes_total: int, best_fn: Callable, decide_fn: Callable, group=None):
+        import torch.distributed as dist
+        self.dist, self.group = dist, group
+        self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
+        self.n_total = n_nodes_total
+        self.best_fn, self.decide_fn = best_fn, decide_fn
+        self.lo, self.hi = shard_range(n_nodes_total, self.world, self.rank)
+
+    def schedule(self, local_battery, local_flags, min_battery, pref_off, pref_ids):
+        """local_* cover nodes [lo, hi); the request arrays are this rank's SLICE (offsets local to
+        the slice). Returns (idx, score) for the slice."""
+        import torch
+        if local_battery.shape[0] != self.hi - self.lo:
+            raise ValueError("local node arrays do not match this rank's shard")
+        bat, idx = self.best_fn(local_battery, local_flags, self.lo)
+        rec_b = torch.tensor([float(bat)], dtype=torch.float64)
+        rec_i = torch.tensor([int(idx)], dtype=torch.int64)
+        all_b = [torch.zeros(1, dtype=torch.float64) for _ in range(self.world)]
+        all_i = [torch.zeros(1, dtype=torch.int64) for _ in range(self.world)]
+        self.dist.all_gather(all_b, rec_b, group=self.group)     # the slot exchange
+        self.dist.all_gather(all_i, rec_i, group=self.group)
+        g_idx, g_bat = -1, 0.0
+        for b, i in zip(all_b, all_i):                           # the fold of the sharded K2
+            b, i = float(b), int(i)
+            if i >= 0 and (g_idx < 0 or b > g_bat or (b == g_bat and i < g_idx)):
+                g_idx, g_bat = i, b
+        shards_b, shards_f = [None] * self.world, [None] * self.world
+        self.dist.all_gather_object(shards_b, local_battery, group=self.group)   # the view of the peers' shards
+        self.dist.all_gather_object(shards_f, local_flags, group=self.group)
+        ranges = [shard_range(self.n_total, self.world, k) for k in range(self.world)]
+
+        def view(node_id: int):
+            if node_id < 0 or node_id >= self.n_total:
+                return None
+            L = ranges[0][1] - ranges[0][0]
+            k = min(node_id // L, self.world - 1) if L > 0 else 0
+            lo = ranges[k][0]
+            return int(shards_f[k][node_id - lo]), float(shards_b[k][node_id - lo])
+
+        return self.decide_fn(view, g_idx, g_bat, min_battery, pref_off, pref_ids)
+
+
+def shard_range(n_nodes: int, world: int, rank: int) -> Tuple[int, int]:
+    """klm_shard_range: shards of ceil(n / world) nodes rounded up to a multiple of 16."""
+    if not (0 <= rank < world):
+        raise ValueError("rank out of range")
+    length = (-(-max(n_nodes, 0) // world) + 15) // 16 * 16
+    lo, hi = min(rank * length, n_nodes), min((rank + 1) * length, n_nodes)
+    return lo, hi
+
+
 def request_shard(n_requests: int, world: int, rank: int) -> Tuple[int, int]:
     """Request sharding needs no exchange: rank r schedules requests [lo, hi) and owns
     out[lo:hi]."""

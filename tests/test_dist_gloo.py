@@ -67,19 +67,52 @@ def _worker(rank, world, port, n, r, seed, out_dir):
     ok_req = np.array_equal(full_i, want_i) and np.array_equal(full_s, want_s)
     covered = sorted((p[0], p[1]) for p in parts)
     ok_cover = covered[0][0] == 0 and covered[-1][1] == r and all(a[1] == b[0] for a, b in zip(covered, covered[1:]))
+    # the fused form (round 2): every rank owns a node shard and a request slice; the 16-byte
+    # exchange + fold + probes of the peers' shards give the slice's decisions directly
+    def best_fn(lb, lf, base):
+        bb, bi = 0.0, -1
+        for i in range(lb.shape[0]):                       # controller.go:190, :198, :160-161
+            if (int(lf[i]) & 3) == 3 and (bi < 0 or float(lb[i]) > bb):
+                bb, bi = float(lb[i]), i
+        return (bb, bi + base) if bi >= 0 else (0.0, -1)
+
+    def decide_fn(view, g, gb, mbt, offt, idst):
+        oi = np.full(mbt.shape[0], -1, np.int32)
+        os_ = np.zeros(mbt.shape[0])
+        for q in range(mbt.shape[0]):
+            m = float(mbt[q])
+            if g < 0 or (m > 0 and gb < m):
+                continue
+            bi, bs = g, gb
+            for k in range(int(offt[q]), int(offt[q + 1])):
+                got = view(int(idst[k]))
+                if got is None or (got[0] & 3) != 3 or (m > 0 and got[1] < m):
+                    continue
+                sc = got[1] + 10
+                if sc > bs or (sc == bs and int(idst[k]) < bi):
+                    bi, bs = int(idst[k]), sc
+            oi[q], os_[q] = bi, bs
+        return oi, os_
+
+    fs = sh.FusedShardedScheduler(n, best_fn, decide_fn)
+    assert (fs.lo, fs.hi) == pkg.binding.shard_range(n, world, rank)     # the library's split
+    q0, q1 = sh.request_shard(r, world, rank)
+    f_off = (off[q0:q1 + 1] - off[q0]).astype(np.int32)
+    fi, fsc = fs.schedule(bat[fs.lo:fs.hi].copy(), flags[fs.lo:fs.hi].copy(), mb[q0:q1], f_off, ids[off[q0]:off[q1]])
+    ok_fused = np.array_equal(fi, want_i[q0:q1]) and np.array_equal(fsc, want_s[q0:q1])
     with open(os.path.join(out_dir, f"rank{rank}.txt"), "w") as f:
-        f.write(f"{int(ok_nodes)} {int(ok_req)} {int(ok_cover)}")
+        f.write(f"{int(ok_nodes)} {int(ok_req)} {int(ok_cover)} {int(ok_fused)}")
     dist.barrier()
     dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("n,r", [(1001, 257), (2, 50)])
+@pytest.mark.parametrize("n,r", [(1001, 257), (2, 50), (40, 33)])
 def test_sharding_two_ranks_gloo(tmp_path, n, r):
     world = 2
     port = 29500 + (os.getpid() % 2000) + n % 7
     mp.spawn(_worker, args=(world, port, n, r, 11, str(tmp_path)), nprocs=world, join=True)
     for rank in range(world):
-        assert open(tmp_path / f"rank{rank}.txt").read() == "1 1 1"
+        assert open(tmp_path / f"rank{rank}.txt").read() == "1 1 1 1"
 
 
 def test_split_range_properties(pkg):
