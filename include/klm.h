@@ -380,7 +380,8 @@ int klm_dev_node_best(const double* battery, const uint8_t* flags,
  * limits one call to klm_dev_node_best_static_max_nodes() = 4 849 664 nodes
  * (larger tables: KLM_ELIMIT). All calls on a device share that array, so calls
  * that could overlap on the GPU race: serialise them. The first call on a device
- * looks up the array's address; make it before any stream capture. Never calls
+ * looks up the array's address; make it before any stream capture. The address is kept
+ * for the life of the process and does not survive cudaDeviceReset(). Never calls
  * cudaMalloc / cudaFree. */
 int64_t klm_dev_node_best_static_max_nodes(void);
 int klm_dev_node_best_static(const double* battery, const uint8_t* flags,

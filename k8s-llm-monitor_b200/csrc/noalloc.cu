@@ -24,6 +24,9 @@
 // Set-up: the first call on a device looks the array's device address up
 // (cudaGetSymbolAddress, with that device current) and remembers it. Make that
 // first call before starting any stream capture.
+// The remembered address belongs to the device's primary context: it does not
+// survive cudaDeviceReset() (or anything else that destroys that context) -- a
+// process that resets a device must not call this entry point on it afterwards.
 //
 // Nothing here calls cudaMalloc, cudaFree or any allocating library routine.
 #include <mutex>

@@ -69,3 +69,50 @@ def test_static_scratch_rejects_oversize(pkg):
                                       torch.cuda.current_stream().cuda_stream)
     assert rc == pkg.binding.KLM_ELIMIT
     assert "exceed" in pkg.binding.last_error()
+
+
+def test_static_k1_feeds_the_dependent_k2(pkg):
+    """The pairing the header names: klm_dev_node_best_static followed by klm_dev_schedule_after_best
+    on the same stream must decide like the allocating pair, on two rounds in a row."""
+    import torch
+    import oracle_binding as ob
+    torch.cuda.set_device(0)
+    lib, dev = pkg.load(), pkg.Dev()
+    stream = torch.cuda.current_stream().cuda_stream
+    for seed, n, r in ((4, 120_000, 50_000), (5, 3000, 800)):
+        bat, flags = pkg.synth.node_table(seed, n)
+        mb, off, ids = pkg.synth.requests(seed, r, n)
+        t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()
+        d_bat, d_flags, d_mb, d_off, d_ids = t(bat), t(flags), t(mb), t(off), t(ids)
+        best = torch.full((2,), -9, dtype=torch.int64, device="cuda")
+        oi = torch.empty(r, dtype=torch.int32, device="cuda")
+        os_ = torch.empty(r, dtype=torch.float64, device="cuda")
+        rc = lib.klm_dev_node_best_static(d_bat.data_ptr(), d_flags.data_ptr(), n, 0, best.data_ptr(), stream)
+        assert rc == 0, pkg.binding.last_error()
+        dev.schedule(d_bat, d_flags, best, d_mb, d_off, d_ids, oi, os_, after_best=True)
+        torch.cuda.synchronize()
+        want = ob.schedule_decomposed(bat, flags, mb, off, ids)
+        assert np.array_equal(oi.cpu().numpy(), want[0]) and np.array_equal(os_.cpu().numpy(), want[1])
+
+
+def test_static_scratch_on_a_second_device(pkg):
+    """Every GPU that loads the library has its own copy of the array; its address is looked up
+    with that device current."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    lib = pkg.load()
+    bat, flags = pkg.synth.node_table(6, 200_000)
+    want = None
+    for d in (1, 0, 1):
+        with torch.cuda.device(d):
+            d_bat, d_flags = torch.from_numpy(bat).cuda(), torch.from_numpy(flags).cuda()
+            got = torch.full((2,), -9, dtype=torch.int64, device="cuda")
+            rc = lib.klm_dev_node_best_static(d_bat.data_ptr(), d_flags.data_ptr(), bat.size, 0, got.data_ptr(),
+                                              torch.cuda.current_stream().cuda_stream)
+            assert rc == 0, pkg.binding.last_error()
+            torch.cuda.synchronize()
+            g = got.cpu().numpy()
+            want = g if want is None else want
+            assert np.array_equal(g, want) and g[0] >= 0
+    torch.cuda.set_device(0)
