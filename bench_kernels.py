@@ -143,7 +143,7 @@ def main():
         del ring3, seen3
     o = [torch.empty(s, dtype=torch.float32, device="cuda") for _ in range(3)]
     om = torch.empty(s, dtype=torch.float64, device="cuda")
-    for variant in ("warp", "pipe", "block"):
+    for variant in ("warp", "stream", "block"):
         k7 = dev.prebind("window_stats", ring, seen, t, o[0], o[1], om, o[2], variant=variant)
         timeit(f"K7 window_stats[{variant}] S={s} T={t}", k7, s * (4 * t + 20), do_flush=False,
                units=("samples/s", s * t))

@@ -627,14 +627,6 @@ int klm_dev_window_stats_hinted(const float* ring, const uint32_t* seen,
                                 int64_t s1, float* out_min, float* out_max,
                                 double* out_mean, float* out_p95, float* state,
                                 void* stream);
-/* The pipelined variant of K7: one persistent CTA per SM, a producer warp streams rows
- * into a ring of shared-memory slots with cp.async.bulk + mbarriers, 15 consumer warps
- * work on them in place. Windows up to 4096 (KLM_ELIMIT beyond); same results. Slower
- * than the warp variant at T = 3600 today, kept as the base for round 2. */
-int klm_dev_window_stats_pipe(const float* ring, const uint32_t* seen,
-                              int32_t window, int32_t pitch, int64_t s0,
-                              int64_t s1, float* out_min, float* out_max,
-                              double* out_mean, float* out_p95, void* stream);
 /* The register-resident (one warp per series) variant of K7, which
  * klm_dev_window_stats uses for windows up to 4096 (KLM_ELIMIT beyond). */
 int klm_dev_window_stats_warp(const float* ring, const uint32_t* seen,

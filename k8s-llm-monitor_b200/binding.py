@@ -147,7 +147,6 @@ SIGNATURES = {
     "klm_dev_window_stats": (C.c_int, [_P, _P, _I32, _I32, _I64, _I64, _P, _P, _P, _P, _P]),
     "klm_dev_window_stats_stream": (C.c_int, [_P, _P, _I32, _I32, _I64, _I64, _P, _P, _P, _P, _P]),
     "klm_dev_window_stats_hinted": (C.c_int, [_P, _P, _I32, _I32, _I64, _I64, _P, _P, _P, _P, _P, _P]),
-    "klm_dev_window_stats_pipe": (C.c_int, [_P, _P, _I32, _I32, _I64, _I64, _P, _P, _P, _P, _P]),
     "klm_dev_window_stats_warp": (C.c_int, [_P, _P, _I32, _I32, _I64, _I64, _P, _P, _P, _P, _P]),
     "klm_dev_window_stats_block": (C.c_int, [_P, _P, _I32, _I32, _I64, _I64, _P, _P, _P, _P, _P]),
 }
@@ -803,7 +802,7 @@ class Dev:
             s1 = n_series
         if block_variant:
             variant = "block"
-        fn = {None: self.lib.klm_dev_window_stats, "pipe": self.lib.klm_dev_window_stats_pipe,
+        fn = {None: self.lib.klm_dev_window_stats,
               "warp": self.lib.klm_dev_window_stats_warp, "stream": self.lib.klm_dev_window_stats_stream,
               "block": self.lib.klm_dev_window_stats_block}[variant]
         if state is not None:

@@ -244,9 +244,6 @@ namespace klm {
 int launch_window_stats_warp(const float* ring, const uint32_t* seen, int32_t window,
                              int32_t pitch, int64_t s0, int64_t s1, float* out_min,
                              float* out_max, double* out_mean, float* out_p95, cudaStream_t st);
-int launch_window_stats_pipe(const float* ring, const uint32_t* seen, int32_t window,
-                             int32_t pitch, int64_t s0, int64_t s1, float* out_min,
-                             float* out_max, double* out_mean, float* out_p95, cudaStream_t st);
 int launch_window_stats_stream(const float* ring, const uint32_t* seen, int32_t window,
                                int32_t pitch, int64_t s0, int64_t s1, float* out_min,
                                float* out_max, double* out_mean, float* out_p95, float* state,
@@ -327,21 +324,6 @@ extern "C" int klm_dev_window_stats_hinted(const float* ring, const uint32_t* se
   }
   return launch_window_stats_stream(ring, seen, window, pitch, s0, s1, out_min, out_max, out_mean,
                                     out_p95, state, as_stream(stream));
-}
-
-extern "C" int klm_dev_window_stats_pipe(const float* ring, const uint32_t* seen, int32_t window,
-                                         int32_t pitch, int64_t s0, int64_t s1, float* out_min,
-                                         float* out_max, double* out_mean, float* out_p95,
-                                         void* stream) {
-  const int rc = window_stats_args_ok(ring, seen, window, pitch, s0, s1);
-  if (rc != KLM_OK || s1 == s0) return rc;
-  const int w = launch_window_stats_pipe(ring, seen, window, pitch, s0, s1, out_min, out_max,
-                                         out_mean, out_p95, as_stream(stream));
-  if (w == 1) {
-    set_error("klm_dev_window_stats_pipe: window %d does not fit the shared-memory slot ring", window);
-    return KLM_ELIMIT;
-  }
-  return w;
 }
 
 extern "C" int klm_dev_window_stats_block(const float* ring, const uint32_t* seen, int32_t window,

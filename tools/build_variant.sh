@@ -9,7 +9,7 @@ root=$(cd "$(dirname "$0")/.." && pwd)
 src=$root/k8s-llm-monitor_b200/csrc
 obj=$(mktemp -d)
 pids=
-for f in abi schedule aggregate ring window_stats_warp window_stats_stream window_stats_pipe noalloc predicates topk; do
+for f in abi schedule aggregate ring window_stats_warp window_stats_stream noalloc predicates topk; do
   /usr/local/cuda/bin/nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -lineinfo \
     -Xcompiler -fPIC,-Wall,-fvisibility=default --expt-relaxed-constexpr $extra \
     -c $src/$f.cu -o $obj/$f.o &

@@ -1,6 +1,6 @@
 #!/usr/bin/env python
 """Three launches of one K7 variant on the C2 ring (for ncu captures):
-   K7_VARIANT=hinted|stream|warp|block|pipe (default: klm_dev_window_stats), K7_DIST=uniform|quantised."""
+   K7_VARIANT=hinted|stream|warp|block (default: klm_dev_window_stats), K7_DIST=uniform|quantised."""
 import os
 import sys
 
