@@ -131,6 +131,17 @@ class Ctx:
             raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={self.world}: launch with torch.distributed.run")
         torch.cuda.set_device(self.local)
         self.host_group = None
+        if self.world > 1 and hasattr(os, "sched_setaffinity"):
+            # N processes each issue ~10 CUDA calls per 100 us step: keep every rank's threads on
+            # their own cores (all GPUs of these boxes report the same CPU affinity, so the
+            # launcher does not spread the ranks by itself)
+            try:
+                cores = sorted(os.sched_getaffinity(0))
+                per = max(1, len(cores) // self.world)
+                mine = cores[self.local * per:(self.local + 1) * per] or cores
+                os.sched_setaffinity(0, mine)
+            except OSError:
+                pass
         if self.world > 1:
             dist.init_process_group("nccl", device_id=torch.device("cuda", self.local))
             # host-only barrier for the phases where one rank drives every GPU (an NCCL barrier
