@@ -169,13 +169,19 @@ __device__ __forceinline__ float select_from_lists(float* lst, float* fin, int l
 #pragma unroll 1
   while (ca - cb > kMaxCand) {
     const uint32_t ka = f32_key(a), kb = (cb == 0) ? f32_key(mx) + 1u : f32_key(b);
-    if (kb - ka <= 1u) return a;  // every candidate equals a
+    if (kb - ka <= 1u) {  // every candidate equals a: the answer sits on a block of equal samples
+      if (next_hint) *next_hint = make_float2(a, a);
+      return a;
+    }
     if (it >= 4 && it < 12) {
       // ties keep the bracket wide: peel its largest distinct value
       const float m = key_f32(list_max_below(lst, m8, b, cb == 0));
       int l1, l2;
       const int c = (int)(list_count2(lst, m8, m, m, l1, l2) & 0xffffu);
-      if (c >= k) return m;  // everything above m is >= b
+      if (c >= k) {  // everything above m is >= b
+        if (next_hint) *next_hint = make_float2(m, m);
+        return m;
+      }
       b = m; cb = c; lane_cb = l1;
     } else {
       float p1, p2;
@@ -249,9 +255,9 @@ __device__ __forceinline__ float select_from_lists(float* lst, float* fin, int l
 // been counted.
 __device__ __forceinline__ bool select_hinted(float* lst, float* fin, int lane, int cnt, int total,
                                               int maxcnt, int k, float fl, float ce, float* result,
-                                              float2* next_hint) {
+                                              float2* next_hint, int prefilled = kListPrefill) {
   const int m8 = (maxcnt + 7) & ~7;
-  for (int e = max(cnt, kListPrefill); e < m8; ++e) lst[e * 32] = NEG_INF;  // (entries < kListPrefill are pre-filled)
+  for (int e = max(cnt, prefilled); e < m8; ++e) lst[e * 32] = NEG_INF;  // (entries < prefilled are pre-filled)
   fin[lane] = NEG_INF;
   fin[lane + 32] = NEG_INF;
   __syncwarp();

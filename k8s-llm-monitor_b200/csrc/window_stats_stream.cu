@@ -31,13 +31,34 @@ constexpr int kWssThreads = kWssWarps * 32;
 constexpr int kWssAux = 256;  // per warp: the 64 candidates of the final sort
 constexpr int kWssSampledMinRows = 7;  // below 7 full rows (896 samples) list everything
 
-template <int CAP>
+template <int CAP, int RS = 0, int D = 0>
 struct WssCfg {
   static constexpr int kListBytes = CAP * 128;  // [entry][lane] f32
   static constexpr int kClamp = CAP - 4;        // a lane is held at this count (four appends may follow)
-  static constexpr size_t kSmem = (size_t)kWssWarps * (kListBytes + kWssAux);
-  static_assert(CAP >= kListPrefill + 8, "the prefilled part must fit");
+  static constexpr int kPrefill = CAP >= kListPrefill + 8 ? kListPrefill : 16;  // entries pre-filled with -inf
+  static constexpr int kRingBytes = RS * D * 512;  // per warp: D stages of RS rows (cp.async landing ring)
+  static constexpr size_t kSmem = (size_t)kWssWarps * (kListBytes + kWssAux + kRingBytes);
+  static_assert(CAP >= kPrefill + 8 && kPrefill % 4 == 0, "the prefilled part must fit");
 };
+
+// 16 bytes global -> shared, asynchronously (LDGSTS), past L1; groups are per thread, and every
+// lane reads back only what it copied itself, so no warp barrier is involved.
+__device__ __forceinline__ void cp_async16(uint32_t dst, const float* src) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+  asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+__device__ __forceinline__ float4 lds_f4(uint32_t a) {
+  float4 r;
+  asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w)
+               : "r"(a)
+               : "memory");
+  return r;
+}
 
 // if (x > lox) { list[c / 128] = x; c += 128; }  c = byte offset of the lane's next slot; the
 // slot address lives in a temporary so that the store never holds up the counter.
@@ -175,18 +196,23 @@ __device__ __noinline__ WssBracket wss_narrow(const float* __restrict__ row, int
 
 // select_from_lists for the fallback path, out of line (one inlined copy serves the hot path)
 __device__ __noinline__ float wss_select_cold(float* lst, float* fin, int lane, int cnt, int total, int maxcnt,
-                                              int k, float a, float mx) {
-  return select_from_lists(lst, fin, lane, cnt, total, maxcnt, k, a, mx, false, 0.f, 0.f, kListPrefill);
+                                              int k, float a, float mx, int prefilled, float2* next_hint) {
+  return select_from_lists(lst, fin, lane, cnt, total, maxcnt, k, a, mx, false, 0.f, 0.f, prefilled, next_hint);
 }
 
-template <int CAP, int MINB, int NBUF>
+// RS, D > 0: the rows do not pass through register buffers but through a per-warp ring of D stages
+// of RS rows in shared memory, filled by cp.async: D - 1 stages are in flight whatever the
+// register budget, and the 32 buffer registers are free, which is what lets 28-32 warps share an
+// SM (the lists must then be short, CAP 24-32: made for the hinted pass, which lists ~200 samples).
+template <int CAP, int MINB, int NBUF, int RS = 0, int D = 0>
 __global__ void __launch_bounds__(kWssThreads, MINB)
 window_stats_stream_kernel(const float* __restrict__ ring, const uint32_t* __restrict__ seen,
                            int32_t window, int32_t pitch, int64_t s0, int64_t n_series,
                            float* __restrict__ out_min, float* __restrict__ out_max,
                            double* __restrict__ out_mean, float* __restrict__ out_p95,
                            float2* __restrict__ state) {
-  using Cfg = WssCfg<CAP>;
+  using Cfg = WssCfg<CAP, RS, D>;
+  constexpr bool kRing = D > 0;
   extern __shared__ __align__(16) unsigned char s_raw[];
 
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
@@ -210,6 +236,9 @@ window_stats_stream_kernel(const float* __restrict__ ring, const uint32_t* __res
   float4* const lst4 = reinterpret_cast<float4*>(list_g) + lane;
   const uint32_t lb = (uint32_t)__cvta_generic_to_shared(list_g) + ((uint32_t)lane << 2);
   float* fin = reinterpret_cast<float*>(s_raw + kWssWarps * Cfg::kListBytes + wib * kWssAux);
+  // this lane's 16 bytes of stage 0, row 0 of the warp's landing ring
+  const uint32_t ring_s = (uint32_t)__cvta_generic_to_shared(s_raw + kWssWarps * (Cfg::kListBytes + kWssAux) +
+                                                             wib * Cfg::kRingBytes) + ((uint32_t)lane << 4);
 
   // ---- 1. first loads: the sample rows and the first NBUF - 1 chunks of four rows, at
   // addresses that depend only on the kernel arguments (a full window is the steady state; a
@@ -236,19 +265,31 @@ window_stats_stream_kernel(const float* __restrict__ ring, const uint32_t* __res
 #pragma unroll
     for (int q = 0; q < 4; ++q) sm[q] = __ldg(p + 128 * (((2 * q + 1) * wjr) >> 3) + q);
   }
-  float4 buf[NBUF][4];
+  float4 buf[kRing ? 1 : NBUF][4];
   auto load_chunk = [&](float4 (&dst)[4], int c) {
 #pragma unroll
     for (int i = 0; i < 4; ++i) dst[i] = ld_stream_f4(p + 128 * (4 * c + i));
   };
+  auto fetch_stage = [&](int slot, int stage) {  // rows stage * RS .. + RS - 1 -> ring slot
 #pragma unroll
-  for (int b = 0; b < NBUF - 1; ++b)
-    if (4 * b + 4 <= wjr) load_chunk(buf[b], b);
-  // While the loads are in flight: fill the first kListPrefill entries of this lane's list with
+    for (int r = 0; r < RS; ++r) cp_async16(ring_s + (uint32_t)((slot * RS + r) * 512), p + 128 * (stage * RS + r));
+  };
+  if constexpr (kRing) {
+#pragma unroll
+    for (int b = 0; b < D - 1; ++b) {
+      if ((b + 1) * RS <= wjr) fetch_stage(b, b);
+      cp_async_commit();  // (one group per stage, empty or not: the waits below count groups)
+    }
+  } else {
+#pragma unroll
+    for (int b = 0; b < NBUF - 1; ++b)
+      if (4 * b + 4 <= wjr) load_chunk(buf[b], b);
+  }
+  // While the loads are in flight: fill the first Cfg::kPrefill entries of this lane's list with
   // -inf (128-bit stores across the warp), so the counting passes need no padding later.
   auto prefill = [&]() {
 #pragma unroll
-    for (int e = 0; e < kListPrefill / 4; ++e)
+    for (int e = 0; e < Cfg::kPrefill / 4; ++e)
       lst4[e * 32] = make_float4(NEG_INF, NEG_INF, NEG_INF, NEG_INF);
     __syncwarp();  // lanes append into slots another lane has just filled
   };
@@ -349,9 +390,30 @@ window_stats_stream_kernel(const float* __restrict__ ring, const uint32_t* __res
   WssAcc acc{POS_INF, POS_INF, NEG_INF, NEG_INF, 0.0, 0.0};
   uint32_t c128 = 0;
   uint32_t tie_gt = 0;  // tie pass: samples > the tied value (c128 then counts those >= it)
-  const int nch = jr >> 2;
+  const int nch = kRing ? 0 : jr >> 2;
+  const int nst = kRing ? jr / (RS > 0 ? RS : 1) : 0;  // full stages
+  const int jdone = kRing ? nst * RS : 4 * nch;        // rows the main loop covers
   auto pass = [&](auto row_fn, auto tail_fn) {
-    if (nch > 0) {
+    if constexpr (kRing) {
+#pragma unroll 1
+      for (int g0 = 0; g0 < nst; g0 += D) {
+#pragma unroll
+        for (int b = 0; b < D; ++b) {
+          const int g = g0 + b;
+          if (g < nst) {
+            // the slot of the stage consumed just before this one is free: refill it D - 1 ahead
+            if (g + D - 1 < nst) fetch_stage((b + D - 1) % D, g + D - 1);
+            cp_async_commit();
+            cp_async_wait<D - 1>();
+            float4 t[RS > 0 ? RS : 1];
+#pragma unroll
+            for (int r = 0; r < RS; ++r) t[r] = lds_f4(ring_s + (uint32_t)((b * RS + r) * 512));
+#pragma unroll
+            for (int r = 0; r < RS; ++r) row_fn(t[r], (b * RS + r) & 1);
+          }
+        }
+      }
+    } else if (nch > 0) {
 #pragma unroll
       for (int b = 0; b < NBUF - 1; ++b)  // chunks the early loads did not cover (cannot happen for
         if (4 * b + 4 > wjr && b < nch) load_chunk(buf[b], b);  // n <= window; keeps buf defined)
@@ -368,9 +430,9 @@ window_stats_stream_kernel(const float* __restrict__ ring, const uint32_t* __res
         }
       }
     }
-    // the rows left over (at most three full ones), then the row that only some lanes hold
+    // the rows left over (fewer than a chunk / a stage), then the row that only some lanes hold
 #pragma unroll 1
-    for (int j = 4 * nch; j < jr; ++j) row_fn(ld_stream_f4(p + 128 * j), false);
+    for (int j = jdone; j < jr; ++j) row_fn(ld_stream_f4(p + 128 * j), false);
     if (lane + 32 * jr < nfull) row_fn(ld_stream_f4(p + 128 * jr), false);
     if (lane < (n & 3)) {
       const float x = row[4 * nfull + lane];
@@ -430,9 +492,9 @@ window_stats_stream_kernel(const float* __restrict__ ring, const uint32_t* __res
     if (hinted) {
       // the bracket's floor lists too few (it has drifted above the answer) or far too many
       if (total < k || maxcnt >= Cfg::kClamp) { narrow = true; break; }
-      if (select_hinted(lst, fin, lane, cnt, total, maxcnt, k, hint.x, hint.y, &result, &next_hint)) break;
+      if (select_hinted(lst, fin, lane, cnt, total, maxcnt, k, hint.x, hint.y, &result, &next_hint, Cfg::kPrefill)) break;
       // the answer left the bracket, or the bracket is wide: the lists still hold everything >= floor
-      result = select_from_lists(lst, fin, lane, cnt, total, maxcnt, k, hint.x, mx, false, 0.f, 0.f, kListPrefill,
+      result = select_from_lists(lst, fin, lane, cnt, total, maxcnt, k, hint.x, mx, false, 0.f, 0.f, Cfg::kPrefill,
                                  &next_hint);
       break;
     }
@@ -455,19 +517,23 @@ window_stats_stream_kernel(const float* __restrict__ ring, const uint32_t* __res
       break;
     }
     result = select_from_lists(lst, fin, lane, cnt, total, maxcnt, k, sampled ? next_up(lox) : mn, mx,
-                               retried, hint_lo, hint_hi, kListPrefill, &next_hint);
+                               retried, hint_lo, hint_hi, Cfg::kPrefill, &next_hint);
   } while (false);
   if (narrow) {
     if (mn == mx) {
       result = mx;
+      next_hint = make_float2(mx, mx);
     } else {
       // first try: a bracket of at most kFit elements on top of the < k above it, listed and
       // selected from; if a single lane's share still overflows, settle by counting alone
 #pragma unroll 1
       for (int attempt = 0; attempt < 2; ++attempt) {
-        const WssBracket br = wss_narrow(row, lane, n, k, mn, mx, attempt == 0 ? 16 * 32 : 0);
+        // (the lists must then hold the < k samples above the bracket and the bracket itself)
+        constexpr int kFit = CAP >= 64 ? 16 * 32 : 0;
+        const int fit = kFit > 0 ? kFit : max(Cfg::kClamp * 16 - k, 32);
+        const WssBracket br = wss_narrow(row, lane, n, k, mn, mx, attempt == 0 ? fit : 0);
         const float a = br.a;
-        if (br.ca < 0) { result = a; break; }
+        if (br.ca < 0) { result = a; next_hint = make_float2(a, a); break; }  // a block of equal samples
         __syncwarp();
         prefill();
         lox = a == NEG_INF ? NEG_INF : next_down(a);
@@ -479,7 +545,7 @@ window_stats_stream_kernel(const float* __restrict__ ring, const uint32_t* __res
         const int maxcnt = warp_max_i32(cnt);
         if (maxcnt >= Cfg::kClamp) continue;
         if (total < k) { result = NEG_INF; break; }  // a = -inf: only -inf samples are unlisted
-        result = wss_select_cold(lst, fin, lane, cnt, total, maxcnt, k, a, mx);
+        result = wss_select_cold(lst, fin, lane, cnt, total, maxcnt, k, a, mx, Cfg::kPrefill, &next_hint);
         break;
       }
     }
@@ -490,12 +556,12 @@ window_stats_stream_kernel(const float* __restrict__ ring, const uint32_t* __res
   }
 }
 
-template <int CAP, int MINB, int NBUF>
+template <int CAP, int MINB, int NBUF, int RS = 0, int D = 0>
 static int launch_stream(const float* ring, const uint32_t* seen, int32_t window, int32_t pitch,
                          int64_t s0, int64_t n_series, float* out_min, float* out_max,
                          double* out_mean, float* out_p95, float2* state, cudaStream_t st) {
-  using Cfg = WssCfg<CAP>;
-  static_assert(MINB * (Cfg::kSmem + 1024) <= 227 * 1024, "the CTAs per SM must fit");
+  using Cfg = WssCfg<CAP, RS, D>;
+  static_assert(MINB * (Cfg::kSmem + 1024) <= 228 * 1024, "the CTAs per SM must fit");
   const int64_t blocks = ceil_div(n_series, kWssWarps);
   if (blocks > 0x7fffffff) {
     set_error("klm_dev_window_stats: too many series for one launch");
@@ -504,17 +570,16 @@ static int launch_stream(const float* ring, const uint32_t* seen, int32_t window
   static PerDeviceOnce attr_set;
   int dev = 0;
   KLM_CUDA(cudaGetDevice(&dev));
+  auto kern = window_stats_stream_kernel<CAP, MINB, NBUF, RS, D>;
   if (!attr_set.done(dev)) {
     // opt in above 48 KB and ask for the largest shared-memory carve-out
-    KLM_CUDA(cudaFuncSetAttribute(window_stats_stream_kernel<CAP, MINB, NBUF>,
-                                  cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::kSmem));
-    KLM_CUDA(cudaFuncSetAttribute(window_stats_stream_kernel<CAP, MINB, NBUF>,
-                                  cudaFuncAttributePreferredSharedMemoryCarveout,
+    KLM_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::kSmem));
+    KLM_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout,
                                   (int)cudaSharedmemCarveoutMaxShared));
     attr_set.set(dev);
   }
-  window_stats_stream_kernel<CAP, MINB, NBUF><<<(unsigned)blocks, kWssThreads, Cfg::kSmem, st>>>(
-      ring, seen, window, pitch, s0, n_series, out_min, out_max, out_mean, out_p95, state);
+  kern<<<(unsigned)blocks, kWssThreads, Cfg::kSmem, st>>>(ring, seen, window, pitch, s0, n_series, out_min, out_max,
+                                                          out_mean, out_p95, state);
   KLM_LAUNCH_CHECK("window_stats_stream_kernel");
   return KLM_OK;
 }
@@ -532,8 +597,40 @@ static int launch_stream(const float* ring, const uint32_t* seen, int32_t window
 int launch_window_stats_stream(const float* ring, const uint32_t* seen, int32_t window, int32_t pitch,
                                int64_t s0, int64_t s1, float* out_min, float* out_max,
                                double* out_mean, float* out_p95, float* state, cudaStream_t st) {
-  return launch_stream<KLM_WSS_CAP, KLM_WSS_MINB, KLM_WSS_NBUF>(ring, seen, window, pitch, s0, s1 - s0, out_min, out_max,
-                                                  out_mean, out_p95, reinterpret_cast<float2*>(state), st);
+  float2* st2 = reinterpret_cast<float2*>(state);
+#define KLM_WSS_GO(...) \
+  return launch_stream<__VA_ARGS__>(ring, seen, window, pitch, s0, s1 - s0, out_min, out_max, out_mean, out_p95, st2, st)
+#ifdef KLM_WSS_EXPERIMENTS
+  // tuning builds: KLM_WSS_VARIANT picks a landing-ring shape at run time
+  static const int variant = [] { const char* e = getenv("KLM_WSS_VARIANT"); return e ? atoi(e) : 0; }();
+  if (state != nullptr && window <= 4096) {
+    switch (variant) {
+      case 5: KLM_WSS_GO(32, 7, 2, 1, 7);
+      case 6: KLM_WSS_GO(32, 6, 2, 2, 4);
+      case 7: KLM_WSS_GO(32, 6, 2, 1, 9);
+      case 9: KLM_WSS_GO(32, 6, 2, 2, 5);
+      case 10: KLM_WSS_GO(32, 6, 2, 3, 3);
+      case 11: KLM_WSS_GO(32, 6, 2, 4, 2);
+      case 12: KLM_WSS_GO(32, 5, 2, 2, 6);
+      case 13: KLM_WSS_GO(32, 7, 2, 2, 3);
+      case 14: KLM_WSS_GO(40, 6, 2, 2, 4);
+      default: break;
+    }
+  }
+  if (window <= 8192) {
+    switch (variant) {
+      case 20: KLM_WSS_GO(64, 4, 2, 2, 4);
+      case 21: KLM_WSS_GO(48, 5, 2, 2, 4);
+      case 22: KLM_WSS_GO(64, 4, 2, 2, 5);
+      default: break;
+    }
+  }
+#endif
+  // carried brackets: the pass lists ~k + 12 samples, so short lists leave shared memory for a
+  // landing ring of five 1 KB stages per warp (77 us at C2 against 96 us through register buffers)
+  if (state != nullptr && window <= 4096) KLM_WSS_GO(32, 6, 2, 2, 5);
+  KLM_WSS_GO(KLM_WSS_CAP, KLM_WSS_MINB, KLM_WSS_NBUF);
+#undef KLM_WSS_GO
 }
 
 }  // namespace klm

@@ -76,6 +76,8 @@ def worker():
                 out[f"{dist}_{name}_us"] = round(float(np.median([a.elapsed_time(b) for a, b in evs])) * 1e3, 2)
             st = state.cpu().numpy()
             out[dist + "_bracketed_frac"] = round(float(np.mean(st[:, 0] < st[:, 1])), 3)
+            out[dist + "_tie_frac"] = round(float(np.mean(st[:, 0] == st[:, 1])), 3)
+            digest.update(o[2].cpu().numpy().tobytes())
         out[dist + "_min_us"] = round(float(min(reps)), 2)
         for x in (o[0], o[1], o[2]):
             digest.update(x.cpu().numpy().tobytes())
