@@ -116,6 +116,33 @@ __device__ __forceinline__ void sort64_desc(uint32_t& k0, uint32_t& k1, int lane
   }
 }
 
+// Bitonic sort of 32 keys, descending, one per lane: element `lane` is k.
+__device__ __forceinline__ void sort32_desc(uint32_t& k, int lane) {
+#pragma unroll
+  for (int size = 2; size <= 32; size <<= 1) {
+    const bool desc = (lane & size) == 0;  // size == 32: every lane descending
+#pragma unroll
+    for (int stride = size >> 1; stride > 0; stride >>= 1) {
+      const bool keepmax = ((lane & stride) == 0) == desc;
+      const uint32_t o = __shfl_xor_sync(0xffffffffu, k, stride);
+      k = keepmax ? max(k, o) : min(k, o);
+    }
+  }
+}
+
+// warp-wide min / max of f32 in one instruction each (CREDUX on sm_100a; NaN inputs are passed over,
+// like fminf / fmaxf)
+__device__ __forceinline__ float warp_min_f32(float v) {
+  float r;
+  asm volatile("redux.sync.min.f32 %0, %1, 0xffffffff;" : "=f"(r) : "f"(v));
+  return r;
+}
+__device__ __forceinline__ float warp_max_f32(float v) {
+  float r;
+  asm volatile("redux.sync.max.f32 %0, %1, 0xffffffff;" : "=f"(r) : "f"(v));
+  return r;
+}
+
 constexpr int kMaxCand = 64;  // candidates sorted exactly at the end of select_from_lists
 constexpr int kHintMargin = 12;  // the hint brackets ranks k - 12 .. k + 12 of the window
 
@@ -129,6 +156,13 @@ __device__ __forceinline__ float2 hint_from_sorted(uint32_t k0, uint32_t k1, int
   const int pl = min(kk - 1 + kHintMargin, n_cand - 1), ph = kk - 1 - kHintMargin;
   const uint32_t lo = __shfl_sync(0xffffffffu, (pl & 1) ? k1 : k0, pl >> 1);
   const uint32_t hi = __shfl_sync(0xffffffffu, (max(ph, 0) & 1) ? k1 : k0, max(ph, 0) >> 1);
+  return make_float2(key_f32(lo), ph >= 0 ? key_f32(hi) : above);
+}
+// the same for 32 sorted candidates held one per lane
+__device__ __forceinline__ float2 hint_from_sorted32(uint32_t key, int kk, int n_cand, float above) {
+  const int pl = min(kk - 1 + kHintMargin, n_cand - 1), ph = kk - 1 - kHintMargin;
+  const uint32_t lo = __shfl_sync(0xffffffffu, key, pl);
+  const uint32_t hi = __shfl_sync(0xffffffffu, key, max(ph, 0));
   return make_float2(key_f32(lo), ph >= 0 ? key_f32(hi) : above);
 }
 constexpr int kListPrefill = 24;  // list entries per lane the kernels pre-fill with -inf
@@ -285,6 +319,13 @@ __device__ __forceinline__ bool select_hinted(float* lst, float* fin, int lane, 
   }
   __syncwarp();
   const int kk = k - cb;
+  if (total - cb <= 32) {  // the usual case (a bracket spans 2 * kHintMargin + 1 ranks): a 32-key sort
+    uint32_t key = f32_key(fin[lane]);
+    sort32_desc(key, lane);
+    *next_hint = hint_from_sorted32(key, kk, total - cb, ce);
+    *result = key_f32(__shfl_sync(0xffffffffu, key, kk - 1));
+    return true;
+  }
   const float2 y = *reinterpret_cast<const float2*>(fin + 2 * lane);
   uint32_t k0 = f32_key(y.x), k1 = f32_key(y.y);
   sort64_desc(k0, k1, lane);

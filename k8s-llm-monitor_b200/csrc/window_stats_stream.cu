@@ -246,6 +246,20 @@ window_stats_stream_kernel(const float* __restrict__ ring, const uint32_t* __res
   const float* p = row + 4 * lane;
   const int wjr = (window >> 2) >> 5;  // full rows of a full window
   const bool want_p95 = out_p95 != nullptr;
+  // (the landing ring first: its copies must not wait for the bracket to arrive)
+  auto fetch_stage = [&](int slot, int stage) {  // rows stage * RS .. + RS - 1 -> ring slot
+#pragma unroll
+    for (int r = 0; r < RS; ++r) cp_async16(ring_s + (uint32_t)((slot * RS + r) * 512), p + 128 * (stage * RS + r));
+  };
+  if constexpr (kRing) {
+#pragma unroll
+    for (int b = 0; b < D - 1; ++b) {
+      if ((b + 1) * RS <= wjr) fetch_stage(b, b);
+      cp_async_commit();  // (one group per stage, empty or not: the waits below count groups)
+    }
+    // the row that only some lanes hold is read last, straight from global memory: ask L2 for it now
+    if (lane + 32 * wjr < (window >> 2)) asm volatile("prefetch.global.L2 [%0];" ::"l"(p + 128 * wjr));
+  }
   // Streaming windows: `state` holds, per series, the bracket (floor, ceil) around the p95 that
   // the previous call left (window_stats.cuh, hint_from_sorted). A usable bracket replaces the
   // sampling: the pass lists everything >= floor, about k + 12 elements, and the finish is one
@@ -270,17 +284,7 @@ window_stats_stream_kernel(const float* __restrict__ ring, const uint32_t* __res
 #pragma unroll
     for (int i = 0; i < 4; ++i) dst[i] = ld_stream_f4(p + 128 * (4 * c + i));
   };
-  auto fetch_stage = [&](int slot, int stage) {  // rows stage * RS .. + RS - 1 -> ring slot
-#pragma unroll
-    for (int r = 0; r < RS; ++r) cp_async16(ring_s + (uint32_t)((slot * RS + r) * 512), p + 128 * (stage * RS + r));
-  };
-  if constexpr (kRing) {
-#pragma unroll
-    for (int b = 0; b < D - 1; ++b) {
-      if ((b + 1) * RS <= wjr) fetch_stage(b, b);
-      cp_async_commit();  // (one group per stage, empty or not: the waits below count groups)
-    }
-  } else {
+  if constexpr (!kRing) {
 #pragma unroll
     for (int b = 0; b < NBUF - 1; ++b)
       if (4 * b + 4 <= wjr) load_chunk(buf[b], b);
@@ -395,23 +399,39 @@ window_stats_stream_kernel(const float* __restrict__ ring, const uint32_t* __res
   const int jdone = kRing ? nst * RS : 4 * nch;        // rows the main loop covers
   auto pass = [&](auto row_fn, auto tail_fn) {
     if constexpr (kRing) {
+      // Stage g lives in slot g mod D. A trip refills the slot consumed one trip earlier with stage
+      // g + D - 1, waits for stage g (all but the D - 1 youngest copy groups) and consumes it; the
+      // last D - 1 trips only drain (empty groups keep the count). Slot addresses and the fetch
+      // pointer are carried in registers: ~12 instructions of ring handling per stage.
+      constexpr uint32_t kStage = RS * 512;
+      const uint32_t ring_end = ring_s + D * kStage;
+      uint32_t cs = ring_s, fs = ring_s + (D - 1) * kStage;
+      const float* pf = p + 128 * RS * (D - 1);
+      auto consume = [&]() {
+        float4 t[RS > 0 ? RS : 1];
+#pragma unroll
+        for (int r = 0; r < RS; ++r) t[r] = lds_f4(cs + (uint32_t)(r * 512));
+#pragma unroll
+        for (int r = 0; r < RS; ++r) row_fn(t[r], r & 1);
+        fs = cs;
+        cs += kStage;
+        if (cs == ring_end) cs = ring_s;
+      };
+      int g = 0;
 #pragma unroll 1
-      for (int g0 = 0; g0 < nst; g0 += D) {
+      for (; g + D - 1 < nst; ++g) {
 #pragma unroll
-        for (int b = 0; b < D; ++b) {
-          const int g = g0 + b;
-          if (g < nst) {
-            // the slot of the stage consumed just before this one is free: refill it D - 1 ahead
-            if (g + D - 1 < nst) fetch_stage((b + D - 1) % D, g + D - 1);
-            cp_async_commit();
-            cp_async_wait<D - 1>();
-            float4 t[RS > 0 ? RS : 1];
-#pragma unroll
-            for (int r = 0; r < RS; ++r) t[r] = lds_f4(ring_s + (uint32_t)((b * RS + r) * 512));
-#pragma unroll
-            for (int r = 0; r < RS; ++r) row_fn(t[r], (b * RS + r) & 1);
-          }
-        }
+        for (int r = 0; r < RS; ++r) cp_async16(fs + (uint32_t)(r * 512), pf + 128 * r);
+        pf += 128 * RS;
+        cp_async_commit();
+        cp_async_wait<D - 1>();
+        consume();
+      }
+#pragma unroll 1
+      for (; g < nst; ++g) {
+        cp_async_commit();
+        cp_async_wait<D - 1>();
+        consume();
       }
     } else if (nch > 0) {
 #pragma unroll
@@ -461,12 +481,10 @@ window_stats_stream_kernel(const float* __restrict__ ring, const uint32_t* __res
   asm volatile("" ::: "memory");  // the appends above are plain shared-memory stores
   float mn = fminf(acc.mn0, acc.mn1), mx = fmaxf(acc.mx0, acc.mx1);
   double sum = acc.sum0 + acc.sum1;
+  mn = warp_min_f32(mn);
+  mx = warp_max_f32(mx);
 #pragma unroll
-  for (int off = 16; off > 0; off >>= 1) {
-    mn = fminf(mn, __shfl_xor_sync(0xffffffffu, mn, off));
-    mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, off));
-    sum += __shfl_xor_sync(0xffffffffu, sum, off);
-  }
+  for (int off = 16; off > 0; off >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, off);
   if (lane == 0) {
     if (out_min) out_min[o] = mn + 0.f;  // -0.0 -> +0.0: one canonical zero in the outputs
     if (out_max) out_max[o] = mx + 0.f;

@@ -63,17 +63,23 @@ def worker():
             k6 = [dev.prebind("ring_ingest", ring, seen, t, ticks[i].contiguous()) for i in range(64)]
             kh = dev.prebind("window_stats", ring, seen, t, o[0], o[1], om, o[2], state=state)
             kc = dev.prebind("window_stats", ring, seen, t, o[0], o[1], om, o[2], variant="stream")
+            def train(fns, reps=20):
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                for i in range(reps):
+                    for f in fns:
+                        (f[(7 + i) % 64] if isinstance(f, list) else f)()
+                e1.record()
+                e1.synchronize()
+                return e0.elapsed_time(e1) / reps * 1e3
             for name, fn in (("hinted", kh), ("stream_cold", kc)):
                 for i in range(6):
                     k6[i](); fn()
-                evs = []
-                for i in range(40):
-                    k6[(6 + i) % 64]()
-                    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-                    e0.record(); fn(); e1.record()
-                    evs.append((e0, e1))
-                torch.cuda.synchronize()
-                out[f"{dist}_{name}_us"] = round(float(np.median([a.elapsed_time(b) for a, b in evs])) * 1e3, 2)
+                # one tick + one K7 per trip, minus the ticks alone (single launches are below the
+                # ~2 us resolution of CUDA events)
+                both = float(np.median([train([k6, fn]) for _ in range(7)]))
+                alone = float(np.median([train([k6]) for _ in range(7)]))
+                out[f"{dist}_{name}_us"] = round(both - alone, 2)
             st = state.cpu().numpy()
             out[dist + "_bracketed_frac"] = round(float(np.mean(st[:, 0] < st[:, 1])), 3)
             out[dist + "_tie_frac"] = round(float(np.mean(st[:, 0] == st[:, 1])), 3)
