@@ -353,7 +353,8 @@ def run_series_workload(ctx, wl):
                 "h2d_bytes_per_step": e2e["h2d"], "d2h_bytes_per_step": e2e["d2h"],
                 "timing": "host wall clock around the klm_* calls of K steps, priming and draining included",
                 "calls_per_step": "klm_collect_begin + klm_collect_end (two cycles in flight, one handle) + "
-                                  "klm_reconcile (scheduler handle)"},
+                                  "klm_reconcile (scheduler handle, its own host thread)",
+                "host_call_us": e2e.get("host_call_us")},
         "gpu_launches": n_launch,
         "roofline": {"bound": "hbm", "kernel": "window_stats" + ("_hinted" if k7_state is not None else ""),
                      "achieved": achieved, "peak": pk["hbm_gbs"],
@@ -422,27 +423,57 @@ def e2e_series(ctx, wl, env):
             begin(next_tick())            # cycle i + 1 goes in ...
             res = end()                   # ... cycle i comes out: statistics, rates, cluster metrics
             sink[0] = float(res["p95"][0]) + res["cluster"]["total_nodes"]
-            reconcile()                   # the scheduler's reconcile: snapshot + batch, one call
 
         def finish():                     # drain: the last cycle begun is completed and read
             while in_flight[0]:
                 end()
                 in_flight[0] = 0
 
-        for _ in range(3):
-            step()
-        finish()
+        # The scheduler reconciles on its own host thread, as it does in the reference (the
+        # controller's loop and the metrics manager's loop are separate goroutines): K steps are K
+        # collect cycles on this thread and K reconciles on that one, and the clock stops when
+        # both are done. (ctypes releases the GIL for the duration of a C call.)
+        def run_steps(n):
+            err = []
+
+            def sched():
+                try:
+                    for _ in range(n):
+                        reconcile()
+                except Exception as e:  # noqa: BLE001
+                    err.append(e)
+            th = threading.Thread(target=sched)
+            th.start()
+            for _ in range(n):
+                step()
+            finish()
+            th.join()
+            if err:
+                raise err[0]
+
+        run_steps(3)
         ctx.barrier()
         est = 2e-4 if wl == "c2" else 2e-3
         reps = max(1, int(np.ceil(MIN_TIMED_S / (steps * est))))
         t0 = time.perf_counter()
-        for _ in range(steps * reps):
-            step()
-        finish()
+        run_steps(steps * reps)
         torch.cuda.synchronize()
         dt = time.perf_counter() - t0
+        # where the host thread spends the step (a second, untimed run of the same calls)
+        acc = {"begin": 0.0, "end": 0.0, "reconcile": 0.0}
+        begin(next_tick())
+        n_probe = min(steps * reps, 400)
+        for _ in range(n_probe):
+            a = time.perf_counter(); begin(next_tick())
+            b = time.perf_counter(); end()
+            c = time.perf_counter(); reconcile()
+            d = time.perf_counter()
+            acc["begin"] += b - a; acc["end"] += c - b; acc["reconcile"] += d - c
+        end()
+        torch.cuda.synchronize()
         h_sched.close()
-    return {"ms_per_step": dt / (steps * reps) * 1e3, "h2d": int(h2d), "d2h": int(d2h)}
+    return {"ms_per_step": dt / (steps * reps) * 1e3, "h2d": int(h2d), "d2h": int(d2h),
+            "host_call_us": {k: round(v / n_probe * 1e6, 1) for k, v in acc.items()}}
 
 
 def run_schedule_workload(ctx, wl):

@@ -646,7 +646,7 @@ int launch_window_stats_stream(const float* ring, const uint32_t* seen, int32_t 
 #endif
   // carried brackets: the pass lists ~k + 12 samples, so short lists leave shared memory for a
   // landing ring of five 1 KB stages per warp (77 us at C2 against 96 us through register buffers)
-  if (state != nullptr && window <= 4096) KLM_WSS_GO(32, 6, 2, 2, 5);
+  if (state != nullptr && window <= 8192) KLM_WSS_GO(32, 6, 2, 2, 5);
   KLM_WSS_GO(KLM_WSS_CAP, KLM_WSS_MINB, KLM_WSS_NBUF);
 #undef KLM_WSS_GO
 }
