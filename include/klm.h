@@ -422,6 +422,22 @@ int klm_dev_schedule_after_best(const double* battery, const uint8_t* flags,
                                 const double* min_battery, const int32_t* pref_off,
                                 const int32_t* pref_ids, int32_t* out_idx,
                                 double* out_score, void* stream);
+/* K1 and K2 as ONE launch (no reference counterpart; same results as
+ * klm_dev_node_best followed by klm_dev_schedule on the whole table). Every
+ * CTA of a one-wave grid scans its share of the node table, the CTAs meet on
+ * a counter in `scratch`, each folds the partial winners and decides its
+ * requests: one cold start instead of two and no block -> ticket -> last
+ * block chain in front of the first decision. `best` (2 x int64, as
+ * klm_dev_node_best writes it) may be NULL. `scratch`: at least
+ * klm_dev_node_best_scratch_bytes() bytes, zero-filled once; overlapping
+ * calls need separate scratch. Launched cooperatively: the grid never exceeds
+ * what the device holds at once, and a device without cooperative launch
+ * returns KLM_ECUDA (callers then take the two-kernel path). */
+int klm_dev_schedule_fused(const double* battery, const uint8_t* flags, int64_t n_nodes,
+                           int64_t node_base, int64_t* best, int64_t n_requests,
+                           const double* min_battery, const int32_t* pref_off,
+                           const int32_t* pref_ids, int32_t* out_idx, double* out_score,
+                           void* scratch, void* stream);
 /* K2b schedule_bruteforce: same result, every request scans every node
  * through shared-memory tiles — the literal loop of controller.go:181-218. */
 int klm_dev_schedule_bruteforce(const double* battery, const uint8_t* flags,

@@ -125,6 +125,7 @@ SIGNATURES = {
     "klm_dev_node_best_static": (C.c_int, [_P, _P, _I64, _I64, _P, _P]),
     "klm_dev_schedule": (C.c_int, [_P, _P, _I64, _I64, _P, _I64, _P, _P, _P, _P, _P, _P]),
     "klm_dev_schedule_after_best": (C.c_int, [_P, _P, _I64, _I64, _P, _I64, _P, _P, _P, _P, _P, _P]),
+    "klm_dev_schedule_fused": (C.c_int, [_P, _P, _I64, _I64, _P, _I64, _P, _P, _P, _P, _P, _P, _P]),
     "klm_dev_schedule_bruteforce": (C.c_int, [_P, _P, _I64, _I64, _I64, _P, _P, _P, _P, _P, _P]),
     "klm_dev_merge_partials": (C.c_int, [C.c_int, _I64, _P, _P, _P, _P, _P]),
     "klm_dev_shard_slots_bytes": (_I64, []),
@@ -663,6 +664,22 @@ class Dev:
         check(fn(_dp(battery), _dp(flags), battery.numel(), node_base, _dp(best),
                                         min_battery.numel(), _dp(min_battery), _dp(pref_off), _dp(pref_ids),
                                         _dp(out_idx), _dp(out_score), _stream_ptr(stream)))
+
+    def schedule_fused(self, battery, flags, min_battery, pref_off, pref_ids, out_idx, out_score,
+                       best=None, node_base: int = 0, stream=None, scratch=None):
+        """klm_dev_schedule_fused: K1 and K2 in one cooperative launch (best: optional int64[2])."""
+        t = self.torch
+        _need(battery, t.float64, "battery"); _need(flags, t.uint8, "flags")
+        _need(min_battery, t.float64, "min_battery"); _need(pref_off, t.int32, "pref_off")
+        _need(pref_ids, t.int32, "pref_ids"); _need(out_idx, t.int32, "out_idx")
+        _need(out_score, t.float64, "out_score")
+        if best is not None:
+            _need(best, t.int64, "best")
+        sc = self.best_scratch if scratch is None else scratch
+        check(self.lib.klm_dev_schedule_fused(_dp(battery), _dp(flags), battery.numel(), node_base,
+                                              _dp(best) if best is not None else None, min_battery.numel(),
+                                              _dp(min_battery), _dp(pref_off), _dp(pref_ids), _dp(out_idx),
+                                              _dp(out_score), _dp(sc), _stream_ptr(stream)))
 
     def schedule_bruteforce(self, battery, flags, min_battery, pref_off, pref_ids, out_idx, out_score,
                             node_base: int = 0, stream=None):

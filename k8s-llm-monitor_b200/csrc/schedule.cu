@@ -388,6 +388,151 @@ schedule_kernel(const double* __restrict__ battery, const uint8_t* __restrict__ 
   }
 }
 
+// K1 and K2 in ONE launch (klm_dev_schedule_fused). Two dependent kernels cost two cold starts and
+// K1's block -> ticket -> last-block chain before any request can be decided; here every CTA of a
+// one-wave grid (all co-resident: cooperative launch) scans its share of the node table, leaves its
+// partial winner in scratch and arrives on a counter, issues the loads of its first request tile
+// (they do not depend on the winner), and only then waits for the counter; each CTA folds the
+// partial winners itself (a few KB from L2) and decides its requests. The counters are
+// self-resetting: the last CTA to leave zeroes them. Same results as K1 + K2.
+constexpr int kFusedMinBlocks = 4;  // CTAs per SM the register budget is set for
+__global__ void __launch_bounds__(kSchedThreads, kFusedMinBlocks)
+schedule_fused_kernel(const double* __restrict__ battery, const uint8_t* __restrict__ flags, int64_t n,
+                      int64_t node_base, int vec_ok, int nscan, unsigned int* __restrict__ arrive,
+                      unsigned int* __restrict__ depart, double* __restrict__ part_bat,
+                      int64_t* __restrict__ part_idx, int64_t* __restrict__ best_out, int64_t n_requests,
+                      const double* __restrict__ min_battery, const int32_t* __restrict__ pref_off,
+                      const int32_t* __restrict__ pref_ids, int32_t* __restrict__ out_idx,
+                      double* __restrict__ out_score) {
+  static_assert(kSchedThreads == kBestThreads, "scan_nodes and block_best assume the K1 block size");
+  __shared__ int64_t s_g;
+  __shared__ double s_gb;
+  int64_t g = -1;
+  double gb = 0.0;
+  bool have_best = false;
+  // all partial winners are in: fold them (every CTA for itself) and leave the barrier
+  auto wait_best = [&]() {
+    if (threadIdx.x == 0) {
+      unsigned int a;
+      do {
+        asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(a) : "l"(arrive) : "memory");
+      } while (a < (unsigned int)nscan);
+    }
+    __syncthreads();
+    Best acc{0.0, -1};
+    for (int b = threadIdx.x; b < nscan; b += kSchedThreads) {
+      Best q;
+      q.bat = __ldcg(part_bat + b);
+      q.idx = __ldcg(part_idx + b);
+      acc = better(acc, q);
+    }
+    acc = block_best(acc);  // warp 0 holds the result
+    if (threadIdx.x == 0) {
+      s_g = acc.idx < 0 ? -1 : acc.idx + node_base;
+      s_gb = acc.idx < 0 ? 0.0 : acc.bat;
+      if (blockIdx.x == 0 && best_out) {
+        best_out[0] = s_g;
+        best_out[1] = __double_as_longlong(s_gb);
+      }
+      if (atomicAdd(depart, 1u) == gridDim.x - 1) {  // everybody is past the wait: ready for the next launch
+        *arrive = 0;
+        *depart = 0;
+      }
+    }
+    __syncthreads();
+    g = s_g;
+    gb = s_gb;
+    have_best = true;
+  };
+  if ((int)blockIdx.x < nscan) {
+    Best me = scan_nodes<false>(battery, flags, n, node_base, vec_ok, ShardPublish{}, ShardSpread{});
+    me = block_best(me);
+    if (threadIdx.x == 0) {
+      part_bat[blockIdx.x] = me.bat;
+      part_idx[blockIdx.x] = me.idx;
+      __threadfence();
+      atomicAdd(arrive, 1u);
+    }
+  }
+  // (Streaming the request tiles through shared memory with cp.async one tile ahead -- a tile's
+  // offsets, thresholds and CSR ids are contiguous -- was tried here and is slower, 27.2 against
+  // 25.2 us at C4: the kernel is bound by its ~140 instructions per request and the three dependent
+  // levels of one or two tiles per CTA, not by bytes.)
+  // Node indices are 32-bit here (n + node_base < 2^31, checked by the caller: preferred ids and
+  // out_idx are int32 anyway), the battery gate is folded into one threshold (-inf: no gate), and a
+  // request is a straight line of predicated selects.
+  const int n32 = (int)n, nb32 = (int)node_base;
+  const int64_t tile = (int64_t)kSchedThreads * kSchedUnroll;
+  for (int64_t base = (int64_t)blockIdx.x * tile; base < n_requests; base += (int64_t)gridDim.x * tile) {
+    const int rem = (int)(n_requests - base < tile ? n_requests - base : tile);
+    const double* __restrict__ t_mb = min_battery + base;
+    const int32_t* __restrict__ t_off = pref_off + base;
+    double mb[kSchedUnroll];
+    int32_t k0[kSchedUnroll], k1[kSchedUnroll];
+#pragma unroll
+    for (int j = 0; j < kSchedUnroll; ++j) {
+      const int i = j * kSchedThreads + (int)threadIdx.x;
+      const bool live = i < rem;
+      mb[j] = live ? t_mb[i] : 0.0;
+      k0[j] = live ? t_off[i] : 0;
+      k1[j] = live ? t_off[i + 1] : 0;
+    }
+    int32_t p[kSchedUnroll][kSchedSlots];
+#pragma unroll
+    for (int j = 0; j < kSchedUnroll; ++j)
+#pragma unroll
+      for (int q = 0; q < kSchedSlots; ++q) p[j][q] = k0[j] + q < k1[j] ? pref_ids[k0[j] + q] : -1;
+    uint32_t f[kSchedUnroll][kSchedSlots];
+    double b[kSchedUnroll][kSchedSlots];
+#pragma unroll
+    for (int j = 0; j < kSchedUnroll; ++j)
+#pragma unroll
+      for (int q = 0; q < kSchedSlots; ++q) {
+        const int lp = p[j][q] - nb32;
+        const bool in = p[j][q] >= 0 && (unsigned)lp < (unsigned)n32;
+        f[j][q] = in ? (uint32_t)flags[lp] : 0u;  // 0 fails the name/status test below
+        b[j][q] = in ? battery[lp] : 0.0;
+      }
+    if (!have_best) wait_best();  // first tile only: every load of this tile is in flight by now
+    const int g32 = (int)g;
+#pragma unroll
+    for (int j = 0; j < kSchedUnroll; ++j) {
+      const int i = j * kSchedThreads + (int)threadIdx.x;
+      if (i >= rem) continue;
+      const double thr = mb[j] > 0 ? mb[j] : __longlong_as_double(0xfff0000000000000ll);  // controller.go:194
+      const bool okg = g32 >= 0 && !(gb < thr);  // g has the largest battery: if it fails the gate, all do
+      double bs = gb;
+      int bi = g32;
+#pragma unroll
+      for (int q = 0; q < kSchedSlots; ++q) {
+        const double sc = b[j][q] + 10;                                // :205-208
+        const bool e = (f[j][q] & 3u) == 3u && !(b[j][q] < thr);       // :190, :198, :194
+        const bool take = e && (sc > bs || (sc == bs && p[j][q] < bi));
+        bs = take ? sc : bs;
+        bi = take ? p[j][q] : bi;
+      }
+      if (okg) {
+        for (int32_t k = k0[j] + kSchedSlots; k < k1[j]; ++k) {  // longer preferred lists
+          const int pk = pref_ids[k];
+          const int lp = pk - nb32;
+          if (pk < 0 || (unsigned)lp >= (unsigned)n32) continue;
+          if ((flags[lp] & 3u) != 3u) continue;
+          const double bk = battery[lp];
+          if (bk < thr) continue;
+          const double sc = bk + 10;
+          if (sc > bs || (sc == bs && pk < bi)) {
+            bs = sc;
+            bi = pk;
+          }
+        }
+      }
+      out_idx[base + i] = okg ? bi : -1;
+      out_score[base + i] = okg ? bs : 0.0;
+    }
+  }
+  if (!have_best) wait_best();  // a CTA without requests still folds (CTA 0 writes best_out) and leaves
+}
+
 // Rendezvous of the ranks on their streams: publish `epoch` into this rank's slot of every rank's
 // array, then wait until this rank's own array carries it from everybody. One warp. Used to line
 // the ranks up in front of a timed region (bench.py) or a snapshot change; the data path itself
@@ -1120,5 +1265,69 @@ extern "C" int klm_dev_shard_error(const void* my_slots, int* out, void* stream)
   const ShardSlot* slots = static_cast<const ShardSlot*>(my_slots);
   KLM_CUDA(cudaMemcpyAsync(out, slots + 2 * kMaxShardParts, sizeof(int), cudaMemcpyDeviceToHost, as_stream(stream)));
   KLM_CUDA(cudaStreamSynchronize(as_stream(stream)));
+  return KLM_OK;
+}
+
+// ---------------------------------------------------------------- K1 + K2 in one launch
+
+extern "C" int klm_dev_schedule_fused(const double* battery, const uint8_t* flags, int64_t n_nodes,
+                                      int64_t node_base, int64_t* best, int64_t n_requests,
+                                      const double* min_battery, const int32_t* pref_off,
+                                      const int32_t* pref_ids, int32_t* out_idx, double* out_score,
+                                      void* scratch, void* stream) {
+  if (n_nodes < 0 || n_requests < 0 || !scratch || (n_nodes > 0 && (!battery || !flags))) {
+    set_error("klm_dev_schedule_fused: bad argument");
+    return KLM_EINVAL;
+  }
+  if (n_requests > 0 && (!min_battery || !pref_off || !out_idx || !out_score)) {
+    set_error("klm_dev_schedule_fused: null request array");
+    return KLM_EINVAL;
+  }
+  if (node_base < 0 || n_nodes + node_base > 0x7fffffffll) {
+    set_error("klm_dev_schedule_fused: node indices must fit int32 (n_nodes + node_base <= 2^31 - 1)");
+    return KLM_ELIMIT;
+  }
+  // one wave: as many CTAs as can be resident at once (asked once per device), never more than
+  // the work needs
+  static PerDeviceOnce cap_known;
+  static int cap_blocks[64];
+  int dev = 0;
+  KLM_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64) {
+    set_error("klm_dev_schedule_fused: device ordinal %d out of range", dev);
+    return KLM_ELIMIT;
+  }
+  if (!cap_known.done(dev)) {
+    int per_sm = 0, sms = 0, coop = 0;
+    KLM_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, schedule_fused_kernel, kSchedThreads, 0));
+    KLM_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    KLM_CUDA(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev));
+    cap_blocks[dev] = coop ? per_sm * sms : 0;
+    cap_known.set(dev);
+  }
+  int64_t cap = cap_blocks[dev];
+  if (cap > kBestMaxBlocks) cap = kBestMaxBlocks;
+  if (cap < 1) {
+    set_error("klm_dev_schedule_fused: cooperative launch is not available on device %d", dev);
+    return KLM_ECUDA;
+  }
+  const int vec_ok = aligned16(battery) && aligned16(flags);
+  const int64_t node_tiles = vec_ok ? ceil_div(n_nodes >> 1, (int64_t)kBestThreads * (kBestNodesPerThread / 2))
+                                    : ceil_div(n_nodes, (int64_t)kBestThreads);
+  const int64_t req_tiles = ceil_div(n_requests, (int64_t)kSchedThreads * kSchedUnroll);
+  int64_t grid = node_tiles > req_tiles ? node_tiles : req_tiles;
+  if (grid < 1) grid = 1;
+  if (grid > cap) grid = cap;
+  int nscan = (int)(node_tiles < grid ? node_tiles : grid);
+  if (nscan < 1) nscan = 1;  // (CTA 0 also takes the odd last node)
+  char* s = static_cast<char*>(scratch);
+  unsigned int* arrive = reinterpret_cast<unsigned int*>(s);
+  unsigned int* depart = arrive + 1;
+  double* part_bat = reinterpret_cast<double*>(s + 256);
+  int64_t* part_idx = reinterpret_cast<int64_t*>(s + 256 + (int64_t)kBestMaxBlocks * 8);
+  void* args[] = {&battery, &flags, &n_nodes, &node_base, const_cast<int*>(&vec_ok), &nscan, &arrive, &depart,
+                  &part_bat, &part_idx, &best, &n_requests, &min_battery, &pref_off, &pref_ids, &out_idx, &out_score};
+  KLM_CUDA(cudaLaunchCooperativeKernel(reinterpret_cast<const void*>(schedule_fused_kernel), dim3((unsigned)grid),
+                                       dim3(kSchedThreads), args, 0, as_stream(stream)));
   return KLM_OK;
 }

@@ -290,6 +290,68 @@ def test_schedule_after_best_overlaps_k1(dev, pkg, n, r):
         _eq((oi.cpu().numpy(), os_.cpu().numpy()), wants[i & 1], f"launch {i}")
 
 
+@pytest.mark.parametrize("n,r", [(1, 1), (7, 0), (1000, 5), (4097, 70_000), (100_000, 300_000),
+                                 (1_000_000, 1_000_000), (2_000_001, 1000)])
+def test_schedule_fused_equals_k1_k2(dev, pkg, n, r):
+    """klm_dev_schedule_fused (K1 and K2 in one cooperative launch) against the oracle and
+    against `best` as klm_dev_node_best writes it. Two tables with different winners alternate
+    back to back on the same scratch without synchronisation: the self-resetting counters must be
+    ready for every next launch, and no CTA may decide with the previous launch's winner."""
+    import torch
+    rng = np.random.default_rng(3 * n + r)
+    mb, off, ids = pkg.synth.requests(6, r, n)
+    t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()
+    d_mb = t(mb if r else np.zeros(1))[:r]
+    d_off, d_ids = t(off), t(ids if ids.size else np.zeros(1, np.int32))
+    tables, wants, bests = [], [], []
+    for k in range(2):
+        bat, flags = pkg.synth.node_table(8 + k, n)
+        bat = bat.copy()
+        bat[rng.integers(0, n)] = 99.95 + k * 0.01
+        tables.append((t(bat), t(flags)))
+        wants.append(ob.schedule_decomposed(bat, flags, mb, off, ids))
+        b = torch.zeros(2, dtype=torch.int64, device="cuda")
+        dev.node_best(tables[k][0], tables[k][1], b)
+        bests.append(b.cpu().numpy().copy())
+    outs = [(torch.full((max(r, 1),), -7, dtype=torch.int32, device="cuda")[:r],
+             torch.empty(max(r, 1), dtype=torch.float64, device="cuda")[:r],
+             torch.zeros(2, dtype=torch.int64, device="cuda")) for _ in range(6)]
+    scratch = torch.zeros(int(dev.lib.klm_dev_node_best_scratch_bytes()), dtype=torch.uint8, device="cuda")
+    for i, (oi, os_, b) in enumerate(outs):
+        d_bat, d_flags = tables[i & 1]
+        dev.schedule_fused(d_bat, d_flags, d_mb, d_off, d_ids, oi, os_, best=b if i != 3 else None,
+                           scratch=scratch)
+    torch.cuda.synchronize()
+    assert not scratch[:8].any(), "the barrier counters must be back at zero"
+    for i, (oi, os_, b) in enumerate(outs):
+        _eq((oi.cpu().numpy(), os_.cpu().numpy()), wants[i & 1], f"launch {i}")
+        if i != 3:
+            assert np.array_equal(b.cpu().numpy(), bests[i & 1]), i
+
+
+def test_schedule_fused_unaligned_and_based(dev, pkg):
+    """Columns that are not 16-byte aligned (scalar scan) and a node_base: indices are global."""
+    import torch
+    n, r, base = 5001, 3000, 4096
+    bat, flags = pkg.synth.node_table(11, n + 3)
+    mb, off, ids = pkg.synth.requests(11, r, n)
+    t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()
+    d_bat, d_flags = t(bat)[1:1 + n], t(flags)[3:3 + n]
+    want = ob.schedule_decomposed(bat[1:1 + n], flags[3:3 + n], mb, off, ids)
+    oi = torch.empty(r, dtype=torch.int32, device="cuda")
+    os_ = torch.empty(r, dtype=torch.float64, device="cuda")
+    dev.schedule_fused(d_bat, d_flags, t(mb), t(off), t(ids), oi, os_)
+    torch.cuda.synchronize()
+    _eq((oi.cpu().numpy(), os_.cpu().numpy()), want, "unaligned")
+    # the same table as the shard [base, base + n) of a larger one: preferred ids are global
+    ids_g = (ids.astype(np.int64) + base).astype(np.int32)
+    dev.schedule_fused(d_bat, d_flags, t(mb), t(off), t(ids_g), oi, os_, node_base=base)
+    torch.cuda.synchronize()
+    gi = oi.cpu().numpy()
+    assert np.array_equal(np.where(gi >= 0, gi - base, gi), want[0])
+    assert np.array_equal(os_.cpu().numpy(), want[1])
+
+
 def test_bruteforce_many_prefs(handle, pkg):
     """More preferred ids than the brute-force kernel keeps in registers."""
     rng = np.random.default_rng(5)
