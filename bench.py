@@ -47,6 +47,7 @@ SHAPES = {"c2": dict(nodes=1000, pods=10_000, series=26_000, window=3600, reques
 CFG_ID = {"c2": 2, "c3": 3, "c4": 4, "c5": 5}
 DTYPE = "f32 samples, f64 sums and scores, int64 aggregates"
 MIN_TIMED_S = 0.2   # the timed region is repeated (rounds) until it lasts at least this long
+L2_BYTES = 126 << 20      # B200 L2 (the request sets of c4 / c5 are sized against it)
 K7_TRAFFIC_C2 = 379.27e6  # dram bytes read + written by one K7 launch at c2 (ncu --set full, profiles/r02_k7_ring_ncu_summary.txt)
 
 
@@ -58,7 +59,9 @@ def config_for(wl):
             "per_rank": "own series shard (weak scaling)" if weak else
                         ("request shard, node table replicated (strong scaling)" if wl == "c4" else
                          "node-range shard + request shard, peers' shards read over NVLink (strong scaling)"),
-            "l2": "inputs exceed L2 (374 MB / 4.6 GB of ring per step)" if weak else "256 MiB L2 flush between steps",
+            "l2": "inputs exceed L2 (374 MB / 4.6 GB of ring per step)" if weak else
+                  "every step takes the next of several request/result sets that together exceed L2 1.5 times "
+                  "(ours; --l2-flush: one set behind a 256 MiB flush)",
             "timed_region": f"K steps x rounds, rounds chosen so that it lasts >= {MIN_TIMED_S} s"}
 
 
@@ -175,7 +178,7 @@ class Ctx:
         return bool(t.item() > 0.5)
 
 
-def timed_rounds(ctx, step, steps, warmup, flush, events, pre_step=None):
+def timed_rounds(ctx, step, steps, warmup, flush, events, pre_step=None, min_timed_s=None):
     """W warm-up steps, then `rounds` x K timed steps between one pair of CUDA events (inputs
     larger than L2) or one pair per step around an L2 flush (inputs that fit L2). Returns
     (ms_per_step, rounds, clocks); max over ranks."""
@@ -193,7 +196,7 @@ def timed_rounds(ctx, step, steps, warmup, flush, events, pre_step=None):
     e1.record()
     e1.synchronize()
     est = ctx.max_over_ranks(e0.elapsed_time(e1) / 3 * 1e-3)
-    rounds = max(1, int(np.ceil(MIN_TIMED_S / max(est * steps, 1e-9))))
+    rounds = max(1, int(np.ceil((MIN_TIMED_S if min_timed_s is None else min_timed_s) / max(est * steps, 1e-9))))
     rounds = min(rounds, 4000)
     events.clear()
     ctx.barrier()
@@ -495,6 +498,18 @@ def run_schedule_workload(ctx, wl):
     d_mb, d_off, d_ids = cu(mb), cu(off), cu(ids if ids.size else np.zeros(1, np.int32))
     o_idx = torch.empty(rl, dtype=torch.int32, device="cuda")
     o_score = torch.empty(rl, dtype=torch.float64, device="cuda")
+    # Every step decides a DIFFERENT batch: the rank's request arrays and result arrays exist in
+    # `nsets` copies (disjoint streams of the same generator) that together exceed L2 1.5 times, so
+    # a step's requests always come from DRAM and its results go there, with no flush kernel between
+    # steps. Set 0 is the BASELINE batch (the one checked and the one the e2e leg ships).
+    set_bytes = mb.nbytes + off.nbytes + ids.nbytes + rl * 12
+    nsets = 1 if args.l2_flush else max(2, int(np.ceil(1.5 * L2_BYTES / max(set_bytes, 1))))
+    req_sets = [(d_mb, d_off, d_ids, o_idx, o_score)]
+    for k in range(1, nsets):
+        mbk, offk, idsk = syn.requests(cid, rl, N, start=r0 + k * R)
+        req_sets.append((cu(mbk), cu(offk), cu(idsk if idsk.size else np.zeros(1, np.int32)),
+                         torch.empty(rl, dtype=torch.int32, device="cuda"),
+                         torch.empty(rl, dtype=torch.float64, device="cuda")))
     keep = []
     spread_ptrs = None
     if wl == "c4" or world == 1:
@@ -569,28 +584,30 @@ def run_schedule_workload(ctx, wl):
                          spread_ptrs[1], epoch)                                                      # K1 + all-gather
     else:
         k1 = dev.prebind("node_best_publish", my_bat, my_flags, lo, world, rank, slot_ptrs, epoch)   # K1 + exchange
-    k2 = dev.prebind("schedule_sharded", N, bat_ptrs, flg_ptrs, slots, epoch, d_mb, d_off, d_ids, o_idx, o_score,
-                     table_from_k1=spread_ptrs is not None)                                          # K2
+    k2s = [dev.prebind("schedule_sharded", N, bat_ptrs, flg_ptrs, slots, epoch, *rs,
+                       table_from_k1=spread_ptrs is not None) for rs in req_sets]                    # K2
     events = []
     # A rank that holds the whole table (c4 at any N, c5 on one GPU) needs no exchange: K1 over
     # the table and K2 over its request slice are ONE cooperative launch (klm_dev_schedule_fused)
     fused = (wl == "c4" or world == 1) and not args.two_kernels
     if fused:
-        kf = dev.prebind("schedule_fused", fb, ff, d_mb, d_off, d_ids, o_idx, o_score)
+        kfs = [dev.prebind("schedule_fused", fb, ff, *rs) for rs in req_sets]
         launches_per_step = 1
         kernel_name = "schedule_fused (K1 + K2 in one cooperative launch, per rank)"
 
         def issue():
-            kf()
+            kfs[which[0]]()
     else:
         launches_per_step = 2
         kernel_name = "node_best_publish+schedule_sharded (per rank)"
 
         def issue():
-            k1(); k2()
+            k1(); k2s[which[0]]()
+    which = [0]   # the request set of the step being issued
 
     def step(timed):
         epoch.value += 1
+        which[0] = (which[0] + 1) % nsets if timed else 0
         if timed and len(events) < 4096:
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record()
@@ -617,8 +634,38 @@ def run_schedule_workload(ctx, wl):
     del fb2, ff2, fi, fs
 
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
-    ms_per_step, rounds, clocks = timed_rounds(ctx, step, args.steps, max(args.warmup, 3), flush, events, pre_step)
-    kern_ms = float(np.mean([a.elapsed_time(b) for a, b in events]))
+    if args.l2_flush:
+        ms_per_step, rounds, clocks = timed_rounds(ctx, step, args.steps, max(args.warmup, 3), flush, events, pre_step)
+        kern_ms = float(np.mean([a.elapsed_time(b) for a, b in events]))
+    else:
+        # the other way to keep L2 out of it, for comparison: one batch, a 256 MiB flush (and, for
+        # N > 1, a rendezvous) before every step, one event pair per step
+        fl_ms, _, _ = timed_rounds(ctx, step, args.steps, 3, flush, events, pre_step, min_timed_s=0.02)
+        extra["ms_per_step_single_batch_after_l2_flush"] = fl_ms
+        # check the rotating sets too (untimed): every set's slice against the unsharded kernels
+        for k in (nsets - 1,):
+            which[0] = k - 1
+            step(True)
+            torch.cuda.synchronize()
+            rs = req_sets[k]
+            ci = torch.empty(rl, dtype=torch.int32, device="cuda")
+            cs = torch.empty(rl, dtype=torch.float64, device="cuda")
+            cb_, cf_ = cu(bat), cu(flags)
+            cbest = torch.empty(2, dtype=torch.int64, device="cuda")
+            dev.node_best(cb_, cf_, cbest)
+            dev.schedule(cb_, cf_, cbest, rs[0], rs[1], rs[2], ci, cs)
+            torch.cuda.synchronize()
+            if not ctx.all_true(bool(torch.equal(rs[3], ci) and torch.equal(rs[4], cs))):
+                raise SystemExit(f"{wl}: request set {k}: sharded result differs from the unsharded one")
+            del ci, cs, cb_, cf_
+        ms_per_step, rounds, clocks = timed_rounds(ctx, step, args.steps, max(args.warmup, 3), None, events)
+        kern_ms = float(np.mean([a.elapsed_time(b) for a, b in events]))
+        extra["request_sets"] = nsets
+        extra["timing"] = ("steps back to back on the stream, each on the next of %d request/result sets "
+                           "(%.0f MB in all, 1.5 x L2); one CUDA event pair around the whole region; max over ranks"
+                           % (nsets, nsets * set_bytes / 1e6))
+        step(False)   # leave set 0's results in place for the e2e comparison below
+        torch.cuda.synchronize()
     n_launch = launches_per_step * rounds * args.steps
     value = R / (ms_per_step * 1e-3)
     alg_bytes = 9 * (N if fused else hi - lo) + int(24 * rl + 13 * ids.size)
@@ -828,6 +875,9 @@ def main():
     ap.add_argument("--k7", choices=["hinted", "stateless"], default="hinted",
                     help="c2 / c3: K7 with the brackets carried from step to step (what klm_collect runs), or "
                          "the stateless klm_dev_window_stats")
+    ap.add_argument("--l2-flush", action="store_true",
+                    help="c4 / c5: one request batch and a 256 MiB L2 flush before every step, instead of "
+                         "rotating request sets that exceed L2")
     ap.add_argument("--two-kernels", action="store_true",
                     help="c4 / c5 on one GPU: K1 and K2 as two launches instead of klm_dev_schedule_fused")
     ap.add_argument("--c5-probe", action="store_true",

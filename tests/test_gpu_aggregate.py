@@ -73,6 +73,29 @@ def test_node_rates(handle, pkg, n):
         assert np.array_equal(got[k], want[k]), k
 
 
+@pytest.mark.parametrize("n,shift", [(1, 0), (2, 0), (4097, 0), (1_000_001, 0), (5000, 1), (303_105, 0)])
+def test_dev_node_rates_pairs_and_unaligned(dev, pkg, n, shift):
+    """klm_dev_node_rates on device columns: the two-nodes-per-thread kernel (odd lengths, every
+    grid shape) and the scalar kernel that columns off 16-byte alignment fall back to."""
+    import torch
+    snap = pkg.synth.cluster_snapshot(5, n + shift, 0)
+    snap["cpu_capacity"][::7] = 0
+    snap["disk_allocatable"][::5] += 1 << 40
+    cu = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()[shift:]
+    cols = {k: cu(snap[k]) for k in ("cpu_capacity", "cpu_usage", "memory_capacity", "memory_usage")}
+    dc, da = cu(snap["disk_capacity"]), cu(snap["disk_allocatable"])
+    out = {"cpu_rate": torch.empty(n, dtype=torch.float64, device="cuda"),
+           "memory_rate": torch.empty(n, dtype=torch.float64, device="cuda"),
+           "disk_usage": torch.empty(n, dtype=torch.int64, device="cuda"),
+           "disk_rate": torch.empty(n, dtype=torch.float64, device="cuda"),
+           "under_pressure": torch.empty(n, dtype=torch.uint8, device="cuda")}
+    dev.node_rates(cols, dc, da, out)
+    torch.cuda.synchronize()
+    want = ob.node_rates({k: v[shift:] for k, v in snap.items() if k != "pod_running" and k != "gpu_usage"})
+    for k in want:
+        assert np.array_equal(out[k].cpu().numpy(), want[k]), k
+
+
 @pytest.mark.parametrize("p", [1, 10_000, 250_000])
 def test_pod_rates(handle, pkg, p):
     c = pkg.synth.pod_containers(2, p)
