@@ -78,6 +78,9 @@ def main():
         k2 = dev.prebind("schedule", d_bat, d_flags, best, d_mb, d_off, d_ids, oi, os_)
         timeit(f"K1 node_best N={n}", k1, 9 * n, "latency-bound below ~1 MB")
         timeit(f"K2 schedule R={r} N={n}", k2, 24 * r + 13 * ids.size, units=("decisions/s", r))
+        kf = dev.prebind("schedule_fused", d_bat, d_flags, d_mb, d_off, d_ids, oi, os_)
+        timeit(f"K1+K2 schedule_fused R={r} N={n}", kf, 9 * n + 24 * r + 13 * ids.size,
+               "one cooperative launch", units=("decisions/s", r))
     g = 8
     pi = torch.randint(-1, 1000, (g, r), dtype=torch.int32, device="cuda")
     ps = torch.rand((g, r), dtype=torch.float64, device="cuda")
@@ -147,6 +150,42 @@ def main():
         k7 = dev.prebind("window_stats", ring, seen, t, o[0], o[1], om, o[2], variant=variant)
         timeit(f"K7 window_stats[{variant}] S={s} T={t}", k7, s * (4 * t + 20), do_flush=False,
                units=("samples/s", s * t))
+    if t <= 8192 and not os.environ.get("KLM_BK_ONCE"):
+        # the streaming product path: one fresh sample per series between launches, brackets carried
+        # in `state`; a train of (tick, K7) pairs minus the train of ticks alone
+        state = torch.full((s, 2), float("nan"), dtype=torch.float32, device="cuda")
+        ticks = (torch.rand((256, s), device="cuda") * 100).float()
+        k6s = [dev.prebind("ring_ingest", ring, seen, t, ticks[i]) for i in range(256)]
+        kh = dev.prebind("window_stats", ring, seen, t, o[0], o[1], om, o[2], state=state)
+        cur = [0]
+
+        def pair():
+            k6s[cur[0] % 256]()
+            cur[0] += 1
+            kh()
+
+        def tick_only():
+            k6s[cur[0] % 256]()
+            cur[0] += 1
+        for _ in range(6):
+            pair()
+
+        def train(fn, iters=20):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            torch.cuda.synchronize()
+            e0.record()
+            for _ in range(iters):
+                fn()
+            e1.record()
+            e1.synchronize()
+            return e0.elapsed_time(e1) / iters
+        tt = float(np.median([train(pair) for _ in range(7)])) - float(np.median([train(tick_only) for _ in range(7)]))
+        alg = s * (4 * t + 36)
+        print(json.dumps({"kernel": f"K7 window_stats[hinted: brackets carried, landing ring] S={s} T={t}",
+                          "us": round(tt * 1e3, 2), "algorithmic_bytes": int(alg), "GB/s": round(alg / tt / 1e6, 1),
+                          "frac_of_measured_hbm_peak": round(alg / tt / 1e6 / peak, 4),
+                          "note": "train of (tick, K7) pairs minus the train of ticks", "samples/s": round(s * t / (tt * 1e-3), 1)}),
+              flush=True)
 
 
 if __name__ == "__main__":
