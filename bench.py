@@ -537,19 +537,27 @@ def run_schedule_workload(ctx, wl):
         # every rank holds a replica in symmetric memory but fills in only its own shard; K1 pushes
         # the shard into the peers' replicas while it scans it, K2 probes the local replica
         import torch.distributed._symmetric_memory as symm_mem
-        sb = symm_mem.empty(N, dtype=torch.float64, device="cuda")
-        sf = symm_mem.empty(N, dtype=torch.uint8, device="cuda")
-        hb = symm_mem.rendezvous(sb, ctx.dist.group.WORLD)
-        hf = symm_mem.rendezvous(sf, ctx.dist.group.WORLD)
-        sb.fill_(-1.0)
-        sf.zero_()
-        sb[lo:hi].copy_(cu(bat[lo:hi]))
-        sf[lo:hi].copy_(cu(flags[lo:hi]))
-        keep += [sb, sf, hb, hf]
-        my_bat, my_flags = sb[lo:hi], sf[lo:hi]
-        bat_ptrs = [sb[a:].data_ptr() if b > a else 0 for a, b in ranges]
-        flg_ptrs = [sf[a:].data_ptr() if b > a else 0 for a, b in ranges]
-        spread_ptrs = ([int(x) for x in hb.buffer_ptrs], [int(x) for x in hf.buffer_ptrs])
+        # Two replicas, used by even and odd epochs in turn: steps run back to back, so a rank that
+        # is one step ahead pushes epoch e + 1 into its peers while they may still probe epoch e's
+        # table (klm.h: a replica may be rewritten only when every rank's K2 of its epoch is done;
+        # no rank can be two steps ahead, so two replicas are enough).
+        par = []
+        for _ in range(2):
+            sb = symm_mem.empty(N, dtype=torch.float64, device="cuda")
+            sf = symm_mem.empty(N, dtype=torch.uint8, device="cuda")
+            hb = symm_mem.rendezvous(sb, ctx.dist.group.WORLD)
+            hf = symm_mem.rendezvous(sf, ctx.dist.group.WORLD)
+            sb.fill_(-1.0)
+            sf.zero_()
+            sb[lo:hi].copy_(cu(bat[lo:hi]))
+            sf[lo:hi].copy_(cu(flags[lo:hi]))
+            keep += [sb, sf, hb, hf]
+            par.append({"my": (sb[lo:hi], sf[lo:hi]),
+                        "bat_ptrs": [sb[a:].data_ptr() if b > a else 0 for a, b in ranges],
+                        "flg_ptrs": [sf[a:].data_ptr() if b > a else 0 for a, b in ranges],
+                        "spread": ([int(x) for x in hb.buffer_ptrs], [int(x) for x in hf.buffer_ptrs])})
+        my_bat, my_flags = par[0]["my"]
+        bat_ptrs, flg_ptrs, spread_ptrs = par[0]["bat_ptrs"], par[0]["flg_ptrs"], par[0]["spread"]
         extra["exchange"] = ("K1 pushes its shard (9 B/node) into every peer's replica over NVLink while scanning it "
                              "(plain stores through peer pointers) + 16 B per rank pair into the slots; K2 probes locally")
     if world > 1:
@@ -579,13 +587,16 @@ def run_schedule_workload(ctx, wl):
         extra["timing"] = ("per step: L2 flush, device-side rendezvous of the ranks, then CUDA events around "
                            "K1 + exchange + K2; max over ranks")
     epoch = ctypes.c_uint64(0)
-    if spread_ptrs is not None:
-        k1 = dev.prebind("node_best_spread", my_bat, my_flags, lo, world, rank, slot_ptrs, spread_ptrs[0],
-                         spread_ptrs[1], epoch)                                                      # K1 + all-gather
+    if spread_ptrs is not None:   # K1 + all-gather into the replica of the epoch's parity; K2 on that replica
+        k1p = [dev.prebind("node_best_spread", q["my"][0], q["my"][1], lo, world, rank, slot_ptrs, q["spread"][0],
+                           q["spread"][1], epoch) for q in par]
+        k2p = [[dev.prebind("schedule_sharded", N, q["bat_ptrs"], q["flg_ptrs"], slots, epoch, *rs, table_from_k1=True)
+                for rs in req_sets] for q in par]
     else:
         k1 = dev.prebind("node_best_publish", my_bat, my_flags, lo, world, rank, slot_ptrs, epoch)   # K1 + exchange
-    k2s = [dev.prebind("schedule_sharded", N, bat_ptrs, flg_ptrs, slots, epoch, *rs,
-                       table_from_k1=spread_ptrs is not None) for rs in req_sets]                    # K2
+        k2s = [dev.prebind("schedule_sharded", N, bat_ptrs, flg_ptrs, slots, epoch, *rs,
+                           table_from_k1=False) for rs in req_sets]                                   # K2
+        k1p, k2p = [k1, k1], [k2s, k2s]
     events = []
     # A rank that holds the whole table (c4 at any N, c5 on one GPU) needs no exchange: K1 over
     # the table and K2 over its request slice are ONE cooperative launch (klm_dev_schedule_fused)
@@ -602,7 +613,8 @@ def run_schedule_workload(ctx, wl):
         kernel_name = "node_best_publish+schedule_sharded (per rank)"
 
         def issue():
-            k1(); k2s[which[0]]()
+            q = epoch.value & 1
+            k1p[q](); k2p[q][which[0]]()
     which = [0]   # the request set of the step being issued
 
     def step(timed):
