@@ -456,3 +456,37 @@ def test_every_call_leaves_a_bracket(dev, t):
         finite_p95 = np.isfinite(want["p95"])
         left = ~np.isnan(st[:, 0]) & ~np.isnan(st[:, 1])
         assert left[finite_p95].mean() > 0.995, (t, tick, float(left[finite_p95].mean()))
+
+
+def test_full_c3_hinted_against_oracle(dev, pkg):
+    """C3 at full size -- 5000 UAV nodes x 64 channels = 320 000 series x 3600 samples (4.6 GB),
+    the BASELINE configuration -- through the product path (brackets carried between calls, the
+    landing-ring kernel): every series of the last of three ticks is compared with the oracle, bit
+    for bit (the threaded quickselect oracle, itself pinned to the sorting one on CPU)."""
+    import os
+    import torch
+    t, nodes, step = 3600, 5000, 250
+    s = nodes * 64
+    ring = torch.empty((s, t), dtype=torch.float32, device="cuda")
+    for a in range(0, nodes, step):
+        rows = pkg.synth.uav_channel_rows(3, a, a + step, t)
+        ring[a * 64:a * 64 + rows.shape[0]] = torch.from_numpy(rows).cuda()
+    seen = torch.full((s,), t, dtype=torch.int32, device="cuda")
+    state = torch.full((s, 2), float("nan"), dtype=torch.float32, device="cuda")
+    o = {k: torch.empty(s, dtype=torch.float64 if k == "mean" else torch.float32, device="cuda")
+         for k in ("min", "max", "mean", "p95")}
+    for tick in range(3):
+        if tick:   # a fresh sample per series: an earlier sample of the same channel
+            vals = ring[:, 7 * tick].clone()
+            dev.ring_ingest(ring, seen, t, vals)
+        dev.window_stats(ring, seen, t, o["min"], o["max"], o["mean"], o["p95"], state=state)
+    torch.cuda.synchronize()
+    st = state.cpu().numpy()
+    assert np.mean(~np.isnan(st[:, 0])) > 0.99, "the calls left no brackets"
+    got = {k: v.cpu().numpy() for k, v in o.items()}
+    threads = os.cpu_count() or 1
+    for a in range(0, s, 40_000):
+        b = min(s, a + 40_000)
+        rows = ring[a:b].cpu().numpy()
+        want = ob.window_stats(rows, np.full(b - a, t + 2, np.uint32), t, fast=True, threads=threads)
+        check_stats({k: v[a:b] for k, v in got.items()}, want, f"full C3 series {a}..{b}")
