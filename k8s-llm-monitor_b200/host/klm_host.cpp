@@ -92,23 +92,41 @@ std::vector<SchedulingRequestStatus> Controller::Reconcile(
   const int64_t n = static_cast<int64_t>(uavs.size());
   std::vector<double> battery(n);
   std::vector<uint8_t> flags(n);
-  std::unordered_map<std::string, std::vector<int32_t>> by_name;  // lower(name) -> every index
+  // lower(name) -> every index that carries it. Names are almost always unique, so the map holds
+  // the first index and a link to the next item of the same name (no vector per name).
+  std::unordered_map<std::string, int32_t> by_name;
+  by_name.reserve(static_cast<size_t>(n) * 2);
+  std::vector<int32_t> next_same(n, -1), last_same(n, -1);
+  static const std::string kActive = "active";
   for (int64_t i = 0; i < n; ++i) {
     const UAVMetricItem& u = uavs[i];
-    const std::string name = u.HasNodeName ? u.NodeName : std::string();
+    const bool named = u.HasNodeName && !u.NodeName.empty();
     battery[i] = u.HasBattery ? u.Battery : 0.0;                                   // :187
-    const std::string st = u.HasStatus ? ToLower(u.CollectionStatus) : std::string();  // :188
     uint8_t f = 0;
-    if (!name.empty()) f |= KLM_NODE_HAS_NAME;                                    // :190
-    if (st.empty() || st == "active") f |= KLM_NODE_STATUS_OK;                    // :198
+    if (named) f |= KLM_NODE_HAS_NAME;                                             // :190
+    if (!u.HasStatus || u.CollectionStatus.empty() || u.CollectionStatus == kActive ||
+        ToLower(u.CollectionStatus) == kActive)
+      f |= KLM_NODE_STATUS_OK;                                                     // :188, :198
     flags[i] = f;
-    if (!name.empty()) by_name[ToLower(name)].push_back(static_cast<int32_t>(i));  // :206
+    if (named) {                                                                   // :206
+      auto ins = by_name.emplace(ToLower(u.NodeName), static_cast<int32_t>(i));
+      if (!ins.second) {  // a duplicate name: append to the chain of its first item
+        const int32_t head = ins.first->second;
+        const int32_t tail = last_same[head] < 0 ? head : last_same[head];
+        next_same[tail] = static_cast<int32_t>(i);
+        last_same[head] = static_cast<int32_t>(i);
+      }
+    }
   }
 
   std::vector<SchedulingRequestStatus> out(requests.size());
   std::vector<size_t> live;  // requests that reach buildCandidates
   std::vector<double> min_battery;
   std::vector<int32_t> pref_off{0}, pref_ids;
+  std::vector<std::string> seen;  // (a request names a handful of nodes: a scan beats a set)
+  live.reserve(requests.size());
+  min_battery.reserve(requests.size());
+  pref_off.reserve(requests.size() + 1);
   for (size_t r = 0; r < requests.size(); ++r) {
     const SchedulingRequest& q = requests[r];
     if (q.HasPhase && !q.Phase.empty() && q.Phase != "Pending") continue;          // :117-119
@@ -120,13 +138,14 @@ std::vector<SchedulingRequestStatus> Controller::Reconcile(
     }
     live.push_back(r);
     min_battery.push_back(q.Spec.MinBatteryPercent);
-    std::unordered_map<std::string, bool> seen;                                    // preferredSet, :175-178
+    seen.clear();                                                                  // preferredSet, :175-178
     for (const std::string& p : q.Spec.PreferredNodes) {
-      const std::string lp = ToLower(p);
-      if (seen.emplace(lp, true).second) {
-        auto it = by_name.find(lp);
-        if (it != by_name.end()) pref_ids.insert(pref_ids.end(), it->second.begin(), it->second.end());
-      }
+      std::string lp = ToLower(p);
+      if (std::find(seen.begin(), seen.end(), lp) != seen.end()) continue;
+      auto it = by_name.find(lp);
+      if (it != by_name.end())
+        for (int32_t i = it->second; i >= 0; i = next_same[i]) pref_ids.push_back(i);
+      seen.push_back(std::move(lp));
     }
     pref_off.push_back(static_cast<int32_t>(pref_ids.size()));
   }

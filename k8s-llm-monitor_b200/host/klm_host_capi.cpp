@@ -113,6 +113,16 @@ int klmh_status_json(void* sv, int i, const char* last_updated, char* dst, int c
   return s->statuses[i].Updated ? 1 : 0;
 }
 
+// every status of the last reconcile encoded in one call (timing: tools/host_bench.py); returns the
+// number of bytes of JSON produced
+int64_t klmh_status_json_all(void* sv, const char* last_updated) {
+  Session* s = static_cast<Session*>(sv);
+  const std::string stamp = last_updated ? last_updated : "";
+  int64_t total = 0;
+  for (const SchedulingRequestStatus& st : s->statuses) total += static_cast<int64_t>(EncodeStatus(st, stamp).size());
+  return total;
+}
+
 // a float64 in Go's encoding/json form (what EncodeStatus writes for `score`)
 void klmh_format_float(double v, char* dst, int cap) { put(dst, cap, FormatJSONFloat(v)); }
 

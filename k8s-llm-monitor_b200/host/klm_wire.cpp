@@ -1,45 +1,62 @@
 #include "klm_wire.h"
 
+#include <charconv>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
 #include <initializer_list>
-#include <map>
-#include <memory>
+#include <deque>
+#include <string_view>
+#include <vector>
 #include <stdexcept>
 
 namespace klmhost {
 namespace {
 
-struct JValue;
-using JPtr = std::shared_ptr<JValue>;
+// The document is one flat array of nodes (children linked as first-child / next-sibling, member
+// names kept in the member's node) over the caller's text: strings without escapes are views into
+// it, the rare escaped ones are decoded into a side pool. No allocation per value, no map per
+// object (the objects of this path have a handful of members; a lookup is a short scan, the LAST
+// member of a name winning as in a Go map built by encoding/json).
+constexpr uint32_t kNil = 0xffffffffu;
 struct JValue {
-  enum Kind { Null, Bool, Int, Float, String, Array, Object } kind = Null;
+  enum Kind : uint8_t { Null, Bool, Int, Float, String, Array, Object } kind = Null;
   bool b = false;
-  double num = 0;  // Int and Float both carry the value here
-  std::string str;
-  std::vector<JPtr> arr;
-  std::map<std::string, JPtr> obj;
-  const JValue* get(const std::string& k) const {
+  uint32_t first = kNil, next = kNil;  // first child, next sibling (indices into the arena)
+  double num = 0;                      // Int and Float both carry the value here
+  std::string_view sv;                 // String: its (unescaped) text
+  std::string_view key;                // member name, when the parent is an object
+  const JValue* base = nullptr;        // the arena (set once parsing is over)
+  const JValue* child() const { return first == kNil ? nullptr : base + first; }
+  const JValue* sibling() const { return next == kNil ? nullptr : base + next; }
+  std::string str() const { return std::string(sv); }
+  const JValue* get(std::string_view k) const {
     if (kind != Object) return nullptr;
-    auto it = obj.find(k);
-    return it == obj.end() ? nullptr : it->second.get();
+    const JValue* hit = nullptr;
+    for (const JValue* c = child(); c; c = c->sibling())
+      if (c->key == k) hit = c;
+    return hit;
   }
 };
 
-class Parser {
+class Doc {
  public:
-  explicit Parser(const std::string& s) : s_(s) {}
-  JPtr parse() {
-    JPtr v = value();
+  explicit Doc(const std::string& s) : s_(s) {
+    nodes_.reserve(s.size() / 6 + 16);
+    const uint32_t root = value();
     ws();
     if (i_ != s_.size()) fail("trailing characters");
-    return v;
+    for (JValue& v : nodes_) v.base = nodes_.data();
+    root_ = root;
   }
+  const JValue& root() const { return nodes_[root_]; }
 
  private:
   const std::string& s_;
   size_t i_ = 0;
+  uint32_t root_ = 0;
+  std::vector<JValue> nodes_;
+  std::deque<std::string> pool_;  // decoded text of strings that carry escapes (stable addresses)
   [[noreturn]] void fail(const char* what) const {
     throw std::runtime_error("JSON: " + std::string(what) + " at offset " + std::to_string(i_));
   }
@@ -75,15 +92,23 @@ class Parser {
     }
     return v;
   }
-  std::string string() {
-    if (s_[i_] != '"') fail("expected string");
+  std::string_view string() {
+    if (i_ >= s_.size() || s_[i_] != '"') fail("expected string");
     ++i_;
-    std::string out;
-    while (i_ < s_.size() && s_[i_] != '"') {
-      char c = s_[i_++];
+    const size_t st = i_;
+    const char* p = s_.data();
+    const size_t n = s_.size();
+    while (i_ < n && p[i_] != '"' && p[i_] != '\\') ++i_;
+    if (i_ < n && p[i_] == '"') {  // the usual case: no escapes, a view into the text
+      ++i_;
+      return std::string_view(p + st, i_ - 1 - st);
+    }
+    std::string out(p + st, i_ - st);
+    while (i_ < n && p[i_] != '"') {
+      char c = p[i_++];
       if (c != '\\') { out += c; continue; }
-      if (i_ >= s_.size()) fail("short escape");
-      char e = s_[i_++];
+      if (i_ >= n) fail("short escape");
+      char e = p[i_++];
       switch (e) {
         case '"': out += '"'; break;
         case '\\': out += '\\'; break;
@@ -106,27 +131,36 @@ class Parser {
         default: fail("bad escape");
       }
     }
-    if (i_ >= s_.size()) fail("unterminated string");
+    if (i_ >= n) fail("unterminated string");
     ++i_;
-    return out;
+    pool_.push_back(std::move(out));
+    return pool_.back();
   }
-  JPtr value() {
+  uint32_t make(JValue::Kind k) {
+    nodes_.emplace_back();
+    nodes_.back().kind = k;
+    return static_cast<uint32_t>(nodes_.size() - 1);
+  }
+  uint32_t value() {
     ws();
     if (i_ >= s_.size()) fail("unexpected end");
-    auto v = std::make_shared<JValue>();
-    char c = s_[i_];
+    const char c = s_[i_];
     if (c == '{') {
-      v->kind = JValue::Object;
+      const uint32_t v = make(JValue::Object);
       ++i_;
       ws();
       if (i_ < s_.size() && s_[i_] == '}') { ++i_; return v; }
+      uint32_t last = kNil;
       for (;;) {
         ws();
-        std::string k = string();
+        const std::string_view k = string();
         ws();
         if (i_ >= s_.size() || s_[i_] != ':') fail("expected ':'");
         ++i_;
-        v->obj[k] = value();
+        const uint32_t m = value();
+        nodes_[m].key = k;
+        if (last == kNil) nodes_[v].first = m; else nodes_[last].next = m;
+        last = m;
         ws();
         if (i_ < s_.size() && s_[i_] == ',') { ++i_; continue; }
         if (i_ < s_.size() && s_[i_] == '}') { ++i_; return v; }
@@ -134,24 +168,32 @@ class Parser {
       }
     }
     if (c == '[') {
-      v->kind = JValue::Array;
+      const uint32_t v = make(JValue::Array);
       ++i_;
       ws();
       if (i_ < s_.size() && s_[i_] == ']') { ++i_; return v; }
+      uint32_t last = kNil;
       for (;;) {
-        v->arr.push_back(value());
+        const uint32_t m = value();
+        if (last == kNil) nodes_[v].first = m; else nodes_[last].next = m;
+        last = m;
         ws();
         if (i_ < s_.size() && s_[i_] == ',') { ++i_; continue; }
         if (i_ < s_.size() && s_[i_] == ']') { ++i_; return v; }
         fail("expected ',' or ']'");
       }
     }
-    if (c == '"') { v->kind = JValue::String; v->str = string(); return v; }
-    if (eat("true")) { v->kind = JValue::Bool; v->b = true; return v; }
-    if (eat("false")) { v->kind = JValue::Bool; return v; }
-    if (eat("null")) return v;
+    if (c == '"') {
+      const std::string_view t = string();
+      const uint32_t v = make(JValue::String);
+      nodes_[v].sv = t;
+      return v;
+    }
+    if (eat("true")) { const uint32_t v = make(JValue::Bool); nodes_[v].b = true; return v; }
+    if (eat("false")) return make(JValue::Bool);
+    if (eat("null")) return make(JValue::Null);
     // number: integral text (no '.', 'e', 'E') is an int64 for apimachinery's decoder
-    size_t st = i_;
+    const size_t st = i_;
     bool integral = true;
     if (s_[i_] == '-') ++i_;
     while (i_ < s_.size()) {
@@ -161,34 +203,51 @@ class Parser {
       break;
     }
     if (i_ == st) fail("unexpected character");
-    v->kind = integral ? JValue::Int : JValue::Float;
-    v->num = std::strtod(s_.substr(st, i_ - st).c_str(), nullptr);
+    const uint32_t v = make(integral ? JValue::Int : JValue::Float);
+    const size_t len = i_ - st;
+    double x;
+    if (integral && len <= 15) {  // exact in a double: no strtod needed
+      int64_t a = 0;
+      size_t k = st + (s_[st] == '-' ? 1 : 0);
+      for (; k < i_; ++k) a = a * 10 + (s_[k] - '0');
+      x = s_[st] == '-' ? -static_cast<double>(a) : static_cast<double>(a);
+    } else if (len < 64) {        // the token alone (strtod must not read past it: "0x1p3", "1e5e5")
+      char buf[64];
+      s_.copy(buf, len, st);
+      buf[len] = 0;
+      x = std::strtod(buf, nullptr);
+    } else {
+      x = std::strtod(s_.substr(st, len).c_str(), nullptr);
+    }
+    nodes_[v].num = x;
     return v;
   }
 };
 
-const std::vector<JPtr>& items_of(const JValue& root) {
-  if (root.kind == JValue::Array) return root.arr;
+// the elements of a list document: the root array, or the root object's "items"
+const JValue* first_item(const JValue& root) {
+  if (root.kind == JValue::Array) return root.child();
   const JValue* it = root.get("items");
   if (!it || it->kind != JValue::Array) throw std::runtime_error("JSON: no \"items\" array");
-  return it->arr;
+  return it->child();
 }
 
 }  // namespace
 
 std::vector<UAVMetricItem> DecodeUAVMetricList(const std::string& json) {
-  JPtr root = Parser(json).parse();
+  const Doc doc(json);
   std::vector<UAVMetricItem> out;
-  for (const JPtr& it : items_of(*root)) {
-    UAVMetricItem u;
+  for (const JValue* it = first_item(doc.root()); it; it = it->sibling()) {
+    out.emplace_back();
+    UAVMetricItem& u = out.back();
     const JValue* spec = it->get("spec");      // NestedMap(item, "spec"), controller.go:182
     const JValue* status = it->get("status");  // :183
     if (spec) {
       if (const JValue* v = spec->get("node_name"); v && v->kind == JValue::String) {  // :185
         u.HasNodeName = true;
-        u.NodeName = v->str;
+        u.NodeName.assign(v->sv);
       }
-      if (const JValue* v = spec->get("uav_id"); v && v->kind == JValue::String) u.UAVID = v->str;  // :186
+      if (const JValue* v = spec->get("uav_id"); v && v->kind == JValue::String) u.UAVID.assign(v->sv);  // :186
       if (const JValue* b = spec->get("battery"))  // readFloat(spec, "battery", "remaining_percent"), :187
         if (const JValue* v = b->get("remaining_percent"); v && (v->kind == JValue::Int || v->kind == JValue::Float)) {
           u.HasBattery = true;  // float64 / int64 cases of the type switch, :262-271
@@ -198,36 +257,35 @@ std::vector<UAVMetricItem> DecodeUAVMetricList(const std::string& json) {
     if (status)
       if (const JValue* v = status->get("collection_status"); v && v->kind == JValue::String) {  // :188
         u.HasStatus = true;
-        u.CollectionStatus = v->str;
+        u.CollectionStatus.assign(v->sv);
       }
-    out.push_back(u);
   }
   return out;
 }
 
 std::vector<SchedulingRequest> DecodeSchedulingRequestList(const std::string& json, bool apimachinery_ints) {
-  JPtr root = Parser(json).parse();
+  const Doc doc(json);
   std::vector<SchedulingRequest> out;
-  for (const JPtr& it : items_of(*root)) {
-    SchedulingRequest q;
+  for (const JValue* it = first_item(doc.root()); it; it = it->sibling()) {
+    out.emplace_back();
+    SchedulingRequest& q = out.back();
     if (const JValue* st = it->get("status"))
       if (const JValue* v = st->get("phase"); v && v->kind == JValue::String) {  // NestedString, :113
         q.HasPhase = true;
-        q.Phase = v->str;
+        q.Phase.assign(v->sv);
       }
     if (const JValue* spec = it->get("spec")) {
       if (const JValue* wl = spec->get("workload"); wl && wl->kind == JValue::Object) {  // :127-131
-        if (const JValue* v = wl->get("name"); v && v->kind == JValue::String) q.Spec.Workload.Name = v->str;
-        if (const JValue* v = wl->get("namespace"); v && v->kind == JValue::String) q.Spec.Workload.Namespace = v->str;
-        if (const JValue* v = wl->get("type"); v && v->kind == JValue::String) q.Spec.Workload.Type = v->str;
+        if (const JValue* v = wl->get("name"); v && v->kind == JValue::String) q.Spec.Workload.Name.assign(v->sv);
+        if (const JValue* v = wl->get("namespace"); v && v->kind == JValue::String) q.Spec.Workload.Namespace.assign(v->sv);
+        if (const JValue* v = wl->get("type"); v && v->kind == JValue::String) q.Spec.Workload.Type.assign(v->sv);
       }
       if (const JValue* v = spec->get("minBatteryPercent"))  // .(float64) only, :133
         if (v->kind == JValue::Float || (v->kind == JValue::Int && !apimachinery_ints)) q.Spec.MinBatteryPercent = v->num;
       if (const JValue* v = spec->get("preferredNodes"); v && v->kind == JValue::Array)  // :137-143
-        for (const JPtr& e : v->arr)
-          if (e->kind == JValue::String) q.Spec.PreferredNodes.push_back(e->str);
+        for (const JValue* e = v->child(); e; e = e->sibling())
+          if (e->kind == JValue::String) q.Spec.PreferredNodes.emplace_back(e->sv);
     }
-    out.push_back(q);
   }
   return out;
 }
@@ -242,7 +300,7 @@ std::string str_field(const JValue* o, const char* k) {
   const JValue* v = o ? o->get(k) : nullptr;
   if (!v || v->kind == JValue::Null) return "";
   if (v->kind != JValue::String) bad_type(k, "string");
-  return v->str;
+  return v->str();
 }
 double num_field(const JValue* o, const char* k) {  // float64 field: any JSON number
   const JValue* v = o ? o->get(k) : nullptr;
@@ -279,9 +337,9 @@ double enum_code(const std::string& s, std::initializer_list<const char*> names)
 }  // namespace
 
 UAVReport DecodeUAVReport(const std::string& json) {
-  JPtr root = Parser(json).parse();
-  if (root->kind != JValue::Object) throw std::runtime_error("JSON: a UAVReport is an object");
-  const JValue* o = root.get();
+  const Doc doc(json);
+  if (doc.root().kind != JValue::Object) throw std::runtime_error("JSON: a UAVReport is an object");
+  const JValue* o = &doc.root();
   UAVReport r;
   r.NodeName = str_field(o, "node_name");     // models.go:183-187
   r.NodeIP = str_field(o, "node_ip");
@@ -338,8 +396,8 @@ bool ApplyUAVReportDefaults(UAVReport& r, const std::string& now_rfc3339) {
   return true;
 }
 
-static std::string quote(const std::string& s) {
-  std::string o = "\"";
+static void quote_into(std::string& o, const std::string& s) {
+  o += '"';
   for (unsigned char c : s) {
     switch (c) {
       case '"': o += "\\\""; break;
@@ -352,7 +410,7 @@ static std::string quote(const std::string& s) {
         else o += static_cast<char>(c);
     }
   }
-  return o + "\"";
+  o += '"';
 }
 
 // Go's encoding/json float64 encoder (encode.go floatEncoder): the shortest digits that
@@ -362,11 +420,10 @@ static std::string quote(const std::string& s) {
 std::string FormatJSONFloat(double v) {
   if (!(v == v) || v == HUGE_VAL || v == -HUGE_VAL) return "0";
   if (v == 0.0) return std::signbit(v) ? "-0" : "0";
-  char e[40];
-  int prec = 0;
-  for (; prec < 17; ++prec) {  // shortest digits that round-trip
-    std::snprintf(e, sizeof(e), "%.*e", prec, v);
-    if (std::strtod(e, nullptr) == v) break;
+  char e[48];
+  {  // shortest digits that round-trip, as d[.ddd]e[+-]XX
+    const std::to_chars_result r = std::to_chars(e, e + sizeof(e) - 1, v, std::chars_format::scientific);
+    *r.ptr = 0;
   }
   // e = [-]d[.ddd]e[+-]XX: digits and decimal exponent
   std::string digits;
@@ -397,11 +454,23 @@ std::string FormatJSONFloat(double v) {
 }
 
 std::string EncodeStatus(const SchedulingRequestStatus& st, const std::string& last_updated) {
-  const std::string score = FormatJSONFloat(st.Score);
-  const std::string phase = st.Phase.empty() ? "Pending" : st.Phase;  // controller.go:238-240
-  return "{\"phase\":" + quote(phase) + ",\"assignedNode\":" + quote(st.AssignedNode) +
-         ",\"assignedUAV\":" + quote(st.AssignedUAV) + ",\"score\":" + score + ",\"message\":" +
-         quote(st.Message) + ",\"lastUpdated\":" + quote(last_updated) + "}";
+  static const std::string kPending = "Pending";
+  std::string o;
+  o.reserve(128 + st.AssignedNode.size() + st.AssignedUAV.size() + st.Message.size() + last_updated.size());
+  o += "{\"phase\":";
+  quote_into(o, st.Phase.empty() ? kPending : st.Phase);  // controller.go:238-240
+  o += ",\"assignedNode\":";
+  quote_into(o, st.AssignedNode);
+  o += ",\"assignedUAV\":";
+  quote_into(o, st.AssignedUAV);
+  o += ",\"score\":";
+  o += FormatJSONFloat(st.Score);
+  o += ",\"message\":";
+  quote_into(o, st.Message);
+  o += ",\"lastUpdated\":";
+  quote_into(o, last_updated);
+  o += '}';
+  return o;
 }
 
 }  // namespace klmhost
