@@ -24,11 +24,15 @@ __device__ __forceinline__ float key_f32(uint32_t k) {
 #define NEG_INF __int_as_float(0xff800000)
 #define POS_INF __int_as_float(0x7f800000)
 
+// Neighbours in VALUE order: -0.0 and +0.0 are adjacent keys but one value, so stepping off a zero
+// must skip the other zero -- `x > next_down(0)` has to hold for every zero sample, and
+// `x >= next_up(0)` for none (a p95 that sits on a plateau of zeros next to a few spikes is an
+// everyday series: idle flags, a drained battery).
 __device__ __forceinline__ float next_up(float x) {   // smallest float > x (x finite or -inf)
-  return key_f32(f32_key(x) + 1u);
+  return x == 0.f ? __uint_as_float(0x00000001u) : key_f32(f32_key(x) + 1u);
 }
 __device__ __forceinline__ float next_down(float x) { // largest float < x (x finite or +inf)
-  return key_f32(f32_key(x) - 1u);
+  return x == 0.f ? __uint_as_float(0x80000001u) : key_f32(f32_key(x) - 1u);
 }
 __device__ __forceinline__ int warp_max_i32(int v) { return __reduce_max_sync(0xffffffffu, v); }
 __device__ __forceinline__ uint32_t warp_max_u32(uint32_t v) { return __reduce_max_sync(0xffffffffu, v); }

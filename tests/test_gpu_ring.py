@@ -490,3 +490,108 @@ def test_full_c3_hinted_against_oracle(dev, pkg):
         rows = ring[a:b].cpu().numpy()
         want = ob.window_stats(rows, np.full(b - a, t + 2, np.uint32), t, fast=True, threads=threads)
         check_stats({k: v[a:b] for k, v in got.items()}, want, f"full C3 series {a}..{b}")
+
+
+@pytest.mark.parametrize("t", [7, 130, 900, 1000, 3600, 4096, 8192])
+def test_window_stats_tick_equals_ingest_then_stats(dev, t):
+    """klm_dev_window_stats_tick: one launch that ingests a sample per series and computes the
+    statistics of the window holding it. The ring, `seen` and every result must equal
+    klm_dev_ring_ingest followed by the oracle -- with the new sample landing in every part of a
+    row (the staged rows, the leftover rows, the partial row, the last odd elements), on rings
+    that are empty, filling, exactly full and wrapped, and with cold, carried and garbage brackets."""
+    import torch
+    rng = np.random.default_rng(4400 + t)
+    s = 320
+    rows = distributions(rng, s, t)
+    pitch = (t + 3) & ~3
+    ring = torch.zeros((s, pitch), dtype=torch.float32, device="cuda")
+    ring[:, :t] = torch.from_numpy(rows).cuda()
+    # positions spread over the whole row: seen = t + offset puts the next sample at `offset`
+    seen_np = (t + rng.integers(0, t, s)).astype(np.int64)
+    seen_np[:8] = [0, 1, 2, t - 2, t - 1, t, max(t // 2, 1), 2 * t - 1]
+    seen_np[8] = 0xffffffff           # saturated counter: stays, the slot is (2^32 - 1) % t
+    ring2 = ring.clone()
+    seen = torch.from_numpy(seen_np.astype(np.uint32).view(np.int32)).cuda()
+    seen2 = seen.clone()
+    state = torch.full((s, 2), float("nan"), dtype=torch.float32, device="cuda")
+    o = {k: torch.empty(s, dtype=torch.float64 if k == "mean" else torch.float32, device="cuda")
+         for k in ("min", "max", "mean", "p95")}
+    for tick in range(10):
+        vals = torch.from_numpy(distributions(rng, s, 1)[:, 0].copy()).cuda()
+        if tick == 6:
+            state.copy_(torch.from_numpy(rng.standard_normal((s, 2)).astype(np.float32) * 100).cuda())
+        dev.window_stats(ring, seen, t, o["min"], o["max"], o["mean"], o["p95"], state=state, tick=vals)
+        dev.ring_ingest(ring2, seen2, t, vals)                       # the two-launch form on a copy
+        torch.cuda.synchronize()
+        assert torch.equal(ring, ring2), f"ring differs after tick {tick}"
+        assert torch.equal(seen, seen2), f"seen differs after tick {tick}"
+        sn = seen2.cpu().numpy().view(np.uint32)
+        want = ob.window_stats(ring2.cpu().numpy(), sn, t, pitch)
+        check_stats({k: v.cpu().numpy() for k, v in o.items()}, want, f"tick t={t} #{tick}")
+
+
+def test_window_stats_tick_on_a_range_and_errors(dev, pkg):
+    import torch
+    s, t = 64, 1000
+    ring = (torch.rand((s, t), device="cuda") * 10).float()
+    seen = torch.full((s,), t, dtype=torch.int32, device="cuda")
+    ring2, seen2 = ring.clone(), seen.clone()
+    state = torch.full((16, 2), float("nan"), dtype=torch.float32, device="cuda")
+    o = [torch.empty(16, dtype=torch.float32, device="cuda") for _ in range(3)]
+    om = torch.empty(16, dtype=torch.float64, device="cuda")
+    vals = torch.arange(16, dtype=torch.float32, device="cuda") + 100
+    dev.window_stats(ring, seen, t, o[0], o[1], om, o[2], s0=20, s1=36, state=state, tick=vals)
+    torch.cuda.synchronize()
+    ring2[20:36, 0] = vals          # seen == t: the slot is 0
+    seen2[20:36] += 1
+    assert torch.equal(ring, ring2) and torch.equal(seen, seen2)
+    assert torch.equal(o[1], vals)  # the new sample is each window's maximum
+    with pytest.raises(pkg.binding.KlmError):
+        big = torch.zeros((2, 8196), dtype=torch.float32, device="cuda")
+        dev.window_stats(big, seen[:2], 8193, o[0][:2], o[1][:2], om[:2], o[2][:2], state=state[:2], tick=vals[:2])
+
+
+@pytest.mark.parametrize("t", [130, 1000, 3600])
+def test_p95_on_and_off_a_plateau_of_zeros(dev, t):
+    """The p95 of a series that is a plateau of zeros (both signs) next to about 5 % spikes moves on
+    and off the plateau from tick to tick. -0.0 and +0.0 are neighbouring keys but one value: a
+    pivot that steps "just below zero" must still list every zero. All variants, stateless and
+    with carried brackets, against the oracle."""
+    import torch
+    rng = np.random.default_rng(7700 + t)
+    s = 256
+    k = t - ((19 * t + 19) // 20 - 1)                       # samples at or above the p95
+    rows = np.where(rng.random((s, t)) < 0.5, -0.0, 0.0).astype(np.float32)
+    for i in range(s):
+        m = max(k + int(rng.integers(-3, 4)), 0)            # spikes: around k of them
+        idx = rng.choice(t, size=min(m, t), replace=False)
+        sign = 1.0 if i % 3 else -1.0                       # every third series: negative dips instead
+        rows[i, idx] = (sign * (rng.random(idx.size) * 50 + 1e-3)).astype(np.float32)
+    pitch = (t + 3) & ~3
+    ring = torch.zeros((s, pitch), dtype=torch.float32, device="cuda")
+    ring[:, :t] = torch.from_numpy(rows).cuda()
+    seen_np = np.full(s, t, np.int64)
+    seen = torch.from_numpy(seen_np.astype(np.int32)).cuda()
+    o = {kk: torch.empty(s, dtype=torch.float64 if kk == "mean" else torch.float32, device="cuda")
+         for kk in ("min", "max", "mean", "p95")}
+    want = ob.window_stats(ring.cpu().numpy(), seen_np.astype(np.uint32), t, pitch)
+    for variant in (None, "warp", "stream", "block"):
+        dev.window_stats(ring, seen, t, o["min"], o["max"], o["mean"], o["p95"], variant=variant)
+        torch.cuda.synchronize()
+        check_stats({kk: v.cpu().numpy() for kk, v in o.items()}, want, f"plateau t={t} {variant}")
+    for fused in (False, True):
+        state = torch.full((s, 2), float("nan"), dtype=torch.float32, device="cuda")
+        for tick in range(14):
+            spike = rng.random(s) < 0.5
+            vals_np = np.where(spike, rng.random(s) * 50 + 1e-3, np.where(rng.random(s) < 0.5, -0.0, 0.0))
+            vals_np[::3] = -np.abs(vals_np[::3])
+            vals = torch.from_numpy(vals_np.astype(np.float32)).cuda()
+            if fused:
+                dev.window_stats(ring, seen, t, o["min"], o["max"], o["mean"], o["p95"], state=state, tick=vals)
+            else:
+                dev.ring_ingest(ring, seen, t, vals)
+                dev.window_stats(ring, seen, t, o["min"], o["max"], o["mean"], o["p95"], state=state)
+            seen_np += 1
+            torch.cuda.synchronize()
+            want = ob.window_stats(ring.cpu().numpy(), seen_np.astype(np.uint32), t, pitch)
+            check_stats({kk: v.cpu().numpy() for kk, v in o.items()}, want, f"plateau t={t} fused={fused} tick={tick}")
