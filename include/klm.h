@@ -643,16 +643,6 @@ int klm_dev_window_stats_hinted(const float* ring, const uint32_t* seen,
                                 int64_t s1, float* out_min, float* out_max,
                                 double* out_mean, float* out_p95, float* state,
                                 void* stream);
-/* One collection tick in ONE launch (no reference counterpart): tick[o] is ingested into series
- * s0 + o exactly as klm_dev_ring_ingest would (slot seen % window, seen + 1), then the statistics
- * of the window that now holds it are computed as by klm_dev_window_stats_hinted -- the kernel
- * patches the new sample into the row it is already streaming, so the separate ingest launch
- * (a few microseconds of latency per tick) disappears. Same results as the two calls. `state`
- * required, windows up to 8192 (KLM_ELIMIT beyond). */
-int klm_dev_window_stats_tick(float* ring, uint32_t* seen, int32_t window, int32_t pitch,
-                              int64_t s0, int64_t s1, const float* tick, float* out_min,
-                              float* out_max, double* out_mean, float* out_p95, float* state,
-                              void* stream);
 /* The register-resident (one warp per series) variant of K7, which
  * klm_dev_window_stats uses for windows up to 4096 (KLM_ELIMIT beyond). */
 int klm_dev_window_stats_warp(const float* ring, const uint32_t* seen,

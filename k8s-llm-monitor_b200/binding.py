@@ -148,7 +148,6 @@ SIGNATURES = {
     "klm_dev_window_stats": (C.c_int, [_P, _P, _I32, _I32, _I64, _I64, _P, _P, _P, _P, _P]),
     "klm_dev_window_stats_stream": (C.c_int, [_P, _P, _I32, _I32, _I64, _I64, _P, _P, _P, _P, _P]),
     "klm_dev_window_stats_hinted": (C.c_int, [_P, _P, _I32, _I32, _I64, _I64, _P, _P, _P, _P, _P, _P]),
-    "klm_dev_window_stats_tick": (C.c_int, [_P, _P, _I32, _I32, _I64, _I64, _P, _P, _P, _P, _P, _P, _P]),
     "klm_dev_window_stats_warp": (C.c_int, [_P, _P, _I32, _I32, _I64, _I64, _P, _P, _P, _P, _P]),
     "klm_dev_window_stats_block": (C.c_int, [_P, _P, _I32, _I32, _I64, _I64, _P, _P, _P, _P, _P]),
 }
@@ -809,10 +808,8 @@ class Dev:
 
     def window_stats(self, ring, seen, window: int, out_min, out_max, out_mean, out_p95,
                      s0: int = 0, s1: Optional[int] = None, stream=None, block_variant: bool = False,
-                     variant: Optional[str] = None, state=None, tick=None):
-        """state: float32 [n_series, 2] tensor (NaN-filled at first) -> klm_dev_window_stats_hinted;
-        with tick (float32, one sample per series of [s0, s1)) -> klm_dev_window_stats_tick: the
-        samples are ingested and the statistics computed in one launch."""
+                     variant: Optional[str] = None, state=None):
+        """state: float32 [n_series, 2] tensor (NaN-filled at first) -> klm_dev_window_stats_hinted."""
         t = self.torch
         _need(ring, t.float32, "ring"); _need(seen, t.int32, "seen")
         _need(out_min, t.float32, "out_min"); _need(out_max, t.float32, "out_max")
@@ -825,14 +822,6 @@ class Dev:
         fn = {None: self.lib.klm_dev_window_stats,
               "warp": self.lib.klm_dev_window_stats_warp, "stream": self.lib.klm_dev_window_stats_stream,
               "block": self.lib.klm_dev_window_stats_block}[variant]
-        if tick is not None:
-            _need(state, t.float32, "state"); _need(tick, t.float32, "tick")
-            if tick.numel() != s1 - s0:
-                raise ValueError("tick: one sample per series of [s0, s1)")
-            check(self.lib.klm_dev_window_stats_tick(_dp(ring), _dp(seen), window, pitch, s0, s1, _dp(tick),
-                                                     _dp(out_min), _dp(out_max), _dp(out_mean), _dp(out_p95),
-                                                     _dp(state), _stream_ptr(stream)))
-            return
         if state is not None:
             _need(state, t.float32, "state")
             check(self.lib.klm_dev_window_stats_hinted(_dp(ring), _dp(seen), window, pitch, s0, s1, _dp(out_min),

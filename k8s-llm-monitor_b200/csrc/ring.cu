@@ -250,12 +250,6 @@ int launch_window_stats_stream(const float* ring, const uint32_t* seen, int32_t 
                                cudaStream_t st);
 }
 
-namespace klm {
-int launch_window_stats_tick(float* ring, uint32_t* seen, int32_t window, int32_t pitch, int64_t s0, int64_t s1,
-                             const float* tick, float* out_min, float* out_max, double* out_mean, float* out_p95,
-                             float* state, cudaStream_t st);
-}
-
 constexpr int kHintedMaxWindow = 8192;  // the streaming kernel's lists hold ~10 % of a window this large
 
 static int window_stats_args_ok(const float* ring, const uint32_t* seen, int32_t window,
@@ -330,25 +324,6 @@ extern "C" int klm_dev_window_stats_hinted(const float* ring, const uint32_t* se
   }
   return launch_window_stats_stream(ring, seen, window, pitch, s0, s1, out_min, out_max, out_mean,
                                     out_p95, state, as_stream(stream));
-}
-
-extern "C" int klm_dev_window_stats_tick(float* ring, uint32_t* seen, int32_t window, int32_t pitch,
-                                         int64_t s0, int64_t s1, const float* tick, float* out_min,
-                                         float* out_max, double* out_mean, float* out_p95, float* state,
-                                         void* stream) {
-  const int rc = window_stats_args_ok(ring, seen, window, pitch, s0, s1);
-  if (rc != KLM_OK || s1 == s0) return rc;
-  if (!tick || !state || (reinterpret_cast<uintptr_t>(state) & 7u)) {
-    set_error("klm_dev_window_stats_tick: tick and state (8-byte aligned, 2 floats per series) must be given");
-    return KLM_EINVAL;
-  }
-  if (window > kHintedMaxWindow) {
-    set_error("klm_dev_window_stats_tick: window %d exceeds %d (use klm_dev_ring_ingest + klm_dev_window_stats)",
-              window, kHintedMaxWindow);
-    return KLM_ELIMIT;
-  }
-  return launch_window_stats_tick(ring, seen, window, pitch, s0, s1, tick, out_min, out_max, out_mean, out_p95,
-                                  state, as_stream(stream));
 }
 
 extern "C" int klm_dev_window_stats_block(const float* ring, const uint32_t* seen, int32_t window,

@@ -204,20 +204,13 @@ __device__ __noinline__ float wss_select_cold(float* lst, float* fin, int lane, 
 // of RS rows in shared memory, filled by cp.async: D - 1 stages are in flight whatever the
 // register budget, and the 32 buffer registers are free, which is what lets 28-32 warps share an
 // SM (the lists must then be short, CAP 24-32: made for the hinted pass, which lists ~200 samples).
-//
-// TICK (landing-ring form only): the kernel first ingests one sample per series -- tick[o] goes to
-// slot seen % window of the row and seen grows by one, exactly what klm_dev_ring_ingest does -- and
-// then computes the statistics of the window that contains it: one launch per collection tick
-// instead of two. The row is fetched before the position is known, so the new sample is patched
-// into the registers of the lane that reads its slot; the rare paths that read the row again go to
-// L2 (ld.global.cg), where the store has landed by then.
-template <int CAP, int MINB, int NBUF, int RS = 0, int D = 0, bool TICK = false>
+template <int CAP, int MINB, int NBUF, int RS = 0, int D = 0>
 __global__ void __launch_bounds__(kWssThreads, MINB)
-window_stats_stream_kernel(const float* ring, const uint32_t* seen,
+window_stats_stream_kernel(const float* __restrict__ ring, const uint32_t* __restrict__ seen,
                            int32_t window, int32_t pitch, int64_t s0, int64_t n_series,
                            float* __restrict__ out_min, float* __restrict__ out_max,
                            double* __restrict__ out_mean, float* __restrict__ out_p95,
-                           float2* __restrict__ state, const float* __restrict__ tick) {
+                           float2* __restrict__ state) {
   using Cfg = WssCfg<CAP, RS, D>;
   constexpr bool kRing = D > 0;
   extern __shared__ __align__(16) unsigned char s_raw[];
@@ -227,10 +220,7 @@ window_stats_stream_kernel(const float* ring, const uint32_t* seen,
   if (o >= n_series) return;                                  // no block-wide barrier below
   const int64_t s = s0 + o;
   const float* __restrict__ row = ring + s * (int64_t)pitch;
-  static_assert(!TICK || D > 0, "the fused tick needs the landing ring");
-  const uint32_t sn0 = seen[s];  // consumed only after the first row loads are in flight
-  float x_new = 0.f;
-  if (TICK) x_new = __ldg(tick + o);
+  const uint32_t sn = seen[s];  // consumed only after the first row loads are in flight
 #ifndef KLM_WSS_PF
 #define KLM_WSS_PF 0
 #endif
@@ -308,24 +298,6 @@ window_stats_stream_kernel(const float* ring, const uint32_t* seen,
     __syncwarp();  // lanes append into slots another lane has just filled
   };
   prefill();
-  // TICK: the sample enters slot sn0 % window and the series has seen one more (klm_dev_ring_ingest)
-  const uint32_t sn = TICK && sn0 != 0xffffffffu ? sn0 + 1u : sn0;
-  const int pos = TICK ? (int)(sn0 % (uint32_t)window) : -1;
-  if (TICK && lane == 0) {
-    const_cast<float*>(row)[pos] = x_new;
-    const_cast<uint32_t*>(seen)[s] = sn;
-  }
-  if (TICK) __syncwarp();
-  const int p_lane = (pos >> 2) & 31, p_row = pos >> 7, p_e = pos & 3;
-  // the new sample, if this lane's 16 bytes of row `j` hold its slot
-  auto patch = [&](float4& t, int j) {
-    if (TICK && j == p_row && lane == p_lane) {
-      t.x = p_e == 0 ? x_new : t.x;
-      t.y = p_e == 1 ? x_new : t.y;
-      t.z = p_e == 2 ? x_new : t.z;
-      t.w = p_e == 3 ? x_new : t.w;
-    }
-  };
   const int n = sn < (uint32_t)window ? (int)sn : window;
   if (n == 0) {
     if (lane == 0) {
@@ -435,19 +407,10 @@ window_stats_stream_kernel(const float* ring, const uint32_t* seen,
       const uint32_t ring_end = ring_s + D * kStage;
       uint32_t cs = ring_s, fs = ring_s + (D - 1) * kStage;
       const float* pf = p + 128 * RS * (D - 1);
-      int gi = 0;  // (TICK) the stage being consumed
-      const int p_stage = RS > 0 ? p_row / (RS > 0 ? RS : 1) : 0;
       auto consume = [&]() {
         float4 t[RS > 0 ? RS : 1];
 #pragma unroll
         for (int r = 0; r < RS; ++r) t[r] = lds_f4(cs + (uint32_t)(r * 512));
-        if (TICK) {
-          if (gi == p_stage) {
-#pragma unroll
-            for (int r = 0; r < RS; ++r) patch(t[r], gi * RS + r);
-          }
-          ++gi;
-        }
 #pragma unroll
         for (int r = 0; r < RS; ++r) row_fn(t[r], r & 1);
         fs = cs;
@@ -489,19 +452,10 @@ window_stats_stream_kernel(const float* ring, const uint32_t* seen,
     }
     // the rows left over (fewer than a chunk / a stage), then the row that only some lanes hold
 #pragma unroll 1
-    for (int j = jdone; j < jr; ++j) {
-      float4 t = ld_stream_f4(p + 128 * j);
-      patch(t, j);
-      row_fn(t, false);
-    }
-    if (lane + 32 * jr < nfull) {
-      float4 t = ld_stream_f4(p + 128 * jr);
-      patch(t, jr);
-      row_fn(t, false);
-    }
+    for (int j = jdone; j < jr; ++j) row_fn(ld_stream_f4(p + 128 * j), false);
+    if (lane + 32 * jr < nfull) row_fn(ld_stream_f4(p + 128 * jr), false);
     if (lane < (n & 3)) {
-      float x = row[4 * nfull + lane];
-      if (TICK && 4 * nfull + lane == pos) x = x_new;
+      const float x = row[4 * nfull + lane];
       acc.mn0 = fminf(acc.mn0, x);
       acc.mx0 = fmaxf(acc.mx0, x);
       acc.sum0 += (double)x;
@@ -620,11 +574,10 @@ window_stats_stream_kernel(const float* ring, const uint32_t* seen,
   }
 }
 
-template <int CAP, int MINB, int NBUF, int RS = 0, int D = 0, bool TICK = false>
+template <int CAP, int MINB, int NBUF, int RS = 0, int D = 0>
 static int launch_stream(const float* ring, const uint32_t* seen, int32_t window, int32_t pitch,
                          int64_t s0, int64_t n_series, float* out_min, float* out_max,
-                         double* out_mean, float* out_p95, float2* state, cudaStream_t st,
-                         const float* tick = nullptr) {
+                         double* out_mean, float* out_p95, float2* state, cudaStream_t st) {
   using Cfg = WssCfg<CAP, RS, D>;
   static_assert(MINB * (Cfg::kSmem + 1024) <= 228 * 1024, "the CTAs per SM must fit");
   const int64_t blocks = ceil_div(n_series, kWssWarps);
@@ -635,7 +588,7 @@ static int launch_stream(const float* ring, const uint32_t* seen, int32_t window
   static PerDeviceOnce attr_set;
   int dev = 0;
   KLM_CUDA(cudaGetDevice(&dev));
-  auto kern = window_stats_stream_kernel<CAP, MINB, NBUF, RS, D, TICK>;
+  auto kern = window_stats_stream_kernel<CAP, MINB, NBUF, RS, D>;
   if (!attr_set.done(dev)) {
     // opt in above 48 KB and ask for the largest shared-memory carve-out
     KLM_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::kSmem));
@@ -644,7 +597,7 @@ static int launch_stream(const float* ring, const uint32_t* seen, int32_t window
     attr_set.set(dev);
   }
   kern<<<(unsigned)blocks, kWssThreads, Cfg::kSmem, st>>>(ring, seen, window, pitch, s0, n_series, out_min, out_max,
-                                                          out_mean, out_p95, state, tick);
+                                                          out_mean, out_p95, state);
   KLM_LAUNCH_CHECK("window_stats_stream_kernel");
   return KLM_OK;
 }
@@ -672,12 +625,13 @@ int launch_window_stats_stream(const float* ring, const uint32_t* seen, int32_t 
     switch (variant) {
       case 5: KLM_WSS_GO(32, 7, 2, 1, 7);
       case 6: KLM_WSS_GO(32, 6, 2, 2, 4);
+      case 7: KLM_WSS_GO(32, 6, 2, 1, 9);
       case 9: KLM_WSS_GO(32, 6, 2, 2, 5);
+      case 10: KLM_WSS_GO(32, 6, 2, 3, 3);
+      case 11: KLM_WSS_GO(32, 6, 2, 4, 2);
       case 12: KLM_WSS_GO(32, 5, 2, 2, 6);
       case 13: KLM_WSS_GO(32, 7, 2, 2, 3);
-      case 15: KLM_WSS_GO(32, 8, 2, 1, 5);
-      case 16: KLM_WSS_GO(32, 8, 2, 2, 2);
-      case 17: KLM_WSS_GO(32, 7, 2, 1, 6);
+      case 14: KLM_WSS_GO(40, 6, 2, 2, 4);
       default: break;
     }
   }
@@ -695,15 +649,6 @@ int launch_window_stats_stream(const float* ring, const uint32_t* seen, int32_t 
   if (state != nullptr && window <= 8192) KLM_WSS_GO(32, 6, 2, 2, 5);
   KLM_WSS_GO(KLM_WSS_CAP, KLM_WSS_MINB, KLM_WSS_NBUF);
 #undef KLM_WSS_GO
-}
-
-// One collection tick in one launch: tick[o] enters series s0 + o, then the statistics of the window
-// that holds it (the landing-ring kernel with TICK). Windows up to 8192, `state` required.
-int launch_window_stats_tick(float* ring, uint32_t* seen, int32_t window, int32_t pitch, int64_t s0, int64_t s1,
-                             const float* tick, float* out_min, float* out_max, double* out_mean, float* out_p95,
-                             float* state, cudaStream_t st) {
-  return launch_stream<32, 6, 2, 2, 5, true>(ring, seen, window, pitch, s0, s1 - s0, out_min, out_max, out_mean,
-                                             out_p95, reinterpret_cast<float2*>(state), st, tick);
 }
 
 }  // namespace klm

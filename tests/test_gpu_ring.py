@@ -493,12 +493,11 @@ def test_full_c3_hinted_against_oracle(dev, pkg):
 
 
 @pytest.mark.parametrize("t", [7, 130, 900, 1000, 3600, 4096, 8192])
-def test_window_stats_tick_equals_ingest_then_stats(dev, t):
-    """klm_dev_window_stats_tick: one launch that ingests a sample per series and computes the
-    statistics of the window holding it. The ring, `seen` and every result must equal
-    klm_dev_ring_ingest followed by the oracle -- with the new sample landing in every part of a
-    row (the staged rows, the leftover rows, the partial row, the last odd elements), on rings
-    that are empty, filling, exactly full and wrapped, and with cold, carried and garbage brackets."""
+def test_hinted_over_many_ticks_everywhere_in_the_row(dev, t):
+    """Ten ticks of ingest + statistics with carried brackets on rings that are empty, filling,
+    exactly full, wrapped and saturated, the new sample landing in every part of a row, with cold,
+    carried and garbage brackets: every result against the oracle. (The t = 130 case is the one that
+    exposed the -0.0 / +0.0 pivot fault: a p95 falling from a spike back onto a plateau of zeros.)"""
     import torch
     rng = np.random.default_rng(4400 + t)
     s = 320
@@ -506,13 +505,10 @@ def test_window_stats_tick_equals_ingest_then_stats(dev, t):
     pitch = (t + 3) & ~3
     ring = torch.zeros((s, pitch), dtype=torch.float32, device="cuda")
     ring[:, :t] = torch.from_numpy(rows).cuda()
-    # positions spread over the whole row: seen = t + offset puts the next sample at `offset`
     seen_np = (t + rng.integers(0, t, s)).astype(np.int64)
     seen_np[:8] = [0, 1, 2, t - 2, t - 1, t, max(t // 2, 1), 2 * t - 1]
     seen_np[8] = 0xffffffff           # saturated counter: stays, the slot is (2^32 - 1) % t
-    ring2 = ring.clone()
     seen = torch.from_numpy(seen_np.astype(np.uint32).view(np.int32)).cuda()
-    seen2 = seen.clone()
     state = torch.full((s, 2), float("nan"), dtype=torch.float32, device="cuda")
     o = {k: torch.empty(s, dtype=torch.float64 if k == "mean" else torch.float32, device="cuda")
          for k in ("min", "max", "mean", "p95")}
@@ -520,35 +516,12 @@ def test_window_stats_tick_equals_ingest_then_stats(dev, t):
         vals = torch.from_numpy(distributions(rng, s, 1)[:, 0].copy()).cuda()
         if tick == 6:
             state.copy_(torch.from_numpy(rng.standard_normal((s, 2)).astype(np.float32) * 100).cuda())
-        dev.window_stats(ring, seen, t, o["min"], o["max"], o["mean"], o["p95"], state=state, tick=vals)
-        dev.ring_ingest(ring2, seen2, t, vals)                       # the two-launch form on a copy
+        dev.ring_ingest(ring, seen, t, vals)
+        dev.window_stats(ring, seen, t, o["min"], o["max"], o["mean"], o["p95"], state=state)
         torch.cuda.synchronize()
-        assert torch.equal(ring, ring2), f"ring differs after tick {tick}"
-        assert torch.equal(seen, seen2), f"seen differs after tick {tick}"
-        sn = seen2.cpu().numpy().view(np.uint32)
-        want = ob.window_stats(ring2.cpu().numpy(), sn, t, pitch)
-        check_stats({k: v.cpu().numpy() for k, v in o.items()}, want, f"tick t={t} #{tick}")
-
-
-def test_window_stats_tick_on_a_range_and_errors(dev, pkg):
-    import torch
-    s, t = 64, 1000
-    ring = (torch.rand((s, t), device="cuda") * 10).float()
-    seen = torch.full((s,), t, dtype=torch.int32, device="cuda")
-    ring2, seen2 = ring.clone(), seen.clone()
-    state = torch.full((16, 2), float("nan"), dtype=torch.float32, device="cuda")
-    o = [torch.empty(16, dtype=torch.float32, device="cuda") for _ in range(3)]
-    om = torch.empty(16, dtype=torch.float64, device="cuda")
-    vals = torch.arange(16, dtype=torch.float32, device="cuda") + 100
-    dev.window_stats(ring, seen, t, o[0], o[1], om, o[2], s0=20, s1=36, state=state, tick=vals)
-    torch.cuda.synchronize()
-    ring2[20:36, 0] = vals          # seen == t: the slot is 0
-    seen2[20:36] += 1
-    assert torch.equal(ring, ring2) and torch.equal(seen, seen2)
-    assert torch.equal(o[1], vals)  # the new sample is each window's maximum
-    with pytest.raises(pkg.binding.KlmError):
-        big = torch.zeros((2, 8196), dtype=torch.float32, device="cuda")
-        dev.window_stats(big, seen[:2], 8193, o[0][:2], o[1][:2], om[:2], o[2][:2], state=state[:2], tick=vals[:2])
+        sn = seen.cpu().numpy().view(np.uint32)
+        want = ob.window_stats(ring.cpu().numpy(), sn, t, pitch)
+        check_stats({k: v.cpu().numpy() for k, v in o.items()}, want, f"t={t} tick {tick}")
 
 
 @pytest.mark.parametrize("t", [130, 1000, 3600])
@@ -579,19 +552,16 @@ def test_p95_on_and_off_a_plateau_of_zeros(dev, t):
         dev.window_stats(ring, seen, t, o["min"], o["max"], o["mean"], o["p95"], variant=variant)
         torch.cuda.synchronize()
         check_stats({kk: v.cpu().numpy() for kk, v in o.items()}, want, f"plateau t={t} {variant}")
-    for fused in (False, True):
+    for rep in range(2):
         state = torch.full((s, 2), float("nan"), dtype=torch.float32, device="cuda")
         for tick in range(14):
             spike = rng.random(s) < 0.5
             vals_np = np.where(spike, rng.random(s) * 50 + 1e-3, np.where(rng.random(s) < 0.5, -0.0, 0.0))
             vals_np[::3] = -np.abs(vals_np[::3])
             vals = torch.from_numpy(vals_np.astype(np.float32)).cuda()
-            if fused:
-                dev.window_stats(ring, seen, t, o["min"], o["max"], o["mean"], o["p95"], state=state, tick=vals)
-            else:
-                dev.ring_ingest(ring, seen, t, vals)
-                dev.window_stats(ring, seen, t, o["min"], o["max"], o["mean"], o["p95"], state=state)
+            dev.ring_ingest(ring, seen, t, vals)
+            dev.window_stats(ring, seen, t, o["min"], o["max"], o["mean"], o["p95"], state=state)
             seen_np += 1
             torch.cuda.synchronize()
             want = ob.window_stats(ring.cpu().numpy(), seen_np.astype(np.uint32), t, pitch)
-            check_stats({kk: v.cpu().numpy() for kk, v in o.items()}, want, f"plateau t={t} fused={fused} tick={tick}")
+            check_stats({kk: v.cpu().numpy() for kk, v in o.items()}, want, f"plateau t={t} rep={rep} tick={tick}")
