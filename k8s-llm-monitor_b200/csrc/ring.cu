@@ -220,7 +220,8 @@ int launch_window_stats_block(const float* ring, const uint32_t* seen, int32_t w
   static PerDeviceOnce attr_set;
   int dev = 0;
   KLM_CUDA(cudaGetDevice(&dev));
-  if (smem > 48 * 1024 && !attr_set.done(dev)) {
+  // (the 48 KB default covers static + dynamic shared memory: opt in well below it)
+  if (smem > 32 * 1024 && !attr_set.done(dev)) {
     KLM_CUDA(cudaFuncSetAttribute(window_stats_block_kernel,
                                   cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     attr_set.set(dev);

@@ -269,9 +269,11 @@ __device__ __forceinline__ float select_from_lists(float* lst, float* fin, int l
       float x[8];
 #pragma unroll
       for (int u = 0; u < 8; ++u) x[u] = lst[(e + u) * 32];
+      // (e + u < cnt: the -inf padding beyond the lane's entries is not a candidate -- it passes
+      // `>= a` when a itself is -inf, i.e. for a window that holds -inf samples and lists everything)
 #pragma unroll
       for (int u = 0; u < 8; ++u)
-        if (x[u] >= a && (open || x[u] < b)) *dst++ = x[u];
+        if (e + u < cnt && x[u] >= a && (open || x[u] < b)) *dst++ = x[u];
     }
   }
   __syncwarp();

@@ -1,0 +1,22 @@
+"""A short run of tools/k7_fuzz.py under pytest: adversarial rings (signed zeros, infinities,
+denormals, plateaus next to spikes, one-lane pile-ups, random fill levels) through every K7
+variant and through runs of ticks with carried / garbage brackets, against the oracle. The long
+runs (minutes, several seeds) are done by hand with the same tool; this keeps the path alive."""
+import json
+import os
+import subprocess
+import sys
+
+import pytest
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.mark.parametrize("seed", [11, 12])
+def test_k7_fuzz_short(seed):
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "k7_fuzz.py"), "8", str(seed)],
+                       capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, (r.stdout[-800:], r.stderr[-800:])
+    line = json.loads(r.stdout.strip().splitlines()[-1])
+    assert line["ok"] and line["kernel_calls_checked"] > 50

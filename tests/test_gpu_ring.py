@@ -565,3 +565,31 @@ def test_p95_on_and_off_a_plateau_of_zeros(dev, t):
             torch.cuda.synchronize()
             want = ob.window_stats(ring.cpu().numpy(), seen_np.astype(np.uint32), t, pitch)
             check_stats({kk: v.cpu().numpy() for kk, v in o.items()}, want, f"plateau t={t} rep={rep} tick={tick}")
+
+
+def test_windows_holding_neg_inf_samples(dev):
+    """A case the fuzzer (tools/k7_fuzz.py) found: 33-sample windows that contain -inf samples. Such
+    a window lists every sample above -inf and selects with a = -inf, and the -inf PADDING of the lane
+    lists then passed the `>= a` test of the gather and overwrote real candidates (p95 several ranks
+    too low; in the tree since round 1). Fixture: the failing rings as generated, 184 series."""
+    import os
+    import torch
+    d = np.load(os.path.join(os.path.dirname(__file__), "golden", "k7_case_neg_inf_small_window.npz"))
+    rows, seen_np, t = d["rows"], d["seen"].astype(np.uint32), int(d["t"])
+    pitch = rows.shape[1]
+    want = ob.window_stats(rows, seen_np, t, pitch)
+    ring = torch.from_numpy(rows).cuda()
+    seen = torch.from_numpy(seen_np.view(np.int32).copy()).cuda()
+    s = rows.shape[0]
+    o = {k: torch.empty(s, dtype=torch.float64 if k == "mean" else torch.float32, device="cuda")
+         for k in ("min", "max", "mean", "p95")}
+    state = torch.full((s, 2), float("nan"), dtype=torch.float32, device="cuda")
+    for variant in (None, "warp", "stream", "block", "hinted", "hinted"):
+        if variant == "hinted":
+            dev.window_stats(ring, seen, t, o["min"], o["max"], o["mean"], o["p95"], state=state)
+        else:
+            dev.window_stats(ring, seen, t, o["min"], o["max"], o["mean"], o["p95"], variant=variant)
+        torch.cuda.synchronize()
+        got = {k: v.cpu().numpy() for k, v in o.items()}
+        for k in ("min", "max", "p95"):
+            assert np.array_equal(got[k].view(np.uint32), want[k].view(np.uint32)), (variant, k)
