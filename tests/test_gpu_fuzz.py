@@ -20,3 +20,14 @@ def test_k7_fuzz_short(seed):
     assert r.returncode == 0, (r.stdout[-800:], r.stderr[-800:])
     line = json.loads(r.stdout.strip().splitlines()[-1])
     assert line["ok"] and line["kernel_calls_checked"] > 50
+
+
+@pytest.mark.parametrize("seed", [21])
+def test_sched_fuzz_short(seed):
+    """tools/sched_fuzz.py: K1 + K2, the dependent launch, the fused launch, the brute-force scan and
+    node-range shards (probe and spread, 2..8 emulated ranks) on adversarial fleets and requests."""
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "sched_fuzz.py"), "8", str(seed)],
+                       capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, (r.stdout[-800:], r.stderr[-800:])
+    line = json.loads(r.stdout.strip().splitlines()[-1])
+    assert line["ok"] and line["checks"] > 100
