@@ -31,3 +31,13 @@ def test_sched_fuzz_short(seed):
     assert r.returncode == 0, (r.stdout[-800:], r.stderr[-800:])
     line = json.loads(r.stdout.strip().splitlines()[-1])
     assert line["ok"] and line["checks"] > 100
+
+
+def test_agg_fuzz_short():
+    """tools/agg_fuzz.py: cluster aggregate, node / pod rates, predicates, fleet scan and the top-k
+    batch on adversarial integer columns and CSR shapes, through the host-buffer ABI."""
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "agg_fuzz.py"), "8", "31"],
+                       capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, (r.stdout[-800:], r.stderr[-800:])
+    line = json.loads(r.stdout.strip().splitlines()[-1])
+    assert line["ok"] and line["checks"] > 50
