@@ -122,12 +122,12 @@ __device__ __forceinline__ void wss_for_each(const float* __restrict__ row, int 
     float4 t[4];
 #pragma unroll
     for (int u = 0; u < 4; ++u)
-      if (g0 + 32 * u < nfull) t[u] = __ldcg(reinterpret_cast<const float4*>(row + 4 * (g0 + 32 * u)));
+      if (g0 + 32 * u < nfull) t[u] = *reinterpret_cast<const float4*>(row + 4 * (g0 + 32 * u));
 #pragma unroll
     for (int u = 0; u < 4; ++u)
       if (g0 + 32 * u < nfull) { f(t[u].x); f(t[u].y); f(t[u].z); f(t[u].w); }
   }
-  if (lane < (n & 3)) f(__ldcg(row + 4 * nfull + lane));
+  if (lane < (n & 3)) f(row[4 * nfull + lane]);
 }
 
 // counts of valid samples >= p1 and >= p2 (warp totals)
