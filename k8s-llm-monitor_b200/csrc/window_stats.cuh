@@ -148,7 +148,16 @@ __device__ __forceinline__ float warp_max_f32(float v) {
 }
 
 constexpr int kMaxCand = 64;  // candidates sorted exactly at the end of select_from_lists
-constexpr int kHintMargin = 12;  // the hint brackets ranks k - 12 .. k + 12 of the window
+constexpr int kHintMargin = 12;    // the hint brackets ranks k - 12 .. k + 18 of the window:
+constexpr int kHintMarginLo = 18;  // wider below, where it cannot be re-centred; <= 31 candidates
+// Elements below the floor are never listed, so a carried floor can only move up: ticks that evict a
+// sample above it and bring one below it walk it towards the answer one rank at a time, and once
+// fewer than k samples are left at or above it the call needs extra passes over the row -- a serial
+// chain of L2 round trips that lengthens the tail of the whole launch (a handful of such series per
+// launch cost C2 about 3 us of 77). So a bracket is dropped when fewer than k + kHintRefresh samples
+// remain above its floor, and the next call takes a fresh one from the sampled pass: about a third
+// more work for that series once in ~2000 ticks, and no straggler.
+constexpr int kHintRefresh = 3;
 
 // The bracket handed to the next call on this series (one tick later at most one sample has
 // entered and one has left, so ranks move by at most one): from the sorted candidates (descending,
@@ -157,14 +166,14 @@ constexpr int kHintMargin = 12;  // the hint brackets ranks k - 12 .. k + 12 of 
 // above (or `above`, a value with fewer than k samples at or over it, when the candidates do not
 // reach that far). A hint is only ever a pivot: any value gives exact results.
 __device__ __forceinline__ float2 hint_from_sorted(uint32_t k0, uint32_t k1, int kk, int n_cand, float above) {
-  const int pl = min(kk - 1 + kHintMargin, n_cand - 1), ph = kk - 1 - kHintMargin;
+  const int pl = min(kk - 1 + kHintMarginLo, n_cand - 1), ph = kk - 1 - kHintMargin;
   const uint32_t lo = __shfl_sync(0xffffffffu, (pl & 1) ? k1 : k0, pl >> 1);
   const uint32_t hi = __shfl_sync(0xffffffffu, (max(ph, 0) & 1) ? k1 : k0, max(ph, 0) >> 1);
   return make_float2(key_f32(lo), ph >= 0 ? key_f32(hi) : above);
 }
 // the same for 32 sorted candidates held one per lane
 __device__ __forceinline__ float2 hint_from_sorted32(uint32_t key, int kk, int n_cand, float above) {
-  const int pl = min(kk - 1 + kHintMargin, n_cand - 1), ph = kk - 1 - kHintMargin;
+  const int pl = min(kk - 1 + kHintMarginLo, n_cand - 1), ph = kk - 1 - kHintMargin;
   const uint32_t lo = __shfl_sync(0xffffffffu, key, pl);
   const uint32_t hi = __shfl_sync(0xffffffffu, key, max(ph, 0));
   return make_float2(key_f32(lo), ph >= 0 ? key_f32(hi) : above);
@@ -329,6 +338,8 @@ __device__ __forceinline__ bool select_hinted(float* lst, float* fin, int lane, 
     uint32_t key = f32_key(fin[lane]);
     sort32_desc(key, lane);
     *next_hint = hint_from_sorted32(key, kk, total - cb, ce);
+    if (total - k < kHintRefresh)  // the floor has drifted close: sample afresh next time
+      *next_hint = make_float2(__int_as_float(0x7fc00000), __int_as_float(0x7fc00000));
     *result = key_f32(__shfl_sync(0xffffffffu, key, kk - 1));
     return true;
   }
@@ -336,6 +347,8 @@ __device__ __forceinline__ bool select_hinted(float* lst, float* fin, int lane, 
   uint32_t k0 = f32_key(y.x), k1 = f32_key(y.y);
   sort64_desc(k0, k1, lane);
   *next_hint = hint_from_sorted(k0, k1, kk, total - cb, ce);
+  if (total - k < kHintRefresh)
+    *next_hint = make_float2(__int_as_float(0x7fc00000), __int_as_float(0x7fc00000));
   const uint32_t pick = ((kk - 1) & 1) ? k1 : k0;
   *result = key_f32(__shfl_sync(0xffffffffu, pick, (kk - 1) >> 1));
   return true;

@@ -26,6 +26,16 @@
 
 namespace klm {
 
+#ifdef KLM_WSS_STATS
+// tuning builds only: how many series took which way through the kernel
+// [0] tie value held  [1] bracket held (one count + sort)  [2] bracket listed but missed (full select)
+// [3] sampled pivot  [4] counting fallback (narrow)  [5] short window / list everything  [6] retried append
+__device__ unsigned long long g_wss_paths[8];
+#define KLM_WSS_COUNT(i) do { if (lane == 0) atomicAdd(&g_wss_paths[i], 1ull); } while (0)
+#else
+#define KLM_WSS_COUNT(i) do { } while (0)
+#endif
+
 constexpr int kWssWarps = 4;  // warps (series) per CTA
 constexpr int kWssThreads = kWssWarps * 32;
 constexpr int kWssAux = 256;  // per warp: the 64 candidates of the final sort
@@ -192,6 +202,28 @@ __device__ __noinline__ WssBracket wss_narrow(const float* __restrict__ row, int
     ++it;
   }
   return WssBracket{a, ca};
+}
+
+// The largest sample strictly below `cur` and how many samples equal it (warp totals; -inf and 0 if
+// there is none): one pass over the row (L2). A carried floor only ever moves up, so after enough
+// ticks that evict a sample above it and bring one below it, fewer than k samples are left at or
+// above it; the answer is then the first or second distinct value under the floor, and stepping
+// down from the floor finds it in one or two passes instead of the counting fallback's five.
+struct WssBelow {
+  float v;
+  int count;
+};
+__device__ __noinline__ WssBelow wss_step_below(const float* __restrict__ row, int lane, int n, float cur) {
+  float m = NEG_INF;
+  int c = 0;
+  wss_for_each(row, lane, n, [&](float x) {
+    if (x < cur) {
+      if (x > m) { m = x; c = 1; }
+      else if (x == m) ++c;
+    }
+  });
+  const float M = warp_max_f32(m);
+  return WssBelow{M, warp_sum_i32(m == M ? c : 0)};
 }
 
 // select_from_lists for the fallback path, out of line (one inlined copy serves the hot path)
@@ -497,7 +529,7 @@ window_stats_stream_kernel(const float* __restrict__ ring, const uint32_t* __res
   do {  // single-trip block: `break` = result (or the request to narrow) is final
     if (tie_hinted) {
       const int c_ge = warp_sum_i32((int)c128), c_gt = warp_sum_i32((int)tie_gt);
-      if (c_gt < k && k <= c_ge) { result = hint.x; next_hint = hint; break; }  // still on the same block
+      if (c_gt < k && k <= c_ge) { KLM_WSS_COUNT(0); result = hint.x; next_hint = hint; break; }  // still on the same block
       narrow = true;  // the p95 moved off that value: settle it from the row
       break;
     }
@@ -508,9 +540,33 @@ window_stats_stream_kernel(const float* __restrict__ ring, const uint32_t* __res
     int total = warp_sum_i32(cnt);
     int maxcnt = warp_max_i32(cnt);
     if (hinted) {
-      // the bracket's floor lists too few (it has drifted above the answer) or far too many
+      if (total < k && maxcnt < Cfg::kClamp) {
+        // the floor has drifted above the answer: step down from it, one distinct value per pass
+        float cur = hint.x;
+        int have = total;
+        bool found = false;
+#pragma unroll 1
+        for (int step = 0; step < 3 && !found; ++step) {
+          const WssBelow bl = wss_step_below(row, lane, n, cur);
+          if (bl.count == 0) break;  // nothing below: only -inf / NaN samples are left
+          if (have + bl.count >= k) {
+            result = bl.v;
+            found = true;
+            // a block of equal samples: carry it as a tie value; else no bracket (the next call samples afresh)
+            if (bl.count > kMaxCand / 2) next_hint = make_float2(bl.v, bl.v);
+          }
+          have += bl.count;
+          cur = bl.v;
+        }
+        KLM_WSS_COUNT(7);
+        if (found) break;
+        narrow = true;
+        break;
+      }
+      // far too many listed (the floor sits on a plateau that has grown): settle by counting
       if (total < k || maxcnt >= Cfg::kClamp) { narrow = true; break; }
-      if (select_hinted(lst, fin, lane, cnt, total, maxcnt, k, hint.x, hint.y, &result, &next_hint, Cfg::kPrefill)) break;
+      if (select_hinted(lst, fin, lane, cnt, total, maxcnt, k, hint.x, hint.y, &result, &next_hint, Cfg::kPrefill)) { KLM_WSS_COUNT(1); break; }
+      KLM_WSS_COUNT(2);
       // the answer left the bracket, or the bracket is wide: the lists still hold everything >= floor
       result = select_from_lists(lst, fin, lane, cnt, total, maxcnt, k, hint.x, mx, false, 0.f, 0.f, Cfg::kPrefill,
                                  &next_hint);
@@ -529,15 +585,18 @@ window_stats_stream_kernel(const float* __restrict__ ring, const uint32_t* __res
       total = warp_sum_i32(cnt);
       maxcnt = warp_max_i32(cnt);
       retried = true;
+      KLM_WSS_COUNT(6);
     }
     if (total < k || maxcnt >= Cfg::kClamp) {  // unlucky pivots, or a lane's list overflowed
       narrow = true;
       break;
     }
+    KLM_WSS_COUNT(sampled ? 3 : 5);
     result = select_from_lists(lst, fin, lane, cnt, total, maxcnt, k, sampled ? next_up(lox) : mn, mx,
                                retried, hint_lo, hint_hi, Cfg::kPrefill, &next_hint);
   } while (false);
   if (narrow) {
+    KLM_WSS_COUNT(4);
     if (mn == mx) {
       result = mx;
       next_hint = make_float2(mx, mx);
@@ -652,3 +711,12 @@ int launch_window_stats_stream(const float* ring, const uint32_t* seen, int32_t 
 }
 
 }  // namespace klm
+
+#ifdef KLM_WSS_STATS
+extern "C" int klm_dbg_wss_paths(unsigned long long* out8, int reset) {
+  unsigned long long z[8] = {0};
+  if (out8 && cudaMemcpyFromSymbol(out8, klm::g_wss_paths, sizeof(z)) != cudaSuccess) return -1;
+  if (reset && cudaMemcpyToSymbol(klm::g_wss_paths, z, sizeof(z)) != cudaSuccess) return -1;
+  return 0;
+}
+#endif
