@@ -92,3 +92,44 @@ def test_go_shim_names_every_host_buffer_symbol():
     missing = [n for n in names if f"C.{n}(" not in go]
     assert not missing, missing
     assert "runtime.LockOSThread()" in go and go.count("C.klm_last_error()") == 1
+
+
+def test_go_shim_calls_match_the_header_arity():
+    """No Go toolchain here or on the GPU box, so the cgo shim has never been compiled; at least every
+    C.klm_*(...) call in it must pass as many arguments as the prototype in include/klm.h takes
+    (a mismatch would be a compile error on the maintainer's side)."""
+    import re
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    h = re.sub(r"/\*.*?\*/", "", open(os.path.join(root, "include", "klm.h")).read(), flags=re.S)
+    protos = {}
+    for m in re.finditer(r"\b(?:int|int64_t|void|const char\*|void\*)\s+\*?(klm_[a-z0-9_]+)\s*\(([^;{]*?)\)\s*;", h, flags=re.S):
+        args = m.group(2).strip()
+        protos[m.group(1)] = 0 if args in ("", "void") else len(re.split(r",(?![^()]*\))", args))
+    assert len(protos) >= 60
+    go = open(os.path.join(root, "go", "klm", "klm.go")).read()
+
+    def top_level_args(s):
+        depth, cur, out = 0, "", []
+        for ch in s:
+            depth += ch in "([{"
+            depth -= ch in ")]}"
+            if ch == "," and depth == 0:
+                out.append(cur)
+                cur = ""
+            else:
+                cur += ch
+        return out + ([cur] if cur.strip() else [])
+
+    bad, seen = [], 0
+    for m in re.finditer(r"C\.(klm_[a-z0-9_]+)\(", go):
+        i = j = m.end()
+        depth = 1
+        while depth:
+            depth += go[j] == "("
+            depth -= go[j] == ")"
+            j += 1
+        n = len(top_level_args(go[i:j - 1]))
+        seen += 1
+        if protos.get(m.group(1)) != n:
+            bad.append((m.group(1), protos.get(m.group(1)), n))
+    assert seen >= 30 and not bad, bad
