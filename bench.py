@@ -48,7 +48,7 @@ CFG_ID = {"c2": 2, "c3": 3, "c4": 4, "c5": 5}
 DTYPE = "f32 samples, f64 sums and scores, int64 aggregates"
 MIN_TIMED_S = 0.2   # the timed region is repeated (rounds) until it lasts at least this long
 L2_BYTES = 126 << 20      # B200 L2 (the request sets of c4 / c5 are sized against it)
-K7_TRAFFIC_C2 = 379.89e6  # dram bytes read + written by one K7 launch at c2 (ncu --set full, profiles/r02_k7_ring_ncu_summary.txt)
+K7_TRAFFIC_C2 = 379.53e6  # dram bytes read + written by one K7 launch at c2 (ncu --set full, profiles/r02_k7_ring_ncu_summary.txt)
 
 
 def config_for(wl):
